@@ -1,0 +1,144 @@
+/* rtb200.h — C-ABI of librtb200.so, the B200-native replacement for the reference's per-pixel hot path.
+ *
+ * The reference (vectorized-runner/unity-raytracer) has NO native/FFI interface of its own: the path is the private
+ * managed call  CastPixelRays(CameraData)  (Assets/RayTracer/Demo-RayTracing/RayTracingSetup.cs:198, body :275-302)
+ * which reads this.Scene / this.ImagePlane / BackgroundColor / MaxReflectionBounces and writes Color[] PixelColors.
+ * This header therefore DEFINES the boundary; every entry point cites the reference member it replaces or mirrors.
+ * All paths below are relative to Assets/RayTracer/ of the reference.
+ *
+ * Conventions
+ *   - plain C, no exceptions, no callbacks; every function returns RT_OK (0) or a negative rt_status.
+ *   - all array arguments are caller-owned HOST memory, read/written only during the call (the library copies);
+ *     rt_ctx is library-owned. Counts of 0 and 0x0 resolutions are valid no-ops (Assets/Scenes/SampleScene.unity
+ *     ships a 0x0 ImagePlane).
+ *   - one caller thread per rt_ctx (Unity main thread); calls are blocking unless stated; contexts are independent.
+ *   - there is no CPU fallback: with no CUDA device rt_create fails with RT_E_CUDA.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTB200_ABI_VERSION 1
+
+typedef struct rt_ctx rt_ctx;
+
+typedef enum {
+    RT_OK = 0,
+    RT_E_INVALID = -1,      /* bad argument */
+    RT_E_CUDA = -2,         /* CUDA runtime error / no device */
+    RT_E_OOM = -3,          /* device or host allocation failed */
+    RT_E_STATE = -4,        /* call order violated (e.g. render before commit) */
+    RT_E_UNSUPPORTED = -5
+} rt_status;
+
+/* ObjectType, Data/Objects/ObjectType.cs:3-9 */
+enum { RT_TYPE_NONE = 0, RT_TYPE_SPHERE = 1, RT_TYPE_TRIANGLE = 2, RT_TYPE_MESH_TRIANGLE = 3 };
+
+/* MaterialData, Data/Shading/MaterialData.cs:7-14. `bool IsMirror` is widened to int32 so the struct is blittable. */
+typedef struct {
+    float diffuse[3];       /* DiffuseReflectance  */
+    float ambient[3];       /* AmbientReflectance  */
+    float mirror[3];        /* MirrorReflectance   */
+    float specular[3];      /* SpecularReflectance */
+    float phong;            /* PhongExponent       */
+    int32_t is_mirror;      /* IsMirror            */
+} rt_material;              /* 56 bytes */
+
+/* CameraData (Data/Camera/CameraData.cs:7-10) + ImagePlane (Data/Camera/ImagePlane.cs:13-21) +
+ * RayTracingSetup.BackgroundColor / MaxReflectionBounces (RayTracingSetup.cs:22-23). */
+typedef struct {
+    float pos[3], fwd[3], right[3], up[3];   /* Position; Forward/Right/Up already normalised by the caller (RTS:173-181) */
+    int32_t res_x, res_y;                    /* Resolution.X, .Y */
+    float dist, half_h, half_v;              /* DistanceToCamera, HalfHorizontalLength, HalfVerticalLength */
+    float background_rgb[3];                 /* 0..1; multiplied by 255 inside (Rgb.cs:15-18) */
+    int32_t max_reflection_bounces;          /* RTS:23 */
+    int32_t spp_grid;                        /* 1 = reference behaviour (one ray at the pixel centre, RTS:291-292);
+                                                g>1 = g*g stratified sample centres, averaged in fixed (j,i) order */
+} rt_render_params;                          /* 92 bytes */
+
+typedef struct {
+    uint64_t rays_primary, rays_shadow, rays_mirror;   /* Scene.IntersectRay-equivalent queries issued by the last render */
+    float ms_render;            /* device time of the last render, ray-gen .. final pixel write (CUDA events) */
+    float ms_d2h;               /* host copy-out time of the last rt_render (0 for rt_render_device) */
+    float ms_commit_upload;     /* last rt_scene_commit: flatten + host->device */
+    float ms_commit_build;      /* last rt_scene_commit: device BVH build */
+    uint64_t h2d_bytes;         /* bytes uploaded by the last commit */
+    uint64_t d2h_bytes;         /* bytes copied out by the last rt_render */
+    uint32_t n_prims, n_nodes;  /* device BVH size */
+    uint32_t kernel_launches;   /* kernels of this library launched by the last render */
+    uint32_t reserved;
+} rt_stats;
+
+/* ---- lifetime ---------------------------------------------------------------------------------------------- */
+/* n_devices in {1,2,4,8}: in-process multi-GPU (screen-space row bands interleaved over the devices, scene replicated,
+ * framebuffer bands written straight into device_ids[0]'s buffers over NVLink peer mappings). */
+int rt_create(rt_ctx** out, const int* device_ids, int n_devices);
+void rt_destroy(rt_ctx* ctx);
+const char* rt_last_error(const rt_ctx* ctx);        /* valid until the next call on the same ctx; ctx may be NULL */
+int rt_abi_version(void);
+
+/* ---- scene: replaces UpdateScene()'s result, RayTracingSetup.cs:120-128. index in array == ObjectId.Index ---- */
+int rt_scene_begin(rt_ctx* ctx);                      /* Scene.*Data.Clear(), RTS:161,250,260 */
+/* SphereData (Data/Objects/SphereData.cs:7-16): center_r2 = 4 floats each = Sphere{Center,RadiusSquared} (Sphere.cs:9-10) */
+int rt_scene_spheres(rt_ctx* ctx, const float* center_r2, const rt_material* materials, int n);
+/* TriangleData (Data/Objects/TriangleData.cs:8-19): v = 9 floats each (Triangle.cs:9-11), normals = 3 each */
+int rt_scene_triangles(rt_ctx* ctx, const float* v, const float* normals, const rt_material* materials, int n);
+/* one Mesh (Data/Objects/Mesh.cs:7-12); call order == ObjectId.MeshIndex; aabb = {Min.xyz, Max.xyz} as the caller
+ * computed it (SceneMesh.cs:22-31) — it is a *semantic* cull in Scene.IntersectRay (Scene.cs:67) and is used verbatim. */
+int rt_scene_mesh(rt_ctx* ctx, const float* v, const float* normals, int n_tris, const rt_material* material,
+                  const float aabb[6]);
+/* Scene.PointLights (6 floats each = PointLightData{Position,Intensity}, PointLightData.cs:9-10) + AmbientLight.Radiance;
+ * ambient_radiance NULL = default(AmbientLightData) = 0 (RTS:132) */
+int rt_scene_lights(rt_ctx* ctx, const float* pos_intensity, int n, const float ambient_radiance[3]);
+/* scene_aabb = Scene.AABB as the caller computed it, or NULL -> recomputed per Scene.CalculateAABB (Scene.cs:17-41).
+ * Uploads, replicates to every device, builds the device BVH. */
+int rt_scene_commit(rt_ctx* ctx, const float scene_aabb[6]);
+int rt_scene_get_aabb(rt_ctx* ctx, float out_aabb[6]);
+
+/* ---- render: replaces CastPixelRays(CameraData), RayTracingSetup.cs:198,275-302 ---------------------------- */
+/* out_rgba32f : X*Y*4 floats == UnityEngine.Color[] PixelColors (RTS:40,300; Rgb.Color = Value/255, alpha 1, Rgb.cs:13)
+ * out_rgba8   : X*Y*4 bytes, clamp(rint(Rgb.Value),0,255), alpha 255 (our definition: the reference never quantises)
+ * out_hit_id  : X*Y*3 int32 {Type, Index, MeshIndex} of the PRIMARY hit (IntersectionResult.ObjectId, ObjectId.cs:7-9);
+ *               MeshIndex is -1 unless Type == RT_TYPE_MESH_TRIANGLE; miss = {0,-1,-1}
+ * out_hit_t   : X*Y floats, IntersectionResult.Distance of the primary hit, FLT_MAX on a miss (Scene.cs:45)
+ * pixel index = x + y*res_x, y = 0 is the top row (RTS:243-246). Any output may be NULL. */
+int rt_render(rt_ctx* ctx, const rt_render_params* params, float* out_rgba32f, uint8_t* out_rgba8,
+              int32_t* out_hit_id, float* out_hit_t, rt_stats* stats);
+
+/* Same render, but the result stays in device memory (the framebuffers owned by the ctx on device_ids[0]);
+ * `want` is a bit mask of RT_OUT_*. Asynchronous with respect to the host only if rt_set_stream gave a stream. */
+enum { RT_OUT_RGBA32F = 1, RT_OUT_RGBA8 = 2, RT_OUT_HIT_ID = 4, RT_OUT_HIT_T = 8 };
+int rt_render_device(rt_ctx* ctx, const rt_render_params* params, int want, rt_stats* stats);
+/* copy the device framebuffers of the last rt_render_device out to host memory (any pointer may be NULL) */
+int rt_read_outputs(rt_ctx* ctx, float* out_rgba32f, uint8_t* out_rgba8, int32_t* out_hit_id, float* out_hit_t);
+/* raw device pointers of those framebuffers (NULL when not allocated): for zero-copy consumers / NCCL gathers */
+int rt_device_outputs(rt_ctx* ctx, void** rgba32f, void** rgba8, void** hit_id, void** hit_t);
+
+/* Scene.IntersectRay(Ray) for n explicit rays (Scene.cs:43-122): out_id 3 int32 each, out_t 1 float each. */
+int rt_intersect(rt_ctx* ctx, const float* origins, const float* directions, int n, int32_t* out_id, float* out_t);
+
+int rt_get_stats(rt_ctx* ctx, rt_stats* stats);
+
+/* ---- one-process-per-GPU plumbing (torchrun / NCCL launches) ------------------------------------------------- */
+/* Use the caller's CUDA stream (cudaStream_t) for all work on device_ids[0]; NULL restores the library's own stream. */
+int rt_set_stream(rt_ctx* ctx, void* cuda_stream);
+/* This ctx renders only the row bands b with b % world == rank (band = band_rows consecutive rows, band_rows % 4 == 0).
+ * Default rank 0 / world 1 / band_rows 32. Outputs keep full-frame indexing. */
+int rt_set_partition(rt_ctx* ctx, int rank, int world, int band_rows);
+/* Peer gather without a collective: rank 0 exports its framebuffers (one 64-byte cudaIpcMemHandle_t each, order
+ * rgba32f, rgba8, hit_id, hit_t; zeroed when not allocated) after rt_alloc_outputs; other ranks import them and
+ * from then on write their bands straight into rank 0's memory over NVLink. */
+int rt_alloc_outputs(rt_ctx* ctx, int res_x, int res_y, int want);
+int rt_export_outputs(rt_ctx* ctx, void* handles_4x64);
+int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_y, int want);
+
+/* tuning knobs (all optional): key in {"chunk_pixels","leaf_max","pad_scale","block","ctas_per_sm"} */
+int rt_set_option(rt_ctx* ctx, const char* key, double value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB200_H */

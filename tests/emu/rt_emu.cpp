@@ -1,0 +1,244 @@
+// rt_emu.cpp — TEST HARNESS ONLY.  Runs the product's host/device headers (rt_core.h, rt_build_steps.h: the very code the
+// CUDA kernels instantiate) serially on the CPU so the BVH build, traversal, shading, wave/depth bookkeeping and pixel
+// mapping can be checked against the oracle in the `-m "not gpu"` suite, where no GPU exists.
+// It exports only emu_* symbols, is built into tests/emu/ and is never loaded by the product package: librtb200.so has
+// no CPU path and fails without a CUDA device.
+#include <vector>
+#include <algorithm>
+#include <numeric>
+#include <cstdio>
+#include "../../unity-raytracer_b200/csrc/rt_core.h"
+#include "../../unity-raytracer_b200/csrc/rt_build_steps.h"
+#include "../../unity-raytracer_b200/csrc/rt_host_scene.h"
+
+namespace {
+
+struct VecStack {
+    int buf[256]; int sp = 0; int max_sp = 0;
+    void push(int v) { buf[sp++] = v; if (sp > max_sp) max_sp = sp; }
+    int pop() { return buf[--sp]; }
+    bool empty() const { return sp == 0; }
+};
+
+struct Emu {
+    RtHostScene host;
+    // "device" memory
+    std::vector<float> raw_v, raw_n; std::vector<float4> raw_s;
+    std::vector<int32_t> mesh_base;
+    std::vector<float4> nodes, prims, pinfo, mats, mesh_aabb, lights;
+    RtScene S{};
+    int n_nodes = 0, max_stack = 0;
+    bool has_mirror = false;
+};
+
+void commit(Emu& E, int leaf_max, double pad_scale, double t_slack) {
+    RtHostScene& H = E.host;
+    const int n_mt = H.n_meshtris(), n_sp = H.n_spheres(), n_lo = H.n_loose(), n_me = H.n_meshes(), n_li = H.n_lights();
+    const int n = (int)H.n_prims();
+    E.raw_v = H.mesh_v; E.raw_v.insert(E.raw_v.end(), H.loose_v.begin(), H.loose_v.end());
+    E.raw_n = H.mesh_n; E.raw_n.insert(E.raw_n.end(), H.loose_n.begin(), H.loose_n.end());
+    E.raw_s.resize(n_sp);
+    for (int i = 0; i < n_sp; ++i) E.raw_s[i] = make_float4(H.spheres[4 * i], H.spheres[4 * i + 1], H.spheres[4 * i + 2], H.spheres[4 * i + 3]);
+    E.mesh_base = H.mesh_base; E.mesh_base.push_back(n_mt);
+    std::vector<float> m = H.pack_materials();
+    E.has_mirror = H.has_mirror;
+    E.mats.resize(m.size() / 4);
+    memcpy(E.mats.data(), m.data(), m.size() * 4);
+    E.mesh_aabb.resize(2 * n_me);
+    for (int k = 0; k < n_me; ++k) {
+        E.mesh_aabb[2 * k] = make_float4(H.mesh_aabb[6 * k], H.mesh_aabb[6 * k + 1], H.mesh_aabb[6 * k + 2], 0.f);
+        E.mesh_aabb[2 * k + 1] = make_float4(H.mesh_aabb[6 * k + 3], H.mesh_aabb[6 * k + 4], H.mesh_aabb[6 * k + 5], 0.f);
+    }
+    E.lights.resize(2 * n_li);
+    for (int k = 0; k < n_li; ++k) {
+        E.lights[2 * k] = make_float4(H.lights[6 * k], H.lights[6 * k + 1], H.lights[6 * k + 2], 0.f);
+        E.lights[2 * k + 1] = make_float4(H.lights[6 * k + 3], H.lights[6 * k + 4], H.lights[6 * k + 5], 0.f);
+    }
+    RtScene& S = E.S; S = RtScene{};
+    S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_mt; S.n_spheres = n_sp; S.n_lights = n_li;
+    S.aabb_min = mk3(H.aabb[0], H.aabb[1], H.aabb[2]); S.aabb_max = mk3(H.aabb[3], H.aabb[4], H.aabb[5]);
+    S.ambient = mk3(H.ambient[0], H.ambient[1], H.ambient[2]);
+    S.t_slack = (float)t_slack;
+    S.mats = E.mats.data(); S.mesh_aabb = E.mesh_aabb.data(); S.mesh_base = E.mesh_base.data(); S.lights = E.lights.data();
+    E.n_nodes = 0;
+    if (n == 0) return;
+    RtRaw R{E.raw_v.data(), E.raw_n.data(), E.raw_s.data(), E.mesh_base.data(), n_me, n_mt, n_sp, n_lo};
+    leaf_max = leaf_max < 1 ? 1 : (leaf_max > 8 ? 8 : leaf_max);
+    float b[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = 0; i < n; ++i) {
+        f3 lo, hi; rt_prim_box(R, i, lo, hi);
+        b[0] = fminf(b[0], lo.x); b[1] = fminf(b[1], lo.y); b[2] = fminf(b[2], lo.z);
+        b[3] = fmaxf(b[3], hi.x); b[4] = fmaxf(b[4], hi.y); b[5] = fmaxf(b[5], hi.z);
+    }
+    float amax = 0.f; for (int k = 0; k < 6; ++k) if (std::isfinite(b[k])) amax = fmaxf(amax, fabsf(b[k]));
+    const float pad = (float)(amax * pad_scale) + 1e-30f;
+    f3 bmin = mk3(b[0], b[1], b[2]);
+    f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
+    std::vector<uint64_t> keys(n); std::vector<int32_t> vals(n);
+    for (int i = 0; i < n; ++i) { f3 lo, hi; rt_prim_box(R, i, lo, hi); keys[i] = rt_morton(lo, hi, bmin, inv_ext); vals[i] = i; }
+    std::stable_sort(vals.begin(), vals.end(), [&](int a, int c) { return keys[a] < keys[c]; });   // radix sort is stable
+    std::vector<uint64_t> skeys(n);
+    for (int i = 0; i < n; ++i) skeys[i] = keys[vals[i]];
+    E.prims.assign((size_t)3 * n, float4{}); E.pinfo.assign(n, float4{});
+    std::vector<float4> leaf_lo(n), leaf_hi(n);
+    for (int s = 0; s < n; ++s) rt_emit_slot(R, s, vals[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
+    S.prims = E.prims.data(); S.pinfo = E.pinfo.data();
+    if (n <= leaf_max) { S.root = ~(n - 1); E.nodes.assign(4, float4{}); S.nodes = E.nodes.data(); return; }
+    const int ni = n - 1;
+    std::vector<int32_t> tp((size_t)5 * ni + n, 0);
+    RtTopo T{tp.data(), tp.data() + ni, tp.data() + 2 * (size_t)ni, tp.data() + 3 * (size_t)ni, tp.data() + 4 * (size_t)ni, tp.data() + 5 * (size_t)ni};
+    for (int i = 0; i < ni; ++i) rt_karras_node(skeys.data(), n, i, T);
+    std::vector<float4> int_lo(ni), int_hi(ni); std::vector<int32_t> flags(ni, 0);
+    for (int s = 0; s < n; ++s) {                                   // k_refit, serialised
+        int p = T.parent_leaf[s];
+        while (p >= 0) {
+            if (flags[p]++ == 0) break;
+            int l = T.left[p], r = T.right[p];
+            float4 alo = l < 0 ? leaf_lo[~l] : int_lo[l], ahi = l < 0 ? leaf_hi[~l] : int_hi[l];
+            float4 blo = r < 0 ? leaf_lo[~r] : int_lo[r], bhi = r < 0 ? leaf_hi[~r] : int_hi[r];
+            int_lo[p] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+            int_hi[p] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+            p = T.parent_int[p];
+        }
+    }
+    std::vector<int32_t> new_index(ni);
+    int run = 0;
+    for (int i = 0; i < ni; ++i) { new_index[i] = run; run += (T.last[i] - T.first[i] + 1 > leaf_max) ? 1 : 0; }
+    E.n_nodes = run;
+    E.nodes.assign((size_t)4 * run, float4{});
+    for (int i = 0; i < ni; ++i) rt_emit_node(i, T, new_index.data(), leaf_max, pad, leaf_lo.data(), leaf_hi.data(), int_lo.data(), int_hi.data(), E.nodes.data());
+    S.root = 0; S.nodes = E.nodes.data();
+}
+
+RtView make_view(const rt_render_params* p, int rank, int world, int band_rows) {
+    RtView V{};
+    V.pos = mk3(p->pos[0], p->pos[1], p->pos[2]); V.fwd = mk3(p->fwd[0], p->fwd[1], p->fwd[2]);
+    V.right = mk3(p->right[0], p->right[1], p->right[2]); V.up = mk3(p->up[0], p->up[1], p->up[2]);
+    V.res_x = p->res_x; V.res_y = p->res_y; V.dist = p->dist; V.half_h = p->half_h; V.half_v = p->half_v;
+    V.bg255 = mk3(p->background_rgb[0] * 255.f, p->background_rgb[1] * 255.f, p->background_rgb[2] * 255.f);
+    V.max_bounces = p->max_reflection_bounces < 0 ? 0 : p->max_reflection_bounces;
+    V.spp_grid = p->spp_grid < 1 ? 1 : p->spp_grid;
+    V.rank = rank; V.world = world; V.band_rows = band_rows;
+    V.tiles_x = (V.res_x + 7) / 8;
+    V.n_local_rows = rt_local_rows(V.res_y, rank, world, band_rows);
+    V.n_tiles = V.tiles_x * ((V.n_local_rows + 3) / 4);
+    return V;
+}
+
+}  // namespace
+
+extern "C" {
+
+void* emu_new() { return new Emu(); }
+void emu_free(void* e) { delete (Emu*)e; }
+int emu_scene_spheres(void* e, const float* c, const rt_material* m, int n) {
+    Emu* E = (Emu*)e; E->host.spheres.insert(E->host.spheres.end(), c, c + 4 * (size_t)n); E->host.sphere_mats.insert(E->host.sphere_mats.end(), m, m + n); return 0;
+}
+int emu_scene_triangles(void* e, const float* v, const float* nn, const rt_material* m, int n) {
+    Emu* E = (Emu*)e;
+    E->host.loose_v.insert(E->host.loose_v.end(), v, v + 9 * (size_t)n); E->host.loose_n.insert(E->host.loose_n.end(), nn, nn + 3 * (size_t)n);
+    E->host.loose_mats.insert(E->host.loose_mats.end(), m, m + n); return 0;
+}
+int emu_scene_mesh(void* e, const float* v, const float* nn, int n, const rt_material* m, const float* aabb) {
+    Emu* E = (Emu*)e;
+    E->host.mesh_base.push_back(E->host.n_meshtris());
+    E->host.mesh_v.insert(E->host.mesh_v.end(), v, v + 9 * (size_t)n); E->host.mesh_n.insert(E->host.mesh_n.end(), nn, nn + 3 * (size_t)n);
+    E->host.mesh_mats.push_back(*m); E->host.mesh_aabb.insert(E->host.mesh_aabb.end(), aabb, aabb + 6); return 0;
+}
+int emu_scene_lights(void* e, const float* pi, int n, const float* amb) {
+    Emu* E = (Emu*)e; E->host.lights.assign(pi, pi + 6 * (size_t)n);
+    for (int k = 0; k < 3; ++k) E->host.ambient[k] = amb ? amb[k] : 0.f; return 0;
+}
+int emu_scene_commit(void* e, const float* aabb, int leaf_max, double pad_scale, double t_slack) {
+    Emu* E = (Emu*)e;
+    if (aabb) for (int k = 0; k < 6; ++k) E->host.aabb[k] = aabb[k]; else E->host.calc_aabb();
+    commit(*E, leaf_max, pad_scale, t_slack);
+    return 0;
+}
+void emu_get_aabb(void* e, float* out) { for (int k = 0; k < 6; ++k) out[k] = ((Emu*)e)->host.aabb[k]; }
+int emu_n_nodes(void* e) { return ((Emu*)e)->n_nodes; }
+int emu_max_stack(void* e) { return ((Emu*)e)->max_stack; }
+
+int emu_intersect(void* e, const float* o, const float* d, int n, int32_t* out_id, float* out_t) {
+    Emu* E = (Emu*)e; const RtScene& S = E->S;
+    VecStack stk;
+    for (int i = 0; i < n; ++i) {
+        f3 O = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+        float bt = FLT_MAX; int bs = -1;
+        if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
+        int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
+        out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
+    }
+    if (stk.max_sp > E->max_stack) E->max_stack = stk.max_sp;
+    return 0;
+}
+
+// Mirrors rt_device_render (rt_render.cu): waves of tiles, depth loop with queues, back-to-front fold, finalize.
+int emu_render(void* e, const rt_render_params* p, int rank, int world, int band_rows, int chunk_pixels,
+               float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t, uint64_t* stats3) {
+    Emu* E = (Emu*)e; const RtScene& S = E->S;
+    RtView V = make_view(p, rank, world, band_rows);
+    int maxd = (E->has_mirror && V.max_bounces > 0) ? (V.max_bounces > 64 ? 64 : V.max_bounces) : 0;
+    V.max_bounces = maxd;
+    uint64_t n_shadow = 0, n_mirror = 0;
+    if (stats3) stats3[0] = stats3[1] = stats3[2] = 0;
+    if (V.n_tiles <= 0 || V.res_x <= 0) return 0;
+    const int g = V.spp_grid, n_pass = g * g;
+    int wave_tiles = std::max(1, chunk_pixels / 32); if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
+    const size_t W = (size_t)wave_tiles * 32;
+    std::vector<float> hit0_t(W), hitq_t(W); std::vector<int32_t> hit0_slot(W), hitq_slot(W);
+    std::vector<std::vector<float4>> local(maxd + 1, std::vector<float4>(W)), link(maxd + 2, std::vector<float4>(W));
+    std::vector<float4> rays[2] = {std::vector<float4>(2 * W), std::vector<float4>(2 * W)};
+    std::vector<float4> accum((size_t)V.n_tiles * 32);
+    RtOut out{(float4*)rgba32f, (uint32_t*)rgba8, hit_id, hit_t};
+    VecStack stk;
+    for (int sj = 0, pass = 0; sj < g; ++sj) for (int si = 0; si < g; ++si, ++pass)
+        for (int tb = 0; tb < V.n_tiles; tb += wave_tiles) {
+            const int nt = std::min(wave_tiles, V.n_tiles - tb);
+            std::vector<unsigned> count(maxd + 2, 0);
+            for (int t = 0; t < nt; ++t) for (int lane = 0; lane < 32; ++lane) {           // k_trace_primary
+                int x, y; bool valid = rt_item_to_pixel(V, tb + t, lane, x, y);
+                float bt = FLT_MAX; int bs = -1;
+                if (valid) { f3 O, D; rt_primary_ray(V, x, y, si, sj, O, D); if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); } }
+                size_t q = (size_t)t * 32 + lane; hit0_t[q] = bt; hit0_slot[q] = valid ? bs : -2;
+            }
+            for (int d = 0; d <= maxd; ++d) {
+                const unsigned n = d == 0 ? (unsigned)nt * 32u : count[d];
+                const std::vector<float4>& rin = rays[(d + 1) & 1]; std::vector<float4>& rout = rays[d & 1];
+                std::vector<float>& ht = d == 0 ? hit0_t : hitq_t; std::vector<int32_t>& hs = d == 0 ? hit0_slot : hitq_slot;
+                if (d > 0) for (unsigned q = 0; q < n; ++q) {                                  // k_trace_queue
+                    f3 O = mk3(rin[2 * q].x, rin[2 * q].y, rin[2 * q].z), D = mk3(rin[2 * q + 1].x, rin[2 * q + 1].y, rin[2 * q + 1].z);
+                    float bt = FLT_MAX; int bs = -1;
+                    if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
+                    ht[q] = bt; hs[q] = bs;
+                }
+                for (unsigned q = 0; q < n; ++q) {                                              // k_shade
+                    RtMirror mir; mir.emit = false;
+                    int slot = hs[q];
+                    if (slot == -1) local[d][q] = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);
+                    else if (slot >= 0) {
+                        f3 O, D;
+                        if (d == 0) { int x, y; rt_item_to_pixel(V, tb + (int)(q >> 5), (int)(q & 31), x, y); rt_primary_ray(V, x, y, si, sj, O, D); }
+                        else { O = mk3(rin[2 * q].x, rin[2 * q].y, rin[2 * q].z); D = mk3(rin[2 * q + 1].x, rin[2 * q + 1].y, rin[2 * q + 1].z); }
+                        uint32_t ns = 0;
+                        f3 c = rt_shade_hit(S, O, D, ht[q], slot, d, V.max_bounces, stk, mir, ns);
+                        n_shadow += ns;
+                        local[d][q] = make_float4(c.x, c.y, c.z, 0.f);
+                    }
+                    if (mir.emit) {
+                        size_t o = count[d + 1]++; ++n_mirror;
+                        rout[2 * o] = make_float4(mir.O.x, mir.O.y, mir.O.z, 0.f); rout[2 * o + 1] = make_float4(mir.D.x, mir.D.y, mir.D.z, 0.f);
+                        link[d + 1][o] = make_float4(mir.km.x, mir.km.y, mir.km.z, i2f((int)q));
+                    }
+                }
+            }
+            for (int d = maxd; d >= 1; --d) for (unsigned q = 0; q < count[d]; ++q) rt_fold_item(q, link[d].data(), local[d].data(), local[d - 1].data());
+            for (unsigned q = 0; q < (unsigned)nt * 32u; ++q)
+                rt_finalize_item(S, V, tb, q, pass, n_pass, local[0].data(), hit0_t.data(), hit0_slot.data(), accum.data(), out);
+        }
+    if (stk.max_sp > E->max_stack) E->max_stack = stk.max_sp;
+    if (stats3) { stats3[0] = (uint64_t)V.res_x * V.n_local_rows * n_pass; stats3[1] = n_shadow; stats3[2] = n_mirror; }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+"""-m gpu: the CUDA path, called through the C-ABI (ctypes -> librtb200.so), against the CPU oracle on the same inputs."""
+import numpy as np
+import pytest
+
+from conftest import compare_renders
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rt(rtb):
+    r = rtb.RayTracer((0,))
+    yield r
+    r.close()
+
+
+def _check(cmp, exact_float=True):
+    assert cmp["id"] == 0 and cmp["t"] == 0, cmp
+    assert cmp["u8_gt1"] == 0, cmp
+    assert cmp["u8_gt0"] <= max(1, cmp["n"] // 1000), cmp          # >= 99.9 % of pixels identical after quantisation
+    if exact_float:
+        # float colour may differ only through pow() (CUDA double pow vs glibc): allow a handful of last-ulp pixels
+        assert cmp["f32"] <= max(2, cmp["n"] // 200), cmp
+
+
+def test_kat_sphere_reference_test(rt, scenes):
+    """Tests/RayTracerTests.cs:8-27: ray (0,0,0)->(1,0,0) vs sphere C=(300,0,0) r2=1 hits at t = 299."""
+    s = scenes.SceneArrays()
+    s.add_sphere((300, 0, 0), 1.0, scenes.material())
+    rt.set_scene(s)
+    ids, t = rt.intersect([(0, 0, 0)], [(1, 0, 0)])
+    assert ids[0].tolist() == [1, 0, -1] and t[0] == np.float32(299.0)
+
+
+def test_cfg1_rt_unity(rt, scenes, oracle):
+    s, p = scenes.rt_unity(), scenes.rt_unity_params()
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    rt.set_scene(s)
+    got = rt.render(p)
+    _check(compare_renders(ref, got))
+    st = got["stats"]
+    assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == ref["stats"]
+    # KAT-2: centre ray hits the sphere at 19.6 and shades to (244.60649, 15, 15)
+    ids, t = rt.intersect([(0, 0, 0)], [(0, 0, 1)])
+    assert ids[0].tolist() == [1, 0, -1] and t[0] == np.float32(19.6)
+
+
+def test_cfg2_mirror_depth4(rt, scenes, oracle):
+    s, p = scenes.rt_unity(mirror_sphere=True), scenes.rt_unity_params(480, 270, 4)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    rt.set_scene(s)
+    got = rt.render(p)
+    _check(compare_renders(ref, got))
+    assert got["stats"]["rays_mirror"] == ref["stats"][2] > 0
+    assert got["stats"]["rays_shadow"] == ref["stats"][1]
+
+
+@pytest.mark.parametrize("seed,spp", [(7, 1), (3, 2)])
+def test_random_soup_vs_faithful_scan(rt, scenes, oracle, seed, spp):
+    s, p = scenes.random_soup(seed=seed), scenes.soup_params(96, 64, 3, spp)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    rt.set_scene(s)
+    got = rt.render(p)
+    _check(compare_renders(ref, got))
+    st = got["stats"]
+    assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == ref["stats"]
+
+
+def test_intersect_random_rays(rt, scenes, oracle):
+    s = scenes.random_soup(seed=11)
+    rng = np.random.default_rng(5)
+    o = rng.uniform(-40, 40, (20000, 3)).astype(np.float32)
+    d = rng.normal(size=(20000, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d = d.astype(np.float32)
+    rid, rt_ = oracle.OracleScene(s).intersect(o, d, oracle.FAITHFUL)
+    rt.set_scene(s)
+    gid, gt = rt.intersect(o, d)
+    assert (rid[:, :2] == gid[:, :2]).all() and (rt_ == gt).all()
+    mesh = rid[:, 0] == 3
+    assert (rid[mesh, 2] == gid[mesh, 2]).all()
+
+
+def test_cfg3_reduced(rt, scenes, oracle):
+    """~130k-triangle displaced sphere, 640x360: full frame vs the accelerated oracle, pixel subset vs the faithful scan."""
+    s, p = scenes.cfg3_scene(n=80), scenes.cfg3_params(640, 360)
+    ora = oracle.OracleScene(s)
+    ref = ora.render(p, oracle.ACCELERATED)
+    rt.set_scene(s)
+    got = rt.render(p)
+    _check(compare_renders(ref, got))
+    px = np.random.default_rng(1).choice(640 * 360, 1024, replace=False)
+    sub = ora.render(p, oracle.FAITHFUL, pixels=px)
+    gsub = {k: got[k][px] for k in ("rgba32f", "rgba8", "hit_id", "hit_t")}
+    _check(compare_renders(sub, gsub))
+
+
+def test_edge_cases(rt, scenes):
+    # empty scene: everything misses, background colour, FLT_MAX distance (Scene.cs:45-61)
+    s = scenes.SceneArrays()
+    rt.set_scene(s)
+    p = scenes.make_params(33, 17, 10.0, 8.0, 5.0, (0.25, 0.5, 1.0))
+    got = rt.render(p)
+    assert (got["hit_id"] == np.array([0, -1, -1])).all()
+    assert (got["hit_t"] == np.finfo(np.float32).max).all()
+    assert (got["rgba8"] == np.array([64, 128, 255, 255], np.uint8)).all()
+    # 0x0 image plane (Assets/Scenes/SampleScene.unity ships one): a no-op
+    got = rt.render(scenes.make_params(0, 0, 10.0, 8.0, 5.0))
+    assert got["rgba32f"].shape == (0, 4) and got["stats"]["rays_primary"] == 0
+    # no lights: ambient only
+    s = scenes.SceneArrays(); s.add_sphere((0, 0, 20), 25.0, scenes.material(ambient=(1, 0.5, 0.25))); s.ambient[:] = (100, 100, 100)
+    rt.set_scene(s)
+    got = rt.render(scenes.make_params(9, 9, 10.0, 1.0, 1.0))
+    assert (got["rgba8"][40] == np.array([100, 50, 25, 255], np.uint8)).all()
+
+
+def test_partition_union_equals_full_frame(rtb, scenes):
+    """rank r of w renders only its row bands; the union over ranks is bit-identical to the 1-rank frame."""
+    s, p = scenes.random_soup(seed=5), scenes.soup_params(100, 77, 2, 1)
+    full = rtb.RayTracer((0,)); full.set_scene(s)
+    ref = full.render(p)
+    for world in (2, 3):
+        acc = {k: np.zeros_like(ref[k]) for k in ("rgba32f", "rgba8", "hit_id", "hit_t")}
+        for r in range(world):
+            part = rtb.RayTracer((0,)); part.set_partition(r, world, 8); part.set_scene(s)
+            g = part.render(p)
+            rows = np.arange(77); mine = ((rows // 8) % world) == r
+            mask = np.repeat(mine, 100)
+            for k in acc:
+                acc[k][mask] = g[k][mask]
+            part.close()
+        for k in acc:
+            assert (acc[k] == ref[k]).all() or k == "rgba32f" and np.array_equal(acc[k], ref[k], equal_nan=True), (world, k)
+    full.close()
+
+
+def test_small_waves_equal_one_wave(rt, scenes):
+    s, p = scenes.random_soup(seed=9), scenes.soup_params(96, 64, 3, 1)
+    rt.set_scene(s)
+    a = rt.render(p)
+    rt.set_option("chunk_pixels", 512)
+    b = rt.render(p)
+    rt.set_option("chunk_pixels", 1 << 23)
+    for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(a[k], b[k], equal_nan=True), k

@@ -1,0 +1,24 @@
+"""Quick on-GPU probe: commit + render timings for a config (not the bench contract; a development aid)."""
+import importlib, sys, time, os, json
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+rtb = importlib.import_module("unity-raytracer_b200")
+sc = rtb.scenes
+cfg = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
+reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+opts = dict(a.split("=") for a in sys.argv[3:])
+t0 = time.time()
+if cfg == "cfg2": s, p = sc.rt_unity(True), sc.rt_unity_params(3840, 2160, 4)
+elif cfg == "cfg3": s, p = sc.cfg3_scene(), sc.cfg3_params()
+elif cfg == "cfg4": s, p = sc.cfg4_scene(), sc.cfg4_params()
+elif cfg == "cfg5": s, p = sc.cfg5_scene(), sc.cfg5_params()
+else: s, p = sc.cfg3_scene(n=int(cfg)), sc.cfg3_params()
+print(f"scene {cfg}: {s.n_prims} prims, generated in {time.time()-t0:.1f}s", flush=True)
+rt = rtb.RayTracer((0,))
+for k, v in opts.items(): rt.set_option(k, float(v))
+t0 = time.time(); rt.set_scene(s); print(f"commit wall {time.time()-t0:.3f}s", flush=True)
+for i in range(reps):
+    st = rt.render_device(p, rtb.host.RT_OUT_RGBA8, sync_stats=True)
+    rays = st["rays_primary"] + st["rays_shadow"] + st["rays_mirror"]
+    print(json.dumps(dict(ms=round(st["ms_render"], 3), mrays=round(rays / st["ms_render"] / 1e3, 1), rays=rays, launches=st["kernel_launches"],
+                          nodes=st["n_nodes"], commit_up=round(st["ms_commit_upload"], 2), commit_build=round(st["ms_commit_build"], 2))), flush=True)

@@ -1,0 +1,431 @@
+// rt_abi.cu — the extern "C" boundary of librtb200.so (include/rtb200.h): context, scene staging, commit, render,
+// multi-device band partition and the peer-store framebuffer gather.  No exceptions cross this boundary.
+#include "rt_internal.h"
+#include <new>
+#include <chrono>
+
+struct rt_ctx {
+    std::vector<RtDevice> devs;
+    RtHostScene host;
+    RtOptions opt;
+    std::string err;
+    rt_stats stats{};
+    bool in_scene = false, committed = false;
+    int ext_rank = 0, ext_world = 1, band_rows = 32;
+    int last_res_x = 0, last_res_y = 0, last_want = 0;
+    bool stats_pending = false;
+    std::vector<RtFrameStats> fstats;
+};
+
+static thread_local std::string g_err;   // rt_last_error(NULL): errors of rt_create
+
+namespace {
+
+int fail(rt_ctx* c, int code, const std::string& msg) { if (c) c->err = msg; else g_err = msg; return code; }
+
+void device_release(RtDevice& D) {
+    if (D.device < 0) return;
+    cudaSetDevice(D.device);
+    for (DevBuf* b : {&D.raw_v, &D.raw_n, &D.raw_s, &D.nodes, &D.prims, &D.pinfo, &D.mats, &D.mesh_aabb, &D.mesh_base, &D.lights, &D.keys,
+                      &D.keys_alt, &D.vals, &D.vals_alt, &D.cub_tmp, &D.bounds, &D.topo_i32, &D.leaf_lo, &D.leaf_hi, &D.int_lo, &D.int_hi,
+                      &D.flags, &D.new_index, &D.hit0_t, &D.hit0_slot, &D.hitq_t, &D.hitq_slot, &D.rays[0], &D.rays[1], &D.counters, &D.accum,
+                      &D.stats, &D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t})
+        b->release();
+    for (auto& b : D.local) b.release();
+    for (auto& b : D.link) b.release();
+    void* imp[4] = {D.o_rgba32f, D.o_rgba8, D.o_hit_id, D.o_hit_t};
+    for (int k = 0; k < 4; ++k) if (D.imported[k] && imp[k]) cudaIpcCloseMemHandle(imp[k]);
+    if (D.ev0) cudaEventDestroy(D.ev0);
+    if (D.ev1) cudaEventDestroy(D.ev1);
+    if (D.own_stream) cudaStreamDestroy(D.own_stream);
+    D.device = -1;
+}
+
+size_t out_bytes(int k, int rx, int ry) {
+    size_t px = (size_t)rx * (size_t)ry;
+    return k == 0 ? px * 16 : (k == 1 ? px * 4 : (k == 2 ? px * 12 : px * 4));
+}
+
+// allocate (on device 0) the full-frame outputs named in `want`; point every device at them (peer mappings in-process)
+int ensure_outputs(rt_ctx* c, int rx, int ry, int want) {
+    std::string& err = c->err;
+    RtDevice& D0 = c->devs[0];
+    RT_CUDA(cudaSetDevice(D0.device));
+    DevBuf* own[4] = {&D0.own_rgba32f, &D0.own_rgba8, &D0.own_hit_id, &D0.own_hit_t};
+    void** ptr[4] = {&D0.o_rgba32f, &D0.o_rgba8, &D0.o_hit_id, &D0.o_hit_t};
+    for (int k = 0; k < 4; ++k) {
+        if (!(want & (1 << k)) || D0.imported[k]) continue;
+        RT_CUDA(own[k]->ensure(out_bytes(k, rx, ry)));
+        *ptr[k] = own[k]->p;
+    }
+    D0.out_res_x = rx; D0.out_res_y = ry;
+    for (size_t i = 1; i < c->devs.size(); ++i) {
+        RtDevice& D = c->devs[i];
+        D.o_rgba32f = D0.o_rgba32f; D.o_rgba8 = D0.o_rgba8; D.o_hit_id = D0.o_hit_id; D.o_hit_t = D0.o_hit_t;
+        D.out_res_x = rx; D.out_res_y = ry;
+    }
+    return RT_OK;
+}
+
+RtView make_view(const rt_ctx* c, const rt_render_params* p, int dev_index) {
+    RtView V{};
+    V.pos = mk3(p->pos[0], p->pos[1], p->pos[2]); V.fwd = mk3(p->fwd[0], p->fwd[1], p->fwd[2]);
+    V.right = mk3(p->right[0], p->right[1], p->right[2]); V.up = mk3(p->up[0], p->up[1], p->up[2]);
+    V.res_x = p->res_x; V.res_y = p->res_y; V.dist = p->dist; V.half_h = p->half_h; V.half_v = p->half_v;
+    V.bg255 = mk3(p->background_rgb[0] * 255.f, p->background_rgb[1] * 255.f, p->background_rgb[2] * 255.f);   // Rgb.cs:15-18
+    V.max_bounces = p->max_reflection_bounces < 0 ? 0 : p->max_reflection_bounces;
+    V.spp_grid = p->spp_grid < 1 ? 1 : p->spp_grid;
+    const int nd = (int)c->devs.size();
+    V.rank = c->ext_rank * nd + dev_index; V.world = c->ext_world * nd; V.band_rows = c->band_rows;
+    V.tiles_x = (V.res_x + 7) / 8;
+    V.n_local_rows = rt_local_rows(V.res_y, V.rank, V.world, V.band_rows);
+    V.n_tiles = V.tiles_x * ((V.n_local_rows + 3) / 4);
+    return V;
+}
+
+int validate_params(rt_ctx* c, const rt_render_params* p) {
+    if (!p) return fail(c, RT_E_INVALID, "params is NULL");
+    if (p->res_x < 0 || p->res_y < 0) return fail(c, RT_E_INVALID, "negative resolution");
+    if ((int64_t)p->res_x * p->res_y > (int64_t)1 << 30) return fail(c, RT_E_UNSUPPORTED, "resolution above 2^30 pixels");
+    if (p->spp_grid > 64) return fail(c, RT_E_INVALID, "spp_grid above 64");
+    return RT_OK;
+}
+
+int finish_stats(rt_ctx* c) {
+    if (!c->stats_pending) return RT_OK;
+    std::string& err = c->err;
+    uint64_t pr = 0, sh = 0, mi = 0; uint32_t launches = 0; float ms = 0.f;
+    for (size_t i = 0; i < c->devs.size(); ++i) {
+        RtDevice& D = c->devs[i];
+        RtFrameStats fs = c->fstats[i];
+        int rc = rt_device_read_stats(D, &fs, err);
+        if (rc) return rc;
+        RT_CUDA(cudaEventSynchronize(D.ev1));
+        float m = 0.f; RT_CUDA(cudaEventElapsedTime(&m, D.ev0, D.ev1));
+        ms = m > ms ? m : ms;
+        pr += fs.primary; sh += fs.shadow; mi += fs.mirror; launches += fs.launches;
+    }
+    c->stats.rays_primary = pr; c->stats.rays_shadow = sh; c->stats.rays_mirror = mi;
+    c->stats.ms_render = ms; c->stats.kernel_launches = launches;
+    c->stats_pending = false;
+    return RT_OK;
+}
+
+int render_device_impl(rt_ctx* c, const rt_render_params* p, int want) {
+    int rc = validate_params(c, p);
+    if (rc) return rc;
+    if (!c->committed) return fail(c, RT_E_STATE, "rt_render before rt_scene_commit");
+    c->last_res_x = p->res_x; c->last_res_y = p->res_y; c->last_want = want;
+    c->stats.rays_primary = c->stats.rays_shadow = c->stats.rays_mirror = 0;
+    c->stats.ms_render = 0.f; c->stats.kernel_launches = 0; c->stats.ms_d2h = 0.f; c->stats.d2h_bytes = 0;
+    if ((int64_t)p->res_x * p->res_y == 0) { c->stats_pending = false; return RT_OK; }     // 0x0 ImagePlane: a no-op
+    rc = ensure_outputs(c, p->res_x, p->res_y, want);
+    if (rc) return rc;
+    c->fstats.assign(c->devs.size(), RtFrameStats{});
+    for (size_t i = 0; i < c->devs.size(); ++i) {
+        RtView V = make_view(c, p, (int)i);
+        rc = rt_device_render(c->devs[i], V, want, c->opt, c->err, &c->fstats[i]);
+        if (rc) return rc;
+    }
+    c->stats_pending = true;
+    return RT_OK;
+}
+
+int sync_all(rt_ctx* c) {
+    std::string& err = c->err;
+    for (auto& D : c->devs) { RT_CUDA(cudaSetDevice(D.device)); RT_CUDA(cudaStreamSynchronize(D.stream)); }
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_abi_version(void) { return RTB200_ABI_VERSION; }
+
+const char* rt_last_error(const rt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_err.c_str(); }
+
+int rt_create(rt_ctx** out, const int* device_ids, int n_devices) {
+    if (!out) return fail(nullptr, RT_E_INVALID, "out is NULL");
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > 16) return fail(nullptr, RT_E_INVALID, "n_devices must be in 1..16");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count < 1)
+        return fail(nullptr, RT_E_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) + " (librtb200 has no CPU fallback)");
+    rt_ctx* c = new (std::nothrow) rt_ctx();
+    if (!c) return fail(nullptr, RT_E_OOM, "host allocation failed");
+    std::string& err = g_err;
+    c->devs.resize(n_devices);
+    auto bail = [&](int code) { for (auto& D : c->devs) device_release(D); delete c; return code; };
+    for (int i = 0; i < n_devices; ++i) {
+        RtDevice& D = c->devs[i];
+        int dev = device_ids ? device_ids[i] : i;
+        if (dev < 0 || dev >= count) { g_err = "device id out of range"; return bail(RT_E_INVALID); }
+        D.device = dev;
+        cudaDeviceProp prop;
+        if ((e = cudaSetDevice(dev)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess ||
+            (e = cudaStreamCreateWithFlags(&D.own_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+            (e = cudaEventCreate(&D.ev0)) != cudaSuccess || (e = cudaEventCreate(&D.ev1)) != cudaSuccess) {
+            g_err = std::string("device init failed: ") + cudaGetErrorString(e);
+            return bail(RT_E_CUDA);
+        }
+        D.stream = D.own_stream;
+        D.sm_count = prop.multiProcessorCount;
+        D.rank = i; D.world = n_devices;
+    }
+    // peer mappings towards the gather device (device_ids[0]) for the fused framebuffer gather
+    for (int i = 1; i < n_devices; ++i) {
+        int can = 0;
+        cudaDeviceCanAccessPeer(&can, c->devs[i].device, c->devs[0].device);
+        if (!can) { g_err = "devices cannot access device_ids[0] as a peer"; return bail(RT_E_UNSUPPORTED); }
+        cudaSetDevice(c->devs[i].device);
+        e = cudaDeviceEnablePeerAccess(c->devs[0].device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { g_err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e); return bail(RT_E_CUDA); }
+        cudaGetLastError();
+    }
+    (void)err;
+    *out = c;
+    return RT_OK;
+}
+
+void rt_destroy(rt_ctx* c) {
+    if (!c) return;
+    for (auto& D : c->devs) { if (D.device >= 0) { cudaSetDevice(D.device); cudaStreamSynchronize(D.stream); } }
+    for (auto& D : c->devs) device_release(D);
+    delete c;
+}
+
+int rt_scene_begin(rt_ctx* c) {
+    if (!c) return RT_E_INVALID;
+    c->host.clear(); c->in_scene = true; c->committed = false;
+    return RT_OK;
+}
+
+int rt_scene_spheres(rt_ctx* c, const float* center_r2, const rt_material* mats, int n) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_spheres outside rt_scene_begin/commit");
+    if (n < 0 || (n > 0 && (!center_r2 || !mats))) return fail(c, RT_E_INVALID, "rt_scene_spheres: bad arguments");
+    c->host.spheres.insert(c->host.spheres.end(), center_r2, center_r2 + 4 * (size_t)n);
+    c->host.sphere_mats.insert(c->host.sphere_mats.end(), mats, mats + n);
+    return RT_OK;
+}
+
+int rt_scene_triangles(rt_ctx* c, const float* v, const float* normals, const rt_material* mats, int n) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_triangles outside rt_scene_begin/commit");
+    if (n < 0 || (n > 0 && (!v || !normals || !mats))) return fail(c, RT_E_INVALID, "rt_scene_triangles: bad arguments");
+    c->host.loose_v.insert(c->host.loose_v.end(), v, v + 9 * (size_t)n);
+    c->host.loose_n.insert(c->host.loose_n.end(), normals, normals + 3 * (size_t)n);
+    c->host.loose_mats.insert(c->host.loose_mats.end(), mats, mats + n);
+    return RT_OK;
+}
+
+int rt_scene_mesh(rt_ctx* c, const float* v, const float* normals, int n_tris, const rt_material* mat, const float aabb[6]) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_mesh outside rt_scene_begin/commit");
+    if (n_tris < 0 || !mat || !aabb || (n_tris > 0 && (!v || !normals))) return fail(c, RT_E_INVALID, "rt_scene_mesh: bad arguments");
+    c->host.mesh_base.push_back(c->host.n_meshtris());
+    c->host.mesh_v.insert(c->host.mesh_v.end(), v, v + 9 * (size_t)n_tris);
+    c->host.mesh_n.insert(c->host.mesh_n.end(), normals, normals + 3 * (size_t)n_tris);
+    c->host.mesh_mats.push_back(*mat);
+    c->host.mesh_aabb.insert(c->host.mesh_aabb.end(), aabb, aabb + 6);
+    return RT_OK;
+}
+
+int rt_scene_lights(rt_ctx* c, const float* pos_intensity, int n, const float ambient[3]) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_lights outside rt_scene_begin/commit");
+    if (n < 0 || (n > 0 && !pos_intensity)) return fail(c, RT_E_INVALID, "rt_scene_lights: bad arguments");
+    c->host.lights.assign(pos_intensity, pos_intensity + 6 * (size_t)n);
+    for (int k = 0; k < 3; ++k) c->host.ambient[k] = ambient ? ambient[k] : 0.f;
+    return RT_OK;
+}
+
+int rt_scene_commit(rt_ctx* c, const float scene_aabb[6]) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_commit without rt_scene_begin");
+    if (scene_aabb) for (int k = 0; k < 6; ++k) c->host.aabb[k] = scene_aabb[k];
+    else c->host.calc_aabb();
+    float up = 0.f, bd = 0.f; uint64_t bytes = 0;
+    for (auto& D : c->devs) {
+        float u = 0.f, b = 0.f; uint64_t by = 0;
+        int rc = rt_device_commit(D, c->host, c->opt, c->err, &u, &b, &by);
+        if (rc) return rc;
+        up += u; bd += b; bytes += by;
+    }
+    c->stats.ms_commit_upload = up; c->stats.ms_commit_build = bd; c->stats.h2d_bytes = bytes;
+    c->stats.n_prims = (uint32_t)c->host.n_prims(); c->stats.n_nodes = c->devs[0].n_nodes;
+    c->in_scene = false; c->committed = true;
+    return RT_OK;
+}
+
+int rt_scene_get_aabb(rt_ctx* c, float out[6]) {
+    if (!c || !out) return RT_E_INVALID;
+    if (!c->committed) return fail(c, RT_E_STATE, "scene not committed");
+    for (int k = 0; k < 6; ++k) out[k] = c->host.aabb[k];
+    return RT_OK;
+}
+
+int rt_render_device(rt_ctx* c, const rt_render_params* p, int want, rt_stats* stats) {
+    if (!c) return RT_E_INVALID;
+    int rc = render_device_impl(c, p, want);
+    if (rc) return rc;
+    if (stats) { rc = rt_get_stats(c, stats); if (rc) return rc; }
+    return RT_OK;
+}
+
+int rt_read_outputs(rt_ctx* c, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t) {
+    if (!c) return RT_E_INVALID;
+    std::string& err = c->err;
+    const int rx = c->last_res_x, ry = c->last_res_y;
+    if ((int64_t)rx * ry == 0) return RT_OK;
+    int rc = sync_all(c);
+    if (rc) return rc;
+    RtDevice& D0 = c->devs[0];
+    RT_CUDA(cudaSetDevice(D0.device));
+    void* dst[4] = {rgba32f, rgba8, hit_id, hit_t};
+    void* src[4] = {D0.o_rgba32f, D0.o_rgba8, D0.o_hit_id, D0.o_hit_t};
+    auto t0 = std::chrono::steady_clock::now();
+    uint64_t bytes = 0;
+    for (int k = 0; k < 4; ++k) {
+        if (!dst[k]) continue;
+        if (!(c->last_want & (1 << k)) || !src[k]) return fail(c, RT_E_STATE, "requested output was not rendered");
+        RT_CUDA(cudaMemcpyAsync(dst[k], src[k], out_bytes(k, rx, ry), cudaMemcpyDeviceToHost, D0.stream));
+        bytes += out_bytes(k, rx, ry);
+    }
+    RT_CUDA(cudaStreamSynchronize(D0.stream));
+    c->stats.ms_d2h = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->stats.d2h_bytes = bytes;
+    return RT_OK;
+}
+
+int rt_render(rt_ctx* c, const rt_render_params* p, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t, rt_stats* stats) {
+    if (!c) return RT_E_INVALID;
+    int want = (rgba32f ? RT_OUT_RGBA32F : 0) | (rgba8 ? RT_OUT_RGBA8 : 0) | (hit_id ? RT_OUT_HIT_ID : 0) | (hit_t ? RT_OUT_HIT_T : 0);
+    int rc = render_device_impl(c, p, want);
+    if (rc) return rc;
+    rc = rt_read_outputs(c, rgba32f, rgba8, hit_id, hit_t);
+    if (rc) return rc;
+    if (stats) { rc = rt_get_stats(c, stats); if (rc) return rc; }
+    return RT_OK;
+}
+
+int rt_device_outputs(rt_ctx* c, void** rgba32f, void** rgba8, void** hit_id, void** hit_t) {
+    if (!c) return RT_E_INVALID;
+    RtDevice& D0 = c->devs[0];
+    if (rgba32f) *rgba32f = D0.o_rgba32f;
+    if (rgba8) *rgba8 = D0.o_rgba8;
+    if (hit_id) *hit_id = D0.o_hit_id;
+    if (hit_t) *hit_t = D0.o_hit_t;
+    return RT_OK;
+}
+
+int rt_get_stats(rt_ctx* c, rt_stats* stats) {
+    if (!c || !stats) return RT_E_INVALID;
+    int rc = finish_stats(c);
+    if (rc) return rc;
+    *stats = c->stats;
+    return RT_OK;
+}
+
+int rt_intersect(rt_ctx* c, const float* origins, const float* dirs, int n, int32_t* out_id, float* out_t) {
+    if (!c) return RT_E_INVALID;
+    if (!c->committed) return fail(c, RT_E_STATE, "rt_intersect before rt_scene_commit");
+    if (n < 0 || (n > 0 && (!origins || !dirs || !out_id || !out_t))) return fail(c, RT_E_INVALID, "rt_intersect: bad arguments");
+    if (n == 0) return RT_OK;
+    std::string& err = c->err;
+    RtDevice& D = c->devs[0];
+    RT_CUDA(cudaSetDevice(D.device));
+    DevBuf o, d, ids, t;
+    auto cleanup = [&]() { o.release(); d.release(); ids.release(); t.release(); };
+    cudaError_t e;
+    if ((e = o.ensure((size_t)n * 12)) || (e = d.ensure((size_t)n * 12)) || (e = ids.ensure((size_t)n * 12)) || (e = t.ensure((size_t)n * 4))) {
+        cleanup(); return fail(c, RT_E_OOM, cudaGetErrorString(e));
+    }
+    int rc = RT_OK;
+    if ((e = cudaMemcpyAsync(o.p, origins, (size_t)n * 12, cudaMemcpyHostToDevice, D.stream)) ||
+        (e = cudaMemcpyAsync(d.p, dirs, (size_t)n * 12, cudaMemcpyHostToDevice, D.stream))) rc = fail(c, RT_E_CUDA, cudaGetErrorString(e));
+    if (!rc) rc = rt_device_intersect(D, o.as<float>(), d.as<float>(), n, ids.as<int32_t>(), t.as<float>(), c->opt, c->err);
+    if (!rc && ((e = cudaMemcpyAsync(out_id, ids.p, (size_t)n * 12, cudaMemcpyDeviceToHost, D.stream)) ||
+                (e = cudaMemcpyAsync(out_t, t.p, (size_t)n * 4, cudaMemcpyDeviceToHost, D.stream)) ||
+                (e = cudaStreamSynchronize(D.stream)))) rc = fail(c, RT_E_CUDA, cudaGetErrorString(e));
+    cleanup();
+    return rc;
+}
+
+int rt_set_stream(rt_ctx* c, void* cuda_stream) {
+    if (!c) return RT_E_INVALID;
+    RtDevice& D = c->devs[0];
+    cudaSetDevice(D.device);
+    cudaStreamSynchronize(D.stream);
+    D.stream = cuda_stream ? (cudaStream_t)cuda_stream : D.own_stream;
+    return RT_OK;
+}
+
+int rt_set_partition(rt_ctx* c, int rank, int world, int band_rows) {
+    if (!c) return RT_E_INVALID;
+    if (world < 1 || rank < 0 || rank >= world || band_rows < 4 || (band_rows % 4) != 0) return fail(c, RT_E_INVALID, "rt_set_partition: bad arguments");
+    c->ext_rank = rank; c->ext_world = world; c->band_rows = band_rows;
+    return RT_OK;
+}
+
+int rt_alloc_outputs(rt_ctx* c, int res_x, int res_y, int want) {
+    if (!c) return RT_E_INVALID;
+    if (res_x < 0 || res_y < 0) return fail(c, RT_E_INVALID, "negative resolution");
+    return ensure_outputs(c, res_x, res_y, want);
+}
+
+int rt_export_outputs(rt_ctx* c, void* handles) {
+    if (!c || !handles) return RT_E_INVALID;
+    std::string& err = c->err;
+    RtDevice& D0 = c->devs[0];
+    RT_CUDA(cudaSetDevice(D0.device));
+    memset(handles, 0, 4 * sizeof(cudaIpcMemHandle_t));
+    void* ptr[4] = {D0.o_rgba32f, D0.o_rgba8, D0.o_hit_id, D0.o_hit_t};
+    for (int k = 0; k < 4; ++k) {
+        if (!ptr[k] || D0.imported[k]) continue;
+        cudaIpcMemHandle_t h;
+        RT_CUDA(cudaIpcGetMemHandle(&h, ptr[k]));
+        memcpy((char*)handles + k * sizeof(h), &h, sizeof(h));
+    }
+    return RT_OK;
+}
+
+int rt_import_outputs(rt_ctx* c, const void* handles, int res_x, int res_y, int want) {
+    if (!c || !handles) return RT_E_INVALID;
+    std::string& err = c->err;
+    RtDevice& D0 = c->devs[0];
+    RT_CUDA(cudaSetDevice(D0.device));
+    void** ptr[4] = {&D0.o_rgba32f, &D0.o_rgba8, &D0.o_hit_id, &D0.o_hit_t};
+    for (int k = 0; k < 4; ++k) {
+        if (!(want & (1 << k))) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char*)handles + k * sizeof(h), sizeof(h));
+        if (D0.imported[k] && *ptr[k]) { cudaIpcCloseMemHandle(*ptr[k]); *ptr[k] = nullptr; D0.imported[k] = false; }
+        void* p = nullptr;
+        RT_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        *ptr[k] = p; D0.imported[k] = true;
+    }
+    D0.out_res_x = res_x; D0.out_res_y = res_y;
+    for (size_t i = 1; i < c->devs.size(); ++i) {
+        RtDevice& D = c->devs[i];
+        D.o_rgba32f = D0.o_rgba32f; D.o_rgba8 = D0.o_rgba8; D.o_hit_id = D0.o_hit_id; D.o_hit_t = D0.o_hit_t;
+    }
+    return RT_OK;
+}
+
+int rt_set_option(rt_ctx* c, const char* key, double value) {
+    if (!c || !key) return RT_E_INVALID;
+    std::string k(key);
+    if (k == "chunk_pixels") { if (value < 32) return fail(c, RT_E_INVALID, "chunk_pixels < 32"); c->opt.chunk_pixels = ((int)value / 32) * 32; }
+    else if (k == "leaf_max") { if (value < 1 || value > 8) return fail(c, RT_E_INVALID, "leaf_max must be 1..8"); c->opt.leaf_max = (int)value; }
+    else if (k == "pad_scale") { if (value < 0) return fail(c, RT_E_INVALID, "pad_scale < 0"); c->opt.pad_scale = value; }
+    else if (k == "t_slack") { if (value < 1) return fail(c, RT_E_INVALID, "t_slack < 1"); c->opt.t_slack = value; }
+    else if (k == "ctas_per_sm") { c->opt.ctas_per_sm = (int)value; }
+    else if (k == "block") { c->opt.block = (int)value; }
+    else return fail(c, RT_E_INVALID, "unknown option: " + k);
+    return RT_OK;
+}
+
+}  // extern "C"

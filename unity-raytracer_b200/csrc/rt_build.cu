@@ -1,0 +1,213 @@
+// rt_build.cu — scene upload + device LBVH build for sm_100a.
+//   upload (scan-ordered staging arrays) -> primitive boxes + bounds -> 63-bit Morton codes -> radix sort (CUB, the
+//   toolkit's library sort; commit is not the timed hot path) -> Karras hierarchy -> atomic bottom-up refit ->
+//   leaf collapse + live-node compaction -> 64-byte BVH2 nodes with padded child boxes.
+// Per-element logic lives in rt_build_steps.h (host/device) so tests can run it on the CPU.
+#include "rt_internal.h"
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+namespace {
+
+constexpr int BT = 256;
+inline int grid_for(int64_t n) { int64_t g = (n + BT - 1) / BT; return (int)(g < 1 ? 1 : (g > 148 * 32 ? 148 * 32 : g)); }
+
+__device__ __forceinline__ uint32_t f_ord(float f) { uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+inline float f_unord(uint32_t u) { u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; float f; memcpy(&f, &u, 4); return f; }
+
+// bounds[0..2] = min (ordered uint), bounds[3..5] = max
+__global__ void k_bounds(RtRaw R, int32_t n, uint32_t* bounds) {
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        f3 a, b; rt_prim_box(R, i, a, b);
+        lo[0] = fminf(lo[0], a.x); lo[1] = fminf(lo[1], a.y); lo[2] = fminf(lo[2], a.z);
+        hi[0] = fmaxf(hi[0], b.x); hi[1] = fmaxf(hi[1], b.y); hi[2] = fmaxf(hi[2], b.z);
+    }
+    for (int k = 0; k < 3; ++k) {
+        for (int o = 16; o; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+        for (int k = 0; k < 3; ++k) { atomicMin(bounds + k, f_ord(lo[k])); atomicMax(bounds + 3 + k, f_ord(hi[k])); }
+    }
+}
+
+__global__ void k_morton(RtRaw R, int32_t n, f3 bmin, f3 inv_ext, uint64_t* keys, int32_t* vals) {
+    for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        f3 a, b; rt_prim_box(R, i, a, b);
+        keys[i] = rt_morton(a, b, bmin, inv_ext);
+        vals[i] = i;
+    }
+}
+
+__global__ void k_emit_slots(RtRaw R, int32_t n, const int32_t* sorted_keys, float4* prims, float4* pinfo, float4* leaf_lo, float4* leaf_hi) {
+    for (int32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x)
+        rt_emit_slot(R, s, sorted_keys[s], prims, pinfo, leaf_lo, leaf_hi);
+}
+
+__global__ void k_karras(const uint64_t* keys, int32_t n, RtTopo T) {
+    for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) rt_karras_node(keys, n, i, T);
+}
+
+__device__ __forceinline__ float4 ld_cg4(const float4* p) { return __ldcg(p); }
+
+// bottom-up refit: the second thread to reach a node computes its box (Karras 2012 §4)
+__global__ void k_refit(int32_t n, RtTopo T, const float4* leaf_lo, const float4* leaf_hi, float4* int_lo, float4* int_hi, int32_t* flags) {
+    for (int32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
+        int32_t p = T.parent_leaf[s];
+        while (p >= 0) {
+            __threadfence();
+            if (atomicAdd(flags + p, 1) == 0) break;            // first arrival: the sibling subtree is not done yet
+            int32_t l = T.left[p], r = T.right[p];
+            float4 alo = l < 0 ? leaf_lo[~l] : ld_cg4(int_lo + l), ahi = l < 0 ? leaf_hi[~l] : ld_cg4(int_hi + l);
+            float4 blo = r < 0 ? leaf_lo[~r] : ld_cg4(int_lo + r), bhi = r < 0 ? leaf_hi[~r] : ld_cg4(int_hi + r);
+            float4 lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+            float4 hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+            __stcg(int_lo + p, lo); __stcg(int_hi + p, hi);
+            p = T.parent_int[p];
+        }
+    }
+}
+
+__global__ void k_live(int32_t n_int, RtTopo T, int32_t leaf_max, int32_t* live) {
+    for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_int; i += gridDim.x * blockDim.x)
+        live[i] = (T.last[i] - T.first[i] + 1 > leaf_max) ? 1 : 0;
+}
+
+__global__ void k_emit_nodes(int32_t n_int, RtTopo T, const int32_t* new_index, int32_t leaf_max, float pad, const float4* leaf_lo,
+                             const float4* leaf_hi, const float4* int_lo, const float4* int_hi, float4* nodes) {
+    for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_int; i += gridDim.x * blockDim.x)
+        rt_emit_node(i, T, new_index, leaf_max, pad, leaf_lo, leaf_hi, int_lo, int_hi, nodes);
+}
+
+}  // namespace
+
+int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
+                     float* ms_build, uint64_t* h2d_bytes) {
+    RT_CUDA(cudaSetDevice(D.device));
+    cudaStream_t st = D.stream;
+    const int32_t n_mt = H.n_meshtris(), n_sp = H.n_spheres(), n_lo = H.n_loose(), n_me = H.n_meshes(), n_li = H.n_lights();
+    const int64_t n64 = H.n_prims();
+    if (n64 > (int64_t)(1 << 28) - 8) { err = "too many primitives (limit 2^28)"; return RT_E_UNSUPPORTED; }
+    const int32_t n = (int32_t)n64;
+    uint64_t up = 0;
+    RT_CUDA(cudaEventRecord(D.ev0, st));
+    // ---- upload ----
+    const size_t ntri = (size_t)n_mt + n_lo;
+    RT_CUDA(D.raw_v.ensure(ntri * 9 * 4)); RT_CUDA(D.raw_n.ensure(ntri * 3 * 4)); RT_CUDA(D.raw_s.ensure((size_t)n_sp * 16));
+    if (n_mt) {
+        RT_CUDA(cudaMemcpyAsync(D.raw_v.p, H.mesh_v.data(), (size_t)n_mt * 36, cudaMemcpyHostToDevice, st));
+        RT_CUDA(cudaMemcpyAsync(D.raw_n.p, H.mesh_n.data(), (size_t)n_mt * 12, cudaMemcpyHostToDevice, st));
+    }
+    if (n_lo) {
+        RT_CUDA(cudaMemcpyAsync((char*)D.raw_v.p + (size_t)n_mt * 36, H.loose_v.data(), (size_t)n_lo * 36, cudaMemcpyHostToDevice, st));
+        RT_CUDA(cudaMemcpyAsync((char*)D.raw_n.p + (size_t)n_mt * 12, H.loose_n.data(), (size_t)n_lo * 12, cudaMemcpyHostToDevice, st));
+    }
+    if (n_sp) RT_CUDA(cudaMemcpyAsync(D.raw_s.p, H.spheres.data(), (size_t)n_sp * 16, cudaMemcpyHostToDevice, st));
+    up += ntri * 48 + (uint64_t)n_sp * 16;
+    RtHostScene& Hm = const_cast<RtHostScene&>(H);
+    std::vector<float> mats = Hm.pack_materials();
+    D.has_mirror = Hm.has_mirror;
+    RT_CUDA(D.mats.ensure(mats.size() * 4));
+    if (!mats.empty()) RT_CUDA(cudaMemcpyAsync(D.mats.p, mats.data(), mats.size() * 4, cudaMemcpyHostToDevice, st));
+    std::vector<float> maabb((size_t)n_me * 8, 0.f);
+    for (int m = 0; m < n_me; ++m) { for (int k = 0; k < 3; ++k) { maabb[8 * m + k] = H.mesh_aabb[6 * m + k]; maabb[8 * m + 4 + k] = H.mesh_aabb[6 * m + 3 + k]; } }
+    RT_CUDA(D.mesh_aabb.ensure(maabb.size() * 4));
+    if (n_me) RT_CUDA(cudaMemcpyAsync(D.mesh_aabb.p, maabb.data(), maabb.size() * 4, cudaMemcpyHostToDevice, st));
+    std::vector<int32_t> mbase(H.mesh_base); mbase.push_back(n_mt);
+    RT_CUDA(D.mesh_base.ensure(mbase.size() * 4));
+    RT_CUDA(cudaMemcpyAsync(D.mesh_base.p, mbase.data(), mbase.size() * 4, cudaMemcpyHostToDevice, st));
+    std::vector<float> lights((size_t)n_li * 8, 0.f);
+    for (int l = 0; l < n_li; ++l) { for (int k = 0; k < 3; ++k) { lights[8 * l + k] = H.lights[6 * l + k]; lights[8 * l + 4 + k] = H.lights[6 * l + 3 + k]; } }
+    RT_CUDA(D.lights.ensure(lights.size() * 4));
+    if (n_li) RT_CUDA(cudaMemcpyAsync(D.lights.p, lights.data(), lights.size() * 4, cudaMemcpyHostToDevice, st));
+    up += mats.size() * 4 + maabb.size() * 4 + mbase.size() * 4 + lights.size() * 4;
+    RT_CUDA(cudaStreamSynchronize(st));        // staging vectors above go out of scope; also separates upload/build timing
+    RT_CUDA(cudaEventRecord(D.ev1, st));
+    RT_CUDA(cudaEventSynchronize(D.ev1));
+    if (ms_upload) RT_CUDA(cudaEventElapsedTime(ms_upload, D.ev0, D.ev1));
+    if (h2d_bytes) *h2d_bytes = up;
+
+    // ---- scene view (pointers filled below) ----
+    RtScene& S = D.S;
+    S = RtScene{};
+    S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_mt; S.n_spheres = n_sp; S.n_lights = n_li;
+    S.aabb_min = mk3(H.aabb[0], H.aabb[1], H.aabb[2]); S.aabb_max = mk3(H.aabb[3], H.aabb[4], H.aabb[5]);
+    S.ambient = mk3(H.ambient[0], H.ambient[1], H.ambient[2]);
+    S.t_slack = (float)opt.t_slack;
+    S.mats = D.mats.as<float4>(); S.mesh_aabb = D.mesh_aabb.as<float4>(); S.mesh_base = D.mesh_base.as<int32_t>();
+    S.lights = D.lights.as<float4>();
+    D.n_nodes = 0;
+    RT_CUDA(cudaEventRecord(D.ev0, st));
+    if (n > 0) {
+        RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_base.as<int32_t>(), n_me, n_mt, n_sp, n_lo};
+        const int leaf_max = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 8 ? 8 : opt.leaf_max);
+        // bounds
+        RT_CUDA(D.bounds.ensure(6 * 4));
+        uint32_t binit[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+        RT_CUDA(cudaMemcpyAsync(D.bounds.p, binit, sizeof(binit), cudaMemcpyHostToDevice, st));
+        k_bounds<<<grid_for(n), BT, 0, st>>>(R, n, D.bounds.as<uint32_t>());
+        uint32_t bord[6];
+        RT_CUDA(cudaMemcpyAsync(bord, D.bounds.p, sizeof(bord), cudaMemcpyDeviceToHost, st));
+        RT_CUDA(cudaStreamSynchronize(st));
+        float b[6]; for (int k = 0; k < 6; ++k) b[k] = f_unord(bord[k]);
+        float amax = 0.f; for (int k = 0; k < 6; ++k) if (std::isfinite(b[k])) amax = fmaxf(amax, fabsf(b[k]));
+        const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
+        f3 bmin = mk3(b[0], b[1], b[2]);
+        f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
+        // morton + sort
+        RT_CUDA(D.keys.ensure((size_t)n * 8)); RT_CUDA(D.keys_alt.ensure((size_t)n * 8));
+        RT_CUDA(D.vals.ensure((size_t)n * 4)); RT_CUDA(D.vals_alt.ensure((size_t)n * 4));
+        k_morton<<<grid_for(n), BT, 0, st>>>(R, n, bmin, inv_ext, D.keys.as<uint64_t>(), D.vals.as<int32_t>());
+        size_t tmp_bytes = 0;
+        RT_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, D.keys.as<uint64_t>(), D.keys_alt.as<uint64_t>(), D.vals.as<int32_t>(),
+                                                D.vals_alt.as<int32_t>(), n, 0, 63, st));
+        size_t scan_bytes = 0;
+        RT_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (int32_t*)nullptr, (int32_t*)nullptr, n, st));
+        RT_CUDA(D.cub_tmp.ensure(tmp_bytes > scan_bytes ? tmp_bytes : scan_bytes));
+        RT_CUDA(cub::DeviceRadixSort::SortPairs(D.cub_tmp.p, tmp_bytes, D.keys.as<uint64_t>(), D.keys_alt.as<uint64_t>(), D.vals.as<int32_t>(),
+                                                D.vals_alt.as<int32_t>(), n, 0, 63, st));
+        const uint64_t* skeys = D.keys_alt.as<uint64_t>();
+        const int32_t* svals = D.vals_alt.as<int32_t>();
+        // slots
+        RT_CUDA(D.prims.ensure((size_t)n * 48)); RT_CUDA(D.pinfo.ensure((size_t)n * 16));
+        RT_CUDA(D.leaf_lo.ensure((size_t)n * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)n * 16));
+        k_emit_slots<<<grid_for(n), BT, 0, st>>>(R, n, svals, D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
+        S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>();
+        if (n <= leaf_max) {
+            S.root = ~(0 * 8 + (n - 1));
+            RT_CUDA(D.nodes.ensure(64));
+            S.nodes = D.nodes.as<float4>();
+        } else {
+            const int32_t ni = n - 1;
+            RT_CUDA(D.topo_i32.ensure(((size_t)ni * 5 + n) * 4));
+            int32_t* tp = D.topo_i32.as<int32_t>();
+            RtTopo T{tp, tp + ni, tp + 2 * (size_t)ni, tp + 3 * (size_t)ni, tp + 4 * (size_t)ni, tp + 5 * (size_t)ni};
+            k_karras<<<grid_for(ni), BT, 0, st>>>(skeys, n, T);
+            RT_CUDA(D.int_lo.ensure((size_t)ni * 16)); RT_CUDA(D.int_hi.ensure((size_t)ni * 16));
+            RT_CUDA(D.flags.ensure((size_t)ni * 4)); RT_CUDA(D.new_index.ensure((size_t)ni * 4));
+            RT_CUDA(cudaMemsetAsync(D.flags.p, 0, (size_t)ni * 4, st));
+            k_refit<<<grid_for(n), BT, 0, st>>>(n, T, D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>(), D.int_lo.as<float4>(), D.int_hi.as<float4>(),
+                                                 D.flags.as<int32_t>());
+            k_live<<<grid_for(ni), BT, 0, st>>>(ni, T, leaf_max, D.flags.as<int32_t>());
+            RT_CUDA(cub::DeviceScan::ExclusiveSum(D.cub_tmp.p, scan_bytes, D.flags.as<int32_t>(), D.new_index.as<int32_t>(), ni, st));
+            int32_t last_idx = 0, last_flag = 0;
+            RT_CUDA(cudaMemcpyAsync(&last_idx, D.new_index.as<int32_t>() + (ni - 1), 4, cudaMemcpyDeviceToHost, st));
+            RT_CUDA(cudaMemcpyAsync(&last_flag, D.flags.as<int32_t>() + (ni - 1), 4, cudaMemcpyDeviceToHost, st));
+            RT_CUDA(cudaStreamSynchronize(st));
+            D.n_nodes = (uint32_t)(last_idx + last_flag);
+            RT_CUDA(D.nodes.ensure((size_t)D.n_nodes * 64));
+            k_emit_nodes<<<grid_for(ni), BT, 0, st>>>(ni, T, D.new_index.as<int32_t>(), leaf_max, pad, D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>(),
+                                                      D.int_lo.as<float4>(), D.int_hi.as<float4>(), D.nodes.as<float4>());
+            S.root = 0;
+            S.nodes = D.nodes.as<float4>();
+        }
+        RT_CUDA(cudaGetLastError());
+    }
+    RT_CUDA(cudaEventRecord(D.ev1, st));
+    RT_CUDA(cudaEventSynchronize(D.ev1));
+    if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
+    return RT_OK;
+}

@@ -1,0 +1,348 @@
+// rt_core.h — the per-ray hot path as host/device inline code: exact primitive tests, BVH traversal, the
+// shading/light loop, ray generation and the pixel<->work-item mapping.
+//
+// The CUDA kernels (rt_render.cu) instantiate these with a shared-memory traversal stack; tests/emu instantiates the
+// very same code on the host (g++ -ffp-contract=off) so the logic can be checked against the oracle without a GPU.
+// This file is NOT a CPU fallback: nothing in the shipped library calls it on the host.
+//
+// Reference citations are into /root/reference/Assets/RayTracer/.
+#pragma once
+#include "rt_hd.h"
+
+#if defined(__CUDA_ARCH__)
+#define RT_LDG4(p) __ldg(p)
+#else
+#define RT_LDG4(p) (*(p))
+#endif
+
+// ---------------------------------------------------------------------------------------------------------------
+// Device scene (all pointers are device memory; layouts in DESIGN.md §3)
+// ---------------------------------------------------------------------------------------------------------------
+struct RtScene {
+    const float4* nodes;      // BVH2 nodes, 4 x float4 each:
+                              //   n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)   n1 = same for child 1
+                              //   n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)   n3 = (ref0, ref1, -, -) int bits
+                              //   ref >= 0: node index;  ref < 0: leaf, ~ref = first_slot*8 + (count-1)
+    const float4* prims;      // 3 x float4 per primitive, in BVH leaf ("slot") order:
+                              //   triangle: (v0.xyz, key) (e1.xyz, 0) (e2.xyz, meshIndex|-1)    e1=v1-v0, e2=v2-v0
+                              //   sphere  : (c.xyz,  key) (r2,0,0, 1) (0,0,0, -1)
+                              //   key = position in the reference's scan order (Scene.cs:64-115), int bits
+    const float4* pinfo;      // per slot: (normal.xyz, material id bits)
+    const float4* mats;       // 4 x float4 per material: (kd, phong) (ka, is_mirror bits) (km, 0) (ks, 0)
+    const float4* mesh_aabb;  // 2 x float4 per mesh: (Min,0) (Max,0) exactly as the caller passed them (Mesh.cs:12)
+    const int32_t* mesh_base; // scan key of triangle 0 of mesh m; [n_meshes] = n_meshtris
+    const float4* lights;     // 2 x float4 per light: (Position,0) (Intensity,0)
+    int32_t root;             // 0 (internal root) or a leaf ref when n_prims <= leaf_max
+    int32_t n_prims, n_meshes, n_meshtris, n_spheres, n_lights;
+    f3 aabb_min, aabb_max;    // Scene.AABB (Scene.cs:15) as given / computed per Scene.cs:17-41
+    f3 ambient;               // AmbientLight.Radiance
+    float t_slack;            // multiplicative slack on the traversal cull distance (conservative)
+};
+
+struct RtView {
+    f3 pos, fwd, right, up;
+    int32_t res_x, res_y;
+    float dist, half_h, half_v;
+    f3 bg255;                 // new Rgb(BackgroundColor) = rgb * 255 (Rgb.cs:15-18)
+    int32_t max_bounces;
+    int32_t spp_grid;
+    // partition of the frame over ranks/devices: this view owns the row bands b with b % world == rank
+    int32_t rank, world, band_rows;
+    int32_t tiles_x;          // ceil(res_x / 8)
+    int32_t n_local_rows;     // rows owned by this rank
+    int32_t n_tiles;          // tiles_x * ceil(n_local_rows / 4); one tile = 8x4 pixels = one warp
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// Exact primitive tests (bit-for-bit the reference's arithmetic)
+// ---------------------------------------------------------------------------------------------------------------
+// RMath.RayAABBIntersection, Math/RMath.cs:12-26
+RT_HD bool rt_ray_aabb_exact(f3 O, f3 D, f3 mn, f3 mx) {
+    float ix = rt_div(1.0f, D.x), iy = rt_div(1.0f, D.y), iz = rt_div(1.0f, D.z);     // rcp(ray.Direction)
+    float tmin = 0.0f, tmax = INFINITY;
+    float t1 = (mn.x - O.x) * ix, t2 = (mx.x - O.x) * ix;
+    tmin = um_min(um_max(t1, tmin), um_max(t2, tmin));
+    tmax = um_max(um_min(t1, tmax), um_min(t2, tmax));
+    t1 = (mn.y - O.y) * iy; t2 = (mx.y - O.y) * iy;
+    tmin = um_min(um_max(t1, tmin), um_max(t2, tmin));
+    tmax = um_max(um_min(t1, tmax), um_min(t2, tmax));
+    t1 = (mn.z - O.z) * iz; t2 = (mx.z - O.z) * iz;
+    tmin = um_min(um_max(t1, tmin), um_max(t2, tmin));
+    tmax = um_max(um_min(t1, tmax), um_min(t2, tmax));
+    return tmin <= tmax;
+}
+
+// RMath.RayTriangleIntersection, Math/RMath.cs:29-73. e1/e2 are the single subtractions v1-v0, v2-v0 (RMath.cs:34-35)
+// precomputed at upload, which is bit-identical to computing them per call.
+RT_HD bool rt_ray_tri(f3 O, f3 D, f3 v0, f3 e1, f3 e2, float& t_out) {
+    f3 h = um_cross(D, e2);
+    float a = um_dot(e1, h);
+    if (a > -RT_EPS && a < RT_EPS) return false;
+    float f = rt_div(1.0f, a);
+    f3 s = O - v0;
+    float u = f * um_dot(s, h);
+    if (u < 0.0f || u > 1.0f) return false;
+    f3 q = um_cross(s, e1);
+    float v = f * um_dot(D, q);
+    if (v < 0.0f || u + v > 1.0f) return false;
+    float t = f * um_dot(e2, q);
+    if (t > RT_EPS) { t_out = t; return true; }
+    return false;
+}
+
+// RMath.RaySphereIntersection, Math/RMath.cs:81-108 (assumes |D| = 1; no epsilon: t may be 0)
+RT_HD bool rt_ray_sphere(f3 O, f3 D, f3 c, float r2, float& t_out) {
+    f3 oc = O - c;
+    float uoc = um_dot(D, oc);
+    float disc = uoc * uoc - (um_dot(oc, oc) - r2);
+    if (disc < 0) return false;
+    float sq = rt_sqrt(disc);
+    float big = -uoc + sq;
+    if (big < 0) return false;
+    float small = -uoc - sq;
+    t_out = small < 0 ? big : small;
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// BVH traversal.  Result-equivalent to the reference's linear scan (Scene.cs:43-122):
+//   closest: argmin over all primitives that pass the exact test of (t, scan key)  == strict-'>' update in scan order
+//   any    : true iff some primitive passes with t*t < d2  == closest-hit-then-compare (RayTracingSetup.cs:333-345),
+//            because every reported t is >= 0 so the closest hit satisfies the predicate whenever any hit does.
+// Node boxes are padded (rt_build) and the cull distance carries a slack, so a primitive whose *computed* t could win is
+// never culled; the per-mesh AABB gate (Scene.cs:67) is applied with the exact formula to any candidate that would be
+// accepted.  The scene AABB gate (Scene.cs:54) is applied by the callers via rt_scene_gate().
+// STK: push(int), pop() -> int, empty().
+// ---------------------------------------------------------------------------------------------------------------
+RT_HD bool rt_scene_gate(const RtScene& S, f3 O, f3 D) { return rt_ray_aabb_exact(O, D, S.aabb_min, S.aabb_max); }
+
+template <bool ANY, class STK>
+RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, float any_d2, STK& stk, float& best_t, int32_t& best_slot) {
+    best_t = FLT_MAX; best_slot = -1;
+    stk.sp = 0;                       // an any-hit query returns early and leaves entries behind
+    if (S.n_prims <= 0) return false;
+    const float tiny = 1e-30f;
+    float idx_ = rt_div(1.0f, fabsf(D.x) > tiny ? D.x : copysignf(tiny, D.x));
+    float idy_ = rt_div(1.0f, fabsf(D.y) > tiny ? D.y : copysignf(tiny, D.y));
+    float idz_ = rt_div(1.0f, fabsf(D.z) > tiny ? D.z : copysignf(tiny, D.z));
+    float oodx = O.x * idx_, oody = O.y * idy_, oodz = O.z * idz_;
+    uint32_t best_key = 0xffffffffu;
+    float tcull = ANY ? rt_sqrt(any_d2) * S.t_slack : INFINITY;
+    int32_t gate_mesh = -1; bool gate_ok = true;
+    int32_t node = S.root;
+    for (;;) {
+        while (node >= 0) {
+            const float4* np = S.nodes + 4 * (size_t)node;
+            float4 n0 = RT_LDG4(np), n1 = RT_LDG4(np + 1), n2 = RT_LDG4(np + 2), n3 = RT_LDG4(np + 3);
+            float ax0 = rt_fma(n0.x, idx_, -oodx), ax1 = rt_fma(n0.y, idx_, -oodx);
+            float ay0 = rt_fma(n0.z, idy_, -oody), ay1 = rt_fma(n0.w, idy_, -oody);
+            float az0 = rt_fma(n2.x, idz_, -oodz), az1 = rt_fma(n2.y, idz_, -oodz);
+            float bx0 = rt_fma(n1.x, idx_, -oodx), bx1 = rt_fma(n1.y, idx_, -oodx);
+            float by0 = rt_fma(n1.z, idy_, -oody), by1 = rt_fma(n1.w, idy_, -oody);
+            float bz0 = rt_fma(n2.z, idz_, -oodz), bz1 = rt_fma(n2.w, idz_, -oodz);
+            float amin = fmaxf(fmaxf(fminf(ax0, ax1), fminf(ay0, ay1)), fmaxf(fminf(az0, az1), 0.0f));
+            float amax = fminf(fminf(fmaxf(ax0, ax1), fmaxf(ay0, ay1)), fminf(fmaxf(az0, az1), tcull));
+            float bmin = fmaxf(fmaxf(fminf(bx0, bx1), fminf(by0, by1)), fmaxf(fminf(bz0, bz1), 0.0f));
+            float bmax = fminf(fminf(fmaxf(bx0, bx1), fmaxf(by0, by1)), fminf(fmaxf(bz0, bz1), tcull));
+            bool ha = amin <= amax, hb = bmin <= bmax;
+            int32_t ra = f2i(n3.x), rb = f2i(n3.y);
+            if (ha && hb) {
+                if (bmin < amin) { int32_t t = ra; ra = rb; rb = t; }
+                stk.push(rb);
+                node = ra;
+            } else if (ha) node = ra;
+            else if (hb) node = rb;
+            else {
+                if (stk.empty()) return best_slot >= 0;
+                node = stk.pop();
+            }
+        }
+        // leaf
+        {
+            int32_t ref = ~node;
+            int32_t first = ref >> 3, cnt = (ref & 7) + 1;
+            for (int32_t k = 0; k < cnt; ++k) {
+                int32_t slot = first + k;
+                const float4* pp = S.prims + 3 * (size_t)slot;
+                float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+                float t; bool hit;
+                if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
+                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), t);
+                if (!hit) continue;
+                uint32_t key = (uint32_t)f2i(p0.w);
+                bool better = ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key));
+                if (!better) continue;
+                int32_t mesh = f2i(p2.w);
+                if (mesh >= 0) {                                    // Scene.cs:67
+                    if (mesh != gate_mesh) {
+                        gate_mesh = mesh;
+                        float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
+                        gate_ok = rt_ray_aabb_exact(O, D, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
+                    }
+                    if (!gate_ok) continue;
+                }
+                if (ANY) { best_t = t; best_slot = slot; return true; }
+                best_t = t; best_key = key; best_slot = slot;
+                tcull = t * S.t_slack;
+            }
+        }
+        if (stk.empty()) return best_slot >= 0;
+        node = stk.pop();
+    }
+}
+
+// slot -> ObjectId {Type, Index, MeshIndex} (ObjectId.cs:7-9)
+RT_HD void rt_slot_to_id(const RtScene& S, int32_t slot, int32_t& type, int32_t& index, int32_t& mesh) {
+    if (slot < 0) { type = 0; index = -1; mesh = -1; return; }
+    const float4* pp = S.prims + 3 * (size_t)slot;
+    int32_t key = f2i(RT_LDG4(pp).w), kind = f2i(RT_LDG4(pp + 1).w), m = f2i(RT_LDG4(pp + 2).w);
+    if (kind != 0) { type = 1; index = key - S.n_meshtris; mesh = -1; }
+    else if (m >= 0) { type = 3; index = key - S.mesh_base[m]; mesh = m; }
+    else { type = 2; index = key - S.n_meshtris - S.n_spheres; mesh = -1; }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Shading: RayTracingSetup.Shade minus the recursion (RayTracingSetup.cs:304-366).  Returns the colour of this bounce
+// (ambient + light loop, Rgb.Value scale 0..255) and, when the surface is a mirror and bounce < max, the reflection ray
+// and MirrorReflectance; the caller adds  km * Shade(reflect)  afterwards, innermost first, like the recursion does.
+// ---------------------------------------------------------------------------------------------------------------
+struct RtMirror { bool emit; f3 O, D, km; };
+
+template <class STK>
+RT_HD f3 rt_shade_hit(const RtScene& S, f3 O, f3 D, float t, int32_t slot, int32_t bounce, int32_t max_bounces,
+                      STK& stk, RtMirror& mir, uint32_t& n_shadow) {
+    const float4* pp = S.prims + 3 * (size_t)slot;
+    float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1);
+    float4 pi = RT_LDG4(S.pinfo + slot);
+    f3 P = O + D * t;                                                        // Ray.GetPoint, Ray.cs:18-21
+    f3 N;
+    if (f2i(p1.w) != 0) N = um_normalize(P - mk3(p0.x, p0.y, p0.z));           // GetSphereNormal, RTS:402-407
+    else N = mk3(pi.x, pi.y, pi.z);                                          // stored normal, RTS:420-431
+    const float4* mp = S.mats + 4 * (size_t)f2i(pi.w);
+    float4 m0 = RT_LDG4(mp), m1 = RT_LDG4(mp + 1), m2 = RT_LDG4(mp + 2), m3 = RT_LDG4(mp + 3);
+    f3 kd = mk3(m0.x, m0.y, m0.z), ka = mk3(m1.x, m1.y, m1.z), km = mk3(m2.x, m2.y, m2.z), ks = mk3(m3.x, m3.y, m3.z);
+    float phong = m0.w; bool is_mirror = f2i(m1.w) != 0;
+    f3 color = S.ambient * ka;                                               // CalculateAmbient, RTS:438-441
+    f3 V = um_normalize(O - P);                                              // RTS:325
+    f3 sO = P + N * RT_SHADOW_EPS;                                           // RTS:331 (also Reflect's origin, RTS:370)
+    for (int32_t li = 0; li < S.n_lights; ++li) {
+        float4 lp = RT_LDG4(S.lights + 2 * li), lint = RT_LDG4(S.lights + 2 * li + 1);
+        f3 Lpos = mk3(lp.x, lp.y, lp.z);
+        f3 Ldir = um_normalize(Lpos - P);                                    // RTS:330
+        f3 dl = Lpos - P;
+        float d2 = um_dot(dl, dl);                                           // distancesq(P, Lpos), RTS:334
+        ++n_shadow;
+        if (rt_scene_gate(S, sO, Ldir)) {                                    // Scene.cs:54 inside the shadow query
+            float st; int32_t ss;
+            if (rt_traverse<true>(S, sO, Ldir, d2, stk, st, ss)) continue;  // occluder in front of the light, RTS:337-345
+        }
+        f3 E = mk3(lint.x, lint.y, lint.z) / d2;                             // RTS:350
+        float ldn = um_dot(Ldir, N);
+        f3 diff = kd * um_max(0.0f, ldn) * E;                                // CalculateDiffuse, RTS:443-455
+        f3 spec;
+        if (ldn <= RT_SPEC_CUTOFF) spec = bc3(0.0f);                         // angle > 90, RTS:384-391
+        else {
+            f3 v = Ldir + V;
+            f3 H = v / um_length(v);
+            float cnh = um_max(0.0f, um_dot(N, H));
+            spec = ks * um_pow(cnh, phong) * E;                              // RTS:398-399
+        }
+        color = color + (diff + spec);                                       // RTS:355
+    }
+    mir.emit = is_mirror && bounce < max_bounces;                            // RTS:358
+    if (mir.emit) {
+        mir.O = sO;
+        mir.D = 2.0f * N * um_dot(V, N) - V;                                 // Reflect, RTS:368-373 (not renormalised)
+        mir.km = km;
+    }
+    return color;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Work-item mapping and ray generation
+// ---------------------------------------------------------------------------------------------------------------
+// rows owned by `rank`: bands b = rank, rank+world, ...; band b covers rows [b*band_rows, min(res_y,(b+1)*band_rows))
+RT_HD int32_t rt_local_rows(int32_t res_y, int32_t rank, int32_t world, int32_t band_rows) {
+    int32_t n_bands = (res_y + band_rows - 1) / band_rows, rows = 0;
+    for (int32_t b = rank; b < n_bands; b += world) {
+        int32_t r = res_y - b * band_rows;
+        rows += r < band_rows ? r : band_rows;
+    }
+    return rows;
+}
+// local work item (tile, lane) -> pixel. One tile is an 8x4 pixel block (one warp) of the rank's local image.
+RT_HD bool rt_item_to_pixel(const RtView& V, int32_t tile, int32_t lane, int32_t& x, int32_t& y) {
+    int32_t tx = tile % V.tiles_x, ty = tile / V.tiles_x;
+    x = tx * 8 + (lane & 7);
+    int32_t r = ty * 4 + (lane >> 3);                       // local row
+    y = ((r / V.band_rows) * V.world + V.rank) * V.band_rows + (r % V.band_rows);
+    return x < V.res_x && r < V.n_local_rows && y < V.res_y;
+}
+
+// CastPixelRays body, RayTracingSetup.cs:275-298 with ImagePlane.GetRect (ImagePlane.cs:26-44); sample (si,sj) of the
+// spp_grid x spp_grid extension replaces the +0.5f pixel-centre offset (spp_grid 1 -> exactly +0.5f).
+RT_HD void rt_primary_ray(const RtView& V, int32_t x, int32_t y, int32_t si, int32_t sj, f3& O, f3& D) {
+    f3 center = V.pos + V.fwd * V.dist;
+    f3 halfUp = V.up * V.half_v, halfRight = V.right * V.half_h;
+    f3 topLeft = center - halfRight + halfUp;
+    float H = V.half_h * 2.0f, Vl = V.half_v * 2.0f;
+    float g = (float)V.spp_grid;
+    float ox = rt_div((float)si + 0.5f, g), oy = rt_div((float)sj + 0.5f, g);
+    float rightMove = rt_div(((float)x + ox) * H, (float)V.res_x);
+    float downMove = rt_div(((float)y + oy) * Vl, (float)V.res_y);
+    f3 pp = topLeft + rightMove * V.right - V.up * downMove;
+    O = V.pos;
+    D = um_normalize(pp - V.pos);
+}
+
+// our u8 quantisation (the reference has none, Rgb.cs:12-13): clamp(round_half_even(Value), 0, 255), NaN -> 0
+RT_HD uint8_t rt_quant(float v) {
+    if (v != v) return 0;
+#if defined(__CUDA_ARCH__)
+    float r = rintf(v);
+#else
+    float r = nearbyintf(v);
+#endif
+    r = r < 0.0f ? 0.0f : (r > 255.0f ? 255.0f : r);
+    return (uint8_t)r;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Per-item bodies of the non-traversal kernels (shared with tests/emu)
+// ---------------------------------------------------------------------------------------------------------------
+// color += new Rgb(mirrorReflectance * Shade(reflectRay).Value), RayTracingSetup.cs:362. link = (km.xyz, parent index)
+RT_HD void rt_fold_item(uint32_t q, const float4* link, const float4* local_cur, float4* local_prev) {
+    float4 l = link[q], c = local_cur[q];
+    int32_t parent = f2i(l.w);
+    float4 p = local_prev[parent];
+    p.x = p.x + l.x * c.x; p.y = p.y + l.y * c.y; p.z = p.z + l.z * c.z;
+    local_prev[parent] = p;
+}
+
+struct RtOut { float4* rgba32f; uint32_t* rgba8; int32_t* hit_id; float* hit_t; };
+
+// One work item of a finished wave -> framebuffer(s).  pass/n_pass: sample index of the spp_grid^2 extension; colours are
+// summed in pass order and divided once, before Rgb.Color (Rgb.cs:13) and the u8 quantisation.
+RT_HD void rt_finalize_item(const RtScene& S, const RtView& V, int32_t tile_begin, uint32_t q, int32_t pass, int32_t n_pass,
+                            const float4* local0, const float* hit_t, const int32_t* hit_slot, float4* accum, const RtOut& out) {
+    int32_t x, y;
+    if (!rt_item_to_pixel(V, tile_begin + (int32_t)(q >> 5), (int32_t)(q & 31), x, y)) return;
+    size_t pix = (size_t)x + (size_t)y * (size_t)V.res_x;                  // GetPixelIndex, RayTracingSetup.cs:243-246
+    if (pass == 0) {
+        if (out.hit_id) {
+            int32_t ty, ix, me; rt_slot_to_id(S, hit_slot[q], ty, ix, me);
+            out.hit_id[3 * pix] = ty; out.hit_id[3 * pix + 1] = ix; out.hit_id[3 * pix + 2] = me;
+        }
+        if (out.hit_t) out.hit_t[pix] = hit_t[q];
+    }
+    float4 c = local0[q];
+    if (n_pass > 1) {
+        size_t a = ((size_t)tile_begin << 5) + q;
+        if (pass > 0) { float4 p = accum[a]; c.x = p.x + c.x; c.y = p.y + c.y; c.z = p.z + c.z; }
+        if (pass < n_pass - 1) { accum[a] = c; return; }
+        float np = (float)n_pass;
+        c.x = rt_div(c.x, np); c.y = rt_div(c.y, np); c.z = rt_div(c.z, np);
+    }
+    if (out.rgba32f) out.rgba32f[pix] = make_float4(rt_div(c.x, 255.f), rt_div(c.y, 255.f), rt_div(c.z, 255.f), 1.f);
+    if (out.rgba8) out.rgba8[pix] = (uint32_t)rt_quant(c.x) | ((uint32_t)rt_quant(c.y) << 8) | ((uint32_t)rt_quant(c.z) << 16) | 0xff000000u;
+}

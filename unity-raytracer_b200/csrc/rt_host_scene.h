@@ -1,0 +1,70 @@
+// rt_host_scene.h — host-side accumulation of the caller's scene arrays (rt_scene_* calls) into the flat, scan-ordered
+// staging arrays that are uploaded verbatim.  Mirrors what UpdateScene() leaves in `Scene`
+// (RayTracingSetup.cs:120-128; Scene.cs:8-15) and Scene.CalculateAABB (Scene.cs:17-41).
+#pragma once
+#include <vector>
+#include <cstring>
+#include <cstdint>
+#include <cmath>
+#include <cfloat>
+#include "rt_hd.h"
+#include "../../include/rtb200.h"
+
+struct RtHostScene {
+    // scan order: mesh triangles (mesh order, triangle order), spheres, loose triangles  (Scene.cs:64-115)
+    std::vector<float> mesh_v, mesh_n;          // 9 / 3 floats per mesh triangle
+    std::vector<int32_t> mesh_base;             // first scan key of each mesh (+ total at the end after finish())
+    std::vector<float> mesh_aabb;               // 6 floats per mesh, verbatim (Mesh.cs:12)
+    std::vector<rt_material> mesh_mats;
+    std::vector<float> spheres;                 // 4 floats each
+    std::vector<rt_material> sphere_mats;
+    std::vector<float> loose_v, loose_n;        // 9 / 3 floats per loose triangle
+    std::vector<rt_material> loose_mats;
+    std::vector<float> lights;                  // 6 floats each
+    float ambient[3] = {0, 0, 0};
+    float aabb[6] = {0, 0, 0, 0, 0, 0};
+    bool has_mirror = false;
+
+    void clear() { *this = RtHostScene(); }
+    int32_t n_meshes() const { return (int32_t)mesh_mats.size(); }
+    int32_t n_meshtris() const { return (int32_t)(mesh_v.size() / 9); }
+    int32_t n_spheres() const { return (int32_t)(spheres.size() / 4); }
+    int32_t n_loose() const { return (int32_t)(loose_v.size() / 9); }
+    int64_t n_prims() const { return (int64_t)n_meshtris() + n_spheres() + n_loose(); }
+    int32_t n_lights() const { return (int32_t)(lights.size() / 6); }
+
+    // Scene.CalculateAABB, Scene.cs:17-41 (AABB.Encapsulate, AABB.cs:10-20; Sphere.AABB, Sphere.cs:17-22)
+    void calc_aabb() {
+        float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};   // float.MinValue == -FLT_MAX
+        for (int32_t m = 0; m < n_meshes(); ++m)
+            for (int k = 0; k < 3; ++k) { mn[k] = um_min(mn[k], mesh_aabb[6 * m + k]); mx[k] = um_max(mx[k], mesh_aabb[6 * m + 3 + k]); }
+        for (size_t t = 0; t < loose_v.size() / 9; ++t)
+            for (int v = 0; v < 3; ++v)
+                for (int k = 0; k < 3; ++k) { float p = loose_v[9 * t + 3 * v + k]; mn[k] = um_min(p, mn[k]); mx[k] = um_max(p, mx[k]); }
+        for (size_t s = 0; s < spheres.size() / 4; ++s) {
+            float r = sqrtf(spheres[4 * s + 3]);
+            for (int k = 0; k < 3; ++k) { mn[k] = um_min(mn[k], spheres[4 * s + k] - r); mx[k] = um_max(mx[k], spheres[4 * s + k] + r); }
+        }
+        for (int k = 0; k < 3; ++k) { aabb[k] = mn[k]; aabb[3 + k] = mx[k]; }
+    }
+
+    // all materials in material-id order: meshes, spheres, loose triangles; 4 x float4 each (layout: RtScene::mats)
+    std::vector<float> pack_materials() {
+        std::vector<float> out;
+        has_mirror = false;
+        auto put = [&](const rt_material& m) {
+            float rec[16] = {m.diffuse[0], m.diffuse[1], m.diffuse[2], m.phong,
+                             m.ambient[0], m.ambient[1], m.ambient[2], 0.f,
+                             m.mirror[0], m.mirror[1], m.mirror[2], 0.f,
+                             m.specular[0], m.specular[1], m.specular[2], 0.f};
+            int32_t im = m.is_mirror ? 1 : 0;
+            std::memcpy(&rec[7], &im, 4);
+            if (im) has_mirror = true;
+            out.insert(out.end(), rec, rec + 16);
+        };
+        for (auto& m : mesh_mats) put(m);
+        for (auto& m : sphere_mats) put(m);
+        for (auto& m : loose_mats) put(m);
+        return out;
+    }
+};

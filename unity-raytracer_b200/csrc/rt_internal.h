@@ -1,0 +1,84 @@
+// rt_internal.h — host-side state of librtb200 (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include "rt_core.h"
+#include "rt_build_steps.h"
+#include "rt_host_scene.h"
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= bytes && p) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; bytes = 0; }
+        if (n == 0) n = 16;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    template <class T> T* as() const { return (T*)p; }
+};
+
+struct RtOptions {
+    int chunk_pixels = 1 << 23;        // work items (pixel samples) per wave; multiple of 32
+    int leaf_max = 4;                  // LBVH subtrees with <= leaf_max primitives become one leaf (<= 8)
+    double pad_scale = 1.0 / 65536.0;  // node-box padding = max |coordinate| * pad_scale
+    double t_slack = 1.000125;         // multiplicative slack on the traversal cull distance
+    int block = 128;
+    int ctas_per_sm = 0;               // 0 = occupancy query
+};
+
+enum { RT_MAX_DEPTH = 64 };           // max_reflection_bounces is clamped to this
+
+struct RtDevice {
+    int device = -1;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;      // stream in use
+    cudaStream_t own_stream = nullptr;  // created by the library
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // ---- scene ----
+    DevBuf raw_v, raw_n, raw_s, nodes, prims, pinfo, mats, mesh_aabb, mesh_base, lights;
+    RtScene S{};
+    uint32_t n_nodes = 0;
+    bool has_mirror = false;
+    // ---- build scratch ----
+    DevBuf keys, keys_alt, vals, vals_alt, cub_tmp, bounds, topo_i32, leaf_lo, leaf_hi, int_lo, int_hi, flags, new_index;
+    // ---- frame work buffers (sized to the wave capacity W) ----
+    size_t wave_cap = 0;
+    DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, accum, stats;
+    std::vector<DevBuf> local;          // [depth] float4 per entry
+    std::vector<DevBuf> link;           // [depth>=1] float4 (km.xyz, parent index bits)
+    size_t accum_items = 0;
+    // ---- outputs: full-frame buffers. Owned on the gather device; other devices/ranks hold peer pointers ----
+    DevBuf own_rgba32f, own_rgba8, own_hit_id, own_hit_t;
+    void* o_rgba32f = nullptr; void* o_rgba8 = nullptr; void* o_hit_id = nullptr; void* o_hit_t = nullptr;
+    bool imported[4] = {false, false, false, false};
+    int out_res_x = 0, out_res_y = 0;
+    // partition
+    int rank = 0, world = 1;
+};
+
+#define RT_CUDA(call)                                                                                     \
+    do {                                                                                                  \
+        cudaError_t _e = (call);                                                                          \
+        if (_e != cudaSuccess) {                                                                          \
+            char _b[512];                                                                                 \
+            snprintf(_b, sizeof(_b), "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            err = _b;                                                                                     \
+            return (_e == cudaErrorMemoryAllocation) ? RT_E_OOM : RT_E_CUDA;                              \
+        }                                                                                                 \
+    } while (0)
+
+// rt_build.cu
+int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
+                     float* ms_build, uint64_t* h2d_bytes);
+// rt_render.cu
+struct RtFrameStats { uint64_t primary, shadow, mirror; uint32_t launches; };
+int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs);
+int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs, int n, int32_t* d_ids, float* d_t,
+                        const RtOptions& opt, std::string& err);
+int rt_device_read_stats(RtDevice& D, RtFrameStats* fs, std::string& err);
