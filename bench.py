@@ -1,0 +1,299 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s (primary + shadow + mirror scene queries) of the per-pixel hot path on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3] [--impl ours|reference]
+
+A step = one frame of the workload (ray-gen -> traversal -> shading -> final pixel write).  N > 1 is launched by
+torchrun, one rank per GPU: the frame is split into interleaved 32-row bands (scene replicated), every rank writes
+its bands straight into rank 0's framebuffer over NVLink (CUDA IPC peer mapping), i.e. strong scaling of one frame.
+Prints ONE JSON line on rank 0.  See DESIGN.md §6 for how each field is measured.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (primary+shadow+mirror)"
+UNIT = "Mrays/s"
+
+
+def workload(name, scenes):
+    """BASELINE.json configs[1..4]; returns (scene arrays, render params, description)."""
+    if name == "cfg2":
+        return scenes.rt_unity(True), scenes.rt_unity_params(3840, 2160, 4), "RayTracing.unity, sphere mirror restored, 3840x2160, depth 4, 1 light"
+    if name == "cfg3":
+        return scenes.cfg3_scene(), scenes.cfg3_params(), "1 003 520-triangle displaced geodesic sphere + ground quad, 3840x2160, 2 point lights, depth 0, 1 spp"
+    if name == "cfg4":
+        return scenes.cfg4_scene(), scenes.cfg4_params(), "125 baked instances x 81 920 = 10 240 000 triangles, 7680x4320, 2 point lights"
+    if name == "cfg5":
+        return scenes.cfg5_scene(), scenes.cfg5_params(), "100 000 spheres (10% mirrors) + 5 000 000-triangle sphere + ground, 3840x2160 x 16 spp, depth 4, 2 lights"
+    raise SystemExit(f"unknown workload {name}")
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, pw, reasons = [], [], [], set()
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); pw.append(float(c[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # "under load": samples in the upper half of the power range seen
+        thr = (min(pw) + max(pw)) / 2 if max(pw) > min(pw) + 20 else min(pw)
+        load = [s for s, w in zip(sm, pw) if w >= thr] or sm
+        return {"sm_mhz": float(np.median(load)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def measured_peak_hbm():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_baseline(scene, params, seconds_target, threads, kind_label="port"):
+    """The oracle's accelerated mode (CPU BVH over the same exact primitive tests) on a bounded random pixel sample of
+    the same workload, all host threads.  Returns the cpu_baseline object."""
+    from oracle import oracle as O
+    ora = O.OracleScene(scene, build_bvh=True)
+    npx = params["res_x"] * params["res_y"]
+    rng = np.random.default_rng(12345)
+    cal = rng.choice(npx, min(npx, 20000), replace=False)
+    r = ora.render(params, O.ACCELERATED, threads, pixels=cal)
+    rate = sum(r["stats"]) / max(r["seconds"], 1e-6)
+    rays_per_px = sum(r["stats"]) / len(cal)
+    n = int(min(npx, max(len(cal), seconds_target * rate / max(rays_per_px, 1e-9))))
+    px = rng.choice(npx, n, replace=False)
+    r = ora.render(params, O.ACCELERATED, threads, pixels=px)
+    rays = sum(r["stats"])
+    return {"value": rays / r["seconds"] / 1e6, "unit": UNIT, "cores": threads, "kind": kind_label,
+            "sample": f"{n} random pixels of the {params['res_x']}x{params['res_y']} frame ({rays} rays, {r['seconds']:.2f} s), "
+                      "C++ restatement of the reference's C# (oracle/, CPU-BVH mode, std::thread); the reference itself is a "
+                      "single-threaded Mono loop with a linear scan and cannot run here (no Unity/.NET)",
+            "seconds": r["seconds"]}, ora
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU path for this workload on the host cores.  The reference is C#/Unity and
+    cannot execute here, so this is the oracle port (kind "port"), multithreaded, each step a bounded pixel sample."""
+    if rank != 0:
+        return
+    rtb = importlib.import_module("unity-raytracer_b200")
+    scene, params, desc = workload(args.workload, rtb.scenes)
+    from oracle import oracle as O
+    threads = os.cpu_count() or 1
+    ora = O.OracleScene(scene, build_bvh=True)
+    npx = params["res_x"] * params["res_y"]
+    rng = np.random.default_rng(12345)
+    cal = rng.choice(npx, min(npx, 20000), replace=False)
+    r = ora.render(params, O.ACCELERATED, threads, pixels=cal)
+    budget = min(3.0, 150.0 / max(1, args.steps + args.warmup))                # seconds of CPU work per step
+    n = int(min(npx, max(2000, budget * len(cal) / max(r["seconds"], 1e-6))))
+    px = rng.choice(npx, n, replace=False)
+    for _ in range(args.warmup):
+        ora.render(params, O.ACCELERATED, threads, pixels=px)
+    rays, secs = 0, 0.0
+    for _ in range(args.steps):
+        r = ora.render(params, O.ACCELERATED, threads, pixels=px)
+        rays += sum(r["stats"]); secs += r["seconds"]
+    v = rays / secs / 1e6
+    sample = f"{n} random pixels of the {params['res_x']}x{params['res_y']} frame per step ({rays // max(1, args.steps)} rays/step)"
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": f"{args.workload}: {desc}", "sample": sample},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample + "; oracle/ C++ restatement of the reference's C# "
+                             "hot path with a CPU BVH (the reference itself: single-threaded Mono linear scan, cannot run here)"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    rtb = importlib.import_module("unity-raytracer_b200")
+    H = rtb.host
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    scene, params, desc = workload(args.workload, rtb.scenes)
+    rt = rtb.RayTracer((local_rank,))
+    stream = torch.cuda.Stream()
+    rt.set_stream(stream.cuda_stream)
+    rt.set_partition(rank, world, 32)
+    t0 = time.perf_counter(); rt.set_scene(scene); commit_wall = time.perf_counter() - t0
+    cstats = rt.stats()
+    X, Y = params["res_x"], params["res_y"]
+    want = H.RT_OUT_RGBA32F
+    gather = "single GPU"
+    if world > 1:                        # peer-store gather: every rank writes its bands into rank 0's framebuffer
+        handles = [None]
+        if rank == 0:
+            rt.alloc_outputs(X, Y, want); handles[0] = rt.export_outputs()
+        dist.broadcast_object_list(handles, src=0)
+        if rank != 0:
+            rt.import_outputs(handles[0], X, Y, want)
+        gather = "fused peer stores into rank 0's framebuffer over NVLink (CUDA IPC), no collective"
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(max(args.warmup, 3)):
+        rt.render_device(params, want)
+    barrier()
+    st = rt.stats()
+    rays_rank = st["rays_primary"] + st["rays_shadow"] + st["rays_mirror"]
+    tot = torch.tensor([rays_rank, st["kernel_launches"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot)
+    rays_step, launches_step = int(tot[0].item()), int(tot[1].item())
+
+    # ---- value: device-resident, per-step CUDA events on the launching stream, L2 flushed between steps ----
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for a, b in ev:
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        barrier()
+        a.record(stream); rt.render_device(params, want); b.record(stream)
+    barrier()
+    ms = torch.tensor([a.elapsed_time(b) for a, b in ev], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.sum().item())
+    clocks = sampler.stop() if sampler else None
+    value = rays_step * args.steps / (ms_total * 1e-3) / 1e6
+
+    # ---- e2e: through the C-ABI with HOST buffers (pinned), D2H of the frame inside the timed region ----
+    host_out = rt.alloc_host_outputs(params, want, pinned=True) if rank == 0 else None
+    walls = []
+    for i in range(args.steps + 2):
+        barrier()
+        t0 = time.perf_counter()
+        if world == 1:
+            rt.render(params, want, out=host_out)                       # rt_render: H2D params, kernels, D2H
+        else:
+            rt.render_device(params, want); barrier()
+            if rank == 0:
+                rt.read_outputs(params, want, out=host_out)
+        walls.append(time.perf_counter() - t0)
+    wt = torch.tensor(walls[2:], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(wt, op=dist.ReduceOp.MAX)
+    e2e_s = float(wt.sum().item())
+    e2e = {"value": rays_step * args.steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 92,
+           "d2h_bytes_per_step": X * Y * 16, "ms_per_step": 1e3 * e2e_s / args.steps,
+           "what": "rt_render() into a pinned host Color[] (RGBA32F, the reference's PixelColors format); scene committed once"}
+
+    # ---- roofline of the dominant kernel: per-kernel CUDA events on the launching stream over K more steps ----
+    rt.set_option("kernel_timing", 1)
+    ksum, kcnt = {}, {}
+    for _ in range(args.steps):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        s2 = rt.render_device(params, want, sync_stats=True)
+        for k, v in s2["ms_kernel"].items():
+            ksum[k] = ksum.get(k, 0.0) + v; kcnt[k] = kcnt.get(k, 0) + s2["launches_kernel"][k]
+    rt.set_option("kernel_timing", 0)
+    if rank == 0:
+        dom = max(ksum, key=ksum.get)
+        n_launch = max(1, kcnt[dom])
+        ms_launch = ksum[dom] / n_launch
+        items = (st["rays_primary"])                                      # work items of this rank per frame
+        scene_bytes = 48 * cstats["n_prims"] + 64 * cstats["n_nodes"]
+        per_item = {"trace_primary": 8, "shade_primary": 8 + 4 + 16, "trace_queue": 32 + 8, "shade_queue": 32 + 8 + 4 + 16, "fold": 48, "finalize": 16 + 8 + 16,
+                    "shadow_primary": 8 + 4, "shadow_queue": 32 + 8 + 4}[dom]
+        extra = 16 * cstats["n_prims"] if dom.startswith("shad") else 0        # pinfo (normals) read by the shading-side kernels
+        launches_per_frame = max(1, kcnt[dom] // args.steps)
+        alg_bytes = scene_bytes + extra + per_item * items / launches_per_frame
+        peak, peak_src = measured_peak_hbm()
+        achieved = alg_bytes / (ms_launch * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": None, "peak_source": peak_src, "ms_per_launch": ms_launch, "algorithmic_bytes_per_launch": alg_bytes,
+                    "kernel_share_of_step": ksum[dom] / max(1e-9, sum(ksum.values())),
+                    "ms_per_step_by_kernel": {k: v / args.steps for k, v in ksum.items() if v > 0},
+                    "note": "BVH traversal is latency/issue-bound, not HBM-bound (scene is L2-resident): see DESIGN.md §5 for the L2/issue bounds"}
+        cb = None
+        if world == 1 and not args.no_cpu:
+            cb, _ = cpu_baseline(scene, params, 12.0, os.cpu_count() or 1)
+            cb.pop("seconds", None)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": f"{args.workload}: {desc}", "rays_per_step": rays_step, "l2": "flushed between timed steps (256 MiB memset), per-step CUDA events",
+                           "partition": f"{world} rank(s), interleaved 32-row bands, scene replicated", "gather": gather, "output": "RGBA32F full frame on GPU 0"},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
+                "commit": {"ms_upload": cstats["ms_commit_upload"], "ms_bvh_build": cstats["ms_commit_build"], "h2d_bytes": cstats["h2d_bytes"],
+                           "wall_ms": 1e3 * commit_wall, "n_prims": cstats["n_prims"], "n_nodes": cstats["n_nodes"]}}
+        print(json.dumps(line), flush=True)
+    barrier()
+    rt.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="cfg3")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -70,7 +70,13 @@ typedef struct {
     uint32_t n_prims, n_nodes;  /* device BVH size */
     uint32_t kernel_launches;   /* kernels of this library launched by the last render */
     uint32_t reserved;
+    /* per-kernel device time of the last render, summed over launches; filled only when option "kernel_timing" is 1
+     * (CUDA events around every launch on the launching stream). Order: RT_K_* below. */
+    float ms_kernel[8];
+    uint32_t launches_kernel[8];
 } rt_stats;
+enum { RT_K_TRACE_PRIMARY = 0, RT_K_SHADE_PRIMARY = 1, RT_K_TRACE_QUEUE = 2, RT_K_SHADE_QUEUE = 3, RT_K_FOLD = 4, RT_K_FINALIZE = 5,
+       RT_K_SHADOW_PRIMARY = 6, RT_K_SHADOW_QUEUE = 7, RT_K_COUNT = 8 };
 
 /* ---- lifetime ---------------------------------------------------------------------------------------------- */
 /* n_devices in {1,2,4,8}: in-process multi-GPU (screen-space row bands interleaved over the devices, scene replicated,
@@ -135,7 +141,7 @@ int rt_alloc_outputs(rt_ctx* ctx, int res_x, int res_y, int want);
 int rt_export_outputs(rt_ctx* ctx, void* handles_4x64);
 int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_y, int want);
 
-/* tuning knobs (all optional): key in {"chunk_pixels","leaf_max","pad_scale","block","ctas_per_sm"} */
+/* tuning knobs (all optional): key in {"chunk_pixels","leaf_max","pad_scale","t_slack","ctas_per_sm","kernel_timing"} */
 int rt_set_option(rt_ctx* ctx, const char* key, double value);
 
 #ifdef __cplusplus

@@ -254,9 +254,9 @@ struct Scene {
                 amax = std::fmax(amax, std::fabs(idx(boxes[i].mx, k)));
             }
         }
-        // generous conservative padding (4x what the device BVH uses): the accelerated oracle must never
+        // generous conservative padding (4x what the device BVH uses, amax/65536): the accelerated oracle must never
         // cull a primitive whose computed t could win.  Cost is irrelevant here.
-        pad = amax * (1.0f / 4096.0f) + 1e-5f;
+        pad = amax * (1.0f / 16384.0f) + 1e-5f;
         nodes.clear(); nodes.reserve(n ? 2 * n / 3 + 16 : 1);
         if (n == 0) { bvh_built = true; return; }
         struct Job { int node; uint32_t lo, hi; };
@@ -320,12 +320,21 @@ struct Scene {
         float best = FLT_MAX; uint32_t best_key = 0xffffffffu;
         float cull = FLT_MAX;
         if (any_tmax2 >= 0.f) cull = std::sqrt(any_tmax2) * 1.001f + pad;
-        int stack[256]; int sp = 0; stack[sp++] = 0;
+        int stack[256]; int sp = 0;
+        if (node_entry(ray.o, inv, nodes[0].box, cull) == INFINITY) return h;
+        stack[sp++] = 0;
         while (sp) {
             const BNode& nd = nodes[stack[--sp]];
             float lim = std::fmin(cull, best * 1.001f + pad);
-            if (node_entry(ray.o, inv, nd.box, lim) == INFINITY) continue;
-            if (nd.count == 0) { stack[sp++] = nd.left; stack[sp++] = nd.right; continue; }
+            if (nd.count == 0) {                       // children tested before the push, nearer child popped first
+                float el = node_entry(ray.o, inv, nodes[nd.left].box, lim), er = node_entry(ray.o, inv, nodes[nd.right].box, lim);
+                if (el != INFINITY && er != INFINITY) {
+                    if (el <= er) { stack[sp++] = nd.right; stack[sp++] = nd.left; } else { stack[sp++] = nd.left; stack[sp++] = nd.right; }
+                } else if (el != INFINITY) stack[sp++] = nd.left;
+                else if (er != INFINITY) stack[sp++] = nd.right;
+                continue;
+            }
+            if (node_entry(ray.o, inv, nd.box, lim) == INFINITY) continue;     // best may have shrunk since the push
             for (int i = 0; i < nd.count; ++i) {
                 uint32_t key = order[nd.first + i];
                 int type, index, mesh; key_decode(key, type, index, mesh);

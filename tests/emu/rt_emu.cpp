@@ -190,6 +190,7 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
     std::vector<std::vector<float4>> local(maxd + 1, std::vector<float4>(W)), link(maxd + 2, std::vector<float4>(W));
     std::vector<float4> rays[2] = {std::vector<float4>(2 * W), std::vector<float4>(2 * W)};
     std::vector<float4> accum((size_t)V.n_tiles * 32);
+    std::vector<uint32_t> occl(W * (size_t)std::max(1, (S.n_lights + 31) / 32));
     RtOut out{(float4*)rgba32f, (uint32_t*)rgba8, hit_id, hit_t};
     VecStack stk;
     for (int sj = 0, pass = 0; sj < g; ++sj) for (int si = 0; si < g; ++si, ++pass)
@@ -212,17 +213,29 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
                     if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
                     ht[q] = bt; hs[q] = bs;
                 }
+                const int n_chunks = (S.n_lights + 31) / 32;
+                auto ray_of = [&](unsigned q, f3& O, f3& D) {
+                    if (d == 0) { int x, y; rt_item_to_pixel(V, tb + (int)(q >> 5), (int)(q & 31), x, y); rt_primary_ray(V, x, y, si, sj, O, D); }
+                    else { O = mk3(rin[2 * q].x, rin[2 * q].y, rin[2 * q].z); D = mk3(rin[2 * q + 1].x, rin[2 * q + 1].y, rin[2 * q + 1].z); }
+                };
+                for (int c = 0; c < n_chunks; ++c)                                              // k_trace_shadow (per-lane form)
+                    for (unsigned q = 0; q < n; ++q) {
+                        uint32_t mask = 0;
+                        if (hs[q] >= 0) {
+                            f3 O, D; ray_of(q, O, D);
+                            uint32_t ns = 0;
+                            mask = rt_shadow_mask(S, O, D, ht[q], hs[q], c * 32, std::min(32, S.n_lights - c * 32), stk, ns);
+                            n_shadow += ns;
+                        }
+                        occl[(size_t)c * W + q] = mask;
+                    }
                 for (unsigned q = 0; q < n; ++q) {                                              // k_shade
                     RtMirror mir; mir.emit = false;
                     int slot = hs[q];
                     if (slot == -1) local[d][q] = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);
                     else if (slot >= 0) {
-                        f3 O, D;
-                        if (d == 0) { int x, y; rt_item_to_pixel(V, tb + (int)(q >> 5), (int)(q & 31), x, y); rt_primary_ray(V, x, y, si, sj, O, D); }
-                        else { O = mk3(rin[2 * q].x, rin[2 * q].y, rin[2 * q].z); D = mk3(rin[2 * q + 1].x, rin[2 * q + 1].y, rin[2 * q + 1].z); }
-                        uint32_t ns = 0;
-                        f3 c = rt_shade_hit(S, O, D, ht[q], slot, d, V.max_bounces, stk, mir, ns);
-                        n_shadow += ns;
+                        f3 O, D; ray_of(q, O, D);
+                        f3 c = rt_shade_masked(S, O, D, ht[q], slot, d, V.max_bounces, occl.data(), W, q, mir);
                         local[d][q] = make_float4(c.x, c.y, c.z, 0.f);
                     }
                     if (mir.emit) {

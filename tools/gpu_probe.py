@@ -16,9 +16,10 @@ else: s, p = sc.cfg3_scene(n=int(cfg)), sc.cfg3_params()
 print(f"scene {cfg}: {s.n_prims} prims, generated in {time.time()-t0:.1f}s", flush=True)
 rt = rtb.RayTracer((0,))
 for k, v in opts.items(): rt.set_option(k, float(v))
+rt.set_option("kernel_timing", 1)
 t0 = time.time(); rt.set_scene(s); print(f"commit wall {time.time()-t0:.3f}s", flush=True)
 for i in range(reps):
     st = rt.render_device(p, rtb.host.RT_OUT_RGBA8, sync_stats=True)
     rays = st["rays_primary"] + st["rays_shadow"] + st["rays_mirror"]
     print(json.dumps(dict(ms=round(st["ms_render"], 3), mrays=round(rays / st["ms_render"] / 1e3, 1), rays=rays, launches=st["kernel_launches"],
-                          nodes=st["n_nodes"], commit_up=round(st["ms_commit_upload"], 2), commit_build=round(st["ms_commit_build"], 2))), flush=True)
+                          nodes=st["n_nodes"], commit_up=round(st["ms_commit_upload"], 2), commit_build=round(st["ms_commit_build"], 2), k={k: round(v, 3) for k, v in st["ms_kernel"].items() if v > 0})), flush=True)

@@ -29,12 +29,14 @@ void device_release(RtDevice& D) {
     for (DevBuf* b : {&D.raw_v, &D.raw_n, &D.raw_s, &D.nodes, &D.prims, &D.pinfo, &D.mats, &D.mesh_aabb, &D.mesh_base, &D.lights, &D.keys,
                       &D.keys_alt, &D.vals, &D.vals_alt, &D.cub_tmp, &D.bounds, &D.topo_i32, &D.leaf_lo, &D.leaf_hi, &D.int_lo, &D.int_hi,
                       &D.flags, &D.new_index, &D.hit0_t, &D.hit0_slot, &D.hitq_t, &D.hitq_slot, &D.rays[0], &D.rays[1], &D.counters, &D.accum,
-                      &D.stats, &D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t})
+                      &D.stats, &D.occl, &D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t})
         b->release();
     for (auto& b : D.local) b.release();
     for (auto& b : D.link) b.release();
     void* imp[4] = {D.o_rgba32f, D.o_rgba8, D.o_hit_id, D.o_hit_t};
     for (int k = 0; k < 4; ++k) if (D.imported[k] && imp[k]) cudaIpcCloseMemHandle(imp[k]);
+    for (cudaEvent_t e : D.kev_pool) cudaEventDestroy(e);
+    D.kev_pool.clear();
     if (D.ev0) cudaEventDestroy(D.ev0);
     if (D.ev1) cudaEventDestroy(D.ev1);
     if (D.own_stream) cudaStreamDestroy(D.own_stream);
@@ -104,6 +106,10 @@ int finish_stats(rt_ctx* c) {
         float m = 0.f; RT_CUDA(cudaEventElapsedTime(&m, D.ev0, D.ev1));
         ms = m > ms ? m : ms;
         pr += fs.primary; sh += fs.shadow; mi += fs.mirror; launches += fs.launches;
+        for (int k = 0; k < RT_K_COUNT; ++k) {       // max over devices: they run concurrently
+            if (i == 0 || fs.ms_kernel[k] > c->stats.ms_kernel[k]) c->stats.ms_kernel[k] = fs.ms_kernel[k];
+            c->stats.launches_kernel[k] = (i == 0 ? 0 : c->stats.launches_kernel[k]) + fs.launches_kernel[k];
+        }
     }
     c->stats.rays_primary = pr; c->stats.rays_shadow = sh; c->stats.rays_mirror = mi;
     c->stats.ms_render = ms; c->stats.kernel_launches = launches;
@@ -424,6 +430,8 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "t_slack") { if (value < 1) return fail(c, RT_E_INVALID, "t_slack < 1"); c->opt.t_slack = value; }
     else if (k == "ctas_per_sm") { c->opt.ctas_per_sm = (int)value; }
     else if (k == "block") { c->opt.block = (int)value; }
+    else if (k == "kernel_timing") { c->opt.kernel_timing = value != 0; }
+    else if (k == "packet") { c->opt.packet = value != 0; for (auto& D : c->devs) D.S.packet = c->opt.packet; }
     else return fail(c, RT_E_INVALID, "unknown option: " + k);
     return RT_OK;
 }

@@ -137,6 +137,12 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     S.aabb_min = mk3(H.aabb[0], H.aabb[1], H.aabb[2]); S.aabb_max = mk3(H.aabb[3], H.aabb[4], H.aabb[5]);
     S.ambient = mk3(H.ambient[0], H.ambient[1], H.ambient[2]);
     S.t_slack = (float)opt.t_slack;
+    S.packet = opt.packet;
+    {   // packet traversal: origins within 5 % of the scene diagonal
+        float dx = H.aabb[3] - H.aabb[0], dy = H.aabb[4] - H.aabb[1], dz = H.aabb[5] - H.aabb[2];
+        float d2 = dx * dx + dy * dy + dz * dz;
+        S.coherent_spread2 = std::isfinite(d2) ? 0.0025f * d2 : 0.f;
+    }
     S.mats = D.mats.as<float4>(); S.mesh_aabb = D.mesh_aabb.as<float4>(); S.mesh_base = D.mesh_base.as<int32_t>();
     S.lights = D.lights.as<float4>();
     D.n_nodes = 0;

@@ -37,6 +37,8 @@ struct RtScene {
     f3 aabb_min, aabb_max;    // Scene.AABB (Scene.cs:15) as given / computed per Scene.cs:17-41
     f3 ambient;               // AmbientLight.Radiance
     float t_slack;            // multiplicative slack on the traversal cull distance (conservative)
+    int32_t packet;           // 1: coherent warps traverse as one packet (rt_packet.cuh); 0: always per-lane
+    float coherent_spread2;   // packet mode needs the warp's ray origins within this squared distance of each other
 };
 
 struct RtView {
@@ -208,54 +210,110 @@ RT_HD void rt_slot_to_id(const RtScene& S, int32_t slot, int32_t& type, int32_t&
 // ---------------------------------------------------------------------------------------------------------------
 struct RtMirror { bool emit; f3 O, D, km; };
 
-template <class STK>
-RT_HD f3 rt_shade_hit(const RtScene& S, f3 O, f3 D, float t, int32_t slot, int32_t bounce, int32_t max_bounces,
-                      STK& stk, RtMirror& mir, uint32_t& n_shadow) {
+// Surface state of one hit between the pieces below (the kernels drive the light loop warp-uniformly so that the shadow
+// query of all 32 lanes can run as one packet; rt_shade_hit strings the same pieces together for a single lane).
+struct RtSurf {
+    f3 P, N, V, sO;           // hit point, normal as stored / sphere normal, view vector, P + N*ShadowRayEpsilon
+    f3 kd, ks, km, color;
+    float phong; bool is_mirror;
+};
+
+// RTS:321-323: surface point and normal (stored normal for triangles, RTS:420-431; GetSphereNormal, RTS:402-407)
+RT_HD void rt_surf_geom(const RtScene& S, f3 O, f3 D, float t, int32_t slot, f3& P, f3& N, int32_t& mat_id) {
     const float4* pp = S.prims + 3 * (size_t)slot;
     float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1);
     float4 pi = RT_LDG4(S.pinfo + slot);
-    f3 P = O + D * t;                                                        // Ray.GetPoint, Ray.cs:18-21
-    f3 N;
-    if (f2i(p1.w) != 0) N = um_normalize(P - mk3(p0.x, p0.y, p0.z));           // GetSphereNormal, RTS:402-407
-    else N = mk3(pi.x, pi.y, pi.z);                                          // stored normal, RTS:420-431
-    const float4* mp = S.mats + 4 * (size_t)f2i(pi.w);
+    P = O + D * t;                                                           // Ray.GetPoint, Ray.cs:18-21
+    if (f2i(p1.w) != 0) N = um_normalize(P - mk3(p0.x, p0.y, p0.z));
+    else N = mk3(pi.x, pi.y, pi.z);
+    mat_id = f2i(pi.w);
+}
+
+// RTS:321-325: + material lookup (RTS:409-436), ambient term (RTS:438-441), view vector
+RT_HD void rt_surf_begin(const RtScene& S, f3 O, f3 D, float t, int32_t slot, RtSurf& sf) {
+    int32_t mat_id;
+    rt_surf_geom(S, O, D, t, slot, sf.P, sf.N, mat_id);
+    const float4* mp = S.mats + 4 * (size_t)mat_id;
     float4 m0 = RT_LDG4(mp), m1 = RT_LDG4(mp + 1), m2 = RT_LDG4(mp + 2), m3 = RT_LDG4(mp + 3);
-    f3 kd = mk3(m0.x, m0.y, m0.z), ka = mk3(m1.x, m1.y, m1.z), km = mk3(m2.x, m2.y, m2.z), ks = mk3(m3.x, m3.y, m3.z);
-    float phong = m0.w; bool is_mirror = f2i(m1.w) != 0;
-    f3 color = S.ambient * ka;                                               // CalculateAmbient, RTS:438-441
-    f3 V = um_normalize(O - P);                                              // RTS:325
-    f3 sO = P + N * RT_SHADOW_EPS;                                           // RTS:331 (also Reflect's origin, RTS:370)
-    for (int32_t li = 0; li < S.n_lights; ++li) {
-        float4 lp = RT_LDG4(S.lights + 2 * li), lint = RT_LDG4(S.lights + 2 * li + 1);
-        f3 Lpos = mk3(lp.x, lp.y, lp.z);
-        f3 Ldir = um_normalize(Lpos - P);                                    // RTS:330
-        f3 dl = Lpos - P;
-        float d2 = um_dot(dl, dl);                                           // distancesq(P, Lpos), RTS:334
+    sf.kd = mk3(m0.x, m0.y, m0.z); sf.km = mk3(m2.x, m2.y, m2.z); sf.ks = mk3(m3.x, m3.y, m3.z);
+    sf.phong = m0.w; sf.is_mirror = f2i(m1.w) != 0;
+    sf.color = S.ambient * mk3(m1.x, m1.y, m1.z);                            // CalculateAmbient, RTS:438-441
+    sf.V = um_normalize(O - sf.P);                                           // RTS:325
+    sf.sO = sf.P + sf.N * RT_SHADOW_EPS;                                     // RTS:331 (also Reflect's origin, RTS:370)
+}
+
+// RTS:329-334: shadow ray direction and lightDistanceSq for light li, from surface point P
+RT_HD void rt_light_ray(const RtScene& S, f3 P, int32_t li, f3& Ldir, float& d2) {
+    float4 lp = RT_LDG4(S.lights + 2 * li);
+    f3 Lpos = mk3(lp.x, lp.y, lp.z);
+    Ldir = um_normalize(Lpos - P);                                           // RTS:330
+    f3 dl = Lpos - P;
+    d2 = um_dot(dl, dl);                                                     // distancesq(P, Lpos), RTS:334
+}
+
+// RTS:350-355 for an unshadowed light: color += diffuse + specular
+RT_HD void rt_light_add(const RtScene& S, RtSurf& sf, int32_t li, f3 Ldir, float d2) {
+    float4 lint = RT_LDG4(S.lights + 2 * li + 1);
+    f3 E = mk3(lint.x, lint.y, lint.z) / d2;                                 // RTS:350
+    float ldn = um_dot(Ldir, sf.N);
+    f3 diff = sf.kd * um_max(0.0f, ldn) * E;                                 // CalculateDiffuse, RTS:443-455
+    f3 spec;
+    if (ldn <= RT_SPEC_CUTOFF) spec = bc3(0.0f);                             // angle > 90, RTS:384-391
+    else {
+        f3 v = Ldir + sf.V;
+        f3 H = v / um_length(v);
+        float cnh = um_max(0.0f, um_dot(sf.N, H));
+        spec = sf.ks * um_pow(cnh, sf.phong) * E;                            // RTS:398-399
+    }
+    sf.color = sf.color + (diff + spec);                                     // RTS:355
+}
+
+// RTS:358-362 + Reflect (RTS:368-373, direction not renormalised)
+RT_HD void rt_surf_mirror(const RtSurf& sf, int32_t bounce, int32_t max_bounces, RtMirror& mir) {
+    mir.emit = sf.is_mirror && bounce < max_bounces;
+    if (mir.emit) {
+        mir.O = sf.sO;
+        mir.D = 2.0f * sf.N * um_dot(sf.V, sf.N) - sf.V;
+        mir.km = sf.km;
+    }
+}
+
+// Shadow queries of one hit for lights [light_begin, light_begin + n) (n <= 32), one lane: bit i set = light
+// light_begin+i is occluded (RTS:331-345).  The kernels run the same loop warp-uniformly with packet traversal.
+template <class STK>
+RT_HD uint32_t rt_shadow_mask(const RtScene& S, f3 O, f3 D, float t, int32_t slot, int32_t light_begin, int32_t n, STK& stk,
+                              uint32_t& n_shadow) {
+    f3 P, N; int32_t mat_id;
+    rt_surf_geom(S, O, D, t, slot, P, N, mat_id);
+    f3 sO = P + N * RT_SHADOW_EPS;                                           // RTS:331
+    uint32_t mask = 0;
+    for (int32_t i = 0; i < n; ++i) {
+        f3 Ldir; float d2;
+        rt_light_ray(S, P, light_begin + i, Ldir, d2);
         ++n_shadow;
         if (rt_scene_gate(S, sO, Ldir)) {                                    // Scene.cs:54 inside the shadow query
             float st; int32_t ss;
-            if (rt_traverse<true>(S, sO, Ldir, d2, stk, st, ss)) continue;  // occluder in front of the light, RTS:337-345
+            if (rt_traverse<true>(S, sO, Ldir, d2, stk, st, ss)) mask |= 1u << i;
         }
-        f3 E = mk3(lint.x, lint.y, lint.z) / d2;                             // RTS:350
-        float ldn = um_dot(Ldir, N);
-        f3 diff = kd * um_max(0.0f, ldn) * E;                                // CalculateDiffuse, RTS:443-455
-        f3 spec;
-        if (ldn <= RT_SPEC_CUTOFF) spec = bc3(0.0f);                         // angle > 90, RTS:384-391
-        else {
-            f3 v = Ldir + V;
-            f3 H = v / um_length(v);
-            float cnh = um_max(0.0f, um_dot(N, H));
-            spec = ks * um_pow(cnh, phong) * E;                              // RTS:398-399
-        }
-        color = color + (diff + spec);                                       // RTS:355
     }
-    mir.emit = is_mirror && bounce < max_bounces;                            // RTS:358
-    if (mir.emit) {
-        mir.O = sO;
-        mir.D = 2.0f * N * um_dot(V, N) - V;                                 // Reflect, RTS:368-373 (not renormalised)
-        mir.km = km;
+    return mask;
+}
+
+// Shade (RTS:304-366 minus the recursion) with the shadow results already known: occl[(li >> 5) * stride + q] bit (li & 31).
+RT_HD f3 rt_shade_masked(const RtScene& S, f3 O, f3 D, float t, int32_t slot, int32_t bounce, int32_t max_bounces,
+                         const uint32_t* occl, size_t stride, size_t q, RtMirror& mir) {
+    RtSurf sf;
+    rt_surf_begin(S, O, D, t, slot, sf);
+    uint32_t mask = 0;
+    for (int32_t li = 0; li < S.n_lights; ++li) {
+        if ((li & 31) == 0) mask = occl[(size_t)(li >> 5) * stride + q];
+        if (mask & (1u << (li & 31))) continue;                              // occluder before the light, RTS:337-345
+        f3 Ldir; float d2;
+        rt_light_ray(S, sf.P, li, Ldir, d2);
+        rt_light_add(S, sf, li, Ldir, d2);
     }
-    return color;
+    rt_surf_mirror(sf, bounce, max_bounces, mir);
+    return sf.color;
 }
 
 // ---------------------------------------------------------------------------------------------------------------

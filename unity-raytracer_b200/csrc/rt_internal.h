@@ -30,6 +30,8 @@ struct RtOptions {
     double t_slack = 1.000125;         // multiplicative slack on the traversal cull distance
     int block = 128;
     int ctas_per_sm = 0;               // 0 = occupancy query
+    int packet = 1;                    // warp-coherent packet traversal for coherent warps
+    int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };
 
 enum { RT_MAX_DEPTH = 64 };           // max_reflection_bounces is clamped to this
@@ -49,7 +51,7 @@ struct RtDevice {
     DevBuf keys, keys_alt, vals, vals_alt, cub_tmp, bounds, topo_i32, leaf_lo, leaf_hi, int_lo, int_hi, flags, new_index;
     // ---- frame work buffers (sized to the wave capacity W) ----
     size_t wave_cap = 0;
-    DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, accum, stats;
+    DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, accum, stats, occl;
     std::vector<DevBuf> local;          // [depth] float4 per entry
     std::vector<DevBuf> link;           // [depth>=1] float4 (km.xyz, parent index bits)
     size_t accum_items = 0;
@@ -60,6 +62,9 @@ struct RtDevice {
     int out_res_x = 0, out_res_y = 0;
     // partition
     int rank = 0, world = 1;
+    // per-launch timing events (option kernel_timing): (kernel class, begin, end)
+    std::vector<cudaEvent_t> kev_pool;
+    std::vector<int> kev_class;        // class of launch i; its events are kev_pool[2i], kev_pool[2i+1]
 };
 
 #define RT_CUDA(call)                                                                                     \
@@ -77,7 +82,7 @@ struct RtDevice {
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
                      float* ms_build, uint64_t* h2d_bytes);
 // rt_render.cu
-struct RtFrameStats { uint64_t primary, shadow, mirror; uint32_t launches; };
+struct RtFrameStats { uint64_t primary, shadow, mirror; uint32_t launches; float ms_kernel[RT_K_COUNT]; uint32_t launches_kernel[RT_K_COUNT]; };
 int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs);
 int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs, int n, int32_t* d_ids, float* d_t,
                         const RtOptions& opt, std::string& err);

@@ -1,0 +1,116 @@
+// rt_packet.cuh — warp-coherent ("packet") BVH traversal, device only.
+//
+// Same query as rt_traverse (rt_core.h) and the same exact primitive tests, but control flow is warp-uniform: all 32
+// lanes walk ONE path, the union of what any lane needs.  Each lane still tests every visited node's child boxes and
+// every visited leaf's primitives with its OWN ray and its OWN cull distance, so each lane tests a superset of the
+// primitives its private traversal would test.  A superset cannot change argmin over (t, scan key) nor the any-hit
+// predicate, hence results are bit-identical to the per-lane traversal (and to the reference's scan).
+//
+// Why: ncu on the per-lane while-while loop showed 13 of 32 lanes active on average (profiles/r1_ncu_summary.md):
+// lanes that reach a leaf early idle while the others descend.  Primary rays of an 8x4 pixel tile, and shadow rays from
+// that tile to one point light, are almost parallel, so the union path is barely longer than a single lane's path while
+// no lane ever idles; node and primitive loads become warp-uniform (one L1 wavefront instead of up to 32).
+// Every lane keeps a private copy of the (identical) stack in its shared-memory column, so a warp can drop to the
+// per-lane traversal at any point without conversion.
+//
+// All 32 lanes of the warp must call; lanes without a ray pass active = false.
+#pragma once
+#include "rt_core.h"
+
+// Cheap coherence test: packet traversal pays off when the rays are nearly parallel and start close together.
+__device__ __forceinline__ bool rt_warp_coherent(f3 O, f3 D, bool active, float max_origin_spread2) {
+    const unsigned full = 0xffffffffu;
+    unsigned m = __ballot_sync(full, active);
+    if (m == 0) return true;
+    int src = __ffs(m) - 1;
+    float ox = __shfl_sync(full, O.x, src), oy = __shfl_sync(full, O.y, src), oz = __shfl_sync(full, O.z, src);
+    float dx = __shfl_sync(full, D.x, src), dy = __shfl_sync(full, D.y, src), dz = __shfl_sync(full, D.z, src);
+    float c = D.x * dx + D.y * dy + D.z * dz;
+    float l2 = (D.x * D.x + D.y * D.y + D.z * D.z) * (dx * dx + dy * dy + dz * dz);
+    float ex = O.x - ox, ey = O.y - oy, ez = O.z - oz;
+    bool ok = !active || (c > 0.f && c * c > 0.9f * l2 && (ex * ex + ey * ey + ez * ez) <= max_origin_spread2);   // cos > ~0.95
+    return __all_sync(full, ok);
+}
+
+template <bool ANY, class STK>
+__device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D, bool active, float any_d2, STK& stk,
+                                                   float& best_t, int32_t& best_slot) {
+    const unsigned full = 0xffffffffu;
+    best_t = FLT_MAX; best_slot = -1;
+    stk.sp = 0;
+    if (S.n_prims <= 0) return false;
+    const float tiny = 1e-30f;
+    float idx_ = rt_div(1.0f, fabsf(D.x) > tiny ? D.x : copysignf(tiny, D.x));
+    float idy_ = rt_div(1.0f, fabsf(D.y) > tiny ? D.y : copysignf(tiny, D.y));
+    float idz_ = rt_div(1.0f, fabsf(D.z) > tiny ? D.z : copysignf(tiny, D.z));
+    float oodx = O.x * idx_, oody = O.y * idy_, oodz = O.z * idz_;
+    uint32_t best_key = 0xffffffffu;
+    float tcull = ANY ? rt_sqrt(any_d2) * S.t_slack : INFINITY;
+    if (!active) tcull = -1.0f;                       // every box test of this lane fails (tmin >= 0 > tcull)
+    int32_t gate_mesh = -1; bool gate_ok = true;
+    bool found = false;                               // ANY: this lane already has its occluder
+    int32_t node = S.root;                            // warp-uniform from here on
+    for (;;) {
+        while (node >= 0) {
+            const float4* np = S.nodes + 4 * (size_t)node;
+            float4 n0 = RT_LDG4(np), n1 = RT_LDG4(np + 1), n2 = RT_LDG4(np + 2), n3 = RT_LDG4(np + 3);
+            float ax0 = rt_fma(n0.x, idx_, -oodx), ax1 = rt_fma(n0.y, idx_, -oodx);
+            float ay0 = rt_fma(n0.z, idy_, -oody), ay1 = rt_fma(n0.w, idy_, -oody);
+            float az0 = rt_fma(n2.x, idz_, -oodz), az1 = rt_fma(n2.y, idz_, -oodz);
+            float bx0 = rt_fma(n1.x, idx_, -oodx), bx1 = rt_fma(n1.y, idx_, -oodx);
+            float by0 = rt_fma(n1.z, idy_, -oody), by1 = rt_fma(n1.w, idy_, -oody);
+            float bz0 = rt_fma(n2.z, idz_, -oodz), bz1 = rt_fma(n2.w, idz_, -oodz);
+            float amin = fmaxf(fmaxf(fminf(ax0, ax1), fminf(ay0, ay1)), fmaxf(fminf(az0, az1), 0.0f));
+            float amax = fminf(fminf(fmaxf(ax0, ax1), fmaxf(ay0, ay1)), fminf(fmaxf(az0, az1), tcull));
+            float bmin = fmaxf(fmaxf(fminf(bx0, bx1), fminf(by0, by1)), fmaxf(fminf(bz0, bz1), 0.0f));
+            float bmax = fminf(fminf(fmaxf(bx0, bx1), fmaxf(by0, by1)), fminf(fmaxf(bz0, bz1), tcull));
+            bool ha = amin <= amax, hb = bmin <= bmax;
+            unsigned ma = __ballot_sync(full, ha), mb = __ballot_sync(full, hb);
+            int32_t ra = f2i(n3.x), rb = f2i(n3.y);
+            if (ma && mb) {
+                unsigned both = ma & mb;
+                unsigned bnear = __ballot_sync(full, ha && hb && bmin < amin);
+                if (2 * __popc(bnear) > __popc(both)) { int32_t t = ra; ra = rb; rb = t; }     // majority vote on the order
+                stk.push(rb);
+                node = ra;
+            } else if (ma) node = ra;
+            else if (mb) node = rb;
+            else {
+                if (stk.empty()) return ANY ? found : best_slot >= 0;
+                node = stk.pop();
+            }
+        }
+        {
+            int32_t ref = ~node;
+            int32_t first = ref >> 3, cnt = (ref & 7) + 1;
+            for (int32_t k = 0; k < cnt; ++k) {
+                int32_t slot = first + k;
+                const float4* pp = S.prims + 3 * (size_t)slot;
+                float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+                if (tcull < 0.0f) continue;                             // lane has no ray / is already occluded
+                float t; bool hit;
+                if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
+                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), t);
+                if (!hit) continue;
+                uint32_t key = (uint32_t)f2i(p0.w);
+                bool better = ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key));
+                if (!better) continue;
+                int32_t mesh = f2i(p2.w);
+                if (mesh >= 0) {                                        // Scene.cs:67
+                    if (mesh != gate_mesh) {
+                        gate_mesh = mesh;
+                        float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
+                        gate_ok = rt_ray_aabb_exact(O, D, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
+                    }
+                    if (!gate_ok) continue;
+                }
+                best_t = t; best_key = key; best_slot = slot;
+                if (ANY) { found = true; tcull = -1.0f; }
+                else tcull = t * S.t_slack;
+            }
+        }
+        if (ANY && __all_sync(full, tcull < 0.0f)) return found;        // every lane is occluded or has no ray
+        if (stk.empty()) return ANY ? found : best_slot >= 0;
+        node = stk.pop();
+    }
+}

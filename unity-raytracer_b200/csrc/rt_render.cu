@@ -11,6 +11,7 @@
 // a global counter; the traversal stack lives in shared memory, strided so a warp's accesses are conflict-free.
 // Compiled with -fmad=false: see rt_hd.h.
 #include "rt_internal.h"
+#include "rt_packet.cuh"
 
 namespace {
 
@@ -38,9 +39,10 @@ __device__ __forceinline__ int warp_fetch(unsigned* counter, int lane) {
     return __shfl_sync(0xffffffffu, t, 0);
 }
 
-// counters layout (unsigned): [0 .. D]: queue counts per depth; [C_WORK + 2*d]: trace work, [C_WORK + 2*d + 1]: shade work
+// counters layout (unsigned): [0 .. D]: queue counts per depth; work counters of depth d at C_WORK + 8*d:
+//   +0 closest-hit trace, +1..+7 shadow-trace launches (one per chunk of 32 lights)
 constexpr int C_WORK = RT_MAX_DEPTH + 2;
-constexpr int C_TOTAL = C_WORK + 2 * (RT_MAX_DEPTH + 2);
+constexpr int C_TOTAL = C_WORK + 8 * (RT_MAX_DEPTH + 2);
 
 __global__ void __launch_bounds__(128) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                         float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work) {
@@ -52,10 +54,12 @@ __global__ void __launch_bounds__(128) k_trace_primary(RtScene S, RtView V, int 
         int x, y;
         bool valid = rt_item_to_pixel(V, tile_begin + t, lane, x, y);
         float bt = FLT_MAX; int bs = -1;
-        if (valid) {
-            f3 O, D; rt_primary_ray(V, x, y, si, sj, O, D);
-            if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
-        }
+        f3 O = V.pos, D = V.fwd;
+        bool active = false;
+        if (valid) { rt_primary_ray(V, x, y, si, sj, O, D); active = rt_scene_gate(S, O, D); }     // Scene.cs:54
+        if (S.packet) {                   // rays of one 8x4 pixel tile share the origin and are almost parallel
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, active, 0.f, stk, bt, bs);
+        } else if (active) rt_traverse<false>(S, O, D, 0.f, stk, bt, bs);
         size_t q = (size_t)t * 32 + lane;
         hit_t[q] = bt; hit_slot[q] = valid ? bs : -2;
     }
@@ -69,48 +73,103 @@ __global__ void __launch_bounds__(128) k_trace_queue(RtScene S, const unsigned* 
     for (;;) {
         unsigned q = (unsigned)warp_fetch(work, lane) * 32u + lane;
         if (q - lane >= n) break;
+        f3 O = mk3(0.f, 0.f, 0.f), D = mk3(0.f, 0.f, 1.f);
+        bool active = false;
         if (q < n) {
             float4 ro = rays[2 * (size_t)q], rd = rays[2 * (size_t)q + 1];
-            f3 O = mk3(ro.x, ro.y, ro.z), D = mk3(rd.x, rd.y, rd.z);
-            float bt = FLT_MAX; int bs = -1;
-            if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
-            hit_t[q] = bt; hit_slot[q] = bs;
+            O = mk3(ro.x, ro.y, ro.z); D = mk3(rd.x, rd.y, rd.z);
+            active = rt_scene_gate(S, O, D);
         }
+        float bt = FLT_MAX; int bs = -1;
+        if (S.packet && rt_warp_coherent(O, D, active, S.coherent_spread2)) {
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, active, 0.f, stk, bt, bs);
+        } else if (active) rt_traverse<false>(S, O, D, 0.f, stk, bt, bs);
+        if (q < n) { hit_t[q] = bt; hit_slot[q] = bs; }
     }
 }
 
-// DEPTH0: items are pixel samples of tiles [tile_begin, tile_begin+n_tiles); rays are regenerated, not stored.
+// item -> the ray that produced its hit. DEPTH0: regenerated from the pixel (never stored); else read from the queue.
 template <bool DEPTH0>
-__global__ void __launch_bounds__(128) k_shade(RtScene S, RtView V, int depth, int tile_begin, int n_tiles, int si, int sj,
-                                                const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
-                                                const float* __restrict__ hit_t, const int* __restrict__ hit_slot, float4* __restrict__ local_out,
-                                                float4* __restrict__ rays_out, float4* __restrict__ link_out, unsigned* next_count, unsigned* work,
-                                                unsigned long long* stats) {
+__device__ __forceinline__ void item_ray(const RtView& V, int tile_begin, unsigned q, int lane, int si, int sj,
+                                         const float4* __restrict__ rays_in, f3& O, f3& D) {
+    if (DEPTH0) { int x, y; rt_item_to_pixel(V, tile_begin + (int)(q >> 5), lane, x, y); rt_primary_ray(V, x, y, si, sj, O, D); }
+    else { float4 ro = rays_in[2 * (size_t)q], rd = rays_in[2 * (size_t)q + 1]; O = mk3(ro.x, ro.y, ro.z); D = mk3(rd.x, rd.y, rd.z); }
+}
+
+// Shadow queries (RTS:329-345) of every hit of a wave for lights [light_begin, light_begin+n_l), n_l <= 32, as any-hit
+// traversals; bit i of occl[q] = light light_begin+i is occluded.  Lean on purpose (no material / colour state is live
+// across the traversal), so it keeps the occupancy of the closest-hit kernels.  The light loop is warp-uniform so the 32
+// queries towards one light go as one packet when the warp's hits lie close together.
+template <bool DEPTH0>
+__global__ void __launch_bounds__(128) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
+                                                       const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
+                                                       const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
+                                                       int light_begin, int n_l, uint32_t* __restrict__ occl, unsigned* work,
+                                                       unsigned long long* stats) {
     SmemStack stk(g_smem_stack + threadIdx.x, blockDim.x);
     const int lane = threadIdx.x & 31;
+    const unsigned full = 0xffffffffu;
     const unsigned n = DEPTH0 ? (unsigned)n_tiles * 32u : *n_ptr;
     unsigned my_shadow = 0;
     for (;;) {
         unsigned q = (unsigned)warp_fetch(work, lane) * 32u + lane;
         if (q - lane >= n) break;
-        RtMirror mir; mir.emit = false;
-        if (q < n) {
-            int slot = hit_slot[q];
-            if (slot == -1) local_out[q] = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);   // RTS:310-311
-            else if (slot >= 0) {
-                f3 O, D;
-                if (DEPTH0) { int x, y; rt_item_to_pixel(V, tile_begin + (int)(q >> 5), lane, x, y); rt_primary_ray(V, x, y, si, sj, O, D); }
-                else { float4 ro = rays_in[2 * (size_t)q], rd = rays_in[2 * (size_t)q + 1]; O = mk3(ro.x, ro.y, ro.z); D = mk3(rd.x, rd.y, rd.z); }
-                f3 c = rt_shade_hit(S, O, D, hit_t[q], slot, depth, V.max_bounces, stk, mir, my_shadow);
-                local_out[q] = make_float4(c.x, c.y, c.z, 0.f);
-            }
+        const int slot = q < n ? hit_slot[q] : -2;
+        const bool has = slot >= 0;
+        if (!__any_sync(full, has)) { if (q < n) occl[q] = 0u; continue; }
+        f3 P = mk3(0.f, 0.f, 0.f), sO = P;
+        if (has) {
+            f3 O, D, N; int mat_id;
+            item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
+            rt_surf_geom(S, O, D, hit_t[q], slot, P, N, mat_id);
+            sO = P + N * RT_SHADOW_EPS;                                                        // RTS:331
         }
-        // warp-aggregated append of the reflection rays to the next depth's queue
-        unsigned m = __ballot_sync(0xffffffffu, mir.emit);
+        uint32_t mask = 0;
+        for (int i = 0; i < n_l; ++i) {
+            f3 Ldir = mk3(0.f, 0.f, 1.f); float d2 = 0.f;
+            bool act = false;
+            if (has) { rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow; act = rt_scene_gate(S, sO, Ldir); }   // Scene.cs:54
+            bool occluded = false;
+            float st; int ss;
+            if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
+                if (__any_sync(full, act)) occluded = rt_traverse_packet<true>(S, sO, Ldir, act, d2, stk, st, ss);
+            } else if (act) occluded = rt_traverse<true>(S, sO, Ldir, d2, stk, st, ss);
+            if (occluded) mask |= 1u << i;
+        }
+        if (q < n) occl[q] = mask;
+    }
+    my_shadow = __reduce_add_sync(full, my_shadow);
+    if (lane == 0 && my_shadow) atomicAdd(stats + 1, (unsigned long long)my_shadow);
+}
+
+// Shading + light loop with the shadow results known (rt_shade_masked); appends the reflection rays of mirror hits to
+// the next depth's queue with a warp-aggregated (ballot/popc) reservation.  Pure streaming kernel: no traversal.
+template <bool DEPTH0>
+__global__ void __launch_bounds__(256) k_shade(RtScene S, RtView V, int depth, int tile_begin, int n_tiles, int si, int sj,
+                                                const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
+                                                const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
+                                                const uint32_t* __restrict__ occl, size_t occl_stride, float4* __restrict__ local_out,
+                                                float4* __restrict__ rays_out, float4* __restrict__ link_out, unsigned* next_count,
+                                                unsigned long long* stats) {
+    const int lane = threadIdx.x & 31;
+    const unsigned full = 0xffffffffu;
+    const unsigned n = DEPTH0 ? (unsigned)n_tiles * 32u : *n_ptr;
+    const unsigned n32 = (n + 31u) & ~31u;                       // whole warps, so the ballots below are convergent
+    for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < n32; q += gridDim.x * blockDim.x) {
+        RtMirror mir; mir.emit = false;
+        const int slot = q < n ? hit_slot[q] : -2;
+        if (slot == -1) local_out[q] = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);       // RTS:310-311
+        else if (slot >= 0) {
+            f3 O, D;
+            item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
+            f3 c = rt_shade_masked(S, O, D, hit_t[q], slot, depth, V.max_bounces, occl, occl_stride, q, mir);
+            local_out[q] = make_float4(c.x, c.y, c.z, 0.f);
+        }
+        unsigned m = __ballot_sync(full, mir.emit);
         if (m) {
             unsigned base = 0;
             if (lane == 0) { base = atomicAdd(next_count, (unsigned)__popc(m)); atomicAdd(stats + 2, (unsigned long long)__popc(m)); }
-            base = __shfl_sync(0xffffffffu, base, 0);
+            base = __shfl_sync(full, base, 0);
             if (mir.emit) {
                 size_t o = base + __popc(m & ((1u << lane) - 1u));
                 rays_out[2 * o] = make_float4(mir.O.x, mir.O.y, mir.O.z, 0.f);
@@ -119,8 +178,6 @@ __global__ void __launch_bounds__(128) k_shade(RtScene S, RtView V, int depth, i
             }
         }
     }
-    my_shadow = __reduce_add_sync(0xffffffffu, my_shadow);
-    if (lane == 0 && my_shadow) atomicAdd(stats + 1, (unsigned long long)my_shadow);
 }
 
 __global__ void k_fold(const unsigned* __restrict__ n_ptr, const float4* __restrict__ link, const float4* __restrict__ local_cur, float4* local_prev) {
@@ -166,6 +223,15 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
     }
     cudaStream_t st = D.stream;
     uint32_t launches = 0;
+    D.kev_class.clear();
+    auto kbegin = [&](int cls) {
+        if (!opt.kernel_timing) return;
+        size_t i = D.kev_class.size();
+        while (D.kev_pool.size() < 2 * (i + 1)) { cudaEvent_t e; cudaEventCreate(&e); D.kev_pool.push_back(e); }
+        D.kev_class.push_back(cls);
+        cudaEventRecord(D.kev_pool[2 * i], st);
+    };
+    auto kend = [&]() { if (opt.kernel_timing) cudaEventRecord(D.kev_pool[2 * (D.kev_class.size() - 1) + 1], st); };
     RT_CUDA(D.stats.ensure(4 * 8));
     RT_CUDA(cudaMemsetAsync(D.stats.p, 0, 4 * 8, st));
     RT_CUDA(cudaEventRecord(D.ev0, st));
@@ -190,13 +256,16 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             for (int d = 1; d <= maxd; ++d) RT_CUDA(D.link[d].ensure(W * 16));
         }
         if (n_pass > 1) RT_CUDA(D.accum.ensure((size_t)V.n_tiles * 32 * 16));
+        const int n_chunks = (D.S.n_lights + 31) / 32;                      // shadow launches per depth
+        RT_CUDA(D.occl.ensure(W * 4 * (size_t)(n_chunks < 1 ? 1 : n_chunks)));
         const int g_trace = persistent_grid(k_trace_primary, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_traceq = persistent_grid(k_trace_queue, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shade0 = persistent_grid(k_shade<true>, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shaden = persistent_grid(k_shade<false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadow0 = persistent_grid(k_trace_shadow<true>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadown = persistent_grid(k_trace_shadow<false>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_flat = D.sm_count * 8;
         unsigned* C = D.counters.as<unsigned>();
         unsigned long long* ST = D.stats.as<unsigned long long>();
+        uint32_t* OC = D.occl.as<uint32_t>();
         RtOut out{(want & RT_OUT_RGBA32F) ? (float4*)D.o_rgba32f : nullptr, (want & RT_OUT_RGBA8) ? (uint32_t*)D.o_rgba8 : nullptr,
                   (want & RT_OUT_HIT_ID) ? (int32_t*)D.o_hit_id : nullptr, (want & RT_OUT_HIT_T) ? (float*)D.o_hit_t : nullptr};
         for (int sj = 0, pass = 0; sj < g; ++sj)
@@ -204,26 +273,45 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                 for (int tb = 0; tb < V.n_tiles; tb += wave_tiles) {
                     const int nt = (V.n_tiles - tb) < wave_tiles ? (V.n_tiles - tb) : wave_tiles;
                     RT_CUDA(cudaMemsetAsync(C, 0, C_TOTAL * 4, st));
+                    kbegin(RT_K_TRACE_PRIMARY);
                     k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, D.hit0_t.as<float>(), D.hit0_slot.as<int>(), C + C_WORK);
-                    k_shade<true><<<g_shade0, block, smem, st>>>(D.S, V, 0, tb, nt, si, sj, nullptr, nullptr, D.hit0_t.as<float>(), D.hit0_slot.as<int>(),
-                                                                  D.local[0].as<float4>(), maxd > 0 ? D.rays[0].as<float4>() : nullptr,
-                                                                  maxd > 0 ? D.link[1].as<float4>() : nullptr, C + 1, C + C_WORK + 1, ST);
-                    launches += 2;
-                    for (int d = 1; d <= maxd; ++d) {
-                        float4* rin = D.rays[(d - 1) & 1].as<float4>();
-                        float4* rout = D.rays[d & 1].as<float4>();
-                        k_trace_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, D.hitq_t.as<float>(), D.hitq_slot.as<int>(), C + C_WORK + 2 * d);
-                        k_shade<false><<<g_shaden, block, smem, st>>>(D.S, V, d, 0, 0, 0, 0, C + d, rin, D.hitq_t.as<float>(), D.hitq_slot.as<int>(),
-                                                                       D.local[d].as<float4>(), d < maxd ? rout : nullptr,
-                                                                       d < maxd ? D.link[d + 1].as<float4>() : nullptr, C + d + 1, C + C_WORK + 2 * d + 1, ST);
-                        launches += 2;
+                    kend(); ++launches;
+                    for (int d = 0; d <= maxd; ++d) {
+                        const float4* rin = d ? D.rays[(d - 1) & 1].as<float4>() : nullptr;
+                        float4* rout = d < maxd ? D.rays[d & 1].as<float4>() : nullptr;
+                        float4* lout = d < maxd ? D.link[d + 1].as<float4>() : nullptr;
+                        const float* ht = d ? D.hitq_t.as<float>() : D.hit0_t.as<float>();
+                        const int* hs = d ? D.hitq_slot.as<int>() : D.hit0_slot.as<int>();
+                        unsigned* wk = C + C_WORK + 8 * d;
+                        if (d > 0) {
+                            kbegin(RT_K_TRACE_QUEUE);
+                            k_trace_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, D.hitq_t.as<float>(), D.hitq_slot.as<int>(), wk);
+                            kend(); ++launches;
+                        }
+                        for (int c = 0; c < n_chunks; ++c) {
+                            unsigned* wc = wk + 1 + (c % 7);
+                            if (c >= 7) RT_CUDA(cudaMemsetAsync(wc, 0, 4, st));
+                            const int lb = c * 32, nl = (D.S.n_lights - lb) < 32 ? (D.S.n_lights - lb) : 32;
+                            kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
+                            if (d == 0) k_trace_shadow<true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST);
+                            else k_trace_shadow<false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST);
+                            kend(); ++launches;
+                        }
+                        kbegin(d ? RT_K_SHADE_QUEUE : RT_K_SHADE_PRIMARY);
+                        if (d == 0) k_shade<true><<<g_flat, 256, 0, st>>>(D.S, V, 0, tb, nt, si, sj, nullptr, nullptr, ht, hs, OC, W, D.local[0].as<float4>(), rout, lout, C + 1, ST);
+                        else k_shade<false><<<g_flat, 256, 0, st>>>(D.S, V, d, 0, 0, 0, 0, C + d, rin, ht, hs, OC, W, D.local[d].as<float4>(), rout, lout, C + d + 1, ST);
+                        kend(); ++launches;
                     }
                     for (int d = maxd; d >= 1; --d) {
+                        kbegin(RT_K_FOLD);
                         k_fold<<<g_flat, 256, 0, st>>>(C + d, D.link[d].as<float4>(), D.local[d].as<float4>(), D.local[d - 1].as<float4>());
+                        kend();
                         ++launches;
                     }
+                    kbegin(RT_K_FINALIZE);
                     k_finalize<<<g_flat, 256, 0, st>>>(D.S, V, tb, nt, pass, n_pass, D.local[0].as<float4>(), D.hit0_t.as<float>(), D.hit0_slot.as<int>(),
                                                         n_pass > 1 ? D.accum.as<float4>() : nullptr, out);
+                    kend();
                     ++launches;
                 }
         RT_CUDA(cudaGetLastError());
@@ -242,6 +330,13 @@ int rt_device_read_stats(RtDevice& D, RtFrameStats* fs, std::string& err) {
         RT_CUDA(cudaStreamSynchronize(D.stream));
     }
     fs->shadow = h[1]; fs->mirror = h[2];
+    for (int k = 0; k < RT_K_COUNT; ++k) { fs->ms_kernel[k] = 0.f; fs->launches_kernel[k] = 0; }
+    for (size_t i = 0; i < D.kev_class.size(); ++i) {
+        float m = 0.f;
+        RT_CUDA(cudaEventSynchronize(D.kev_pool[2 * i + 1]));
+        RT_CUDA(cudaEventElapsedTime(&m, D.kev_pool[2 * i], D.kev_pool[2 * i + 1]));
+        fs->ms_kernel[D.kev_class[i]] += m; fs->launches_kernel[D.kev_class[i]] += 1;
+    }
     return RT_OK;
 }
 

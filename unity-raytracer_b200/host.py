@@ -35,10 +35,16 @@ class Stats(C.Structure):
     _fields_ = [("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_mirror", C.c_uint64),
                 ("ms_render", C.c_float), ("ms_d2h", C.c_float), ("ms_commit_upload", C.c_float), ("ms_commit_build", C.c_float),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("n_prims", C.c_uint32), ("n_nodes", C.c_uint32),
-                ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32),
+                ("ms_kernel", C.c_float * 8), ("launches_kernel", C.c_uint32 * 8)]
+
+    KERNELS = ("trace_primary", "shade_primary", "trace_queue", "shade_queue", "fold", "finalize", "shadow_primary", "shadow_queue")
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in ("reserved", "ms_kernel", "launches_kernel")}
+        d["ms_kernel"] = {n: float(self.ms_kernel[i]) for i, n in enumerate(self.KERNELS)}
+        d["launches_kernel"] = {n: int(self.launches_kernel[i]) for i, n in enumerate(self.KERNELS)}
+        return d
 
 
 def make_params(p):
@@ -194,8 +200,8 @@ class RayTracer:
         self._chk(self.L.rt_render_device(self.h, C.byref(q), want, None))
         return None
 
-    def read_outputs(self, params, want=RT_OUT_ALL):
-        out = self.alloc_host_outputs(params, want)
+    def read_outputs(self, params, want=RT_OUT_ALL, out=None):
+        out = out if out is not None else self.alloc_host_outputs(params, want)
         ptr = lambda k: out[k].ctypes.data if k in out else None
         self._chk(self.L.rt_read_outputs(self.h, ptr("rgba32f"), ptr("rgba8"), ptr("hit_id"), ptr("hit_t")))
         return out
