@@ -228,7 +228,7 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.all_reduce(wt, op=dist.ReduceOp.MAX)
     e2e_s = float(wt.sum().item())
-    e2e = {"value": rays_step * args.steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 92,
+    e2e = {"value": rays_step * args.steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 88,
            "d2h_bytes_per_step": X * Y * 16, "ms_per_step": 1e3 * e2e_s / args.steps,
            "what": "rt_render() into a pinned host Color[] (RGBA32F, the reference's PixelColors format); scene committed once"}
 

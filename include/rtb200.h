@@ -57,7 +57,7 @@ typedef struct {
     int32_t max_reflection_bounces;          /* RTS:23 */
     int32_t spp_grid;                        /* 1 = reference behaviour (one ray at the pixel centre, RTS:291-292);
                                                 g>1 = g*g stratified sample centres, averaged in fixed (j,i) order */
-} rt_render_params;                          /* 92 bytes */
+} rt_render_params;                          /* 88 bytes */
 
 typedef struct {
     uint64_t rays_primary, rays_shadow, rays_mirror;   /* Scene.IntersectRay-equivalent queries issued by the last render */

@@ -1,0 +1,149 @@
+"""-m "not gpu": the product's host/device headers (rt_core.h traversal + shading, rt_build_steps.h LBVH build,
+rt_host_scene.h flattening) instantiated serially on the CPU by tests/emu and compared with the oracle.
+
+This checks the *logic* the CUDA kernels run — LBVH build, BVH-vs-linear-scan equivalence incl. tie-break and AABB gates,
+wave/depth bookkeeping, pixel<->tile mapping, band partition — where no GPU exists.  It is not a CPU path of the product:
+tests/emu is test infrastructure and librtb200.so never links it (tests/test_abi.py checks the product fails without CUDA).
+"""
+import numpy as np
+import pytest
+
+from conftest import compare_renders
+
+
+def _strict(cmp):
+    # same libm on both sides here, so even the float colour must be bit-identical
+    assert cmp["id"] == 0 and cmp["t"] == 0 and cmp["u8_gt0"] == 0 and cmp["f32"] == 0, cmp
+
+
+def test_cfg1_rt_unity(emu, oracle, scenes):
+    s, p = scenes.rt_unity(), scenes.rt_unity_params()
+    e = emu.EmuTracer(); e.set_scene(s)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    got = e.render(p)
+    _strict(compare_renders(ref, got))
+    assert (got["stats"]["rays_primary"], got["stats"]["rays_shadow"], got["stats"]["rays_mirror"]) == ref["stats"]
+    assert np.array_equal(e.scene_aabb(), oracle.OracleScene(s).aabb())
+
+
+def test_cfg2_mirror_recursion_order(emu, oracle, scenes):
+    """Iterative wave + back-to-front fold == the reference's recursion (RayTracingSetup.cs:358-363), bit for bit."""
+    s, p = scenes.rt_unity(mirror_sphere=True), scenes.rt_unity_params(160, 90, 4)
+    e = emu.EmuTracer(); e.set_scene(s)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    got = e.render(p)
+    _strict(compare_renders(ref, got))
+    assert got["stats"]["rays_mirror"] == ref["stats"][2] > 0
+
+
+@pytest.mark.parametrize("leaf_max", [1, 4, 8])
+def test_bvh_equals_linear_scan(emu, oracle, scenes, leaf_max):
+    s, p = scenes.random_soup(seed=7), scenes.soup_params(64, 48, 3, 1)
+    e = emu.EmuTracer(leaf_max=leaf_max); e.set_scene(s)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    _strict(compare_renders(ref, e.render(p)))
+    assert e.max_stack() < 64
+
+
+def test_spp_grid_extension(emu, oracle, scenes):
+    s, p = scenes.random_soup(seed=3), scenes.soup_params(48, 32, 2, 2)
+    e = emu.EmuTracer(); e.set_scene(s)
+    _strict(compare_renders(oracle.OracleScene(s).render(p, oracle.FAITHFUL), e.render(p)))
+
+
+def test_intersect_random_rays(emu, oracle, scenes):
+    s = scenes.random_soup(seed=11)
+    rng = np.random.default_rng(5)
+    o = rng.uniform(-40, 40, (4000, 3)).astype(np.float32)
+    d = rng.normal(size=(4000, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d = d.astype(np.float32)
+    rid, rt_ = oracle.OracleScene(s).intersect(o, d, oracle.FAITHFUL)
+    e = emu.EmuTracer(); e.set_scene(s)
+    gid, gt = e.intersect(o, d)
+    assert (rid[:, :2] == gid[:, :2]).all() and (rt_ == gt).all()
+
+
+def test_duplicate_primitives_tie_break(emu, scenes):
+    """Identical primitives (equal Morton codes, equal t): the lowest scan index must win (Scene.cs strict '>')."""
+    s = scenes.SceneArrays()
+    tri = np.array((-1, -1, 5, 1, -1, 5, 0, 1, 5), np.float32)
+    n = scenes.triangle_normal(tri)[0]
+    for _ in range(9):
+        s.add_triangle(tri, n, scenes.material())
+    s.add_sphere((0, 0, 6), 1.0, scenes.material())          # front pole also at t = 5: sphere (class 1) beats loose tris (class 2)
+    for leaf_max in (1, 4):
+        e = emu.EmuTracer(leaf_max=leaf_max); e.set_scene(s)
+        ids, t = e.intersect([(0, 0, 0)], [(0, 0, 1)])
+        assert t[0] == np.float32(5.0) and ids[0, :2].tolist() == [1, 0]
+    s.spheres = s.spheres[:0]; s.sphere_mats = s.sphere_mats[:0]
+    e = emu.EmuTracer(leaf_max=2); e.set_scene(s)
+    assert e.intersect([(0, 0, 0)], [(0, 0, 1)])[0][0, :2].tolist() == [2, 0]
+
+
+def test_mesh_aabb_gate_is_semantic(emu, oracle, scenes):
+    """Scene.cs:67: a mesh whose (caller-supplied) AABB the ray misses is skipped even if a triangle would be hit."""
+    s = scenes.SceneArrays()
+    tri = np.array((-1, -1, 5, 1, -1, 5, 0, 1, 5), np.float32).reshape(1, 9)
+    nm, _ = scenes.mesh_from_world_tris(tri)
+    s.add_mesh(tri, nm, scenes.material(), np.array((10, 10, 10, 11, 11, 11), np.float32))     # deliberately wrong box
+    s.scene_aabb = np.array((-20, -20, -20, 20, 20, 20), np.float32)
+    e = emu.EmuTracer(); e.set_scene(s)
+    ids, t = e.intersect([(0, 0, 0)], [(0, 0, 1)])
+    rid, rt_ = oracle.OracleScene(s).intersect([(0, 0, 0)], [(0, 0, 1)])
+    assert ids[0].tolist() == rid[0].tolist() == [0, -1, -1] and t[0] == rt_[0]
+
+
+def test_scene_aabb_gate_is_semantic(emu, oracle, scenes):
+    """Scene.cs:54: a ray that misses the (caller-supplied) scene AABB misses everything."""
+    s = scenes.rt_unity()
+    s.scene_aabb = np.array((100, 100, 100, 101, 101, 101), np.float32)
+    e = emu.EmuTracer(); e.set_scene(s)
+    p = scenes.rt_unity_params(20, 20)
+    got, ref = e.render(p), oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    assert (got["hit_id"][:, 0] == 0).all()
+    _strict(compare_renders(ref, got))
+
+
+def test_partition_union_and_waves(emu, scenes):
+    s, p = scenes.random_soup(seed=5), scenes.soup_params(100, 77, 2, 1)
+    e = emu.EmuTracer(); e.set_scene(s)
+    ref = e.render(p)
+    e.set_option("chunk_pixels", 256)
+    small = e.render(p)
+    for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(ref[k], small[k], equal_nan=True), k
+    e.set_option("chunk_pixels", 1 << 23)
+    for world in (2, 3, 8):
+        acc = {k: np.zeros_like(ref[k]) for k in ("rgba32f", "rgba8", "hit_id", "hit_t")}
+        rays = 0
+        for r in range(world):
+            e.set_partition(r, world, 8)
+            g = e.render(p)
+            rays += g["stats"]["rays_primary"]
+            mine = np.repeat(((np.arange(77) // 8) % world) == r, 100)
+            for k in acc:
+                acc[k][mine] = g[k][mine]
+        e.set_partition(0, 1, 32)
+        assert rays == 100 * 77
+        for k in acc:
+            assert np.array_equal(acc[k], ref[k], equal_nan=True), (world, k)
+
+
+def test_empty_and_degenerate(emu, scenes):
+    e = emu.EmuTracer(); e.set_scene(scenes.SceneArrays())
+    got = e.render(scenes.make_params(5, 3, 10.0, 8.0, 5.0, (0.25, 0.5, 1.0)))
+    assert (got["hit_id"] == np.array([0, -1, -1])).all() and (got["rgba8"] == np.array([64, 128, 255, 255], np.uint8)).all()
+    got = e.render(scenes.make_params(0, 0, 10.0, 8.0, 5.0))
+    assert got["rgba32f"].shape == (0, 4)
+    # one primitive: root is a leaf
+    s = scenes.SceneArrays(); s.add_sphere((0, 0, 20), 25.0, scenes.material(ambient=(1, 0.5, 0.25))); s.ambient[:] = (100, 100, 100)
+    e = emu.EmuTracer(); e.set_scene(s)
+    got = e.render(scenes.make_params(9, 9, 10.0, 1.0, 1.0))
+    assert (got["rgba8"][40] == np.array([100, 50, 25, 255], np.uint8)).all()
+
+
+def test_cfg3_reduced(emu, oracle, scenes):
+    s, p = scenes.cfg3_scene(n=24), scenes.cfg3_params(160, 90)
+    e = emu.EmuTracer(); e.set_scene(s)
+    ora = oracle.OracleScene(s)
+    _strict(compare_renders(ora.render(p, oracle.ACCELERATED), e.render(p)))
