@@ -1,0 +1,32 @@
+"""Summarise an .ncu-rep (ncu --set full) into markdown: one column per profiled launch, the counters DESIGN.md §5 uses.
+    python tools/ncu_summary.py gpurun_out/X.ncu-rep > profiles/X.md"""
+import csv, io, subprocess, sys
+rep = sys.argv[1]
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+H, U, R = rows[0], rows[1], rows[2:]
+M = [("gpu__time_duration.sum", "duration"), ("launch__grid_size", "grid"), ("launch__block_size", "block"),
+     ("launch__registers_per_thread", "regs/thread"), ("launch__shared_mem_per_block_dynamic", "dyn smem/block"),
+     ("sm__warps_active.avg.pct_of_peak_sustained_active", "achieved occupancy"),
+     ("smsp__inst_executed.sum", "warp instructions"), ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue-slot utilisation"),
+     ("sm__inst_executed.avg.per_cycle_elapsed", "IPC (per SM, elapsed)"),
+     ("smsp__thread_inst_executed_per_inst_executed.ratio", "active lanes / warp instruction"),
+     ("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "FMA pipe active"),
+     ("sass__inst_executed_global_loads", "global load instr"), ("sass__inst_executed_shared_loads", "shared load instr"),
+     ("sass__inst_executed_shared_stores", "shared store instr"), ("sass__inst_executed_local_loads", "local load instr"),
+     ("sass__inst_executed_local_stores", "local store instr"),
+     ("l1tex__t_sector_hit_rate.pct", "L1 hit rate"), ("lts__t_sectors.sum", "L2 sectors (32 B)"), ("lts__t_sector_hit_rate.pct", "L2 hit rate"),
+     ("dram__bytes_read.sum", "DRAM read"), ("dram__bytes_write.sum", "DRAM write"),
+     ("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "stall long_scoreboard / issue"),
+     ("smsp__average_warps_issue_stalled_wait_per_issue_active.ratio", "stall wait / issue"),
+     ("smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "stall not_selected / issue"),
+     ("smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio", "stall math_pipe / issue"),
+     ("smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "stall branch / issue"),
+     ("smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio", "stall short_scoreboard / issue")]
+names = [r[H.index("Kernel Name")].split("(")[0].replace("<unnamed>::", "").replace("void ", "") for r in R]
+print("| counter | " + " | ".join(names) + " |")
+print("|---|" + "---|" * len(names))
+for key, label in M:
+    if key not in H: continue
+    i = H.index(key)
+    print(f"| {label} (`{key}`) [{U[i]}] | " + " | ".join(r[i] for r in R) + " |")
