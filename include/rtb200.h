@@ -141,7 +141,9 @@ int rt_alloc_outputs(rt_ctx* ctx, int res_x, int res_y, int want);
 int rt_export_outputs(rt_ctx* ctx, void* handles_4x64);
 int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_y, int want);
 
-/* tuning knobs (all optional): key in {"chunk_pixels","leaf_max","pad_scale","t_slack","ctas_per_sm","kernel_timing"} */
+/* tuning knobs (all optional): key in {"chunk_pixels","leaf_max","pad_scale","t_slack","ctas_per_sm","kernel_timing","packet",
+ * "builder"}; builder 0 = device LBVH (default, ~10 ms per million primitives), 1 = host binned-SAH BVH (slower commit,
+ * fewer node visits per ray); takes effect at the next rt_scene_commit */
 int rt_set_option(rt_ctx* ctx, const char* key, double value);
 
 #ifdef __cplusplus

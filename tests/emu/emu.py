@@ -25,10 +25,11 @@ def lib():
         L.emu_scene_triangles.argtypes = [vp, fp, fp, vp, C.c_int]
         L.emu_scene_mesh.argtypes = [vp, fp, fp, C.c_int, vp, fp]
         L.emu_scene_lights.argtypes = [vp, fp, C.c_int, fp]
-        L.emu_scene_commit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double]
+        L.emu_scene_commit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double, C.c_int]
         L.emu_get_aabb.argtypes = [vp, fp]
         L.emu_n_nodes.argtypes = [vp]
         L.emu_max_stack.argtypes = [vp]
+        L.emu_ray_triangle.argtypes = [fp, fp, fp, C.c_float, fp]
         L.emu_intersect.argtypes = [vp, fp, fp, C.c_int, ip, fp]
         L.emu_render.argtypes = [vp, C.POINTER(host.RenderParams), C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp,
                                  C.POINTER(C.c_uint64)]
@@ -41,10 +42,10 @@ def _fp(a):
 
 
 class EmuTracer:
-    def __init__(self, leaf_max=4, pad_scale=1.0 / 65536.0, t_slack=1.000125):
+    def __init__(self, leaf_max=4, pad_scale=1.0 / 65536.0, t_slack=1.000125, builder=0):
         self.L = lib()
         self.h = C.c_void_p(self.L.emu_new())
-        self.opts = (leaf_max, pad_scale, t_slack)
+        self.opts = (leaf_max, pad_scale, t_slack, builder)
         self.rank, self.world, self.band_rows, self.chunk = 0, 1, 32, 1 << 23
 
     def __del__(self):
@@ -68,7 +69,7 @@ class EmuTracer:
         li, amb = f32(sa.lights), f32(sa.ambient)
         L.emu_scene_lights(h, _fp(li), li.shape[0], _fp(amb))
         bb = _fp(f32(sa.scene_aabb)) if sa.scene_aabb is not None else None
-        L.emu_scene_commit(h, bb, self.opts[0], self.opts[1], self.opts[2])
+        L.emu_scene_commit(h, bb, self.opts[0], self.opts[1], self.opts[2], self.opts[3])
 
     def scene_aabb(self):
         out = np.zeros(6, np.float32)
@@ -105,3 +106,12 @@ class EmuTracer:
                           ptr("hit_id"), ptr("hit_t"), st)
         out["stats"] = dict(rays_primary=int(st[0]), rays_shadow=int(st[1]), rays_mirror=int(st[2]))
         return out
+
+
+def ray_triangle(o, d, v9, tmax=float("inf")):
+    """rt_core.h rt_ray_tri (division-free rejections + exact accept path) for one ray/triangle pair."""
+    f = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+    o, d, v9 = f(o), f(d), f(v9)
+    t = C.c_float(0)
+    hit = lib().emu_ray_triangle(_fp(o), _fp(d), _fp(v9), C.c_float(tmax), C.byref(t))
+    return bool(hit), np.float32(t.value)

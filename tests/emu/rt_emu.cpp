@@ -10,6 +10,7 @@
 #include "../../unity-raytracer_b200/csrc/rt_core.h"
 #include "../../unity-raytracer_b200/csrc/rt_build_steps.h"
 #include "../../unity-raytracer_b200/csrc/rt_host_scene.h"
+#include "../../unity-raytracer_b200/csrc/rt_sah.h"
 
 namespace {
 
@@ -31,7 +32,7 @@ struct Emu {
     bool has_mirror = false;
 };
 
-void commit(Emu& E, int leaf_max, double pad_scale, double t_slack) {
+void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder) {
     RtHostScene& H = E.host;
     const int n_mt = H.n_meshtris(), n_sp = H.n_spheres(), n_lo = H.n_loose(), n_me = H.n_meshes(), n_li = H.n_lights();
     const int n = (int)H.n_prims();
@@ -74,6 +75,20 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack) {
     const float pad = (float)(amax * pad_scale) + 1e-30f;
     f3 bmin = mk3(b[0], b[1], b[2]);
     f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
+    if (builder == 1) {                                            // host binned-SAH path of rt_device_commit
+        std::vector<RtSahBox> pb(n);
+        for (int i = 0; i < n; ++i) { f3 lo, hi; rt_prim_box(R, i, lo, hi); pb[i] = RtSahBox{{lo.x, lo.y, lo.z}, {hi.x, hi.y, hi.z}}; }
+        RtSahBuilder B;
+        int root = B.run(pb.data(), n, leaf_max, pad, 4);
+        E.prims.assign((size_t)3 * n, float4{}); E.pinfo.assign(n, float4{});
+        std::vector<float4> leaf_lo(n), leaf_hi(n);
+        for (int s = 0; s < n; ++s) rt_emit_slot(R, s, B.order[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
+        E.n_nodes = (int)(B.nodes.size() / 16);
+        E.nodes.assign(std::max<size_t>(4, B.nodes.size() / 4), float4{});
+        memcpy(E.nodes.data(), B.nodes.data(), B.nodes.size() * 4);
+        S.prims = E.prims.data(); S.pinfo = E.pinfo.data(); S.nodes = E.nodes.data(); S.root = root;
+        return;
+    }
     std::vector<uint64_t> keys(n); std::vector<int32_t> vals(n);
     for (int i = 0; i < n; ++i) { f3 lo, hi; rt_prim_box(R, i, lo, hi); keys[i] = rt_morton(lo, hi, bmin, inv_ext); vals[i] = i; }
     std::stable_sort(vals.begin(), vals.end(), [&](int a, int c) { return keys[a] < keys[c]; });   // radix sort is stable
@@ -149,15 +164,25 @@ int emu_scene_lights(void* e, const float* pi, int n, const float* amb) {
     Emu* E = (Emu*)e; E->host.lights.assign(pi, pi + 6 * (size_t)n);
     for (int k = 0; k < 3; ++k) E->host.ambient[k] = amb ? amb[k] : 0.f; return 0;
 }
-int emu_scene_commit(void* e, const float* aabb, int leaf_max, double pad_scale, double t_slack) {
+int emu_scene_commit(void* e, const float* aabb, int leaf_max, double pad_scale, double t_slack, int builder) {
     Emu* E = (Emu*)e;
     if (aabb) for (int k = 0; k < 6; ++k) E->host.aabb[k] = aabb[k]; else E->host.calc_aabb();
-    commit(*E, leaf_max, pad_scale, t_slack);
+    commit(*E, leaf_max, pad_scale, t_slack, builder);
     return 0;
 }
 void emu_get_aabb(void* e, float* out) { for (int k = 0; k < 6; ++k) out[k] = ((Emu*)e)->host.aabb[k]; }
 int emu_n_nodes(void* e) { return ((Emu*)e)->n_nodes; }
 int emu_max_stack(void* e) { return ((Emu*)e)->max_stack; }
+
+// rt_ray_tri exactly as the kernels call it (e1/e2 precomputed like rt_emit_slot does); tmax = the caller's cull distance
+int emu_ray_triangle(const float* o, const float* d, const float* v, float tmax, float* t) {
+    f3 v0 = mk3(v[0], v[1], v[2]);
+    f3 e1 = mk3(v[3] - v[0], v[4] - v[1], v[5] - v[2]), e2 = mk3(v[6] - v[0], v[7] - v[1], v[8] - v[2]);
+    float tt = 0.f;
+    bool hit = rt_ray_tri(mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2]), v0, e1, e2, tmax, tt);
+    *t = tt;
+    return hit ? 1 : 0;
+}
 
 int emu_intersect(void* e, const float* o, const float* d, int n, int32_t* out_id, float* out_t) {
     Emu* E = (Emu*)e; const RtScene& S = E->S;
@@ -165,7 +190,7 @@ int emu_intersect(void* e, const float* o, const float* d, int n, int32_t* out_i
     for (int i = 0; i < n; ++i) {
         f3 O = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
         float bt = FLT_MAX; int bs = -1;
-        if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
+        { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } }
         int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
         out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
     }
@@ -200,7 +225,7 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
             for (int t = 0; t < nt; ++t) for (int lane = 0; lane < 32; ++lane) {           // k_trace_primary
                 int x, y; bool valid = rt_item_to_pixel(V, tb + t, lane, x, y);
                 float bt = FLT_MAX; int bs = -1;
-                if (valid) { f3 O, D; rt_primary_ray(V, x, y, si, sj, O, D); if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); } }
+                if (valid) { f3 O, D; rt_primary_ray(V, x, y, si, sj, O, D); { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } } }
                 size_t q = (size_t)t * 32 + lane; hit0_t[q] = bt; hit0_slot[q] = valid ? bs : -2;
             }
             for (int d = 0; d <= maxd; ++d) {
@@ -210,7 +235,7 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
                 if (d > 0) for (unsigned q = 0; q < n; ++q) {                                  // k_trace_queue
                     f3 O = mk3(rin[2 * q].x, rin[2 * q].y, rin[2 * q].z), D = mk3(rin[2 * q + 1].x, rin[2 * q + 1].y, rin[2 * q + 1].z);
                     float bt = FLT_MAX; int bs = -1;
-                    if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
+                    { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } }
                     ht[q] = bt; hs[q] = bs;
                 }
                 const int n_chunks = (S.n_lights + 31) / 32;

@@ -36,10 +36,11 @@ def test_cfg2_mirror_recursion_order(emu, oracle, scenes):
     assert got["stats"]["rays_mirror"] == ref["stats"][2] > 0
 
 
-@pytest.mark.parametrize("leaf_max", [1, 4, 8])
-def test_bvh_equals_linear_scan(emu, oracle, scenes, leaf_max):
+@pytest.mark.parametrize("leaf_max,builder", [(1, 0), (4, 0), (8, 0), (1, 1), (4, 1), (8, 1)])
+def test_bvh_equals_linear_scan(emu, oracle, scenes, leaf_max, builder):
+    """device-LBVH logic (builder 0) and the host binned-SAH builder (builder 1, rt_sah.h) vs the reference's scan"""
     s, p = scenes.random_soup(seed=7), scenes.soup_params(64, 48, 3, 1)
-    e = emu.EmuTracer(leaf_max=leaf_max); e.set_scene(s)
+    e = emu.EmuTracer(leaf_max=leaf_max, builder=builder); e.set_scene(s)
     ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
     _strict(compare_renders(ref, e.render(p)))
     assert e.max_stack() < 64
@@ -71,8 +72,8 @@ def test_duplicate_primitives_tie_break(emu, scenes):
     for _ in range(9):
         s.add_triangle(tri, n, scenes.material())
     s.add_sphere((0, 0, 6), 1.0, scenes.material())          # front pole also at t = 5: sphere (class 1) beats loose tris (class 2)
-    for leaf_max in (1, 4):
-        e = emu.EmuTracer(leaf_max=leaf_max); e.set_scene(s)
+    for leaf_max, builder in ((1, 0), (4, 0), (1, 1), (4, 1)):
+        e = emu.EmuTracer(leaf_max=leaf_max, builder=builder); e.set_scene(s)
         ids, t = e.intersect([(0, 0, 0)], [(0, 0, 1)])
         assert t[0] == np.float32(5.0) and ids[0, :2].tolist() == [1, 0]
     s.spheres = s.spheres[:0]; s.sphere_mats = s.sphere_mats[:0]
@@ -142,8 +143,45 @@ def test_empty_and_degenerate(emu, scenes):
     assert (got["rgba8"][40] == np.array([100, 50, 25, 255], np.uint8)).all()
 
 
-def test_cfg3_reduced(emu, oracle, scenes):
+@pytest.mark.parametrize("builder", [0, 1])
+def test_cfg3_reduced(emu, oracle, scenes, builder):
     s, p = scenes.cfg3_scene(n=24), scenes.cfg3_params(160, 90)
-    e = emu.EmuTracer(); e.set_scene(s)
+    e = emu.EmuTracer(builder=builder); e.set_scene(s)
     ora = oracle.OracleScene(s)
     _strict(compare_renders(ora.render(p, oracle.ACCELERATED), e.render(p)))
+
+
+def test_ray_tri_division_free_rejections_match_reference(emu, oracle):
+    """rt_ray_tri decides most rejections on undivided numerators; every outcome must equal RMath.cs:29-73 (the oracle),
+    including rays aimed exactly at edges/vertices (u, v, u+v on their thresholds), tiny and huge triangles, and NaN/inf."""
+    rng = np.random.default_rng(42)
+    n_checked = n_hit = 0
+    for it in range(6000):
+        scale = 10.0 ** rng.uniform(-2.5, 2.5)
+        v = (rng.normal(size=(3, 3)) * scale + rng.normal(size=3) * 20).astype(np.float32)
+        o = (rng.normal(size=3) * 30).astype(np.float32)
+        mode = it % 4
+        if mode == 0:                                      # random interior/exterior point
+            w = rng.dirichlet((1, 1, 1)) if rng.uniform() < 0.7 else rng.normal(size=3)
+        elif mode == 1:                                    # on an edge
+            w = np.array([rng.uniform(), 0.0, 0.0]); w[1] = 1 - w[0]; w = np.roll(w, it % 3)
+        elif mode == 2:                                    # on a vertex
+            w = np.roll(np.array([1.0, 0.0, 0.0]), it % 3)
+        else:                                              # just outside / inside an edge
+            w = np.array([rng.uniform(), 0.0, 0.0]); w[1] = 1 - w[0] + rng.normal() * 1e-6; w = np.roll(w, it % 3)
+        target = (w[:, None] * v.astype(np.float64)).sum(0) / max(w.sum(), 1e-9) if abs(w.sum()) > 1e-6 else v[0]
+        d = target - o
+        d = (d / np.linalg.norm(d)).astype(np.float32)
+        if it % 7 == 0:
+            d = -d
+        rh, rt_ = oracle.ray_triangle(o, d, v.reshape(9))
+        gh, gt = emu.ray_triangle(o, d, v.reshape(9))
+        assert rh == gh and (not rh or rt_ == gt), (it, rh, gh, rt_, gt)
+        n_checked += 1; n_hit += rh
+        if rh:                                             # tmax rule: a cull distance beyond the hit never rejects it ...
+            gh2, gt2 = emu.ray_triangle(o, d, v.reshape(9), float(rt_) * 1.000125)
+            assert gh2 and gt2 == rt_
+    assert n_hit > 1000
+    for bad in (np.nan, np.inf):
+        v = np.array((0, 0, 5, 1, 0, 5, 0, 1, 5), np.float32); v[4] = bad
+        assert emu.ray_triangle((0.2, 0.2, 0), (0, 0, 1), v)[0] == oracle.ray_triangle((0.2, 0.2, 0), (0, 0, 1), v)[0]

@@ -430,6 +430,7 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "t_slack") { if (value < 1) return fail(c, RT_E_INVALID, "t_slack < 1"); c->opt.t_slack = value; }
     else if (k == "ctas_per_sm") { c->opt.ctas_per_sm = (int)value; }
     else if (k == "block") { c->opt.block = (int)value; }
+    else if (k == "builder") { if (value != 0 && value != 1) return fail(c, RT_E_INVALID, "builder must be 0 (device LBVH) or 1 (host SAH)"); c->opt.builder = (int)value; }
     else if (k == "kernel_timing") { c->opt.kernel_timing = value != 0; }
     else if (k == "packet") { c->opt.packet = value != 0; for (auto& D : c->devs) D.S.packet = c->opt.packet; }
     else return fail(c, RT_E_INVALID, "unknown option: " + k);

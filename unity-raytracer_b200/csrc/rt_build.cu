@@ -4,6 +4,7 @@
 //   leaf collapse + live-node compaction -> 64-byte BVH2 nodes with padded child boxes.
 // Per-element logic lives in rt_build_steps.h (host/device) so tests can run it on the CPU.
 #include "rt_internal.h"
+#include "rt_sah.h"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -150,6 +151,46 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     if (n > 0) {
         RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_base.as<int32_t>(), n_me, n_mt, n_sp, n_lo};
         const int leaf_max = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 8 ? 8 : opt.leaf_max);
+        if (opt.builder == 1) {
+            // ---- host binned-SAH build (rt_sah.h); the device only re-lays the primitives out in leaf order ----
+            std::vector<RtSahBox> pb((size_t)n);
+            float amax = 0.f;
+            for (int32_t key = 0; key < n; ++key) {
+                RtSahBox& x = pb[key];
+                if (key >= n_mt && key < n_mt + n_sp) {
+                    const float* sp = H.spheres.data() + 4 * (size_t)(key - n_mt);
+                    const float r = sqrtf(sp[3]);
+                    for (int k = 0; k < 3; ++k) { x.lo[k] = sp[k] - r; x.hi[k] = sp[k] + r; }
+                } else {
+                    const float* v = key < n_mt ? H.mesh_v.data() + 9 * (size_t)key : H.loose_v.data() + 9 * (size_t)(key - n_mt - n_sp);
+                    for (int k = 0; k < 3; ++k) { x.lo[k] = fminf(v[k], fminf(v[3 + k], v[6 + k])); x.hi[k] = fmaxf(v[k], fmaxf(v[3 + k], v[6 + k])); }
+                }
+                for (int k = 0; k < 3; ++k) {
+                    if (std::isfinite(x.lo[k])) amax = fmaxf(amax, fabsf(x.lo[k]));
+                    if (std::isfinite(x.hi[k])) amax = fmaxf(amax, fabsf(x.hi[k]));
+                }
+            }
+            const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
+            RtSahBuilder B;
+            int threads = (int)std::thread::hardware_concurrency();
+            const int32_t root = B.run(pb.data(), n, leaf_max, pad, threads < 1 ? 1 : threads);
+            RT_CUDA(D.vals_alt.ensure((size_t)n * 4));
+            RT_CUDA(cudaMemcpyAsync(D.vals_alt.p, B.order.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+            D.n_nodes = (uint32_t)(B.nodes.size() / 16);
+            RT_CUDA(D.nodes.ensure(B.nodes.size() * 4 + 64));
+            if (!B.nodes.empty()) RT_CUDA(cudaMemcpyAsync(D.nodes.p, B.nodes.data(), B.nodes.size() * 4, cudaMemcpyHostToDevice, st));
+            RT_CUDA(D.prims.ensure((size_t)n * 48)); RT_CUDA(D.pinfo.ensure((size_t)n * 16));
+            RT_CUDA(D.leaf_lo.ensure((size_t)n * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)n * 16));
+            k_emit_slots<<<grid_for(n), BT, 0, st>>>(R, n, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
+            RT_CUDA(cudaGetLastError());
+            RT_CUDA(cudaStreamSynchronize(st));                   // B.order / B.nodes go out of scope
+            S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
+            S.root = root;
+            RT_CUDA(cudaEventRecord(D.ev1, st));
+            RT_CUDA(cudaEventSynchronize(D.ev1));
+            if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
+            return RT_OK;
+        }
         // bounds
         RT_CUDA(D.bounds.ensure(6 * 4));
         uint32_t binit[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};

@@ -58,36 +58,61 @@ struct RtView {
 // ---------------------------------------------------------------------------------------------------------------
 // Exact primitive tests (bit-for-bit the reference's arithmetic)
 // ---------------------------------------------------------------------------------------------------------------
-// RMath.RayAABBIntersection, Math/RMath.cs:12-26
-RT_HD bool rt_ray_aabb_exact(f3 O, f3 D, f3 mn, f3 mx) {
-    float ix = rt_div(1.0f, D.x), iy = rt_div(1.0f, D.y), iz = rt_div(1.0f, D.z);     // rcp(ray.Direction)
+// RMath.RayAABBIntersection, Math/RMath.cs:12-26.  inv = rcp(ray.Direction) (RMath.cs:14) is computed once per ray
+// (rt_rcp3) and shared by the scene gate, the mesh gates and the traversal.
+RT_HD f3 rt_rcp3(f3 D) { return mk3(rt_div(1.0f, D.x), rt_div(1.0f, D.y), rt_div(1.0f, D.z)); }
+RT_HD bool rt_ray_aabb_inv(f3 O, f3 inv, f3 mn, f3 mx) {
     float tmin = 0.0f, tmax = INFINITY;
-    float t1 = (mn.x - O.x) * ix, t2 = (mx.x - O.x) * ix;
+    float t1 = (mn.x - O.x) * inv.x, t2 = (mx.x - O.x) * inv.x;
     tmin = um_min(um_max(t1, tmin), um_max(t2, tmin));
     tmax = um_max(um_min(t1, tmax), um_min(t2, tmax));
-    t1 = (mn.y - O.y) * iy; t2 = (mx.y - O.y) * iy;
+    t1 = (mn.y - O.y) * inv.y; t2 = (mx.y - O.y) * inv.y;
     tmin = um_min(um_max(t1, tmin), um_max(t2, tmin));
     tmax = um_max(um_min(t1, tmax), um_min(t2, tmax));
-    t1 = (mn.z - O.z) * iz; t2 = (mx.z - O.z) * iz;
+    t1 = (mn.z - O.z) * inv.z; t2 = (mx.z - O.z) * inv.z;
     tmin = um_min(um_max(t1, tmin), um_max(t2, tmin));
     tmax = um_max(um_min(t1, tmax), um_min(t2, tmax));
     return tmin <= tmax;
 }
+RT_HD bool rt_ray_aabb_exact(f3 O, f3 D, f3 mn, f3 mx) { return rt_ray_aabb_inv(O, rt_rcp3(D), mn, mx); }
 
 // RMath.RayTriangleIntersection, Math/RMath.cs:29-73. e1/e2 are the single subtractions v1-v0, v2-v0 (RMath.cs:34-35)
 // precomputed at upload, which is bit-identical to computing them per call.
-RT_HD bool rt_ray_tri(f3 O, f3 D, f3 v0, f3 e1, f3 e2, float& t_out) {
+//
+// The reference divides first (f = 1/a) and then rejects on u, v, t.  An IEEE division costs ~12 instructions, and almost
+// every tested triangle is rejected, so the rejections are decided on the *undivided* numerators wherever the outcome of
+// the reference's own comparison is certain; only candidates that survive are divided and re-tested with the reference's
+// exact expressions.  With f = fl(1/a) and x = fl(f*n) the relative error of x against n/a is < 2^-22, hence:
+//   sign(n) != sign(a), n/a not tiny     =>  x < 0 for sure           (u < 0, v < 0;  for t: x <= 0, never > eps)
+//   |n| > |a| * (1 + 2^-19)              =>  x > 1 for sure           (u > 1, u + v > 1)
+//   |n_t| > |a| * tmax                   =>  t > tmax / (1 + 2^-22): the caller's tmax carries a 1.25e-4 slack, so such a
+//                                            hit can neither beat the current best nor satisfy the any-hit predicate
+// tmax = INFINITY disables the last rule.  Returns exactly what the reference returns for every hit with t <= ~tmax.
+RT_HD bool rt_ray_tri(f3 O, f3 D, f3 v0, f3 e1, f3 e2, float tmax, float& t_out) {
     f3 h = um_cross(D, e2);
     float a = um_dot(e1, h);
     if (a > -RT_EPS && a < RT_EPS) return false;
-    float f = rt_div(1.0f, a);
+    const float aa = fabsf(a);
+    const bool aneg = a < 0.0f;
+    const bool sane = aa < 1e10f;                           // n/a cannot underflow to -0 when |n| > 1e-20
     f3 s = O - v0;
-    float u = f * um_dot(s, h);
-    if (u < 0.0f || u > 1.0f) return false;
+    float nu = um_dot(s, h);
+    const float a1 = aa * 1.000002f;
+    if (fabsf(nu) > a1) return false;                       // u > 1 or u < -1
+    if ((nu < 0.0f) != aneg && fabsf(nu) > 1e-20f && sane) return false;          // u < 0
     f3 q = um_cross(s, e1);
-    float v = f * um_dot(D, q);
+    float nv = um_dot(D, q);
+    if ((nv < 0.0f) != aneg && fabsf(nv) > 1e-20f && sane) return false;          // v < 0
+    if (fabsf(nu) + fabsf(nv) > a1 && (nu < 0.0f) == aneg && (nv < 0.0f) == aneg) return false;   // u + v > 1
+    float nt = um_dot(e2, q);
+    if ((nt < 0.0f) != aneg || nt == 0.0f) return false;    // t <= 0 (or -0): fails t > eps
+    if (fabsf(nt) > aa * tmax) return false;                // t beyond the caller's (slackened) cull distance
+    float f = rt_div(1.0f, a);
+    float u = f * nu;
+    if (u < 0.0f || u > 1.0f) return false;
+    float v = f * nv;
     if (v < 0.0f || u + v > 1.0f) return false;
-    float t = f * um_dot(e2, q);
+    float t = f * nt;
     if (t > RT_EPS) { t_out = t; return true; }
     return false;
 }
@@ -116,17 +141,16 @@ RT_HD bool rt_ray_sphere(f3 O, f3 D, f3 c, float r2, float& t_out) {
 // accepted.  The scene AABB gate (Scene.cs:54) is applied by the callers via rt_scene_gate().
 // STK: push(int), pop() -> int, empty().
 // ---------------------------------------------------------------------------------------------------------------
-RT_HD bool rt_scene_gate(const RtScene& S, f3 O, f3 D) { return rt_ray_aabb_exact(O, D, S.aabb_min, S.aabb_max); }
+RT_HD bool rt_scene_gate(const RtScene& S, f3 O, f3 inv) { return rt_ray_aabb_inv(O, inv, S.aabb_min, S.aabb_max); }
+// traversal's own (conservative) inverse direction: the exact one, with zero components replaced by a huge finite value
+RT_HD float rt_safe_inv(float d, float inv) { return fabsf(d) > 1e-30f ? inv : copysignf(1e30f, d); }
 
 template <bool ANY, class STK>
-RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, float any_d2, STK& stk, float& best_t, int32_t& best_slot) {
+RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& stk, float& best_t, int32_t& best_slot) {
     best_t = FLT_MAX; best_slot = -1;
     stk.sp = 0;                       // an any-hit query returns early and leaves entries behind
     if (S.n_prims <= 0) return false;
-    const float tiny = 1e-30f;
-    float idx_ = rt_div(1.0f, fabsf(D.x) > tiny ? D.x : copysignf(tiny, D.x));
-    float idy_ = rt_div(1.0f, fabsf(D.y) > tiny ? D.y : copysignf(tiny, D.y));
-    float idz_ = rt_div(1.0f, fabsf(D.z) > tiny ? D.z : copysignf(tiny, D.z));
+    float idx_ = rt_safe_inv(D.x, inv.x), idy_ = rt_safe_inv(D.y, inv.y), idz_ = rt_safe_inv(D.z, inv.z);
     float oodx = O.x * idx_, oody = O.y * idy_, oodz = O.z * idz_;
     uint32_t best_key = 0xffffffffu;
     float tcull = ANY ? rt_sqrt(any_d2) * S.t_slack : INFINITY;
@@ -169,7 +193,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, float any_d2, STK& stk, flo
                 float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
                 float t; bool hit;
                 if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
-                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), t);
+                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);
                 if (!hit) continue;
                 uint32_t key = (uint32_t)f2i(p0.w);
                 bool better = ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key));
@@ -179,7 +203,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, float any_d2, STK& stk, flo
                     if (mesh != gate_mesh) {
                         gate_mesh = mesh;
                         float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
-                        gate_ok = rt_ray_aabb_exact(O, D, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
+                        gate_ok = rt_ray_aabb_inv(O, inv, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
                     }
                     if (!gate_ok) continue;
                 }
@@ -291,9 +315,10 @@ RT_HD uint32_t rt_shadow_mask(const RtScene& S, f3 O, f3 D, float t, int32_t slo
         f3 Ldir; float d2;
         rt_light_ray(S, P, light_begin + i, Ldir, d2);
         ++n_shadow;
-        if (rt_scene_gate(S, sO, Ldir)) {                                    // Scene.cs:54 inside the shadow query
+        f3 inv = rt_rcp3(Ldir);
+        if (rt_scene_gate(S, sO, inv)) {                                     // Scene.cs:54 inside the shadow query
             float st; int32_t ss;
-            if (rt_traverse<true>(S, sO, Ldir, d2, stk, st, ss)) mask |= 1u << i;
+            if (rt_traverse<true>(S, sO, Ldir, inv, d2, stk, st, ss)) mask |= 1u << i;
         }
     }
     return mask;

@@ -31,6 +31,7 @@ struct RtOptions {
     int block = 128;
     int ctas_per_sm = 0;               // 0 = occupancy query
     int packet = 1;                    // warp-coherent packet traversal for coherent warps
+    int builder = 0;                   // 0 = device LBVH (fast commit), 1 = host binned-SAH (rt_sah.h; slower commit, fewer node visits)
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };
 

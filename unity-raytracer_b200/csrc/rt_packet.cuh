@@ -33,16 +33,13 @@ __device__ __forceinline__ bool rt_warp_coherent(f3 O, f3 D, bool active, float 
 }
 
 template <bool ANY, class STK>
-__device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D, bool active, float any_d2, STK& stk,
+__device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D, f3 inv, bool active, float any_d2, STK& stk,
                                                    float& best_t, int32_t& best_slot) {
     const unsigned full = 0xffffffffu;
     best_t = FLT_MAX; best_slot = -1;
     stk.sp = 0;
     if (S.n_prims <= 0) return false;
-    const float tiny = 1e-30f;
-    float idx_ = rt_div(1.0f, fabsf(D.x) > tiny ? D.x : copysignf(tiny, D.x));
-    float idy_ = rt_div(1.0f, fabsf(D.y) > tiny ? D.y : copysignf(tiny, D.y));
-    float idz_ = rt_div(1.0f, fabsf(D.z) > tiny ? D.z : copysignf(tiny, D.z));
+    float idx_ = rt_safe_inv(D.x, inv.x), idy_ = rt_safe_inv(D.y, inv.y), idz_ = rt_safe_inv(D.z, inv.z);
     float oodx = O.x * idx_, oody = O.y * idy_, oodz = O.z * idz_;
     uint32_t best_key = 0xffffffffu;
     float tcull = ANY ? rt_sqrt(any_d2) * S.t_slack : INFINITY;
@@ -90,7 +87,7 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                 if (tcull < 0.0f) continue;                             // lane has no ray / is already occluded
                 float t; bool hit;
                 if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
-                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), t);
+                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);
                 if (!hit) continue;
                 uint32_t key = (uint32_t)f2i(p0.w);
                 bool better = ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key));
@@ -100,7 +97,7 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                     if (mesh != gate_mesh) {
                         gate_mesh = mesh;
                         float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
-                        gate_ok = rt_ray_aabb_exact(O, D, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
+                        gate_ok = rt_ray_aabb_inv(O, inv, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
                     }
                     if (!gate_ok) continue;
                 }

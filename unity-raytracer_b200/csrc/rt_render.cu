@@ -18,10 +18,11 @@ namespace {
 constexpr int STK_CAP = 24;      // shared-memory stack entries per thread
 constexpr int STK_OVF = 104;     // local-memory overflow entries (LBVH depth bound: 64 key bits + 32 index bits)
 
+// sp lives in a register; the (rarely used) overflow array is a separate local object so that indexing it dynamically
+// does not drag the whole stack object into local memory (ncu on the first version: one STL per push/pop for sp).
 struct SmemStack {
-    int* base; int stride; int sp;
-    int ovf[STK_OVF];
-    __device__ __forceinline__ SmemStack(int* b, int s) : base(b), stride(s), sp(0) {}
+    int* base; int stride; int sp; int* ovf;
+    __device__ __forceinline__ SmemStack(int* b, int s, int* o) : base(b), stride(s), sp(0), ovf(o) {}
     __device__ __forceinline__ void push(int v) {
         if (sp < STK_CAP) base[sp * stride] = v;
         else if (sp - STK_CAP < STK_OVF) ovf[sp - STK_CAP] = v;
@@ -30,6 +31,7 @@ struct SmemStack {
     __device__ __forceinline__ int pop() { --sp; return sp < STK_CAP ? base[sp * stride] : ovf[sp - STK_CAP < STK_OVF ? sp - STK_CAP : STK_OVF - 1]; }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
 };
+#define RT_DECL_STACK(name) int name##_ovf[STK_OVF]; SmemStack name(g_smem_stack + threadIdx.x, blockDim.x, name##_ovf)
 
 extern __shared__ int g_smem_stack[];
 
@@ -46,7 +48,7 @@ constexpr int C_TOTAL = C_WORK + 8 * (RT_MAX_DEPTH + 2);
 
 __global__ void __launch_bounds__(128) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                         float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work) {
-    SmemStack stk(g_smem_stack + threadIdx.x, blockDim.x);
+    RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
     for (;;) {
         int t = warp_fetch(work, lane);
@@ -56,10 +58,12 @@ __global__ void __launch_bounds__(128) k_trace_primary(RtScene S, RtView V, int 
         float bt = FLT_MAX; int bs = -1;
         f3 O = V.pos, D = V.fwd;
         bool active = false;
-        if (valid) { rt_primary_ray(V, x, y, si, sj, O, D); active = rt_scene_gate(S, O, D); }     // Scene.cs:54
+        if (valid) rt_primary_ray(V, x, y, si, sj, O, D);
+        const f3 inv = rt_rcp3(D);
+        if (valid) active = rt_scene_gate(S, O, inv);                                               // Scene.cs:54
         if (S.packet) {                   // rays of one 8x4 pixel tile share the origin and are almost parallel
-            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, active, 0.f, stk, bt, bs);
-        } else if (active) rt_traverse<false>(S, O, D, 0.f, stk, bt, bs);
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
+        } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
         size_t q = (size_t)t * 32 + lane;
         hit_t[q] = bt; hit_slot[q] = valid ? bs : -2;
     }
@@ -67,7 +71,7 @@ __global__ void __launch_bounds__(128) k_trace_primary(RtScene S, RtView V, int 
 
 __global__ void __launch_bounds__(128) k_trace_queue(RtScene S, const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays,
                                                       float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work) {
-    SmemStack stk(g_smem_stack + threadIdx.x, blockDim.x);
+    RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
     const unsigned n = *n_ptr;
     for (;;) {
@@ -78,12 +82,13 @@ __global__ void __launch_bounds__(128) k_trace_queue(RtScene S, const unsigned* 
         if (q < n) {
             float4 ro = rays[2 * (size_t)q], rd = rays[2 * (size_t)q + 1];
             O = mk3(ro.x, ro.y, ro.z); D = mk3(rd.x, rd.y, rd.z);
-            active = rt_scene_gate(S, O, D);
         }
+        const f3 inv = rt_rcp3(D);
+        if (q < n) active = rt_scene_gate(S, O, inv);
         float bt = FLT_MAX; int bs = -1;
         if (S.packet && rt_warp_coherent(O, D, active, S.coherent_spread2)) {
-            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, active, 0.f, stk, bt, bs);
-        } else if (active) rt_traverse<false>(S, O, D, 0.f, stk, bt, bs);
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
+        } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
         if (q < n) { hit_t[q] = bt; hit_slot[q] = bs; }
     }
 }
@@ -106,7 +111,7 @@ __global__ void __launch_bounds__(128) k_trace_shadow(RtScene S, RtView V, int t
                                                        const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
                                                        int light_begin, int n_l, uint32_t* __restrict__ occl, unsigned* work,
                                                        unsigned long long* stats) {
-    SmemStack stk(g_smem_stack + threadIdx.x, blockDim.x);
+    RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
     const unsigned full = 0xffffffffu;
     const unsigned n = DEPTH0 ? (unsigned)n_tiles * 32u : *n_ptr;
@@ -128,12 +133,14 @@ __global__ void __launch_bounds__(128) k_trace_shadow(RtScene S, RtView V, int t
         for (int i = 0; i < n_l; ++i) {
             f3 Ldir = mk3(0.f, 0.f, 1.f); float d2 = 0.f;
             bool act = false;
-            if (has) { rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow; act = rt_scene_gate(S, sO, Ldir); }   // Scene.cs:54
+            if (has) { rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow; }
+            const f3 inv = rt_rcp3(Ldir);
+            if (has) act = rt_scene_gate(S, sO, inv);                                              // Scene.cs:54
             bool occluded = false;
             float st; int ss;
             if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
-                if (__any_sync(full, act)) occluded = rt_traverse_packet<true>(S, sO, Ldir, act, d2, stk, st, ss);
-            } else if (act) occluded = rt_traverse<true>(S, sO, Ldir, d2, stk, st, ss);
+                if (__any_sync(full, act)) occluded = rt_traverse_packet<true>(S, sO, Ldir, inv, act, d2, stk, st, ss);
+            } else if (act) occluded = rt_traverse<true>(S, sO, Ldir, inv, d2, stk, st, ss);
             if (occluded) mask |= 1u << i;
         }
         if (q < n) occl[q] = mask;
@@ -194,11 +201,12 @@ __global__ void k_finalize(RtScene S, RtView V, int tile_begin, int n_tiles, int
 
 __global__ void __launch_bounds__(128) k_intersect(RtScene S, int n, const float* __restrict__ o, const float* __restrict__ d,
                                                     int32_t* __restrict__ out_id, float* __restrict__ out_t) {
-    SmemStack stk(g_smem_stack + threadIdx.x, blockDim.x);
+    RT_DECL_STACK(stk);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         f3 O = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
         float bt = FLT_MAX; int bs = -1;
-        if (rt_scene_gate(S, O, D)) { stk.sp = 0; rt_traverse<false>(S, O, D, 0.f, stk, bt, bs); }
+        const f3 inv = rt_rcp3(D);
+        if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); }
         int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
         out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
     }

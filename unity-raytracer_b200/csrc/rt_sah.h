@@ -1,0 +1,134 @@
+// rt_sah.h — host-side binned-SAH BVH2 builder (option "builder" = 1), the north star's alternative to the device
+// LBVH: "the host-built BVH is re-laid out as a compact node array".  The reference's own builder
+// (Data/Collision/BVH.cs:13-79) is a longest-axis midpoint split that stops at `throw new NotImplementedException()`
+// (BVH.cs:77-79) and is never called; this finishes the idea with a surface-area heuristic and emits the device node
+// format directly (rt_core.h RtScene::nodes: 64-byte nodes holding both child boxes, padded like the LBVH's).
+//
+// Host only, C++17, std::thread task parallelism over subtrees.  Output:
+//   order[s]  = scan key of the primitive in leaf slot s (uploaded; k_emit_slots builds the slot records from it)
+//   nodes     = 16 floats per node; node 0 is the root (unless the whole scene is one leaf)
+// Result equivalence with the reference's scan does not depend on the tree at all (rt_core.h), only on the boxes being
+// conservative, which the padding guarantees exactly as for the LBVH.
+#pragma once
+#include <vector>
+#include <thread>
+#include <future>
+#include <atomic>
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <cfloat>
+#include <cmath>
+
+struct RtSahBox { float lo[3], hi[3]; };
+
+struct RtSahBuilder {
+    const RtSahBox* boxes = nullptr;          // per scan key
+    int32_t n = 0, leaf_max = 4;
+    float pad = 0.f;
+    std::vector<int32_t> order;               // leaf-slot order of scan keys
+    std::vector<float> nodes;                 // 16 floats per node
+    std::atomic<int32_t> n_nodes{0};
+    int spawn_depth = 0;
+    static constexpr int NB = 16;             // bins per axis
+
+    static inline float area(const float* lo, const float* hi) {
+        float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        return (dx < 0.f || dy < 0.f || dz < 0.f) ? 0.f : dx * dy + dy * dz + dz * dx;
+    }
+    static inline void grow(float* lo, float* hi, const float* blo, const float* bhi) {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::fmin(lo[k], blo[k]); hi[k] = std::fmax(hi[k], bhi[k]); }
+    }
+    static inline void reset(float* lo, float* hi) { for (int k = 0; k < 3; ++k) { lo[k] = FLT_MAX; hi[k] = -FLT_MAX; } }
+
+    // Builds the subtree over order[b, e); returns its traversal ref (>= 0 node index, < 0 leaf) and its (unpadded) box.
+    int32_t build(int32_t b, int32_t e, int depth, float* out_lo, float* out_hi) {
+        const int32_t cnt = e - b;
+        float lo[3], hi[3], clo[3], chi[3];
+        reset(lo, hi); reset(clo, chi);
+        for (int32_t i = b; i < e; ++i) {
+            const RtSahBox& x = boxes[order[i]];
+            grow(lo, hi, x.lo, x.hi);
+            for (int k = 0; k < 3; ++k) { float c = 0.5f * (x.lo[k] + x.hi[k]); clo[k] = std::fmin(clo[k], c); chi[k] = std::fmax(chi[k], c); }
+        }
+        for (int k = 0; k < 3; ++k) { out_lo[k] = lo[k]; out_hi[k] = hi[k]; }
+        if (cnt <= leaf_max) return ~(b * 8 + (cnt - 1));
+        // ---- binned SAH over the three axes ----
+        int best_axis = -1, best_bin = -1; float best_cost = FLT_MAX;
+        for (int ax = 0; ax < 3; ++ax) {
+            const float ext = chi[ax] - clo[ax];
+            if (!(ext > 0.f) || !std::isfinite(ext)) continue;
+            const float scale = (float)NB / ext;
+            int32_t bc[NB]; float blo[NB][3], bhi[NB][3];
+            for (int j = 0; j < NB; ++j) { bc[j] = 0; reset(blo[j], bhi[j]); }
+            for (int32_t i = b; i < e; ++i) {
+                const RtSahBox& x = boxes[order[i]];
+                int j = (int)((0.5f * (x.lo[ax] + x.hi[ax]) - clo[ax]) * scale);
+                j = j < 0 ? 0 : (j >= NB ? NB - 1 : j);
+                ++bc[j]; grow(blo[j], bhi[j], x.lo, x.hi);
+            }
+            float ra[NB]; int32_t rc[NB];
+            float tlo[3], thi[3]; reset(tlo, thi); int32_t c = 0;
+            for (int j = NB - 1; j >= 1; --j) { if (bc[j]) grow(tlo, thi, blo[j], bhi[j]); c += bc[j]; ra[j] = area(tlo, thi); rc[j] = c; }
+            reset(tlo, thi); c = 0;
+            for (int j = 0; j < NB - 1; ++j) {
+                if (bc[j]) grow(tlo, thi, blo[j], bhi[j]);
+                c += bc[j];
+                if (c == 0 || rc[j + 1] == 0) continue;
+                float cost = area(tlo, thi) * (float)c + ra[j + 1] * (float)rc[j + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = j; }
+            }
+        }
+        int32_t mid;
+        if (best_axis < 0) {
+            mid = b + cnt / 2;                                   // all centroids coincide: split by count
+        } else {
+            const int ax = best_axis;
+            const float scale = (float)NB / (chi[ax] - clo[ax]);
+            const float c0 = clo[ax];
+            const int bb = best_bin;
+            auto it = std::partition(order.begin() + b, order.begin() + e, [&](int32_t k) {
+                const RtSahBox& x = boxes[k];
+                int j = (int)((0.5f * (x.lo[ax] + x.hi[ax]) - c0) * scale);
+                j = j < 0 ? 0 : (j >= NB ? NB - 1 : j);
+                return j <= bb;
+            });
+            mid = (int32_t)(it - order.begin());
+            if (mid == b || mid == e) mid = b + cnt / 2;
+        }
+        const int32_t me = n_nodes.fetch_add(1);
+        float llo[3], lhi[3], rlo[3], rhi[3];
+        int32_t rl, rr;
+        if (depth < spawn_depth && cnt > 8192) {
+            auto fut = std::async(std::launch::async, [&]() { return build(b, mid, depth + 1, llo, lhi); });
+            rr = build(mid, e, depth + 1, rlo, rhi);
+            rl = fut.get();
+        } else {
+            rl = build(b, mid, depth + 1, llo, lhi);
+            rr = build(mid, e, depth + 1, rlo, rhi);
+        }
+        float* np = nodes.data() + 16 * (size_t)me;              // layout: RtScene::nodes (rt_core.h)
+        np[0] = llo[0] - pad; np[1] = lhi[0] + pad; np[2] = llo[1] - pad; np[3] = lhi[1] + pad;
+        np[4] = rlo[0] - pad; np[5] = rhi[0] + pad; np[6] = rlo[1] - pad; np[7] = rhi[1] + pad;
+        np[8] = llo[2] - pad; np[9] = lhi[2] + pad; np[10] = rlo[2] - pad; np[11] = rhi[2] + pad;
+        std::memcpy(np + 12, &rl, 4); std::memcpy(np + 13, &rr, 4); np[14] = 0.f; np[15] = 0.f;
+        return me;
+    }
+
+    // returns the root ref; the root node (if any) is moved to index 0 because traversal starts at S.root
+    int32_t run(const RtSahBox* prim_boxes, int32_t n_prims, int32_t leaf_max_, float pad_, int threads) {
+        boxes = prim_boxes; n = n_prims; leaf_max = leaf_max_ < 1 ? 1 : (leaf_max_ > 8 ? 8 : leaf_max_); pad = pad_;
+        order.resize(n);
+        for (int32_t i = 0; i < n; ++i) order[i] = i;
+        nodes.assign((size_t)16 * (n > 1 ? n - 1 : 1), 0.f);
+        n_nodes = 0;
+        spawn_depth = 0;
+        for (int t = threads < 1 ? 1 : threads; t > 1; t >>= 1) ++spawn_depth;
+        spawn_depth += 1;                                        // a few more tasks than threads, for balance
+        if (n == 0) return -1;
+        float lo[3], hi[3];
+        int32_t root = build(0, n, 0, lo, hi);
+        nodes.resize((size_t)16 * n_nodes.load());
+        return root;                                             // the first fetch_add happened at the root: root == 0
+    }
+};
