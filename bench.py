@@ -161,6 +161,7 @@ def run_ours(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     scene, params, desc = workload(args.workload, rtb.scenes)
     rt = rtb.RayTracer((local_rank,))
+    rt.set_option("builder", 1 if args.builder == "sah" else 0)
     stream = torch.cuda.Stream()
     rt.set_stream(stream.cuda_stream)
     rt.set_partition(rank, world, 32)
@@ -271,7 +272,7 @@ def run_ours(args, rank, world, local_rank):
                            "partition": f"{world} rank(s), interleaved 32-row bands, scene replicated", "gather": gather, "output": "RGBA32F full frame on GPU 0"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
                 "commit": {"ms_upload": cstats["ms_commit_upload"], "ms_bvh_build": cstats["ms_commit_build"], "h2d_bytes": cstats["h2d_bytes"],
-                           "wall_ms": 1e3 * commit_wall, "n_prims": cstats["n_prims"], "n_nodes": cstats["n_nodes"]}}
+                           "wall_ms": 1e3 * commit_wall, "n_prims": cstats["n_prims"], "n_nodes": cstats["n_nodes"], "builder": args.builder}}
         print(json.dumps(line), flush=True)
     barrier()
     rt.close()
@@ -287,6 +288,8 @@ def main():
     ap.add_argument("--workload", default="cfg3")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--builder", default="sah", choices=["sah", "lbvh"],
+                    help="BVH builder at commit: host binned-SAH (default; static scene, best frame time) or device LBVH (fast commit)")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":

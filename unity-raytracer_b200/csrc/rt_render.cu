@@ -20,15 +20,23 @@ constexpr int STK_OVF = 104;     // local-memory overflow entries (LBVH depth bo
 
 // sp lives in a register; the (rarely used) overflow array is a separate local object so that indexing it dynamically
 // does not drag the whole stack object into local memory (ncu on the first version: one STL per push/pop for sp).
+// The shared-memory column is addressed through a precomputed 32-bit shared-window address with explicit st/ld.shared:
+// the generic-pointer form made the compiler rebuild the window base (S2R SR_CgaCtaId, LEA, 2 IMAD) on every push and pop.
 struct SmemStack {
-    int* base; int stride; int sp; int* ovf;
-    __device__ __forceinline__ SmemStack(int* b, int s, int* o) : base(b), stride(s), sp(0), ovf(o) {}
+    unsigned base; unsigned stride4; int sp; int* ovf;
+    __device__ __forceinline__ SmemStack(int* b, int s, int* o) : base((unsigned)__cvta_generic_to_shared(b)), stride4((unsigned)s * 4u), sp(0), ovf(o) {}
     __device__ __forceinline__ void push(int v) {
-        if (sp < STK_CAP) base[sp * stride] = v;
+        if (sp < STK_CAP) asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (unsigned)sp * stride4), "r"(v) : "memory");
         else if (sp - STK_CAP < STK_OVF) ovf[sp - STK_CAP] = v;
         ++sp;
     }
-    __device__ __forceinline__ int pop() { --sp; return sp < STK_CAP ? base[sp * stride] : ovf[sp - STK_CAP < STK_OVF ? sp - STK_CAP : STK_OVF - 1]; }
+    __device__ __forceinline__ int pop() {
+        --sp;
+        int v;
+        if (sp < STK_CAP) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + (unsigned)sp * stride4) : "memory");
+        else v = ovf[sp - STK_CAP < STK_OVF ? sp - STK_CAP : STK_OVF - 1];
+        return v;
+    }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
 };
 #define RT_DECL_STACK(name) int name##_ovf[STK_OVF]; SmemStack name(g_smem_stack + threadIdx.x, blockDim.x, name##_ovf)

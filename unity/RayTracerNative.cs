@@ -1,0 +1,111 @@
+// RayTracerNative.cs — managed side of the drop-in boundary (include/rtb200.h).  SOURCE ONLY: this image has no
+// .NET/Mono/Unity toolchain, so this file has never been compiled here; it is the [DllImport] binding a maintainer of
+// vectorized-runner/unity-raytracer adds under Assets/RayTracer/ next to RayTracingSetup.cs (see INTEGRATION.md).
+//
+// float3 is three packed floats, so Sphere (16 B), Triangle (36 B), PointLightData (24 B), AABB (24 B), CameraData (48 B)
+// and UnityEngine.Color (16 B) are blittable and are passed as pinned arrays without `unsafe` (RayTracer.asmdef forbids
+// it).  MaterialData holds a `bool` (MaterialData.cs:14) and is NOT blittable: NativeMaterial mirrors it with an int.
+using System;
+using System.Collections.Generic;
+using System.Runtime.InteropServices;
+using Unity.Mathematics;
+using UnityEngine;
+
+namespace RayTracer
+{
+	[StructLayout(LayoutKind.Sequential)]
+	public struct NativeMaterial                     // rt_material, 56 bytes
+	{
+		public float3 Diffuse, Ambient, Mirror, Specular;
+		public float PhongExponent;
+		public int IsMirror;
+
+		public NativeMaterial(MaterialData m)
+		{
+			Diffuse = m.DiffuseReflectance; Ambient = m.AmbientReflectance; Mirror = m.MirrorReflectance;
+			Specular = m.SpecularReflectance; PhongExponent = m.PhongExponent; IsMirror = m.IsMirror ? 1 : 0;
+		}
+	}
+
+	[StructLayout(LayoutKind.Sequential)]
+	public struct NativeRenderParams                 // rt_render_params, 88 bytes
+	{
+		public float3 Position, Forward, Right, Up;  // CameraData.cs:7-10
+		public int ResX, ResY;                       // Resolution.cs:8-9
+		public float DistanceToCamera, HalfHorizontalLength, HalfVerticalLength;   // ImagePlane.cs:13-21
+		public float3 BackgroundRgb;                 // RayTracingSetup.BackgroundColor (0..1)
+		public int MaxReflectionBounces;             // RayTracingSetup.cs:23
+		public int SppGrid;                          // 1 = reference behaviour
+	}
+
+	public static class RayTracerNative
+	{
+		const string Lib = "rtb200";                 // librtb200.so / rtb200.dll in Assets/Plugins/x86_64
+
+		[DllImport(Lib)] static extern int rt_create(out IntPtr ctx, int[] deviceIds, int nDevices);
+		[DllImport(Lib)] static extern void rt_destroy(IntPtr ctx);
+		[DllImport(Lib)] static extern IntPtr rt_last_error(IntPtr ctx);
+		[DllImport(Lib)] static extern int rt_scene_begin(IntPtr ctx);
+		[DllImport(Lib)] static extern int rt_scene_spheres(IntPtr ctx, Sphere[] centerR2, NativeMaterial[] materials, int n);
+		[DllImport(Lib)] static extern int rt_scene_triangles(IntPtr ctx, Triangle[] v, float3[] normals, NativeMaterial[] materials, int n);
+		[DllImport(Lib)] static extern int rt_scene_mesh(IntPtr ctx, Triangle[] v, float3[] normals, int nTris, ref NativeMaterial material, ref AABB aabb);
+		[DllImport(Lib)] static extern int rt_scene_lights(IntPtr ctx, PointLightData[] posIntensity, int n, ref float3 ambientRadiance);
+		[DllImport(Lib)] static extern int rt_scene_commit(IntPtr ctx, ref AABB sceneAabb);
+		[DllImport(Lib)] static extern int rt_render(IntPtr ctx, ref NativeRenderParams p, Color[] outRgba32f, IntPtr outRgba8,
+		                                             IntPtr outHitId, IntPtr outHitT, IntPtr stats);
+
+		static IntPtr ctx = IntPtr.Zero;
+
+		static void Check(int rc)
+		{
+			if (rc != 0) throw new InvalidOperationException("librtb200: " + Marshal.PtrToStringAnsi(rt_last_error(ctx)));
+		}
+
+		static NativeMaterial[] Convert(List<MaterialData> mats)
+		{
+			var r = new NativeMaterial[mats.Count];
+			for (int i = 0; i < r.Length; i++) r[i] = new NativeMaterial(mats[i]);
+			return r;
+		}
+
+		/// Replaces what UpdateScene() hands to the CPU path (RayTracingSetup.cs:120-128): call after Scene.CalculateAABB().
+		public static void UploadScene(ref Scene scene)
+		{
+			if (ctx == IntPtr.Zero) Check(rt_create(out ctx, new[] { 0 }, 1));
+			Check(rt_scene_begin(ctx));
+			Check(rt_scene_spheres(ctx, scene.SphereData.Spheres.ToArray(), Convert(scene.SphereData.Materials), scene.SphereData.Spheres.Count));
+			Check(rt_scene_triangles(ctx, scene.TriangleData.Triangles.ToArray(), scene.TriangleData.Normals.ToArray(),
+			                         Convert(scene.TriangleData.Materials), scene.TriangleData.Triangles.Count));
+			foreach (var mesh in scene.MeshData.Meshes)          // list order == ObjectId.MeshIndex (Scene.cs:64)
+			{
+				var mat = new NativeMaterial(mesh.MaterialData);
+				var box = mesh.AABB;
+				Check(rt_scene_mesh(ctx, mesh.Triangles, mesh.TriangleNormals, mesh.Triangles.Length, ref mat, ref box));
+			}
+			var ambient = scene.AmbientLight.Radiance;
+			Check(rt_scene_lights(ctx, scene.PointLights.ToArray(), scene.PointLights.Count, ref ambient));
+			var aabb = scene.AABB;                               // Scene.cs:15, computed by Scene.CalculateAABB()
+			Check(rt_scene_commit(ctx, ref aabb));
+		}
+
+		/// Replaces CastPixelRays(CameraData) (RayTracingSetup.cs:275-302): fills PixelColors (x + y * ResX, y = 0 top row).
+		public static void CastPixelRays(CameraData cam, ImagePlane plane, Color background, int maxBounces, Color[] pixelColors)
+		{
+			var p = new NativeRenderParams
+			{
+				Position = cam.Position, Forward = cam.Forward, Right = cam.Right, Up = cam.Up,
+				ResX = plane.Resolution.X, ResY = plane.Resolution.Y,
+				DistanceToCamera = plane.DistanceToCamera, HalfHorizontalLength = plane.HalfHorizontalLength,
+				HalfVerticalLength = plane.HalfVerticalLength,
+				BackgroundRgb = new float3(background.r, background.g, background.b),
+				MaxReflectionBounces = maxBounces, SppGrid = 1
+			};
+			Check(rt_render(ctx, ref p, pixelColors, IntPtr.Zero, IntPtr.Zero, IntPtr.Zero, IntPtr.Zero));
+		}
+
+		public static void Shutdown()
+		{
+			if (ctx != IntPtr.Zero) { rt_destroy(ctx); ctx = IntPtr.Zero; }
+		}
+	}
+}
