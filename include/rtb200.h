@@ -142,7 +142,9 @@ int rt_export_outputs(rt_ctx* ctx, void* handles_4x64);
 int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_y, int want);
 
 /* tuning knobs (all optional): key in {"chunk_pixels","leaf_max","pad_scale","t_slack","ctas_per_sm","kernel_timing","packet",
- * "builder"}; builder 0 = device LBVH (default, ~10 ms per million primitives), 1 = host binned-SAH BVH (slower commit,
+ * "builder","copy_waves","waves","lanes"}; waves = minimum number of waves rt_render_device cuts a pass into, lanes = 1|2
+ * streams the waves alternate over (2: the drain of one wave overlaps the start of the next); copy_waves = number of waves rt_render splits a frame into so the copy-out of one wave overlaps
+ * the kernels of the next (default 8, 1 = off); builder 0 = device LBVH (default, ~10 ms per million primitives), 1 = host binned-SAH BVH (slower commit,
  * fewer node visits per ray); takes effect at the next rt_scene_commit */
 int rt_set_option(rt_ctx* ctx, const char* key, double value);
 

@@ -222,3 +222,17 @@ def test_render_full_size_properties(rt, scenes):
     miss = a["hit_id"][:, 0] == 0
     assert (a["rgba8"][miss] == np.array([0, 0, 0, 255], np.uint8)).all()
     assert (a["hit_t"][miss] == np.finfo(np.float32).max).all()
+
+
+def test_pipelined_copy_out_equals_plain(rt, scenes):
+    """rt_render overlaps the copy-out of finished waves with the next waves' kernels (copy_waves): same bytes out."""
+    s, p = scenes.random_soup(seed=9), scenes.soup_params(333, 201, 2, 1)
+    rt.set_scene(s)
+    rt.set_option("copy_waves", 1)
+    a = rt.render(p)
+    for w in (2, 8, 64):
+        rt.set_option("copy_waves", w)
+        b = rt.render(p)
+        for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+            assert np.array_equal(a[k], b[k], equal_nan=True), (w, k)
+    rt.set_option("copy_waves", 8)

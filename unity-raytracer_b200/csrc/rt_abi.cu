@@ -28,17 +28,27 @@ void device_release(RtDevice& D) {
     cudaSetDevice(D.device);
     for (DevBuf* b : {&D.raw_v, &D.raw_n, &D.raw_s, &D.nodes, &D.prims, &D.pinfo, &D.mats, &D.mesh_aabb, &D.mesh_base, &D.lights, &D.keys,
                       &D.keys_alt, &D.vals, &D.vals_alt, &D.cub_tmp, &D.bounds, &D.topo_i32, &D.leaf_lo, &D.leaf_hi, &D.int_lo, &D.int_hi,
-                      &D.flags, &D.new_index, &D.hit0_t, &D.hit0_slot, &D.hitq_t, &D.hitq_slot, &D.rays[0], &D.rays[1], &D.counters, &D.accum,
-                      &D.stats, &D.occl, &D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t})
+                      &D.flags, &D.new_index, &D.accum, &D.stats, &D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t})
         b->release();
-    for (auto& b : D.local) b.release();
-    for (auto& b : D.link) b.release();
+    for (auto& L : D.lanes) {
+        for (DevBuf* b : {&L.hit0_t, &L.hit0_slot, &L.hitq_t, &L.hitq_slot, &L.rays[0], &L.rays[1], &L.counters, &L.occl}) b->release();
+        for (auto& b : L.local) b.release();
+        for (auto& b : L.link) b.release();
+        if (L.done) cudaEventDestroy(L.done);
+        if (L.own_stream) cudaStreamDestroy(L.own_stream);
+        L.done = nullptr; L.own_stream = nullptr;
+    }
+    for (cudaEvent_t e : D.fin_ev) cudaEventDestroy(e);
+    D.fin_ev.clear();
     void* imp[4] = {D.o_rgba32f, D.o_rgba8, D.o_hit_id, D.o_hit_t};
     for (int k = 0; k < 4; ++k) if (D.imported[k] && imp[k]) cudaIpcCloseMemHandle(imp[k]);
     for (cudaEvent_t e : D.kev_pool) cudaEventDestroy(e);
     D.kev_pool.clear();
     if (D.ev0) cudaEventDestroy(D.ev0);
     if (D.ev1) cudaEventDestroy(D.ev1);
+    for (cudaEvent_t e : D.wave_ev) cudaEventDestroy(e);
+    D.wave_ev.clear();
+    if (D.copy_stream) cudaStreamDestroy(D.copy_stream);
     if (D.own_stream) cudaStreamDestroy(D.own_stream);
     D.device = -1;
 }
@@ -117,7 +127,7 @@ int finish_stats(rt_ctx* c) {
     return RT_OK;
 }
 
-int render_device_impl(rt_ctx* c, const rt_render_params* p, int want) {
+int render_device_impl(rt_ctx* c, const rt_render_params* p, int want, int split = 0) {
     int rc = validate_params(c, p);
     if (rc) return rc;
     if (!c->committed) return fail(c, RT_E_STATE, "rt_render before rt_scene_commit");
@@ -130,7 +140,7 @@ int render_device_impl(rt_ctx* c, const rt_render_params* p, int want) {
     c->fstats.assign(c->devs.size(), RtFrameStats{});
     for (size_t i = 0; i < c->devs.size(); ++i) {
         RtView V = make_view(c, p, (int)i);
-        rc = rt_device_render(c->devs[i], V, want, c->opt, c->err, &c->fstats[i]);
+        rc = rt_device_render(c->devs[i], V, want, c->opt, c->err, &c->fstats[i], split ? split : c->opt.waves);
         if (rc) return rc;
     }
     c->stats_pending = true;
@@ -306,12 +316,46 @@ int rt_read_outputs(rt_ctx* c, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, 
     return RT_OK;
 }
 
+// rt_render with one device: the frame is rendered in `copy_waves` waves of whole pixel rows and the copy-out of wave k
+// (on a second stream, after the wave's event) overlaps the kernels of wave k+1.  The 4K Color[] frame is 132.7 MB, i.e.
+// ~2.4 ms over PCIe Gen5 — as long as the render itself — so without the overlap the call would take twice as long.
+static int read_outputs_pipelined(rt_ctx* c, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t) {
+    std::string& err = c->err;
+    RtDevice& D = c->devs[0];
+    RT_CUDA(cudaSetDevice(D.device));
+    if (!D.copy_stream) RT_CUDA(cudaStreamCreateWithFlags(&D.copy_stream, cudaStreamNonBlocking));
+    const size_t rx = (size_t)c->last_res_x;
+    char* dst[4] = {(char*)rgba32f, (char*)rgba8, (char*)hit_id, (char*)hit_t};
+    char* src[4] = {(char*)D.o_rgba32f, (char*)D.o_rgba8, (char*)D.o_hit_id, (char*)D.o_hit_t};
+    const size_t bpp[4] = {16, 4, 12, 4};
+    auto t0 = std::chrono::steady_clock::now();
+    uint64_t bytes = 0;
+    for (size_t w = 0; w < D.wave_marks.size(); ++w) {
+        RT_CUDA(cudaStreamWaitEvent(D.copy_stream, D.wave_ev[w], 0));
+        const size_t r0 = (size_t)D.wave_marks[w].row0, r1 = (size_t)D.wave_marks[w].row1;
+        for (int k = 0; k < 4; ++k) {
+            if (!dst[k] || r1 <= r0) continue;
+            const size_t off = r0 * rx * bpp[k], len = (r1 - r0) * rx * bpp[k];
+            RT_CUDA(cudaMemcpyAsync(dst[k] + off, src[k] + off, len, cudaMemcpyDeviceToHost, D.copy_stream));
+            bytes += len;
+        }
+    }
+    RT_CUDA(cudaStreamSynchronize(D.copy_stream));
+    RT_CUDA(cudaStreamSynchronize(D.stream));
+    c->stats.ms_d2h = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->stats.d2h_bytes = bytes;
+    return RT_OK;
+}
+
 int rt_render(rt_ctx* c, const rt_render_params* p, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t, rt_stats* stats) {
     if (!c) return RT_E_INVALID;
     int want = (rgba32f ? RT_OUT_RGBA32F : 0) | (rgba8 ? RT_OUT_RGBA8 : 0) | (hit_id ? RT_OUT_HIT_ID : 0) | (hit_t ? RT_OUT_HIT_T : 0);
-    int rc = render_device_impl(c, p, want);
+    const bool pipelined = want && c->devs.size() == 1 && c->ext_world == 1 && c->opt.copy_waves > 1 && p && p->res_y >= 64 &&
+                           !c->devs[0].imported[0] && !c->devs[0].imported[1] && !c->devs[0].imported[2] && !c->devs[0].imported[3];
+    int rc = render_device_impl(c, p, want, pipelined ? -c->opt.copy_waves : 0);
     if (rc) return rc;
-    rc = rt_read_outputs(c, rgba32f, rgba8, hit_id, hit_t);
+    if (pipelined && !c->devs[0].wave_marks.empty()) rc = read_outputs_pipelined(c, rgba32f, rgba8, hit_id, hit_t);
+    else rc = rt_read_outputs(c, rgba32f, rgba8, hit_id, hit_t);
     if (rc) return rc;
     if (stats) { rc = rt_get_stats(c, stats); if (rc) return rc; }
     return RT_OK;
@@ -430,6 +474,9 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "t_slack") { if (value < 1) return fail(c, RT_E_INVALID, "t_slack < 1"); c->opt.t_slack = value; }
     else if (k == "ctas_per_sm") { c->opt.ctas_per_sm = (int)value; }
     else if (k == "block") { c->opt.block = (int)value; }
+    else if (k == "waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "waves must be 1..64"); c->opt.waves = (int)value; }
+    else if (k == "lanes") { if (value != 1 && value != 2) return fail(c, RT_E_INVALID, "lanes must be 1 or 2"); c->opt.lanes = (int)value; }
+    else if (k == "copy_waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "copy_waves must be 1..64"); c->opt.copy_waves = (int)value; }
     else if (k == "builder") { if (value != 0 && value != 1) return fail(c, RT_E_INVALID, "builder must be 0 (device LBVH) or 1 (host SAH)"); c->opt.builder = (int)value; }
     else if (k == "kernel_timing") { c->opt.kernel_timing = value != 0; }
     else if (k == "packet") { c->opt.packet = value != 0; for (auto& D : c->devs) D.S.packet = c->opt.packet; }

@@ -32,6 +32,10 @@ struct RtOptions {
     int ctas_per_sm = 0;               // 0 = occupancy query
     int packet = 1;                    // warp-coherent packet traversal for coherent warps
     int builder = 0;                   // 0 = device LBVH (fast commit), 1 = host binned-SAH (rt_sah.h; slower commit, fewer node visits)
+    int waves = 2;                     // rt_render_device: minimum number of waves per pass (2 lanes: tails overlap)
+    int lanes = 2;                     // 1 = all waves on one stream; 2 = alternate waves over two streams (tail overlap)
+    int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
+                                       // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };
 
@@ -50,12 +54,19 @@ struct RtDevice {
     bool has_mirror = false;
     // ---- build scratch ----
     DevBuf keys, keys_alt, vals, vals_alt, cub_tmp, bounds, topo_i32, leaf_lo, leaf_hi, int_lo, int_hi, flags, new_index;
-    // ---- frame work buffers (sized to the wave capacity W) ----
-    size_t wave_cap = 0;
-    DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, accum, stats, occl;
-    std::vector<DevBuf> local;          // [depth] float4 per entry
-    std::vector<DevBuf> link;           // [depth>=1] float4 (km.xyz, parent index bits)
-    size_t accum_items = 0;
+    // ---- frame work buffers (sized to the wave capacity W), one set per lane ----
+    // A frame is cut into waves; consecutive waves alternate between two lanes (stream + buffer set) so that the drain
+    // of one wave's persistent kernels is filled by the next wave's kernels instead of idling the SMs.
+    struct Lane {
+        cudaStream_t own_stream = nullptr;   // lane 0 runs on D.stream, the others on their own stream
+        cudaEvent_t done = nullptr;
+        DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, occl;
+        std::vector<DevBuf> local;          // [depth] float4 per entry
+        std::vector<DevBuf> link;           // [depth>=1] float4 (km.xyz, parent index bits)
+    };
+    Lane lanes[2];
+    DevBuf accum, stats;
+    std::vector<cudaEvent_t> fin_ev;        // spp passes: finalize of (pass p, wave i) follows finalize of (pass p-1, wave i)
     // ---- outputs: full-frame buffers. Owned on the gather device; other devices/ranks hold peer pointers ----
     DevBuf own_rgba32f, own_rgba8, own_hit_id, own_hit_t;
     void* o_rgba32f = nullptr; void* o_rgba8 = nullptr; void* o_hit_id = nullptr; void* o_hit_t = nullptr;
@@ -66,6 +77,11 @@ struct RtDevice {
     // per-launch timing events (option kernel_timing): (kernel class, begin, end)
     std::vector<cudaEvent_t> kev_pool;
     std::vector<int> kev_class;        // class of launch i; its events are kev_pool[2i], kev_pool[2i+1]
+    // pipelined copy-out (rt_render with host buffers): one event per finished wave + the pixel rows it completed
+    cudaStream_t copy_stream = nullptr;
+    std::vector<cudaEvent_t> wave_ev;
+    struct WaveMark { int row0, row1; };
+    std::vector<WaveMark> wave_marks;
 };
 
 #define RT_CUDA(call)                                                                                     \
@@ -84,7 +100,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
                      float* ms_build, uint64_t* h2d_bytes);
 // rt_render.cu
 struct RtFrameStats { uint64_t primary, shadow, mirror; uint32_t launches; float ms_kernel[RT_K_COUNT]; uint32_t launches_kernel[RT_K_COUNT]; };
-int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs);
+int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs, int split = 0);
 int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs, int n, int32_t* d_ids, float* d_t,
                         const RtOptions& opt, std::string& err);
 int rt_device_read_stats(RtDevice& D, RtFrameStats* fs, std::string& err);

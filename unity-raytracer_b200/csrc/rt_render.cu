@@ -230,14 +230,16 @@ int persistent_grid(K kernel, int block, size_t smem, int sm_count, int ctas_per
 
 }  // namespace
 
-int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs) {
+// split < 0: cut the frame into |split| waves of whole pixel rows AND record one event per finished wave (rt_render's
+// pipelined copy-out); split > 1: just cut into that many waves; else one wave per chunk_pixels.
+int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs, int split) {
     RT_CUDA(cudaSetDevice(D.device));
     RtView V = V_in;
     {   // reflection depth actually needed: none without a mirror material (RTS:358); clamp to the buffer limit
         int md = (D.has_mirror && V.max_bounces > 0) ? (V.max_bounces > RT_MAX_DEPTH ? RT_MAX_DEPTH : V.max_bounces) : 0;
         V.max_bounces = md;
     }
-    cudaStream_t st = D.stream;
+    cudaStream_t st = D.stream;                 // stream of the wave being enqueued (one of the lanes')
     uint32_t launches = 0;
     D.kev_class.clear();
     auto kbegin = [&](int cls) {
@@ -249,59 +251,88 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
     };
     auto kend = [&]() { if (opt.kernel_timing) cudaEventRecord(D.kev_pool[2 * (D.kev_class.size() - 1) + 1], st); };
     RT_CUDA(D.stats.ensure(4 * 8));
-    RT_CUDA(cudaMemsetAsync(D.stats.p, 0, 4 * 8, st));
-    RT_CUDA(cudaEventRecord(D.ev0, st));
+    RT_CUDA(cudaMemsetAsync(D.stats.p, 0, 4 * 8, D.stream));
+    RT_CUDA(cudaEventRecord(D.ev0, D.stream));
     const int g = V.spp_grid, n_pass = g * g;
     uint64_t primary = 0;
+    D.wave_marks.clear();
     if (V.n_tiles > 0 && V.res_x > 0) {
         const int block = 128;
         const size_t smem = (size_t)STK_CAP * block * sizeof(int);
         int wave_tiles = (opt.chunk_pixels / 32) < 1 ? 1 : (opt.chunk_pixels / 32);
         if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
+        bool mark = split < 0 && V.world == 1;
+        const int n_split = split < 0 ? -split : split;
+        if (n_split > 1) {
+            // waves of whole tile rows (4 pixel rows each): a finished wave is a contiguous block of the (1-rank) frame
+            const int tile_rows = V.n_tiles / V.tiles_x;
+            int rows_per_wave = (tile_rows + n_split - 1) / n_split;
+            const int cap_rows = wave_tiles / V.tiles_x;
+            if (cap_rows >= 1) {
+                if (rows_per_wave > cap_rows) rows_per_wave = cap_rows;
+                if (rows_per_wave < 1) rows_per_wave = 1;
+                wave_tiles = rows_per_wave * V.tiles_x;
+            } else mark = false;
+        } else mark = false;
+        const int waves_per_pass = (V.n_tiles + wave_tiles - 1) / wave_tiles;
+        const int n_lanes = (opt.lanes > 1 && !opt.kernel_timing && waves_per_pass * n_pass > 1) ? 2 : 1;
         const size_t W = (size_t)wave_tiles * 32;
         const int maxd = V.max_bounces;
-        // work buffers
-        RT_CUDA(D.hit0_t.ensure(W * 4)); RT_CUDA(D.hit0_slot.ensure(W * 4));
-        RT_CUDA(D.counters.ensure(C_TOTAL * 4));
-        if ((int)D.local.size() < maxd + 1) D.local.resize(maxd + 1);
-        if ((int)D.link.size() < maxd + 1) D.link.resize(maxd + 1);
-        for (int d = 0; d <= maxd; ++d) RT_CUDA(D.local[d].ensure(W * 16));
-        if (maxd > 0) {
-            RT_CUDA(D.hitq_t.ensure(W * 4)); RT_CUDA(D.hitq_slot.ensure(W * 4));
-            RT_CUDA(D.rays[0].ensure(W * 32)); RT_CUDA(D.rays[1].ensure(W * 32));
-            for (int d = 1; d <= maxd; ++d) RT_CUDA(D.link[d].ensure(W * 16));
-        }
-        if (n_pass > 1) RT_CUDA(D.accum.ensure((size_t)V.n_tiles * 32 * 16));
         const int n_chunks = (D.S.n_lights + 31) / 32;                      // shadow launches per depth
-        RT_CUDA(D.occl.ensure(W * 4 * (size_t)(n_chunks < 1 ? 1 : n_chunks)));
+        for (int li = 0; li < n_lanes; ++li) {                              // work buffers of each lane
+            RtDevice::Lane& L = D.lanes[li];
+            RT_CUDA(L.hit0_t.ensure(W * 4)); RT_CUDA(L.hit0_slot.ensure(W * 4));
+            RT_CUDA(L.counters.ensure(C_TOTAL * 4));
+            if ((int)L.local.size() < maxd + 1) L.local.resize(maxd + 1);
+            if ((int)L.link.size() < maxd + 1) L.link.resize(maxd + 1);
+            for (int d = 0; d <= maxd; ++d) RT_CUDA(L.local[d].ensure(W * 16));
+            if (maxd > 0) {
+                RT_CUDA(L.hitq_t.ensure(W * 4)); RT_CUDA(L.hitq_slot.ensure(W * 4));
+                RT_CUDA(L.rays[0].ensure(W * 32)); RT_CUDA(L.rays[1].ensure(W * 32));
+                for (int d = 1; d <= maxd; ++d) RT_CUDA(L.link[d].ensure(W * 16));
+            }
+            RT_CUDA(L.occl.ensure(W * 4 * (size_t)(n_chunks < 1 ? 1 : n_chunks)));
+            if (li > 0) {
+                if (!L.own_stream) RT_CUDA(cudaStreamCreateWithFlags(&L.own_stream, cudaStreamNonBlocking));
+                if (!L.done) RT_CUDA(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
+                RT_CUDA(cudaStreamWaitEvent(L.own_stream, D.ev0, 0));        // after everything queued before this frame
+            }
+        }
+        if (n_pass > 1) {
+            RT_CUDA(D.accum.ensure((size_t)V.n_tiles * 32 * 16));
+            while (n_lanes > 1 && (int)D.fin_ev.size() < waves_per_pass) { cudaEvent_t e; RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.fin_ev.push_back(e); }
+        }
         const int g_trace = persistent_grid(k_trace_primary, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_traceq = persistent_grid(k_trace_queue, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_shadow0 = persistent_grid(k_trace_shadow<true>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_shadown = persistent_grid(k_trace_shadow<false>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_flat = D.sm_count * 8;
-        unsigned* C = D.counters.as<unsigned>();
         unsigned long long* ST = D.stats.as<unsigned long long>();
-        uint32_t* OC = D.occl.as<uint32_t>();
         RtOut out{(want & RT_OUT_RGBA32F) ? (float4*)D.o_rgba32f : nullptr, (want & RT_OUT_RGBA8) ? (uint32_t*)D.o_rgba8 : nullptr,
                   (want & RT_OUT_HIT_ID) ? (int32_t*)D.o_hit_id : nullptr, (want & RT_OUT_HIT_T) ? (float*)D.o_hit_t : nullptr};
+        int wave_seq = 0;
         for (int sj = 0, pass = 0; sj < g; ++sj)
             for (int si = 0; si < g; ++si, ++pass)
-                for (int tb = 0; tb < V.n_tiles; tb += wave_tiles) {
+                for (int tb = 0, wi = 0; tb < V.n_tiles; tb += wave_tiles, ++wi, ++wave_seq) {
                     const int nt = (V.n_tiles - tb) < wave_tiles ? (V.n_tiles - tb) : wave_tiles;
+                    RtDevice::Lane& L = D.lanes[wave_seq % n_lanes];
+                    st = (wave_seq % n_lanes) ? L.own_stream : D.stream;
+                    unsigned* C = L.counters.as<unsigned>();
+                    uint32_t* OC = L.occl.as<uint32_t>();
                     RT_CUDA(cudaMemsetAsync(C, 0, C_TOTAL * 4, st));
                     kbegin(RT_K_TRACE_PRIMARY);
-                    k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, D.hit0_t.as<float>(), D.hit0_slot.as<int>(), C + C_WORK);
+                    k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK);
                     kend(); ++launches;
                     for (int d = 0; d <= maxd; ++d) {
-                        const float4* rin = d ? D.rays[(d - 1) & 1].as<float4>() : nullptr;
-                        float4* rout = d < maxd ? D.rays[d & 1].as<float4>() : nullptr;
-                        float4* lout = d < maxd ? D.link[d + 1].as<float4>() : nullptr;
-                        const float* ht = d ? D.hitq_t.as<float>() : D.hit0_t.as<float>();
-                        const int* hs = d ? D.hitq_slot.as<int>() : D.hit0_slot.as<int>();
+                        const float4* rin = d ? L.rays[(d - 1) & 1].as<float4>() : nullptr;
+                        float4* rout = d < maxd ? L.rays[d & 1].as<float4>() : nullptr;
+                        float4* lout = d < maxd ? L.link[d + 1].as<float4>() : nullptr;
+                        const float* ht = d ? L.hitq_t.as<float>() : L.hit0_t.as<float>();
+                        const int* hs = d ? L.hitq_slot.as<int>() : L.hit0_slot.as<int>();
                         unsigned* wk = C + C_WORK + 8 * d;
                         if (d > 0) {
                             kbegin(RT_K_TRACE_QUEUE);
-                            k_trace_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, D.hitq_t.as<float>(), D.hitq_slot.as<int>(), wk);
+                            k_trace_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, L.hitq_t.as<float>(), L.hitq_slot.as<int>(), wk);
                             kend(); ++launches;
                         }
                         for (int c = 0; c < n_chunks; ++c) {
@@ -314,26 +345,40 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                             kend(); ++launches;
                         }
                         kbegin(d ? RT_K_SHADE_QUEUE : RT_K_SHADE_PRIMARY);
-                        if (d == 0) k_shade<true><<<g_flat, 256, 0, st>>>(D.S, V, 0, tb, nt, si, sj, nullptr, nullptr, ht, hs, OC, W, D.local[0].as<float4>(), rout, lout, C + 1, ST);
-                        else k_shade<false><<<g_flat, 256, 0, st>>>(D.S, V, d, 0, 0, 0, 0, C + d, rin, ht, hs, OC, W, D.local[d].as<float4>(), rout, lout, C + d + 1, ST);
+                        if (d == 0) k_shade<true><<<g_flat, 256, 0, st>>>(D.S, V, 0, tb, nt, si, sj, nullptr, nullptr, ht, hs, OC, W, L.local[0].as<float4>(), rout, lout, C + 1, ST);
+                        else k_shade<false><<<g_flat, 256, 0, st>>>(D.S, V, d, 0, 0, 0, 0, C + d, rin, ht, hs, OC, W, L.local[d].as<float4>(), rout, lout, C + d + 1, ST);
                         kend(); ++launches;
                     }
                     for (int d = maxd; d >= 1; --d) {
                         kbegin(RT_K_FOLD);
-                        k_fold<<<g_flat, 256, 0, st>>>(C + d, D.link[d].as<float4>(), D.local[d].as<float4>(), D.local[d - 1].as<float4>());
+                        k_fold<<<g_flat, 256, 0, st>>>(C + d, L.link[d].as<float4>(), L.local[d].as<float4>(), L.local[d - 1].as<float4>());
                         kend();
                         ++launches;
                     }
+                    // spp passes accumulate per pixel: pass p of these tiles must follow pass p-1 of the same tiles
+                    if (n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
                     kbegin(RT_K_FINALIZE);
-                    k_finalize<<<g_flat, 256, 0, st>>>(D.S, V, tb, nt, pass, n_pass, D.local[0].as<float4>(), D.hit0_t.as<float>(), D.hit0_slot.as<int>(),
+                    k_finalize<<<g_flat, 256, 0, st>>>(D.S, V, tb, nt, pass, n_pass, L.local[0].as<float4>(), L.hit0_t.as<float>(), L.hit0_slot.as<int>(),
                                                         n_pass > 1 ? D.accum.as<float4>() : nullptr, out);
                     kend();
                     ++launches;
+                    if (n_pass > 1 && n_lanes > 1 && pass < n_pass - 1) RT_CUDA(cudaEventRecord(D.fin_ev[wi], st));
+                    if (mark && pass == n_pass - 1) {
+                        const size_t i = D.wave_marks.size();
+                        while (D.wave_ev.size() <= i) { cudaEvent_t e; RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.wave_ev.push_back(e); }
+                        RT_CUDA(cudaEventRecord(D.wave_ev[i], st));
+                        const int r0 = (tb / V.tiles_x) * 4, r1 = ((tb + nt) / V.tiles_x) * 4;
+                        D.wave_marks.push_back(RtDevice::WaveMark{r0, r1 < V.res_y ? r1 : V.res_y});
+                    }
                 }
+        for (int li = 1; li < n_lanes; ++li) {                               // join the lanes back into the caller's stream
+            RT_CUDA(cudaEventRecord(D.lanes[li].done, D.lanes[li].own_stream));
+            RT_CUDA(cudaStreamWaitEvent(D.stream, D.lanes[li].done, 0));
+        }
         RT_CUDA(cudaGetLastError());
         primary = (uint64_t)V.res_x * (uint64_t)V.n_local_rows * (uint64_t)n_pass;
     }
-    RT_CUDA(cudaEventRecord(D.ev1, st));
+    RT_CUDA(cudaEventRecord(D.ev1, D.stream));
     if (fs) { fs->primary = primary; fs->shadow = 0; fs->mirror = 0; fs->launches = launches; }
     return RT_OK;
 }
