@@ -22,6 +22,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+_OUT = sys.stdout
 METRIC = "Mrays/s (primary+shadow+mirror)"
 UNIT = "Mrays/s"
 
@@ -146,7 +147,7 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample + "; oracle/ C++ restatement of the reference's C# "
                              "hot path with a CPU BVH (the reference itself: single-threaded Mono linear scan, cannot run here)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 def run_ours(args, rank, world, local_rank):
@@ -273,7 +274,7 @@ def run_ours(args, rank, world, local_rank):
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
                 "commit": {"ms_upload": cstats["ms_commit_upload"], "ms_bvh_build": cstats["ms_commit_build"], "h2d_bytes": cstats["h2d_bytes"],
                            "wall_ms": 1e3 * commit_wall, "n_prims": cstats["n_prims"], "n_nodes": cstats["n_nodes"], "builder": args.builder}}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
     barrier()
     rt.close()
     if world > 1:
@@ -281,6 +282,10 @@ def run_ours(args, rank, world, local_rank):
 
 
 def main():
+    # stdout carries exactly ONE JSON line: libraries that print to fd 1 (NCCL's "NCCL version ..." banner) go to stderr
+    global _OUT
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

@@ -134,9 +134,7 @@ RtView make_view(const rt_render_params* p, int rank, int world, int band_rows) 
     V.max_bounces = p->max_reflection_bounces < 0 ? 0 : p->max_reflection_bounces;
     V.spp_grid = p->spp_grid < 1 ? 1 : p->spp_grid;
     V.rank = rank; V.world = world; V.band_rows = band_rows;
-    V.tiles_x = (V.res_x + 7) / 8;
-    V.n_local_rows = rt_local_rows(V.res_y, rank, world, band_rows);
-    V.n_tiles = V.tiles_x * ((V.n_local_rows + 3) / 4);
+    rt_view_finish(V);
     return V;
 }
 

@@ -185,3 +185,22 @@ def test_ray_tri_division_free_rejections_match_reference(emu, oracle):
     for bad in (np.nan, np.inf):
         v = np.array((0, 0, 5, 1, 0, 5, 0, 1, 5), np.float32); v[4] = bad
         assert emu.ray_triangle((0.2, 0.2, 0), (0, 0, 1), v)[0] == oracle.ray_triangle((0.2, 0.2, 0), (0, 0, 1), v)[0]
+
+
+def test_tile_mapping_division_by_multiplication(emu, scenes):
+    """rt_item_to_pixel divides the tile index by tiles_x with a multiply + fix-up: odd widths/heights, all partitions."""
+    s = scenes.SceneArrays(); s.add_sphere((0, 0, 20), 25.0, scenes.material(ambient=(1, 1, 1))); s.ambient[:] = (50, 50, 50)
+    e = emu.EmuTracer(); e.set_scene(s)
+    for (rx, ry) in ((1, 1), (7, 5), (9, 33), (1023, 3), (130, 131)):
+        p = scenes.make_params(rx, ry, 10.0, 8.0, 5.0)
+        full = e.render(p)
+        assert full["stats"]["rays_primary"] == rx * ry
+        for world, band in ((3, 4), (2, 12), (5, 32)):            # power-of-two and non-power-of-two band heights
+            acc = np.zeros_like(full["hit_t"]); cnt = 0
+            for r in range(world):
+                e.set_partition(r, world, band)
+                g = e.render(p)
+                mine = np.repeat(((np.arange(ry) // band) % world) == r, rx)
+                acc[mine] = g["hit_t"][mine]; cnt += g["stats"]["rays_primary"]
+            e.set_partition(0, 1, 32)
+            assert cnt == rx * ry and np.array_equal(acc, full["hit_t"]), (rx, ry, world, band)

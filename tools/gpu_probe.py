@@ -7,6 +7,9 @@ sc = rtb.scenes
 cfg = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 opts = dict(a.split("=") for a in sys.argv[3:])
+timing = int(opts.pop("timing", 1))
+flush = int(opts.pop("flush", 0))
+part = int(opts.pop("part", 1))
 t0 = time.time()
 if cfg == "cfg2": s, p = sc.rt_unity(True), sc.rt_unity_params(3840, 2160, 4)
 elif cfg == "cfg3": s, p = sc.cfg3_scene(), sc.cfg3_params()
@@ -15,10 +18,17 @@ elif cfg == "cfg5": s, p = sc.cfg5_scene(), sc.cfg5_params()
 else: s, p = sc.cfg3_scene(n=int(cfg)), sc.cfg3_params()
 print(f"scene {cfg}: {s.n_prims} prims, generated in {time.time()-t0:.1f}s", flush=True)
 rt = rtb.RayTracer((0,))
+if part > 1: rt.set_partition(0, part, 32)
 for k, v in opts.items(): rt.set_option(k, float(v))
-rt.set_option("kernel_timing", 1)
+rt.set_option("kernel_timing", timing)
 t0 = time.time(); rt.set_scene(s); print(f"commit wall {time.time()-t0:.3f}s", flush=True)
+fl = None
+if flush:
+    import torch
+    fl = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
 for i in range(reps):
+    if fl is not None:
+        fl.zero_(); torch.cuda.synchronize()
     st = rt.render_device(p, rtb.host.RT_OUT_RGBA8, sync_stats=True)
     rays = st["rays_primary"] + st["rays_shadow"] + st["rays_mirror"]
     print(json.dumps(dict(ms=round(st["ms_render"], 3), mrays=round(rays / st["ms_render"] / 1e3, 1), rays=rays, launches=st["kernel_launches"],

@@ -12,10 +12,11 @@ from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(HERE, "librtb200.so")
+OUT = os.environ.get("RTB200_OUT", os.path.join(HERE, "librtb200.so"))
 SOURCES = ["rt_build.cu", "rt_render.cu", "rt_abi.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false", "-prec-div=true",
+EXTRA = os.environ.get("RTB200_EXTRA_NVCC_FLAGS", "").split()      # development builds only (e.g. -DRT_TILE_TIMING)
+FLAGS = EXTRA + ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false", "-prec-div=true",
          "-prec-sqrt=true", "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "-Xptxas", "-v", "-I", os.path.join(HERE, "..", "include")]
 
 

@@ -38,6 +38,7 @@ void device_release(RtDevice& D) {
         if (L.own_stream) cudaStreamDestroy(L.own_stream);
         L.done = nullptr; L.own_stream = nullptr;
     }
+    for (auto* hh : {&D.hint_primary, &D.hint_shadow}) for (int k = 0; k < 2; ++k) { hh->lists[k].release(); hh->counts[k].release(); }
     for (cudaEvent_t e : D.fin_ev) cudaEventDestroy(e);
     D.fin_ev.clear();
     void* imp[4] = {D.o_rgba32f, D.o_rgba8, D.o_hit_id, D.o_hit_t};
@@ -89,9 +90,7 @@ RtView make_view(const rt_ctx* c, const rt_render_params* p, int dev_index) {
     V.spp_grid = p->spp_grid < 1 ? 1 : p->spp_grid;
     const int nd = (int)c->devs.size();
     V.rank = c->ext_rank * nd + dev_index; V.world = c->ext_world * nd; V.band_rows = c->band_rows;
-    V.tiles_x = (V.res_x + 7) / 8;
-    V.n_local_rows = rt_local_rows(V.res_y, V.rank, V.world, V.band_rows);
-    V.n_tiles = V.tiles_x * ((V.n_local_rows + 3) / 4);
+    rt_view_finish(V);
     return V;
 }
 
@@ -476,6 +475,8 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "block") { c->opt.block = (int)value; }
     else if (k == "waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "waves must be 1..64"); c->opt.waves = (int)value; }
     else if (k == "lanes") { if (value != 1 && value != 2) return fail(c, RT_E_INVALID, "lanes must be 1 or 2"); c->opt.lanes = (int)value; }
+    else if (k == "fuse_shade") { c->opt.fuse_shade = value != 0; }
+    else if (k == "hints") { c->opt.hints = value != 0; }
     else if (k == "copy_waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "copy_waves must be 1..64"); c->opt.copy_waves = (int)value; }
     else if (k == "builder") { if (value != 0 && value != 1) return fail(c, RT_E_INVALID, "builder must be 0 (device LBVH) or 1 (host SAH)"); c->opt.builder = (int)value; }
     else if (k == "kernel_timing") { c->opt.kernel_timing = value != 0; }

@@ -11,8 +11,14 @@
 
 #if defined(__CUDA_ARCH__)
 #define RT_LDG4(p) __ldg(p)
+// wave buffers and framebuffers are written once and read once: streaming (evict-first) accesses keep them from pushing
+// the BVH nodes and primitives out of L2
+#define RT_ST_STREAM(p, v) __stcs((p), (v))
+#define RT_LD_STREAM(p) __ldcs(p)
 #else
 #define RT_LDG4(p) (*(p))
+#define RT_ST_STREAM(p, v) (*(p) = (v))
+#define RT_LD_STREAM(p) (*(p))
 #endif
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -51,6 +57,8 @@ struct RtView {
     // partition of the frame over ranks/devices: this view owns the row bands b with b % world == rank
     int32_t rank, world, band_rows;
     int32_t tiles_x;          // ceil(res_x / 8)
+    uint32_t tiles_x_magic;   // floor(2^32 / tiles_x) (0xffffffff for tiles_x == 1): division by multiplication, rt_view_finish()
+    int32_t band_shift;       // log2(band_rows) when it is a power of two, else -1
     int32_t n_local_rows;     // rows owned by this rank
     int32_t n_tiles;          // tiles_x * ceil(n_local_rows / 4); one tile = 8x4 pixels = one warp
 };
@@ -353,12 +361,26 @@ RT_HD int32_t rt_local_rows(int32_t res_y, int32_t rank, int32_t world, int32_t 
     }
     return rows;
 }
+// fills the derived fields of a view (tiles, local rows, division constants) from res/rank/world/band_rows
+RT_HD void rt_view_finish(RtView& V) {
+    V.tiles_x = (V.res_x + 7) / 8;
+    V.n_local_rows = rt_local_rows(V.res_y, V.rank, V.world, V.band_rows);
+    V.n_tiles = V.tiles_x * ((V.n_local_rows + 3) / 4);
+    V.tiles_x_magic = V.tiles_x <= 1 ? 0xffffffffu : (uint32_t)(0x100000000ull / (uint64_t)V.tiles_x);
+    V.band_shift = -1;
+    for (int32_t k = 0; k < 31; ++k) if (V.band_rows == (1 << k)) V.band_shift = k;
+}
 // local work item (tile, lane) -> pixel. One tile is an 8x4 pixel block (one warp) of the rank's local image.
+// tile / tiles_x by multiplication: q' = mulhi(tile, floor(2^32/d)) is q or q-1 for every 32-bit tile; one fix-up step.
 RT_HD bool rt_item_to_pixel(const RtView& V, int32_t tile, int32_t lane, int32_t& x, int32_t& y) {
-    int32_t tx = tile % V.tiles_x, ty = tile / V.tiles_x;
-    x = tx * 8 + (lane & 7);
-    int32_t r = ty * 4 + (lane >> 3);                       // local row
-    y = ((r / V.band_rows) * V.world + V.rank) * V.band_rows + (r % V.band_rows);
+    uint32_t ty = (uint32_t)(((uint64_t)(uint32_t)tile * (uint64_t)V.tiles_x_magic) >> 32);
+    uint32_t tx = (uint32_t)tile - ty * (uint32_t)V.tiles_x;
+    if (tx >= (uint32_t)V.tiles_x) { tx -= (uint32_t)V.tiles_x; ++ty; }
+    x = (int32_t)tx * 8 + (lane & 7);
+    int32_t r = (int32_t)ty * 4 + (lane >> 3);              // local row
+    if (V.world == 1) y = r;
+    else if (V.band_shift >= 0) y = ((((r >> V.band_shift) * V.world + V.rank)) << V.band_shift) + (r & (V.band_rows - 1));
+    else y = ((r / V.band_rows) * V.world + V.rank) * V.band_rows + (r % V.band_rows);
     return x < V.res_x && r < V.n_local_rows && y < V.res_y;
 }
 
@@ -406,19 +428,18 @@ struct RtOut { float4* rgba32f; uint32_t* rgba8; int32_t* hit_id; float* hit_t; 
 
 // One work item of a finished wave -> framebuffer(s).  pass/n_pass: sample index of the spp_grid^2 extension; colours are
 // summed in pass order and divided once, before Rgb.Color (Rgb.cs:13) and the u8 quantisation.
-RT_HD void rt_finalize_item(const RtScene& S, const RtView& V, int32_t tile_begin, uint32_t q, int32_t pass, int32_t n_pass,
-                            const float4* local0, const float* hit_t, const int32_t* hit_slot, float4* accum, const RtOut& out) {
+RT_HD void rt_finalize_value(const RtScene& S, const RtView& V, int32_t tile_begin, uint32_t q, int32_t pass, int32_t n_pass,
+                             float4 c, float ht, int32_t hslot, float4* accum, const RtOut& out) {
     int32_t x, y;
     if (!rt_item_to_pixel(V, tile_begin + (int32_t)(q >> 5), (int32_t)(q & 31), x, y)) return;
     size_t pix = (size_t)x + (size_t)y * (size_t)V.res_x;                  // GetPixelIndex, RayTracingSetup.cs:243-246
     if (pass == 0) {
         if (out.hit_id) {
-            int32_t ty, ix, me; rt_slot_to_id(S, hit_slot[q], ty, ix, me);
+            int32_t ty, ix, me; rt_slot_to_id(S, hslot, ty, ix, me);
             out.hit_id[3 * pix] = ty; out.hit_id[3 * pix + 1] = ix; out.hit_id[3 * pix + 2] = me;
         }
-        if (out.hit_t) out.hit_t[pix] = hit_t[q];
+        if (out.hit_t) RT_ST_STREAM(out.hit_t + pix, ht);
     }
-    float4 c = local0[q];
     if (n_pass > 1) {
         size_t a = ((size_t)tile_begin << 5) + q;
         if (pass > 0) { float4 p = accum[a]; c.x = p.x + c.x; c.y = p.y + c.y; c.z = p.z + c.z; }
@@ -426,6 +447,11 @@ RT_HD void rt_finalize_item(const RtScene& S, const RtView& V, int32_t tile_begi
         float np = (float)n_pass;
         c.x = rt_div(c.x, np); c.y = rt_div(c.y, np); c.z = rt_div(c.z, np);
     }
-    if (out.rgba32f) out.rgba32f[pix] = make_float4(rt_div(c.x, 255.f), rt_div(c.y, 255.f), rt_div(c.z, 255.f), 1.f);
-    if (out.rgba8) out.rgba8[pix] = (uint32_t)rt_quant(c.x) | ((uint32_t)rt_quant(c.y) << 8) | ((uint32_t)rt_quant(c.z) << 16) | 0xff000000u;
+    if (out.rgba32f) RT_ST_STREAM(out.rgba32f + pix, make_float4(rt_div(c.x, 255.f), rt_div(c.y, 255.f), rt_div(c.z, 255.f), 1.f));
+    if (out.rgba8) RT_ST_STREAM(out.rgba8 + pix, (uint32_t)rt_quant(c.x) | ((uint32_t)rt_quant(c.y) << 8) | ((uint32_t)rt_quant(c.z) << 16) | 0xff000000u);
+}
+
+RT_HD void rt_finalize_item(const RtScene& S, const RtView& V, int32_t tile_begin, uint32_t q, int32_t pass, int32_t n_pass,
+                            const float4* local0, const float* hit_t, const int32_t* hit_slot, float4* accum, const RtOut& out) {
+    rt_finalize_value(S, V, tile_begin, q, pass, n_pass, local0[q], hit_t[q], hit_slot[q], accum, out);
 }

@@ -36,6 +36,8 @@ struct RtOptions {
     int lanes = 2;                     // 1 = all waves on one stream; 2 = alternate waves over two streams (tail overlap)
     int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
                                        // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
+    int fuse_shade = 1;                // shading (+ pixel write at depth 0) inside the shadow-trace kernel when <= 32 lights
+    int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };
 
@@ -66,6 +68,11 @@ struct RtDevice {
     };
     Lane lanes[2];
     DevBuf accum, stats;
+    // heavy-first tile order (rt_render.cu "cost hints"): per tile-indexed trace kernel, double-buffered class lists
+    struct Hints { DevBuf lists[2], counts[2]; };
+    Hints hint_primary, hint_shadow;
+    int hint_cur = 0; bool hint_ready = false;
+    long long hint_sig[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     std::vector<cudaEvent_t> fin_ev;        // spp passes: finalize of (pass p, wave i) follows finalize of (pass p-1, wave i)
     // ---- outputs: full-frame buffers. Owned on the gather device; other devices/ranks hold peer pointers ----
     DevBuf own_rgba32f, own_rgba8, own_hit_id, own_hit_t;

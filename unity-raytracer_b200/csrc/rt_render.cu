@@ -49,18 +49,62 @@ __device__ __forceinline__ int warp_fetch(unsigned* counter, int lane) {
     return __shfl_sync(0xffffffffu, t, 0);
 }
 
+// ---- heavy-first tile order ("cost hints") ----------------------------------------------------------------------------
+// Tile costs are extremely skewed (cfg3, ncu/clock64: median 2.5 us, p99 70 us, max 190 us — silhouette tiles whose rays
+// graze the displaced shell), so a persistent kernel that hands tiles out in image order ends with a long tail: the last
+// heavy tiles start late and the other warps idle (17 % of k_trace_primary on the full 4K frame, > 50 % on a 1/8 band
+// partition).  Each tile-indexed trace kernel therefore measures every tile (clock64) and files it under one of 8 cost
+// classes (log2 of its cycles); the NEXT frame hands the tiles of the same wave out class by class, most expensive first
+// (longest-processing-time-first list scheduling), falling back to image order when no hints exist (first frame, changed
+// resolution / partition / wave layout).  Hints only reorder work: results are unaffected, stale hints are harmless.
+constexpr int RT_NCLS = 8;
+struct RtHintIn { const int* lists; const unsigned* counts; size_t stride; };     // lists[c * stride + i], counts[c]; null = image order
+struct RtHintOut { int* lists; unsigned* counts; size_t stride; };                // null = do not record
+
+__device__ __forceinline__ int rt_cost_class(long long cycles) {
+    int c = 63 - __clzll((cycles >> 11) | 1);             // < 2K cycles: 0, 2-4K: 1, ... >= 256K: 7
+    return c > RT_NCLS - 1 ? RT_NCLS - 1 : c;
+}
+// k-th work item of the wave -> tile index within the wave, heaviest class first
+__device__ __forceinline__ int rt_hint_tile(const RtHintIn& h, int k, int lane) {
+    if (!h.lists) return k;
+    unsigned cnt = lane < RT_NCLS ? h.counts[RT_NCLS - 1 - lane] : 0u;          // lane 0 holds the heaviest class
+    unsigned incl = cnt;
+    for (int o = 1; o < RT_NCLS; o <<= 1) { unsigned v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+    unsigned m = __ballot_sync(0xffffffffu, lane < RT_NCLS && (unsigned)k < incl);
+    int src = __ffs(m) - 1;                                // first class whose inclusive prefix exceeds k
+    if (src < 0) return k;                                 // inconsistent hints: cannot happen when the host validated them
+    unsigned excl = __shfl_sync(0xffffffffu, incl - cnt, src);
+    return h.lists[(size_t)(RT_NCLS - 1 - src) * h.stride + ((unsigned)k - excl)];
+}
+__device__ __forceinline__ void rt_hint_record(const RtHintOut& h, int tile, long long cycles, int lane) {
+    if (!h.lists || lane != 0) return;
+    int c = rt_cost_class(cycles);
+    unsigned pos = atomicAdd(h.counts + c, 1u);
+    h.lists[(size_t)c * h.stride + pos] = tile;
+}
+
 // counters layout (unsigned): [0 .. D]: queue counts per depth; work counters of depth d at C_WORK + 8*d:
 //   +0 closest-hit trace, +1..+7 shadow-trace launches (one per chunk of 32 lights)
 constexpr int C_WORK = RT_MAX_DEPTH + 2;
 constexpr int C_TOTAL = C_WORK + 8 * (RT_MAX_DEPTH + 2);
 
-__global__ void __launch_bounds__(128) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
-                                                        float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work) {
+#ifdef RT_TILE_TIMING
+__device__ unsigned long long* g_rt_tile_dbg = nullptr;      // per tile: (start ns, duration ns); development aid only
+#endif
+__global__ void __launch_bounds__(128, 8) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
+                                                        float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work,
+                                                        RtHintIn hin, RtHintOut hout) {
     RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
     for (;;) {
         int t = warp_fetch(work, lane);
         if (t >= n_tiles) break;
+        t = rt_hint_tile(hin, t, lane);
+        const long long c0 = clock64();
+#ifdef RT_TILE_TIMING
+        unsigned long long dbg_t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+#endif
         int x, y;
         bool valid = rt_item_to_pixel(V, tile_begin + t, lane, x, y);
         float bt = FLT_MAX; int bs = -1;
@@ -73,11 +117,16 @@ __global__ void __launch_bounds__(128) k_trace_primary(RtScene S, RtView V, int 
             if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
         } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
         size_t q = (size_t)t * 32 + lane;
-        hit_t[q] = bt; hit_slot[q] = valid ? bs : -2;
+        RT_ST_STREAM(hit_t + q, bt); RT_ST_STREAM(hit_slot + q, valid ? bs : -2);
+        rt_hint_record(hout, t, clock64() - c0, lane);
+#ifdef RT_TILE_TIMING
+        unsigned long long dbg_t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t1));
+        if (lane == 0 && g_rt_tile_dbg) { g_rt_tile_dbg[2 * (size_t)(tile_begin + t)] = dbg_t0; g_rt_tile_dbg[2 * (size_t)(tile_begin + t) + 1] = dbg_t1 - dbg_t0; }
+#endif
     }
 }
 
-__global__ void __launch_bounds__(128) k_trace_queue(RtScene S, const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays,
+__global__ void __launch_bounds__(128, 8) k_trace_queue(RtScene S, const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays,
                                                       float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work) {
     RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
@@ -110,51 +159,91 @@ __device__ __forceinline__ void item_ray(const RtView& V, int tile_begin, unsign
 }
 
 // Shadow queries (RTS:329-345) of every hit of a wave for lights [light_begin, light_begin+n_l), n_l <= 32, as any-hit
-// traversals; bit i of occl[q] = light light_begin+i is occluded.  Lean on purpose (no material / colour state is live
-// across the traversal), so it keeps the occupancy of the closest-hit kernels.  The light loop is warp-uniform so the 32
-// queries towards one light go as one packet when the warp's hits lie close together.
-template <bool DEPTH0>
-__global__ void __launch_bounds__(128) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
-                                                       const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
-                                                       const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
-                                                       int light_begin, int n_l, uint32_t* __restrict__ occl, unsigned* work,
-                                                       unsigned long long* stats) {
+// traversals; bit i of occl[q] = light light_begin+i is occluded.  The light loop is warp-uniform so the 32 queries towards
+// one light go as one packet when the warp's hits lie close together.
+// FUSE (scenes with <= 32 lights): the rest of Shade (RTS:321-362: ambient, diffuse, Blinn-Phong, mirror-ray emission) runs
+// right here once the occlusion mask is known, and with `fin` set (no deeper wave pending) so does the pixel write — the hit
+// record, surface point and mask never travel through memory and two launches per depth disappear.
+struct RtFuse {
+    int depth;                         // bounce index of this wave
+    float4* local_out;                 // colour of this bounce per item
+    float4* rays_out; float4* link_out; unsigned* next_count;      // mirror-ray queue of the next depth (null at max depth)
+    int fin;                           // 1: also finalize (depth 0 wave, no mirror depth above it)
+    int pass, n_pass; float4* accum; RtOut out;
+};
+
+template <bool DEPTH0, bool FUSE>
+__global__ void __launch_bounds__(128, 8) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
+                                                          const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
+                                                          const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
+                                                          int light_begin, int n_l, uint32_t* __restrict__ occl, unsigned* work,
+                                                          unsigned long long* stats, RtFuse F, RtHintIn hin, RtHintOut hout) {
     RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
     const unsigned full = 0xffffffffu;
     const unsigned n = DEPTH0 ? (unsigned)n_tiles * 32u : *n_ptr;
-    unsigned my_shadow = 0;
+    unsigned my_shadow = 0, my_mirror = 0;
     for (;;) {
-        unsigned q = (unsigned)warp_fetch(work, lane) * 32u + lane;
-        if (q - lane >= n) break;
-        const int slot = q < n ? hit_slot[q] : -2;
+        int wt = warp_fetch(work, lane);
+        if ((unsigned)wt * 32u >= n) break;
+        if (DEPTH0) wt = rt_hint_tile(hin, wt, lane);
+        const long long c0 = clock64();
+        const unsigned q = (unsigned)wt * 32u + lane;
+        const int slot = q < n ? RT_LD_STREAM(hit_slot + q) : -2;
         const bool has = slot >= 0;
-        if (!__any_sync(full, has)) { if (q < n) occl[q] = 0u; continue; }
-        f3 P = mk3(0.f, 0.f, 0.f), sO = P;
-        if (has) {
-            f3 O, D, N; int mat_id;
-            item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
-            rt_surf_geom(S, O, D, hit_t[q], slot, P, N, mat_id);
-            sO = P + N * RT_SHADOW_EPS;                                                        // RTS:331
-        }
         uint32_t mask = 0;
-        for (int i = 0; i < n_l; ++i) {
-            f3 Ldir = mk3(0.f, 0.f, 1.f); float d2 = 0.f;
-            bool act = false;
-            if (has) { rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow; }
-            const f3 inv = rt_rcp3(Ldir);
-            if (has) act = rt_scene_gate(S, sO, inv);                                              // Scene.cs:54
-            bool occluded = false;
-            float st; int ss;
-            if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
-                if (__any_sync(full, act)) occluded = rt_traverse_packet<true>(S, sO, Ldir, inv, act, d2, stk, st, ss);
-            } else if (act) occluded = rt_traverse<true>(S, sO, Ldir, inv, d2, stk, st, ss);
-            if (occluded) mask |= 1u << i;
+        f3 O = mk3(0.f, 0.f, 0.f), D = mk3(0.f, 0.f, 1.f);
+        float ht = 0.f;
+        if (__any_sync(full, has)) {
+            f3 P = mk3(0.f, 0.f, 0.f), sO = P;
+            if (has) {
+                f3 N; int mat_id;
+                item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
+                ht = RT_LD_STREAM(hit_t + q);
+                rt_surf_geom(S, O, D, ht, slot, P, N, mat_id);
+                sO = P + N * RT_SHADOW_EPS;                                                        // RTS:331
+            }
+            for (int i = 0; i < n_l; ++i) {
+                f3 Ldir = mk3(0.f, 0.f, 1.f); float d2 = 0.f;
+                bool act = false;
+                if (has) { rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow; }
+                const f3 inv = rt_rcp3(Ldir);
+                if (has) act = rt_scene_gate(S, sO, inv);                                              // Scene.cs:54
+                bool occluded = false;
+                float st; int ss;
+                if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
+                    if (__any_sync(full, act)) occluded = rt_traverse_packet<true>(S, sO, Ldir, inv, act, d2, stk, st, ss);
+                } else if (act) occluded = rt_traverse<true>(S, sO, Ldir, inv, d2, stk, st, ss);
+                if (occluded) mask |= 1u << i;
+            }
         }
-        if (q < n) occl[q] = mask;
+        if (!FUSE) { if (q < n) occl[q] = mask; if (DEPTH0) rt_hint_record(hout, wt, clock64() - c0, lane); continue; }
+        // ---- fused shading (k_shade's body) ----
+        RtMirror mir; mir.emit = false;
+        float4 col = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);                            // RTS:310-311
+        if (has) {
+            f3 c = rt_shade_masked(S, O, D, ht, slot, F.depth, V.max_bounces, &mask, 0, 0, mir);
+            col = make_float4(c.x, c.y, c.z, 0.f);
+        }
+        if (!(DEPTH0 && F.fin) && slot >= -1) RT_ST_STREAM(F.local_out + q, col);
+        unsigned m = __ballot_sync(full, mir.emit);
+        if (m) {
+            unsigned base = 0;
+            if (lane == 0) { base = atomicAdd(F.next_count, (unsigned)__popc(m)); my_mirror += (unsigned)__popc(m); }
+            base = __shfl_sync(full, base, 0);
+            if (mir.emit) {
+                size_t o = base + __popc(m & ((1u << lane) - 1u));
+                F.rays_out[2 * o] = make_float4(mir.O.x, mir.O.y, mir.O.z, 0.f);
+                F.rays_out[2 * o + 1] = make_float4(mir.D.x, mir.D.y, mir.D.z, 0.f);
+                F.link_out[o] = make_float4(mir.km.x, mir.km.y, mir.km.z, __int_as_float((int)q));
+            }
+        }
+        if (DEPTH0 && F.fin && slot >= -1) rt_finalize_value(S, V, tile_begin, q, F.pass, F.n_pass, col, has ? ht : FLT_MAX, slot, F.accum, F.out);
+        if (DEPTH0) rt_hint_record(hout, wt, clock64() - c0, lane);
     }
     my_shadow = __reduce_add_sync(full, my_shadow);
     if (lane == 0 && my_shadow) atomicAdd(stats + 1, (unsigned long long)my_shadow);
+    if (FUSE && lane == 0 && my_mirror) atomicAdd(stats + 2, (unsigned long long)my_mirror);
 }
 
 // Shading + light loop with the shadow results known (rt_shade_masked); appends the reflection rays of mirror hits to
@@ -302,10 +391,40 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             RT_CUDA(D.accum.ensure((size_t)V.n_tiles * 32 * 16));
             while (n_lanes > 1 && (int)D.fin_ev.size() < waves_per_pass) { cudaEvent_t e; RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.fin_ev.push_back(e); }
         }
+        // ---- cost hints of the previous frame (same layout only) / recording for the next ----
+        const long long sig[8] = {V.n_tiles, wave_tiles, V.res_x, V.res_y, V.rank, V.world, V.band_rows, (long long)D.S.n_prims};
+        bool hint_in = opt.hints && D.hint_ready;
+        for (int k = 0; k < 8; ++k) hint_in = hint_in && D.hint_sig[k] == sig[k];
+        const bool hint_rec = opt.hints != 0;
+        const int hb_in = D.hint_cur, hb_out = 1 - D.hint_cur;
+        const size_t hstride = (size_t)V.n_tiles;
+        if (hint_rec) {
+            for (auto* hh : {&D.hint_primary, &D.hint_shadow}) {
+                for (int k = 0; k < 2; ++k) { RT_CUDA(hh->lists[k].ensure(hstride * RT_NCLS * 4)); RT_CUDA(hh->counts[k].ensure((size_t)waves_per_pass * RT_NCLS * 4)); }
+                RT_CUDA(cudaMemsetAsync(hh->counts[hb_out].p, 0, (size_t)waves_per_pass * RT_NCLS * 4, D.stream));
+            }
+            if (n_lanes > 1) {                                               // the lanes must see the cleared counters
+                RT_CUDA(cudaEventRecord(D.lanes[1].done, D.stream));
+                RT_CUDA(cudaStreamWaitEvent(D.lanes[1].own_stream, D.lanes[1].done, 0));
+            }
+        }
+        auto hin_of = [&](RtDevice::Hints& hh, int tb, int wi) {
+            RtHintIn h{nullptr, nullptr, 0};
+            if (hint_in) h = RtHintIn{hh.lists[hb_in].as<int>() + tb, hh.counts[hb_in].as<unsigned>() + (size_t)wi * RT_NCLS, hstride};
+            return h;
+        };
+        auto hout_of = [&](RtDevice::Hints& hh, int tb, int wi, bool on) {
+            RtHintOut h{nullptr, nullptr, 0};
+            if (hint_rec && on) h = RtHintOut{hh.lists[hb_out].as<int>() + tb, hh.counts[hb_out].as<unsigned>() + (size_t)wi * RT_NCLS, hstride};
+            return h;
+        };
         const int g_trace = persistent_grid(k_trace_primary, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_traceq = persistent_grid(k_trace_queue, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shadow0 = persistent_grid(k_trace_shadow<true>, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shadown = persistent_grid(k_trace_shadow<false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const bool fuse = opt.fuse_shade && n_chunks == 1;                  // shade (+ finalize) inside the shadow kernel
+        const int g_shadow0 = fuse ? persistent_grid(k_trace_shadow<true, true>, block, smem, D.sm_count, opt.ctas_per_sm)
+                                   : persistent_grid(k_trace_shadow<true, false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadown = fuse ? persistent_grid(k_trace_shadow<false, true>, block, smem, D.sm_count, opt.ctas_per_sm)
+                                   : persistent_grid(k_trace_shadow<false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_flat = D.sm_count * 8;
         unsigned long long* ST = D.stats.as<unsigned long long>();
         RtOut out{(want & RT_OUT_RGBA32F) ? (float4*)D.o_rgba32f : nullptr, (want & RT_OUT_RGBA8) ? (uint32_t*)D.o_rgba8 : nullptr,
@@ -321,7 +440,8 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                     uint32_t* OC = L.occl.as<uint32_t>();
                     RT_CUDA(cudaMemsetAsync(C, 0, C_TOTAL * 4, st));
                     kbegin(RT_K_TRACE_PRIMARY);
-                    k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK);
+                    k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
+                                                                   hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
                     kend(); ++launches;
                     for (int d = 0; d <= maxd; ++d) {
                         const float4* rin = d ? L.rays[(d - 1) & 1].as<float4>() : nullptr;
@@ -335,13 +455,25 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                             k_trace_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, L.hitq_t.as<float>(), L.hitq_slot.as<int>(), wk);
                             kend(); ++launches;
                         }
+                        if (fuse) {
+                            RtFuse F{d, L.local[d].as<float4>(), rout, lout, C + d + 1, (d == 0 && maxd == 0) ? 1 : 0, pass, n_pass,
+                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out};
+                            if (F.fin && n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
+                            kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
+                            if (d == 0) k_trace_shadow<true, true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
+                                                                                                  hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0));
+                            else k_trace_shadow<false, true><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
+                            kend(); ++launches;
+                            continue;
+                        }
                         for (int c = 0; c < n_chunks; ++c) {
                             unsigned* wc = wk + 1 + (c % 7);
                             if (c >= 7) RT_CUDA(cudaMemsetAsync(wc, 0, 4, st));
                             const int lb = c * 32, nl = (D.S.n_lights - lb) < 32 ? (D.S.n_lights - lb) : 32;
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
-                            if (d == 0) k_trace_shadow<true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST);
-                            else k_trace_shadow<false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST);
+                            if (d == 0) k_trace_shadow<true, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
+                                                                                                   hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0 && c == 0));
+                            else k_trace_shadow<false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                         }
                         kbegin(d ? RT_K_SHADE_QUEUE : RT_K_SHADE_PRIMARY);
@@ -355,13 +487,15 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                         kend();
                         ++launches;
                     }
-                    // spp passes accumulate per pixel: pass p of these tiles must follow pass p-1 of the same tiles
-                    if (n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
-                    kbegin(RT_K_FINALIZE);
-                    k_finalize<<<g_flat, 256, 0, st>>>(D.S, V, tb, nt, pass, n_pass, L.local[0].as<float4>(), L.hit0_t.as<float>(), L.hit0_slot.as<int>(),
-                                                        n_pass > 1 ? D.accum.as<float4>() : nullptr, out);
-                    kend();
-                    ++launches;
+                    if (!(fuse && maxd == 0)) {
+                        // spp passes accumulate per pixel: pass p of these tiles must follow pass p-1 of the same tiles
+                        if (n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
+                        kbegin(RT_K_FINALIZE);
+                        k_finalize<<<g_flat, 256, 0, st>>>(D.S, V, tb, nt, pass, n_pass, L.local[0].as<float4>(), L.hit0_t.as<float>(), L.hit0_slot.as<int>(),
+                                                            n_pass > 1 ? D.accum.as<float4>() : nullptr, out);
+                        kend();
+                        ++launches;
+                    }
                     if (n_pass > 1 && n_lanes > 1 && pass < n_pass - 1) RT_CUDA(cudaEventRecord(D.fin_ev[wi], st));
                     if (mark && pass == n_pass - 1) {
                         const size_t i = D.wave_marks.size();
@@ -376,12 +510,24 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             RT_CUDA(cudaStreamWaitEvent(D.stream, D.lanes[li].done, 0));
         }
         RT_CUDA(cudaGetLastError());
+        if (hint_rec) { D.hint_cur = hb_out; D.hint_ready = true; for (int k = 0; k < 8; ++k) D.hint_sig[k] = sig[k]; }
+        else D.hint_ready = false;
         primary = (uint64_t)V.res_x * (uint64_t)V.n_local_rows * (uint64_t)n_pass;
     }
     RT_CUDA(cudaEventRecord(D.ev1, D.stream));
     if (fs) { fs->primary = primary; fs->shadow = 0; fs->mirror = 0; fs->launches = launches; }
     return RT_OK;
 }
+
+#ifdef RT_TILE_TIMING
+extern "C" int rt_debug_tile_times(int n_tiles, unsigned long long* host_out) {       // (start, duration) per tile of the last frame
+    static unsigned long long* buf = nullptr; static int cap = 0;
+    if (host_out && buf) return (int)cudaMemcpy(host_out, buf, (size_t)(n_tiles < cap ? n_tiles : cap) * 16, cudaMemcpyDeviceToHost);
+    if (n_tiles > cap) { if (buf) cudaFree(buf); cudaMalloc(&buf, (size_t)n_tiles * 16); cap = n_tiles; }
+    cudaMemset(buf, 0, (size_t)cap * 16);
+    return (int)cudaMemcpyToSymbol(g_rt_tile_dbg, &buf, sizeof(buf));
+}
+#endif
 
 int rt_device_read_stats(RtDevice& D, RtFrameStats* fs, std::string& err) {
     RT_CUDA(cudaSetDevice(D.device));
