@@ -30,3 +30,24 @@ for key, label in M:
     if key not in H: continue
     i = H.index(key)
     print(f"| {label} (`{key}`) [{U[i]}] | " + " | ".join(r[i] for r in R) + " |")
+
+if len(sys.argv) > 3 and sys.argv[2] == "--json":
+    # python tools/ncu_summary.py X.ncu-rep --json <workload> : merge per-kernel facts into profiles/r1_ncu_kernels.json
+    import json, os, re
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "r1_ncu_kernels.json")
+    db = json.load(open(out)) if os.path.exists(out) else {}
+    wl = db.setdefault(sys.argv[3], {})
+    def val(r, key, scale=1.0):
+        i = H.index(key); u = U[i]
+        v = float(r[i].replace(",", ""))
+        mult = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0, "ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(u, 1.0)
+        return v * mult * scale
+    alias = {"k_trace_shadow<1, 1>": "k_shadow_primary", "k_trace_shadow<1, 0>": "k_shadow_primary", "k_trace_shadow<0, 1>": "k_shadow_queue",
+             "k_trace_shadow<0, 0>": "k_shadow_queue", "k_trace_shadow<1>": "k_shadow_primary", "k_trace_shadow<0>": "k_shadow_queue"}
+    for nm, r in zip(names, R):
+        nm = nm.strip()
+        wl[alias.get(nm, nm)] = {"dram_bytes_per_launch": val(r, "dram__bytes_read.sum") + val(r, "dram__bytes_write.sum"),
+                  "issue_slot_util_pct": val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                  "warp_instructions": val(r, "smsp__inst_executed.sum"), "active_lanes": val(r, "smsp__thread_inst_executed_per_inst_executed.ratio"),
+                  "duration_ms_under_ncu": val(r, "gpu__time_duration.sum"), "source": "profiles/" + os.path.basename(rep).replace(".ncu-rep", ".md")}
+    json.dump(db, open(out, "w"), indent=1)
