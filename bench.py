@@ -109,7 +109,12 @@ def cpu_baseline(scene, params, seconds_target, threads, kind_label="port"):
     px = rng.choice(npx, n, replace=False)
     r = ora.render(params, O.ACCELERATED, threads, pixels=px)
     rays = sum(r["stats"])
-    return {"value": rays / r["seconds"] / 1e6, "unit": UNIT, "cores": threads, "kind": kind_label,
+    # the reference's own algorithm (linear scan over every primitive, Scene.cs:43-122) on a small fixed pixel subset
+    sub = rng.choice(npx, 256 if scene.n_prims > 100000 else min(npx, 65536), replace=False)
+    rf = O.OracleScene(scene, build_bvh=False).render(params, O.FAITHFUL, threads, pixels=sub)
+    faithful = {"value": sum(rf["stats"]) / max(rf["seconds"], 1e-9) / 1e6, "unit": UNIT, "cores": threads,
+                "sample": f"{len(sub)} random pixels, {sum(rf['stats'])} rays, {rf['seconds']:.2f} s, linear scan as in the reference (no BVH)"}
+    return {"value": rays / r["seconds"] / 1e6, "unit": UNIT, "cores": threads, "kind": kind_label, "faithful_scan": faithful,
             "sample": f"{n} random pixels of the {params['res_x']}x{params['res_y']} frame ({rays} rays, {r['seconds']:.2f} s), "
                       "C++ restatement of the reference's C# (oracle/, CPU-BVH mode, std::thread); the reference itself is a "
                       "single-threaded Mono loop with a linear scan and cannot run here (no Unity/.NET)",

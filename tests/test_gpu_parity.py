@@ -236,3 +236,49 @@ def test_pipelined_copy_out_equals_plain(rt, scenes):
         for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
             assert np.array_equal(a[k], b[k], equal_nan=True), (w, k)
     rt.set_option("copy_waves", 8)
+
+
+def test_cfg3_full_size(rtb, scenes, oracle):
+    """BASELINE config 3 at full size (1 003 522 primitives, 3840x2160): (a) frames from the device LBVH and from the host SAH
+    BVH are bit-identical (the result may not depend on the tree), (b) 4 096 random pixels equal the oracle (CPU BVH mode),
+    (c) ray counts: one shadow query per (hit, light)."""
+    s, p = scenes.cfg3_scene(), scenes.cfg3_params()
+    want = 2 | 4 | 8
+    frames = []
+    for builder in (0, 1):
+        r = rtb.RayTracer((0,)); r.set_option("builder", builder); r.set_scene(s)
+        frames.append(r.render(p, want))
+        frames.append(r.render(p, want))                 # second frame runs in heavy-first tile order: same bytes
+        r.close()
+    for f in frames[1:]:
+        for k in ("rgba8", "hit_id", "hit_t"):
+            assert np.array_equal(frames[0][k], f[k]), k
+    st = frames[0]["stats"]
+    hits = int((frames[0]["hit_id"][:, 0] != 0).sum())
+    assert st["rays_primary"] == 3840 * 2160 and st["rays_shadow"] == 2 * hits and st["rays_mirror"] == 0
+    px = np.random.default_rng(3).choice(3840 * 2160, 4096, replace=False)
+    ref = oracle.OracleScene(s).render(p, oracle.ACCELERATED, pixels=px)
+    got = {k: frames[0][k][px] for k in ("rgba8", "hit_id", "hit_t")}
+    assert np.array_equal(ref["hit_id"][:, :2], got["hit_id"][:, :2]) and np.array_equal(ref["hit_t"], got["hit_t"])
+    assert np.abs(ref["rgba8"].astype(int) - got["rgba8"].astype(int)).max() <= 1
+
+
+def test_cfg4_reduced_many_meshes(rt, scenes, oracle):
+    """BASELINE config 4 scaled down (2x2x2 baked instances of a 5 120-triangle sphere): per-mesh AABB gates + per-mesh materials."""
+    s, p = scenes.cfg4_scene(n=16, grid=2), scenes.cfg4_params(480, 270)
+    ref = oracle.OracleScene(s).render(p, oracle.ACCELERATED)
+    rt.set_scene(s)
+    got = rt.render(p)
+    _check(compare_renders(ref, got))
+    assert (got["hit_id"][:, 0] == 3).any() and len(np.unique(got["hit_id"][got["hit_id"][:, 0] == 3, 2])) > 3
+
+
+def test_cfg5_reduced_spheres_mirrors_spp(rt, scenes, oracle):
+    """BASELINE config 5 scaled down (2 000 spheres with 10 % mirrors + 8 000-triangle sphere, 2x2 spp, depth 4)."""
+    s, p = scenes.cfg5_scene(n=20, n_spheres=2000), scenes.cfg5_params(240, 135, 2, 4)
+    ref = oracle.OracleScene(s).render(p, oracle.ACCELERATED)
+    rt.set_scene(s)
+    got = rt.render(p)
+    _check(compare_renders(ref, got))
+    st = got["stats"]
+    assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == ref["stats"] and st["rays_mirror"] > 0
