@@ -10,6 +10,7 @@ opts = dict(a.split("=") for a in sys.argv[3:])
 timing = int(opts.pop("timing", 1))
 flush = int(opts.pop("flush", 0))
 part = int(opts.pop("part", 1))
+if "lib" in opts: rtb.host.LIB_PATH = opts.pop("lib")       # alternative build of the library (development)
 t0 = time.time()
 if cfg == "cfg2": s, p = sc.rt_unity(True), sc.rt_unity_params(3840, 2160, 4)
 elif cfg == "cfg3": s, p = sc.cfg3_scene(), sc.cfg3_params()

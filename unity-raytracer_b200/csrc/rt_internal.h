@@ -37,6 +37,8 @@ struct RtOptions {
     int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
                                        // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
     int fuse_shade = 1;                // shading (+ pixel write at depth 0) inside the shadow-trace kernel when <= 32 lights
+    int mega = 0;                      // with fuse_shade: primary trace too in the same kernel. Measured SLOWER (cfg3 2.49 -> 3.06 ms:
+                                       // the combined code no longer fits the instruction cache), kept as an option only
     int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };

@@ -15,6 +15,15 @@
 
 namespace {
 
+// Resident 128-thread CTAs per SM the trace kernels are compiled for.  The traversal is a dependent pointer chase, so
+// more resident warps hide more load latency: 8 -> 10 CTAs (64 -> 48 registers, a few spills outside the node loop)
+// measured 2.66 -> 2.50 ms on cfg3; 12 (40 registers) helps only the lean primary kernel.
+#ifndef RT_MIN_CTAS
+#define RT_MIN_CTAS 10
+#endif
+#ifndef RT_MIN_CTAS_PRIMARY
+#define RT_MIN_CTAS_PRIMARY 12
+#endif
 constexpr int STK_CAP = 24;      // shared-memory stack entries per thread
 constexpr int STK_OVF = 104;     // local-memory overflow entries (LBVH depth bound: 64 key bits + 32 index bits)
 
@@ -92,7 +101,7 @@ constexpr int C_TOTAL = C_WORK + 8 * (RT_MAX_DEPTH + 2);
 #ifdef RT_TILE_TIMING
 __device__ unsigned long long* g_rt_tile_dbg = nullptr;      // per tile: (start ns, duration ns); development aid only
 #endif
-__global__ void __launch_bounds__(128, 8) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
+__global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                         float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work,
                                                         RtHintIn hin, RtHintOut hout) {
     RT_DECL_STACK(stk);
@@ -126,7 +135,7 @@ __global__ void __launch_bounds__(128, 8) k_trace_primary(RtScene S, RtView V, i
     }
 }
 
-__global__ void __launch_bounds__(128, 8) k_trace_queue(RtScene S, const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays,
+__global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_queue(RtScene S, const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays,
                                                       float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work) {
     RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
@@ -170,10 +179,14 @@ struct RtFuse {
     float4* rays_out; float4* link_out; unsigned* next_count;      // mirror-ray queue of the next depth (null at max depth)
     int fin;                           // 1: also finalize (depth 0 wave, no mirror depth above it)
     int pass, n_pass; float4* accum; RtOut out;
+    float* hit_t_out; int* hit_slot_out;       // MEGA only: primary hit record, written when a later kernel needs it (!fin)
 };
 
-template <bool DEPTH0, bool FUSE>
-__global__ void __launch_bounds__(128, 8) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
+// MEGA (depth 0, FUSE): ray generation and the closest-hit query of k_trace_primary run in this kernel too, so a pixel goes
+// from camera ray to final colour in registers: no hit record round trip, no regeneration of the primary ray, one launch
+// and one drain per wave instead of two.
+template <bool DEPTH0, bool FUSE, bool MEGA>
+__global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                           const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
                                                           const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
                                                           int light_begin, int n_l, uint32_t* __restrict__ occl, unsigned* work,
@@ -189,17 +202,34 @@ __global__ void __launch_bounds__(128, 8) k_trace_shadow(RtScene S, RtView V, in
         if (DEPTH0) wt = rt_hint_tile(hin, wt, lane);
         const long long c0 = clock64();
         const unsigned q = (unsigned)wt * 32u + lane;
-        const int slot = q < n ? RT_LD_STREAM(hit_slot + q) : -2;
-        const bool has = slot >= 0;
-        uint32_t mask = 0;
         f3 O = mk3(0.f, 0.f, 0.f), D = mk3(0.f, 0.f, 1.f);
         float ht = 0.f;
+        int slot;
+        if (MEGA) {                                            // k_trace_primary's body
+            int x, y;
+            const bool valid = rt_item_to_pixel(V, tile_begin + wt, lane, x, y);
+            float bt = FLT_MAX; int bs = -1;
+            O = V.pos; D = V.fwd;
+            bool active = false;
+            if (valid) rt_primary_ray(V, x, y, si, sj, O, D);
+            const f3 inv = rt_rcp3(D);
+            if (valid) active = rt_scene_gate(S, O, inv);                                           // Scene.cs:54
+            if (S.packet) {
+                if (__any_sync(full, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
+            } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
+            slot = valid ? bs : -2; ht = bt;
+            if (!F.fin) { RT_ST_STREAM(F.hit_t_out + q, bt); RT_ST_STREAM(F.hit_slot_out + q, slot); }
+        } else slot = q < n ? RT_LD_STREAM(hit_slot + q) : -2;
+        const bool has = slot >= 0;
+        uint32_t mask = 0;
         if (__any_sync(full, has)) {
             f3 P = mk3(0.f, 0.f, 0.f), sO = P;
             if (has) {
                 f3 N; int mat_id;
-                item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
-                ht = RT_LD_STREAM(hit_t + q);
+                if (!MEGA) {
+                    item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
+                    ht = RT_LD_STREAM(hit_t + q);
+                }
                 rt_surf_geom(S, O, D, ht, slot, P, N, mat_id);
                 sO = P + N * RT_SHADOW_EPS;                                                        // RTS:331
             }
@@ -421,10 +451,12 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         const int g_trace = persistent_grid(k_trace_primary, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_traceq = persistent_grid(k_trace_queue, block, smem, D.sm_count, opt.ctas_per_sm);
         const bool fuse = opt.fuse_shade && n_chunks == 1;                  // shade (+ finalize) inside the shadow kernel
-        const int g_shadow0 = fuse ? persistent_grid(k_trace_shadow<true, true>, block, smem, D.sm_count, opt.ctas_per_sm)
-                                   : persistent_grid(k_trace_shadow<true, false>, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shadown = fuse ? persistent_grid(k_trace_shadow<false, true>, block, smem, D.sm_count, opt.ctas_per_sm)
-                                   : persistent_grid(k_trace_shadow<false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const bool mega = fuse && opt.mega;                                 // ... and the primary trace too
+        const int g_shadow0 = mega ? persistent_grid(k_trace_shadow<true, true, true>, block, smem, D.sm_count, opt.ctas_per_sm)
+                            : fuse ? persistent_grid(k_trace_shadow<true, true, false>, block, smem, D.sm_count, opt.ctas_per_sm)
+                                   : persistent_grid(k_trace_shadow<true, false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadown = fuse ? persistent_grid(k_trace_shadow<false, true, false>, block, smem, D.sm_count, opt.ctas_per_sm)
+                                   : persistent_grid(k_trace_shadow<false, false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_flat = D.sm_count * 8;
         unsigned long long* ST = D.stats.as<unsigned long long>();
         RtOut out{(want & RT_OUT_RGBA32F) ? (float4*)D.o_rgba32f : nullptr, (want & RT_OUT_RGBA8) ? (uint32_t*)D.o_rgba8 : nullptr,
@@ -439,10 +471,12 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                     unsigned* C = L.counters.as<unsigned>();
                     uint32_t* OC = L.occl.as<uint32_t>();
                     RT_CUDA(cudaMemsetAsync(C, 0, C_TOTAL * 4, st));
+                    if (!mega) {
                     kbegin(RT_K_TRACE_PRIMARY);
                     k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
                                                                    hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
                     kend(); ++launches;
+                    }
                     for (int d = 0; d <= maxd; ++d) {
                         const float4* rin = d ? L.rays[(d - 1) & 1].as<float4>() : nullptr;
                         float4* rout = d < maxd ? L.rays[d & 1].as<float4>() : nullptr;
@@ -457,12 +491,14 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                         }
                         if (fuse) {
                             RtFuse F{d, L.local[d].as<float4>(), rout, lout, C + d + 1, (d == 0 && maxd == 0) ? 1 : 0, pass, n_pass,
-                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out};
+                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out, L.hit0_t.as<float>(), L.hit0_slot.as<int>()};
                             if (F.fin && n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
-                            kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
-                            if (d == 0) k_trace_shadow<true, true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
+                            kbegin(d ? RT_K_SHADOW_QUEUE : (mega ? RT_K_TRACE_PRIMARY : RT_K_SHADOW_PRIMARY));
+                            if (d == 0 && mega) k_trace_shadow<true, true, true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
+                                                                                                  hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
+                            else if (d == 0) k_trace_shadow<true, true, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
                                                                                                   hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0));
-                            else k_trace_shadow<false, true><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
+                            else k_trace_shadow<false, true, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                             continue;
                         }
@@ -471,9 +507,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                             if (c >= 7) RT_CUDA(cudaMemsetAsync(wc, 0, 4, st));
                             const int lb = c * 32, nl = (D.S.n_lights - lb) < 32 ? (D.S.n_lights - lb) : 32;
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
-                            if (d == 0) k_trace_shadow<true, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
+                            if (d == 0) k_trace_shadow<true, false, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
                                                                                                    hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0 && c == 0));
-                            else k_trace_shadow<false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
+                            else k_trace_shadow<false, false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                         }
                         kbegin(d ? RT_K_SHADE_QUEUE : RT_K_SHADE_PRIMARY);
