@@ -380,6 +380,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         const size_t smem = (size_t)STK_CAP * block * sizeof(int);
         int wave_tiles = (opt.chunk_pixels / 32) < 1 ? 1 : (opt.chunk_pixels / 32);
         if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
+        const int chunk_tiles = wave_tiles;                                 // capacity limit set by chunk_pixels
         bool mark = split < 0 && V.world == 1;
         const int n_split = split < 0 ? -split : split;
         if (n_split > 1) {
@@ -393,7 +394,27 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                 wave_tiles = rows_per_wave * V.tiles_x;
             } else mark = false;
         } else mark = false;
-        const int waves_per_pass = (V.n_tiles + wave_tiles - 1) / wave_tiles;
+        // wave plan: first tile of every wave (+ end).  Uniform, except for the pipelined copy-out with the default
+        // copy_waves = 8, where small waves sit at both ends: 1,2,4,4,2,2,1 sixteenths of the rows.  The copy engine needs
+        // as long as the SMs (2.3 ms of PCIe for a 4K Color[] frame), so the call ends at
+        // max(first wave + copy of everything, render of everything + copy of the last wave): both ends want to be small,
+        // while every extra wave costs a drain, so the middle ones stay big.
+        std::vector<int> wave_tb;
+        {
+            const int tile_rows = V.n_tiles / V.tiles_x;
+            const int cap_rows = chunk_tiles / V.tiles_x;
+            static const int plan16[7] = {1, 2, 4, 4, 2, 2, 1};
+            if (mark && n_split == 8 && tile_rows >= 64 && cap_rows >= tile_rows / 4 + 2) {
+                int acc = 0;
+                for (int k = 0; k < 7; ++k) { wave_tb.push_back((int)((long long)tile_rows * acc / 16) * V.tiles_x); acc += plan16[k]; }
+                wave_tiles = ((tile_rows * 4 + 15) / 16 + 1) * V.tiles_x;            // capacity: the largest wave
+                if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
+            } else {
+                for (int tb = 0; tb < V.n_tiles; tb += wave_tiles) wave_tb.push_back(tb);
+            }
+            wave_tb.push_back(V.n_tiles);
+        }
+        const int waves_per_pass = (int)wave_tb.size() - 1;
         const int n_lanes = (opt.lanes > 1 && !opt.kernel_timing && waves_per_pass * n_pass > 1) ? 2 : 1;
         const size_t W = (size_t)wave_tiles * 32;
         const int maxd = V.max_bounces;
@@ -422,7 +443,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             while (n_lanes > 1 && (int)D.fin_ev.size() < waves_per_pass) { cudaEvent_t e; RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.fin_ev.push_back(e); }
         }
         // ---- cost hints of the previous frame (same layout only) / recording for the next ----
-        const long long sig[8] = {V.n_tiles, wave_tiles, V.res_x, V.res_y, V.rank, V.world, V.band_rows, (long long)D.S.n_prims};
+        const long long sig[8] = {V.n_tiles, (long long)wave_tiles * 64 + waves_per_pass, V.res_x, V.res_y, V.rank, V.world, V.band_rows, (long long)D.S.n_prims};
         bool hint_in = opt.hints && D.hint_ready;
         for (int k = 0; k < 8; ++k) hint_in = hint_in && D.hint_sig[k] == sig[k];
         const bool hint_rec = opt.hints != 0;
@@ -464,8 +485,8 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         int wave_seq = 0;
         for (int sj = 0, pass = 0; sj < g; ++sj)
             for (int si = 0; si < g; ++si, ++pass)
-                for (int tb = 0, wi = 0; tb < V.n_tiles; tb += wave_tiles, ++wi, ++wave_seq) {
-                    const int nt = (V.n_tiles - tb) < wave_tiles ? (V.n_tiles - tb) : wave_tiles;
+                for (int wi = 0; wi < waves_per_pass; ++wi, ++wave_seq) {
+                    const int tb = wave_tb[wi], nt = wave_tb[wi + 1] - tb;
                     RtDevice::Lane& L = D.lanes[wave_seq % n_lanes];
                     st = (wave_seq % n_lanes) ? L.own_stream : D.stream;
                     unsigned* C = L.counters.as<unsigned>();
