@@ -170,7 +170,7 @@ def run_ours(args, rank, world, local_rank):
     rt.set_option("builder", 1 if args.builder == "sah" else 0)
     stream = torch.cuda.Stream()
     rt.set_stream(stream.cuda_stream)
-    rt.set_partition(rank, world, 32)
+    rt.set_partition(rank, world, args.band_rows)
     t0 = time.perf_counter(); rt.set_scene(scene); commit_wall = time.perf_counter() - t0
     cstats = rt.stats()
     X, Y = params["res_x"], params["res_y"]
@@ -212,7 +212,12 @@ def run_ours(args, rank, world, local_rank):
         a.record(stream); rt.render_device(params, want); b.record(stream)
     barrier()
     ms = torch.tensor([a.elapsed_time(b) for a, b in ev], dtype=torch.float64, device="cuda")
+    ms_by_rank = [float(ms.mean().item())]
     if world > 1:
+        mine = ms.mean().reshape(1)
+        allm = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allm, mine)
+        ms_by_rank = [float(x.item()) for x in allm]
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.sum().item())
     clocks = sampler.stop() if sampler else None
@@ -292,10 +297,10 @@ def run_ours(args, rank, world, local_rank):
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
                 "config": {"workload": f"{args.workload}: {desc}", "rays_per_step": rays_step, "l2": "flushed between timed steps (256 MiB memset), per-step CUDA events",
-                           "partition": f"{world} rank(s), interleaved 32-row bands, scene replicated", "gather": gather, "output": "RGBA32F full frame on GPU 0",
+                           "partition": f"{world} rank(s), interleaved {args.band_rows}-row bands, scene replicated", "gather": gather, "output": "RGBA32F full frame on GPU 0",
                            "bvh": f"builder={args.builder} (commit is outside the timed region and reported under `commit`)",
                            "tile_order": "heavy-first from the previous frame's measured tile costs (warm-up frames establish it)"},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
+                "ms_per_step_by_rank": ms_by_rank, "rays_rank0": rays_rank, "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
                 "commit": {"ms_upload": cstats["ms_commit_upload"], "ms_bvh_build": cstats["ms_commit_build"], "h2d_bytes": cstats["h2d_bytes"],
                            "wall_ms": 1e3 * commit_wall, "n_prims": cstats["n_prims"], "n_nodes": cstats["n_nodes"], "builder": args.builder}}
         print(json.dumps(line), file=_OUT, flush=True)
@@ -317,6 +322,7 @@ def main():
     ap.add_argument("--workload", default="cfg3")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--band-rows", type=int, default=32, help="height of the interleaved row bands of the N-rank partition (multiple of 4)")
     ap.add_argument("--builder", default="sah", choices=["sah", "lbvh"],
                     help="BVH builder at commit: host binned-SAH (default; static scene, best frame time) or device LBVH (fast commit)")
     args = ap.parse_args()

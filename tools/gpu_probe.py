@@ -10,6 +10,7 @@ opts = dict(a.split("=") for a in sys.argv[3:])
 timing = int(opts.pop("timing", 1))
 flush = int(opts.pop("flush", 0))
 part = int(opts.pop("part", 1))
+host_time = int(opts.pop("host", 0))
 if "lib" in opts: rtb.host.LIB_PATH = opts.pop("lib")       # alternative build of the library (development)
 t0 = time.time()
 if cfg == "cfg2": s, p = sc.rt_unity(True), sc.rt_unity_params(3840, 2160, 4)
@@ -19,7 +20,7 @@ elif cfg == "cfg5": s, p = sc.cfg5_scene(), sc.cfg5_params()
 else: s, p = sc.cfg3_scene(n=int(cfg)), sc.cfg3_params()
 print(f"scene {cfg}: {s.n_prims} prims, generated in {time.time()-t0:.1f}s", flush=True)
 rt = rtb.RayTracer((0,))
-if part > 1: rt.set_partition(0, part, 32)
+if part > 1: rt.set_partition(int(opts.pop('rank', 0)), part, 32)
 for k, v in opts.items(): rt.set_option(k, float(v))
 rt.set_option("kernel_timing", timing)
 t0 = time.time(); rt.set_scene(s); print(f"commit wall {time.time()-t0:.3f}s", flush=True)
@@ -30,6 +31,12 @@ if flush:
 for i in range(reps):
     if fl is not None:
         fl.zero_(); torch.cuda.synchronize()
+    if host_time:                                            # host enqueue time of one frame (no sync inside the call)
+        import torch
+        torch.cuda.synchronize(); h0 = time.perf_counter()
+        rt.render_device(p, rtb.host.RT_OUT_RGBA8, sync_stats=False)
+        h1 = time.perf_counter(); torch.cuda.synchronize(); h2 = time.perf_counter()
+        print(f"host enqueue {1e3*(h1-h0):.3f} ms, enqueue+drain {1e3*(h2-h0):.3f} ms", flush=True)
     st = rt.render_device(p, rtb.host.RT_OUT_RGBA8, sync_stats=True)
     rays = st["rays_primary"] + st["rays_shadow"] + st["rays_mirror"]
     print(json.dumps(dict(ms=round(st["ms_render"], 3), mrays=round(rays / st["ms_render"] / 1e3, 1), rays=rays, launches=st["kernel_launches"],
