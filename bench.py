@@ -94,6 +94,51 @@ def measured_peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def microbench_peaks(device):
+    """L2-resident read bandwidth (GB/s) and FP32 FMA rate (TFLOP/s) measured on this box by librtb200_microbench.so
+    (unity-raytracer_b200/csrc/rt_microbench.cu): the denominators of SURVEY.md §8(d)'s T_l2 and T_issue."""
+    import ctypes as C
+    try:
+        lib = C.CDLL(os.path.join(ROOT, "unity-raytracer_b200", "librtb200_microbench.so"))
+        lib.rtmb_l2_read_gbs.restype = C.c_double; lib.rtmb_l2_read_gbs.argtypes = [C.c_int, C.c_int, C.c_int]
+        lib.rtmb_fp32_tflops.restype = C.c_double; lib.rtmb_fp32_tflops.argtypes = [C.c_int, C.c_int]
+        l2 = lib.rtmb_l2_read_gbs(device, 32, 200)
+        fp = lib.rtmb_fp32_tflops(device, 1 << 16)
+        if l2 > 0 and fp > 0:
+            return l2, fp, "measured live (rt_microbench.cu: 32 MiB L2-resident ld.cg sweep; 8-chain FFMA loop)"
+    except OSError:
+        pass
+    return 18000.0, 64.7, "fallback (profiles/r1_microbench.json, measured on this pool's B200)"
+
+
+def three_bounds(workload, builder, dom, ms_launch, launches_per_frame, t_hbm_ms, device):
+    """T_hbm, T_l2 and T_issue lower bounds of the dominant kernel from the instrumented build's visit
+    counters (profiles/r1_visit_counts_<workload>.json; deterministic for a given BVH), against its measured time."""
+    try:
+        with open(os.path.join(ROOT, "profiles", f"r1_visit_counts_{workload}.json")) as f:
+            rec = json.load(f)[f"builder={builder},packet=1"]
+    except Exception:
+        return None
+    c = rec["any" if dom.startswith("shadow") else "closest"]
+    l2_gbs, fp_tf, src = microbench_peaks(device)
+    lane_nodes = c["lane_node_visits"] + c["packet_lane_node_visits"]; lane_prims = c["lane_prim_tests"] + c["packet_lane_prim_tests"]
+    flops = 48 * lane_nodes + 53 * lane_prims                          # 2 boxes x 24 flops per node visit, 53 per triangle test (§8(d) model)
+    l2_bytes = 64 * (c["lane_node_visits"] + c["packet_node_fetches"]) + 48 * (c["lane_prim_tests"] + c["packet_prim_fetches"])
+    t_frame = ms_launch * launches_per_frame
+    t_l2, t_issue = l2_bytes / (l2_gbs * 1e9) * 1e3, flops / (fp_tf * 1e12) * 1e3
+    bounds = {"hbm_ms": t_hbm_ms, "l2_ms": t_l2, "issue_ms": t_issue}
+    binding = max(bounds, key=bounds.get)
+    rays = c["lane_rays"] + c["packet_rays"]
+    return {"per_frame_ms": bounds, "binding": binding.replace("_ms", ""), "measured_ms": t_frame, "frac_of_binding": bounds[binding] / t_frame,
+            "flops": flops, "l2_request_bytes": l2_bytes, "l2_peak_gbs": l2_gbs, "fp32_peak_tflops": fp_tf, "peaks": src,
+            "per_ray": {"node_visits": lane_nodes / max(1, rays), "prim_tests": lane_prims / max(1, rays),
+                        "node_fetches": (c["lane_node_visits"] + c["packet_node_fetches"]) / max(1, rays),
+                        "prim_fetches": (c["lane_prim_tests"] + c["packet_prim_fetches"]) / max(1, rays)},
+            "counts": f"profiles/r1_visit_counts_{workload}.json (instrumented build, tools/visit_counts.py)",
+            "note": "flops: 24 per box test, 53 per triangle test, every lane of a packet counted (FMA peak counts 2 flops per "
+                    "instruction; the slab/triangle arithmetic is -fmad=false mul/add/min/max, 1 flop per instruction, so 50% is the ceiling)"}
+
+
 def cpu_baseline(scene, params, seconds_target, threads, kind_label="port"):
     """The oracle's accelerated mode (CPU BVH over the same exact primitive tests) on a bounded random pixel sample of
     the same workload, all host threads.  Returns the cpu_baseline object."""
@@ -168,6 +213,8 @@ def run_ours(args, rank, world, local_rank):
     scene, params, desc = workload(args.workload, rtb.scenes)
     rt = rtb.RayTracer((local_rank,))
     rt.set_option("builder", 1 if args.builder == "sah" else 0)
+    for kv in args.opt:
+        k, v = kv.split("="); rt.set_option(k, float(v))
     stream = torch.cuda.Stream()
     rt.set_stream(stream.cuda_stream)
     rt.set_partition(rank, world, args.band_rows)
@@ -176,7 +223,9 @@ def run_ours(args, rank, world, local_rank):
     X, Y = params["res_x"], params["res_y"]
     want = H.RT_OUT_RGBA32F
     gather = "single GPU"
-    if world > 1:                        # peer-store gather: every rank writes its bands into rank 0's framebuffer
+    if world > 1 and args.local_out:
+        gather = "NONE (--local-out, development run)"
+    elif world > 1:                      # peer-store gather: every rank writes its bands into rank 0's framebuffer
         handles = [None]
         if rank == 0:
             rt.alloc_outputs(X, Y, want); handles[0] = rt.export_outputs()
@@ -282,11 +331,14 @@ def run_ours(args, rank, world, local_rank):
                          "source": prof.get("source")}
         except Exception:
             pass
+        tb = None
+        if world == 1:
+            tb = three_bounds(args.workload, args.builder, dom, ms_launch, launches_per_frame, alg_bytes * launches_per_frame / (peak * 1e9) * 1e3, local_rank)
         roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": traffic, "peak_source": peak_src, "ms_per_launch": ms_launch, "algorithmic_bytes_per_launch": alg_bytes,
                     "kernel_share_of_step": ksum[dom] / max(1e-9, sum(ksum.values())),
                     "ms_per_step_by_kernel": {k: v / args.steps for k, v in ksum.items() if v > 0},
-                    "issue": issue,
+                    "issue": issue, "three_bounds": tb,
                     "note": "BVH traversal is bound by SM issue slots / dependent-load latency, not by HBM (the scene is L2-resident): the hbm "
                             "fraction is reported because the bench vocabulary is hbm|tensor; `issue` carries the binding bound (DESIGN.md §5)"}
         cb = None
@@ -298,7 +350,7 @@ def run_ours(args, rank, world, local_rank):
                 "data": "synthetic",
                 "config": {"workload": f"{args.workload}: {desc}", "rays_per_step": rays_step, "l2": "flushed between timed steps (256 MiB memset), per-step CUDA events",
                            "partition": f"{world} rank(s), interleaved {args.band_rows}-row bands, scene replicated", "gather": gather, "output": "RGBA32F full frame on GPU 0",
-                           "bvh": f"builder={args.builder} (commit is outside the timed region and reported under `commit`)",
+                           "options": args.opt, "bvh": f"builder={args.builder} (commit is outside the timed region and reported under `commit`)",
                            "tile_order": "heavy-first from the previous frame's measured tile costs (warm-up frames establish it)"},
                 "ms_per_step_by_rank": ms_by_rank, "rays_rank0": rays_rank, "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
                 "commit": {"ms_upload": cstats["ms_commit_upload"], "ms_bvh_build": cstats["ms_commit_build"], "h2d_bytes": cstats["h2d_bytes"],
@@ -323,6 +375,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--band-rows", type=int, default=32, help="height of the interleaved row bands of the N-rank partition (multiple of 4)")
+    ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE", help="library option passed to rt_set_option (development)")
+    ap.add_argument("--local-out", action="store_true", help="N>1: every rank keeps its bands in its own framebuffer (development: "
+                    "isolates the cost of the peer-store gather; the frame is then NOT assembled on GPU 0)")
     ap.add_argument("--builder", default="sah", choices=["sah", "lbvh"],
                     help="BVH builder at commit: host binned-SAH (default; static scene, best frame time) or device LBVH (fast commit)")
     args = ap.parse_args()

@@ -29,6 +29,7 @@ def _newest_dep():
 
 
 def build(force=False, verbose=False):
+    build_microbench(force)
     if not force and os.path.exists(OUT) and os.path.getmtime(OUT) >= _newest_dep():
         return OUT
     objdir = os.path.join(HERE, "build")
@@ -58,6 +59,23 @@ def build(force=False, verbose=False):
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("link failed")
     return OUT
+
+
+MICROBENCH_OUT = os.path.join(HERE, "librtb200_microbench.so")
+
+
+def build_microbench(force=False):
+    """Measurement infrastructure (L2 read bandwidth, FP32 FMA rate) for bench.py's rooflines; not part of librtb200.so."""
+    src = os.path.join(CSRC, "rt_microbench.cu")
+    if not force and os.path.exists(MICROBENCH_OUT) and os.path.getmtime(MICROBENCH_OUT) >= os.path.getmtime(src):
+        return MICROBENCH_OUT
+    cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-shared",
+           src, "-o", MICROBENCH_OUT]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc failed on rt_microbench.cu")
+    return MICROBENCH_OUT
 
 
 if __name__ == "__main__":

@@ -476,7 +476,6 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "waves must be 1..64"); c->opt.waves = (int)value; }
     else if (k == "lanes") { if (value != 1 && value != 2) return fail(c, RT_E_INVALID, "lanes must be 1 or 2"); c->opt.lanes = (int)value; }
     else if (k == "fuse_shade") { c->opt.fuse_shade = value != 0; }
-    else if (k == "mega") { c->opt.mega = value != 0; }
     else if (k == "prefetch") { c->opt.prefetch = value != 0; }
     else if (k == "prefetch_max_mb") { c->opt.prefetch_max_mb = (int)value; }
     else if (k == "hints") { c->opt.hints = value != 0; }

@@ -151,6 +151,26 @@ RT_HD bool rt_ray_sphere(f3 O, f3 D, f3 c, float r2, float& t_out) {
 // ---------------------------------------------------------------------------------------------------------------
 RT_HD bool rt_scene_gate(const RtScene& S, f3 O, f3 inv) { return rt_ray_aabb_inv(O, inv, S.aabb_min, S.aabb_max); }
 // traversal's own (conservative) inverse direction: the exact one, with zero components replaced by a huge finite value
+// Visit counters of the instrumented development build (-DRT_COUNT_VISITS, tools/visit_counts.py): per query class
+// (closest-hit = 0, any-hit = 10): +0 rays, +1 node visits, +2 primitive tests of the per-lane traversal; +3 warps, +4 rays,
+// +5 warp-level node fetches, +6 lane-level node visits, +7 warp-level primitive fetches, +8 lane-level primitive tests of
+// the packet traversal.  Compiled out of the product build.
+#if defined(RT_COUNT_VISITS) && defined(__CUDACC__)
+static __device__ unsigned long long g_rt_visits[20];
+#endif
+#if defined(RT_COUNT_VISITS) && defined(__CUDA_ARCH__)
+#define RT_COUNT(i, n) atomicAdd(&g_rt_visits[i], (unsigned long long)(n))
+#else
+#define RT_COUNT(i, n) ((void)0)
+#endif
+#ifdef RT_COUNT_VISITS
+#define RT_CNT_PARAM , int cbase
+#define RT_CNT_ARG(ANY) , ((ANY) ? 10 : 0)
+#else
+#define RT_CNT_PARAM
+#define RT_CNT_ARG(ANY)
+#endif
+
 RT_HD float rt_safe_inv(float d, float inv) { return fabsf(d) > 1e-30f ? inv : copysignf(1e30f, d); }
 
 template <bool ANY, class STK>
@@ -164,8 +184,10 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
     float tcull = ANY ? rt_sqrt(any_d2) * S.t_slack : INFINITY;
     int32_t gate_mesh = -1; bool gate_ok = true;
     int32_t node = S.root;
+    RT_COUNT((ANY ? 10 : 0) + 0, 1);
     for (;;) {
         while (node >= 0) {
+            RT_COUNT((ANY ? 10 : 0) + 1, 1);
             const float4* np = S.nodes + 4 * (size_t)node;
             float4 n0 = RT_LDG4(np), n1 = RT_LDG4(np + 1), n2 = RT_LDG4(np + 2), n3 = RT_LDG4(np + 3);
             float ax0 = rt_fma(n0.x, idx_, -oodx), ax1 = rt_fma(n0.y, idx_, -oodx);
@@ -199,6 +221,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
                 int32_t slot = first + k;
                 const float4* pp = S.prims + 3 * (size_t)slot;
                 float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+                RT_COUNT((ANY ? 10 : 0) + 2, 1);
                 float t; bool hit;
                 if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
                 else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);

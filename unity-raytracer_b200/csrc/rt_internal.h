@@ -37,8 +37,6 @@ struct RtOptions {
     int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
                                        // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
     int fuse_shade = 1;                // shading (+ pixel write at depth 0) inside the shadow-trace kernel when <= 32 lights
-    int mega = 0;                      // with fuse_shade: primary trace too in the same kernel. Measured SLOWER (cfg3 2.49 -> 3.06 ms:
-                                       // the combined code no longer fits the instruction cache), kept as an option only
     int prefetch = 0;                  // bulk L2 prefetch of nodes + primitives at the start of every frame ...
     int prefetch_max_mb = 96;          // ... when they total at most this many MiB (L2 is 126 MB)
     int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs

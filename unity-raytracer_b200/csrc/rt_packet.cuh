@@ -40,11 +40,15 @@ __device__ __forceinline__ bool rt_warp_coherent(f3 O, f3 D, bool active, float 
 #define RT_PACKET_DONE ((int32_t)0x80000000)
 template <int OCT, class STK>
 __device__ __forceinline__ int32_t rt_packet_descend(const float4* __restrict__ nodes, float idx_, float idy_, float idz_,
-                                                     float oodx, float oody, float oodz, float tcull, STK& stk, int32_t node) {
+                                                     float oodx, float oody, float oodz, float tcull, STK& stk, int32_t node RT_CNT_PARAM) {
     const unsigned full = 0xffffffffu;
     while (node >= 0) {
         const float4* np = nodes + 4 * (size_t)node;
         float4 n0 = RT_LDG4(np), n1 = RT_LDG4(np + 1), n2 = RT_LDG4(np + 2), n3 = RT_LDG4(np + 3);
+#ifdef RT_COUNT_VISITS
+        { unsigned live = __ballot_sync(full, tcull >= 0.0f);
+          if ((threadIdx.x & 31) == 0) { RT_COUNT(cbase + 5, 1); RT_COUNT(cbase + 6, __popc(live)); } }
+#endif
         float amin, amax, bmin, bmax;
         if (OCT == 8) {
             float ax0 = rt_fma(n0.x, idx_, -oodx), ax1 = rt_fma(n0.y, idx_, -oodx);
@@ -113,17 +117,21 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
     }
     const float4* __restrict__ nodes = S.nodes;
     int32_t node = S.root;                            // warp-uniform from here on
+#ifdef RT_COUNT_VISITS
+    { unsigned am = __ballot_sync(full, active);
+      if ((threadIdx.x & 31) == 0) { RT_COUNT((ANY ? 10 : 0) + 3, 1); RT_COUNT((ANY ? 10 : 0) + 4, __popc(am)); } }
+#endif
     for (;;) {
         switch (oct) {
-            case 0: node = rt_packet_descend<0>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            case 1: node = rt_packet_descend<1>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            case 2: node = rt_packet_descend<2>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            case 3: node = rt_packet_descend<3>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            case 4: node = rt_packet_descend<4>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            case 5: node = rt_packet_descend<5>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            case 6: node = rt_packet_descend<6>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            case 7: node = rt_packet_descend<7>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
-            default: node = rt_packet_descend<8>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node); break;
+            case 0: node = rt_packet_descend<0>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 1: node = rt_packet_descend<1>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 2: node = rt_packet_descend<2>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 3: node = rt_packet_descend<3>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 4: node = rt_packet_descend<4>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 5: node = rt_packet_descend<5>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 6: node = rt_packet_descend<6>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 7: node = rt_packet_descend<7>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            default: node = rt_packet_descend<8>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
         }
         if (node == RT_PACKET_DONE) return ANY ? found : best_slot >= 0;
         {
@@ -133,6 +141,10 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                 int32_t slot = first + k;
                 const float4* pp = S.prims + 3 * (size_t)slot;
                 float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+#ifdef RT_COUNT_VISITS
+                { unsigned live = __ballot_sync(full, tcull >= 0.0f);
+                  if ((threadIdx.x & 31) == 0) { RT_COUNT((ANY ? 10 : 0) + 7, 1); RT_COUNT((ANY ? 10 : 0) + 8, __popc(live)); } }
+#endif
                 if (tcull < 0.0f) continue;                             // lane has no ray / is already occluded
                 float t; bool hit;
                 if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);

@@ -24,7 +24,10 @@ namespace {
 #ifndef RT_MIN_CTAS_PRIMARY
 #define RT_MIN_CTAS_PRIMARY 12
 #endif
-constexpr int STK_CAP = 24;      // shared-memory stack entries per thread
+#ifndef RT_STK_CAP
+#define RT_STK_CAP 24
+#endif
+constexpr int STK_CAP = RT_STK_CAP;   // shared-memory stack entries per thread
 constexpr int STK_OVF = 104;     // local-memory overflow entries (LBVH depth bound: 64 key bits + 32 index bits)
 
 // sp lives in a register; the (rarely used) overflow array is a separate local object so that indexing it dynamically
@@ -179,13 +182,11 @@ struct RtFuse {
     float4* rays_out; float4* link_out; unsigned* next_count;      // mirror-ray queue of the next depth (null at max depth)
     int fin;                           // 1: also finalize (depth 0 wave, no mirror depth above it)
     int pass, n_pass; float4* accum; RtOut out;
-    float* hit_t_out; int* hit_slot_out;       // MEGA only: primary hit record, written when a later kernel needs it (!fin)
 };
 
-// MEGA (depth 0, FUSE): ray generation and the closest-hit query of k_trace_primary run in this kernel too, so a pixel goes
-// from camera ray to final colour in registers: no hit record round trip, no regeneration of the primary ray, one launch
-// and one drain per wave instead of two.
-template <bool DEPTH0, bool FUSE, bool MEGA>
+// (A "mega" variant that also ran k_trace_primary's body here, camera ray to final colour in registers, was measured
+// SLOWER on cfg3 — 2.49 -> 3.06 ms, instruction-cache pressure of the two traversal instantiations in one loop — and removed.)
+template <bool DEPTH0, bool FUSE>
 __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                           const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
                                                           const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
@@ -205,31 +206,15 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
         f3 O = mk3(0.f, 0.f, 0.f), D = mk3(0.f, 0.f, 1.f);
         float ht = 0.f;
         int slot;
-        if (MEGA) {                                            // k_trace_primary's body
-            int x, y;
-            const bool valid = rt_item_to_pixel(V, tile_begin + wt, lane, x, y);
-            float bt = FLT_MAX; int bs = -1;
-            O = V.pos; D = V.fwd;
-            bool active = false;
-            if (valid) rt_primary_ray(V, x, y, si, sj, O, D);
-            const f3 inv = rt_rcp3(D);
-            if (valid) active = rt_scene_gate(S, O, inv);                                           // Scene.cs:54
-            if (S.packet) {
-                if (__any_sync(full, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
-            } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
-            slot = valid ? bs : -2; ht = bt;
-            if (!F.fin) { RT_ST_STREAM(F.hit_t_out + q, bt); RT_ST_STREAM(F.hit_slot_out + q, slot); }
-        } else slot = q < n ? RT_LD_STREAM(hit_slot + q) : -2;
+        slot = q < n ? RT_LD_STREAM(hit_slot + q) : -2;
         const bool has = slot >= 0;
         uint32_t mask = 0;
         if (__any_sync(full, has)) {
             f3 P = mk3(0.f, 0.f, 0.f), sO = P;
             if (has) {
                 f3 N; int mat_id;
-                if (!MEGA) {
-                    item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
-                    ht = RT_LD_STREAM(hit_t + q);
-                }
+                item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
+                ht = RT_LD_STREAM(hit_t + q);
                 rt_surf_geom(S, O, D, ht, slot, P, N, mat_id);
                 sO = P + N * RT_SHADOW_EPS;                                                        // RTS:331
             }
@@ -488,12 +473,10 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         const int g_trace = persistent_grid(k_trace_primary, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_traceq = persistent_grid(k_trace_queue, block, smem, D.sm_count, opt.ctas_per_sm);
         const bool fuse = opt.fuse_shade && n_chunks == 1;                  // shade (+ finalize) inside the shadow kernel
-        const bool mega = fuse && opt.mega;                                 // ... and the primary trace too
-        const int g_shadow0 = mega ? persistent_grid(k_trace_shadow<true, true, true>, block, smem, D.sm_count, opt.ctas_per_sm)
-                            : fuse ? persistent_grid(k_trace_shadow<true, true, false>, block, smem, D.sm_count, opt.ctas_per_sm)
-                                   : persistent_grid(k_trace_shadow<true, false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shadown = fuse ? persistent_grid(k_trace_shadow<false, true, false>, block, smem, D.sm_count, opt.ctas_per_sm)
-                                   : persistent_grid(k_trace_shadow<false, false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadow0 = fuse ? persistent_grid(k_trace_shadow<true, true>, block, smem, D.sm_count, opt.ctas_per_sm)
+                                   : persistent_grid(k_trace_shadow<true, false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadown = fuse ? persistent_grid(k_trace_shadow<false, true>, block, smem, D.sm_count, opt.ctas_per_sm)
+                                   : persistent_grid(k_trace_shadow<false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_flat = D.sm_count * 8;
         unsigned long long* ST = D.stats.as<unsigned long long>();
         RtOut out{(want & RT_OUT_RGBA32F) ? (float4*)D.o_rgba32f : nullptr, (want & RT_OUT_RGBA8) ? (uint32_t*)D.o_rgba8 : nullptr,
@@ -515,7 +498,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                     unsigned* C = L.counters.as<unsigned>();
                     uint32_t* OC = L.occl.as<uint32_t>();
                     RT_CUDA(cudaMemsetAsync(C, 0, C_TOTAL * 4, st));
-                    if (!mega) {
+                    {
                     kbegin(RT_K_TRACE_PRIMARY);
                     k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
                                                                    hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
@@ -535,14 +518,12 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                         }
                         if (fuse) {
                             RtFuse F{d, L.local[d].as<float4>(), rout, lout, C + d + 1, (d == 0 && maxd == 0) ? 1 : 0, pass, n_pass,
-                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out, L.hit0_t.as<float>(), L.hit0_slot.as<int>()};
+                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out};
                             if (F.fin && n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
-                            kbegin(d ? RT_K_SHADOW_QUEUE : (mega ? RT_K_TRACE_PRIMARY : RT_K_SHADOW_PRIMARY));
-                            if (d == 0 && mega) k_trace_shadow<true, true, true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
-                                                                                                  hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
-                            else if (d == 0) k_trace_shadow<true, true, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
+                            kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
+                            if (d == 0) k_trace_shadow<true, true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
                                                                                                   hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0));
-                            else k_trace_shadow<false, true, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
+                            else k_trace_shadow<false, true><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                             continue;
                         }
@@ -551,9 +532,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                             if (c >= 7) RT_CUDA(cudaMemsetAsync(wc, 0, 4, st));
                             const int lb = c * 32, nl = (D.S.n_lights - lb) < 32 ? (D.S.n_lights - lb) : 32;
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
-                            if (d == 0) k_trace_shadow<true, false, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
+                            if (d == 0) k_trace_shadow<true, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
                                                                                                    hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0 && c == 0));
-                            else k_trace_shadow<false, false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
+                            else k_trace_shadow<false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                         }
                         kbegin(d ? RT_K_SHADE_QUEUE : RT_K_SHADE_PRIMARY);
@@ -606,6 +587,15 @@ extern "C" int rt_debug_tile_times(int n_tiles, unsigned long long* host_out) { 
     if (n_tiles > cap) { if (buf) cudaFree(buf); cudaMalloc(&buf, (size_t)n_tiles * 16); cap = n_tiles; }
     cudaMemset(buf, 0, (size_t)cap * 16);
     return (int)cudaMemcpyToSymbol(g_rt_tile_dbg, &buf, sizeof(buf));
+}
+#endif
+
+#ifdef RT_COUNT_VISITS
+extern "C" int rt_debug_visit_counts(unsigned long long* host_out20, int reset) {       // counters of rt_core.h's RT_COUNT
+    int rc = 0;
+    if (host_out20) rc = (int)cudaMemcpyFromSymbol(host_out20, g_rt_visits, 20 * sizeof(unsigned long long));
+    if (reset) { unsigned long long z[20] = {0}; rc |= (int)cudaMemcpyToSymbol(g_rt_visits, z, sizeof(z)); }
+    return rc;
 }
 #endif
 
