@@ -141,11 +141,20 @@ int rt_alloc_outputs(rt_ctx* ctx, int res_x, int res_y, int want);
 int rt_export_outputs(rt_ctx* ctx, void* handles_4x64);
 int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_y, int want);
 
-/* tuning knobs (all optional): key in {"chunk_pixels","leaf_max","pad_scale","t_slack","ctas_per_sm","kernel_timing","packet",
- * "builder","copy_waves","waves","lanes"}; waves = minimum number of waves rt_render_device cuts a pass into, lanes = 1|2
- * streams the waves alternate over (2: the drain of one wave overlaps the start of the next); copy_waves = number of waves rt_render splits a frame into so the copy-out of one wave overlaps
- * the kernels of the next (default 8, 1 = off); builder 0 = device LBVH (default, ~10 ms per million primitives), 1 = host binned-SAH BVH (slower commit,
- * fewer node visits per ray); takes effect at the next rt_scene_commit */
+/* Tuning knobs (all optional; results never depend on them).  Unknown keys return RT_E_INVALID.
+ *   builder        0 = device LBVH (default, ~10 ms per million primitives), 1 = host binned-SAH BVH2 (slower commit, fewer node
+ *                  visits per ray); takes effect at the next rt_scene_commit.  leaf_max (1..8, default 4), pad_scale, t_slack likewise.
+ *   packet         1 = warp-coherent packet traversal for coherent warps (default), 0 = always the per-lane loop
+ *   fuse_shade     1 = shading (and the pixel write at depth 0) inside the shadow-trace kernel when the scene has <= 32 lights (default)
+ *   hints          1 = heavy-first tile order from the previous frame's measured tile costs (default)
+ *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 2) and the 1|2 streams they alternate over
+ *                  (2: the drain of one wave overlaps the start of the next)
+ *   copy_waves     number of waves rt_render splits a frame into so that the copy-out of one wave overlaps the kernels of the
+ *                  next (default 8, 1 = off)
+ *   chunk_pixels   upper bound of a wave in pixels (bounds the wave buffers)
+ *   ctas_per_sm    cap on the resident CTAs per SM of the persistent kernels (0 = occupancy limit)
+ *   prefetch, prefetch_max_mb   bulk L2 prefetch of nodes + primitives at the start of a frame when they fit (default off)
+ *   kernel_timing  1 = CUDA events around every launch, reported in rt_stats.ms_kernel (serialises the lanes) */
 int rt_set_option(rt_ctx* ctx, const char* key, double value);
 
 #ifdef __cplusplus
