@@ -63,7 +63,7 @@ typedef struct {
     uint64_t rays_primary, rays_shadow, rays_mirror;   /* Scene.IntersectRay-equivalent queries issued by the last render */
     float ms_render;            /* device time of the last render, ray-gen .. final pixel write (CUDA events) */
     float ms_d2h;               /* host copy-out time of the last rt_render (0 for rt_render_device) */
-    float ms_commit_upload;     /* last rt_scene_commit: flatten + host->device */
+    float ms_commit_upload;     /* last rt_scene_commit / rt_scene_recommit: host->device (incl. the uploads inside rt_scene_mesh / rt_scene_update_*) */
     float ms_commit_build;      /* last rt_scene_commit: device BVH build */
     uint64_t h2d_bytes;         /* bytes uploaded by the last commit */
     uint64_t d2h_bytes;         /* bytes copied out by the last rt_render */
@@ -104,6 +104,18 @@ int rt_scene_lights(rt_ctx* ctx, const float* pos_intensity, int n, const float 
 int rt_scene_commit(rt_ctx* ctx, const float scene_aabb[6]);
 int rt_scene_get_aabb(rt_ctx* ctx, float out_aabb[6]);
 
+/* Dirty-tracking updates of a committed scene.  The reference rebuilds its whole Scene every frame (UpdateScene(),
+ * RayTracingSetup.cs:120-128, called from Update() at :184) although usually only a few transforms moved; these entry points let
+ * the shim re-send only what changed.  Counts and materials stay as committed; the arrays replace the object's data in place
+ * (same layouts as rt_scene_mesh / rt_scene_triangles / rt_scene_spheres / rt_scene_lights; mesh_index and first are the
+ * reference's MeshIndex / Index).  After one or more updates rt_scene_recommit rebuilds the BVH from the device-resident
+ * arrays (scene_aabb as for rt_scene_commit); rendering between an update and the recommit returns RT_E_STATE. */
+int rt_scene_update_mesh(rt_ctx* ctx, int mesh_index, const float* vertices, const float* normals, const float aabb[6]);
+int rt_scene_update_triangles(rt_ctx* ctx, int first, int n, const float* vertices, const float* normals);
+int rt_scene_update_spheres(rt_ctx* ctx, int first, int n, const float* center_r2);
+int rt_scene_update_lights(rt_ctx* ctx, const float* pos_intensity, int n, const float ambient_radiance[3]);
+int rt_scene_recommit(rt_ctx* ctx, const float scene_aabb[6]);
+
 /* ---- render: replaces CastPixelRays(CameraData), RayTracingSetup.cs:198,275-302 ---------------------------- */
 /* out_rgba32f : X*Y*4 floats == UnityEngine.Color[] PixelColors (RTS:40,300; Rgb.Color = Value/255, alpha 1, Rgb.cs:13)
  * out_rgba8   : X*Y*4 bytes, clamp(rint(Rgb.Value),0,255), alpha 255 (our definition: the reference never quantises)
@@ -142,8 +154,8 @@ int rt_export_outputs(rt_ctx* ctx, void* handles_4x64);
 int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_y, int want);
 
 /* Tuning knobs (all optional; results never depend on them).  Unknown keys return RT_E_INVALID.
- *   builder        0 = device LBVH (default, ~10 ms per million primitives), 1 = host binned-SAH BVH2 (slower commit, fewer node
- *                  visits per ray); takes effect at the next rt_scene_commit.  leaf_max (1..8, default 4), pad_scale, t_slack likewise.
+ *   builder        0 = device LBVH (default, 0.65 ms per million primitives once the buffers exist), 1 = host binned-SAH BVH2 (slower commit, fewer node
+ *                  visits per ray); takes effect at the next rt_scene_begin.  leaf_max (1..8, default 4), pad_scale, t_slack likewise.
  *   packet         1 = warp-coherent packet traversal for coherent warps (default), 0 = always the per-lane loop
  *   fuse_shade     1 = shading (and the pixel write at depth 0) inside the shadow-trace kernel when the scene has <= 32 lights (default)
  *   hints          1 = heavy-first tile order from the previous frame's measured tile costs (default)
@@ -154,6 +166,8 @@ int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_
  *   chunk_pixels   upper bound of a wave in pixels (bounds the wave buffers)
  *   ctas_per_sm    cap on the resident CTAs per SM of the persistent kernels (0 = occupancy limit)
  *   prefetch, prefetch_max_mb   bulk L2 prefetch of nodes + primitives at the start of a frame when they fit (default off)
+ *   stream_upload  1 = rt_scene_mesh uploads straight from the caller's arrays, no host staging (default; single device, builder 0)
+ *   upload_threads host threads that fill the pinned bounce buffers of an upload from pageable memory (default 4; 1 = cudaMemcpyAsync)
  *   kernel_timing  1 = CUDA events around every launch, reported in rt_stats.ms_kernel (serialises the lanes) */
 int rt_set_option(rt_ctx* ctx, const char* key, double value);
 

@@ -156,6 +156,7 @@ int emu_scene_mesh(void* e, const float* v, const float* nn, int n, const rt_mat
     Emu* E = (Emu*)e;
     E->host.mesh_base.push_back(E->host.n_meshtris());
     E->host.mesh_v.insert(E->host.mesh_v.end(), v, v + 9 * (size_t)n); E->host.mesh_n.insert(E->host.mesh_n.end(), nn, nn + 3 * (size_t)n);
+    E->host.mesh_tris += n;
     E->host.mesh_mats.push_back(*m); E->host.mesh_aabb.insert(E->host.mesh_aabb.end(), aabb, aabb + 6); return 0;
 }
 int emu_scene_lights(void* e, const float* pi, int n, const float* amb) {

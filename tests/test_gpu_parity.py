@@ -282,3 +282,71 @@ def test_cfg5_reduced_spheres_mirrors_spp(rt, scenes, oracle):
     _check(compare_renders(ref, got))
     st = got["stats"]
     assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == ref["stats"] and st["rays_mirror"] > 0
+
+
+def test_streaming_commit_equals_staged_commit_and_recommits(rtb, scenes, oracle):
+    """Commit path: rt_scene_mesh uploads straight from the caller's arrays (stream_upload, the default
+    with the device builder) — same frame as the host-staged commit, also when scenes of different sizes follow each other on
+    one context, as the reference's per-frame UpdateScene does (RayTracingSetup.cs:120-128,184)."""
+    big, pb = scenes.cfg4_scene(n=16, grid=2), scenes.cfg4_params(240, 135)
+    small, ps = scenes.rt_unity(), scenes.rt_unity_params()
+    want = {}
+    for name, (s, p) in {"big": (big, pb), "small": (small, ps)}.items():
+        r = rtb.RayTracer((0,)); r.set_option("stream_upload", 0); r.set_scene(s)
+        want[name] = r.render(p); r.close()
+    _check(compare_renders(oracle.OracleScene(big).render(pb, oracle.ACCELERATED), want["big"]))
+    r = rtb.RayTracer((0,))
+    for name in ("small", "big", "small", "big", "big"):           # grow, shrink, grow again, identical re-commit
+        s, p = (big, pb) if name == "big" else (small, ps)
+        r.set_scene(s)
+        got = r.render(p)
+        for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+            assert np.array_equal(want[name][k], got[k]), (name, k)
+        assert r.stats()["h2d_bytes"] >= 48 * s.n_prims - 32 * s.spheres.shape[0]
+    r.close()
+
+
+def _moved_copy(s, d):
+    """the same scene after every sphere, loose triangle, mesh 0 and the lights moved by d (a translation keeps the normals)"""
+    import copy
+    d = np.asarray(d, np.float32)
+    m = copy.deepcopy(s)
+    m.spheres[:, :3] += d
+    m.tris += np.tile(d, 3)
+    v, n, mat, aabb = m.meshes[0]
+    m.meshes[0] = (v + np.tile(d, 3), n, mat, aabb + np.tile(d, 2))
+    m.lights[:, :3] += d
+    return m
+
+
+@pytest.mark.parametrize("builder", [0, 1])
+def test_dirty_updates_plus_recommit_equal_full_commit(rtb, scenes, oracle, builder):
+    """rt_scene_update_* + rt_scene_recommit = committing the moved scene from scratch = the oracle."""
+    s, p = scenes.cfg5_scene(n=12, n_spheres=500), scenes.cfg5_params(160, 90, 1, 2)
+    s2 = _moved_copy(s, (0.75, -0.5, 1.25))
+    ref = oracle.OracleScene(s2).render(p, oracle.ACCELERATED)
+    fresh = rtb.RayTracer((0,)); fresh.set_option("builder", builder); fresh.set_scene(s2)
+    want = fresh.render(p); fresh.close()
+    _check(compare_renders(ref, want))
+    r = rtb.RayTracer((0,)); r.set_option("builder", builder); r.set_scene(s)
+    r.render(p)
+    half = s.spheres.shape[0] // 2
+    r.update_spheres(0, s2.spheres[:half]); r.update_spheres(half, s2.spheres[half:])
+    r.update_triangles(0, s2.tris, s2.tri_normals)
+    r.update_mesh(0, s2.meshes[0][0], s2.meshes[0][1], s2.meshes[0][3])
+    r.update_lights(s2.lights, s2.ambient)
+    with pytest.raises(RuntimeError):
+        r.render(p)                                             # dirty scene: RT_E_STATE until rt_scene_recommit
+    r.recommit()
+    got = r.render(p)
+    for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+        assert np.array_equal(want[k], got[k]), k
+    st = r.stats()
+    dirty = 48 * (s.tris.shape[0] + s.meshes[0][0].shape[0]) + 16 * s.spheres.shape[0]
+    assert dirty <= st["h2d_bytes"] < dirty + 4096                  # the dirty arrays + the small tables; materials stay on the device
+    with pytest.raises(RuntimeError):
+        r.update_spheres(s.spheres.shape[0] - 1, s2.spheres[:2])    # beyond the committed count
+    r.recommit()
+    got = r.render(p)
+    assert np.array_equal(want["hit_id"], got["hit_id"])
+    r.close()

@@ -11,6 +11,7 @@ timing = int(opts.pop("timing", 1))
 flush = int(opts.pop("flush", 0))
 part = int(opts.pop("part", 1))
 host_time = int(opts.pop("host", 0))
+recommit = int(opts.pop("recommit", 0))
 if "lib" in opts: rtb.host.LIB_PATH = opts.pop("lib")       # alternative build of the library (development)
 t0 = time.time()
 if cfg == "cfg2": s, p = sc.rt_unity(True), sc.rt_unity_params(3840, 2160, 4)
@@ -24,6 +25,10 @@ if part > 1: rt.set_partition(int(opts.pop('rank', 0)), part, 32)
 for k, v in opts.items(): rt.set_option(k, float(v))
 rt.set_option("kernel_timing", timing)
 t0 = time.time(); rt.set_scene(s); print(f"commit wall {time.time()-t0:.3f}s", flush=True)
+for i in range(recommit):                                  # steady-state re-commit (buffers already allocated), as the reference's per-frame UpdateScene
+    t0 = time.perf_counter(); rt.set_scene(s); w = time.perf_counter() - t0
+    st = rt.stats()
+    print(f"recommit {i}: wall {1e3*w:.2f} ms, upload {st['ms_commit_upload']:.2f} ms, build {st['ms_commit_build']:.2f} ms, {s.n_prims/w/1e6:.1f} Mprims/s", flush=True)
 fl = None
 if flush:
     import torch

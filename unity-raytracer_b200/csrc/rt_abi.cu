@@ -11,9 +11,11 @@ struct rt_ctx {
     std::string err;
     rt_stats stats{};
     bool in_scene = false, committed = false;
+    bool dirty = false;                                     // rt_scene_update_* since the last (re)commit: rendering needs rt_scene_recommit
     int ext_rank = 0, ext_world = 1, band_rows = 32;
     int last_res_x = 0, last_res_y = 0, last_want = 0;
     bool stats_pending = false;
+    float stream_ms = 0.f; uint64_t stream_bytes = 0;      // streaming commit: time / bytes spent inside rt_scene_mesh
     std::vector<RtFrameStats> fstats;
 };
 
@@ -30,6 +32,7 @@ void device_release(RtDevice& D) {
                       &D.keys_alt, &D.vals, &D.vals_alt, &D.cub_tmp, &D.bounds, &D.topo_i32, &D.leaf_lo, &D.leaf_hi, &D.int_lo, &D.int_hi,
                       &D.flags, &D.new_index, &D.accum, &D.stats, &D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t})
         b->release();
+    rt_upload_release(D);
     for (auto& L : D.lanes) {
         for (DevBuf* b : {&L.hit0_t, &L.hit0_slot, &L.hitq_t, &L.hitq_slot, &L.rays[0], &L.rays[1], &L.counters, &L.occl}) b->release();
         for (auto& b : L.local) b.release();
@@ -213,7 +216,12 @@ void rt_destroy(rt_ctx* c) {
 
 int rt_scene_begin(rt_ctx* c) {
     if (!c) return RT_E_INVALID;
-    c->host.clear(); c->in_scene = true; c->committed = false;
+    int rc = sync_all(c);                       // frames still in flight read the buffers the new scene overwrites
+    if (rc) return rc;
+    c->host.clear(); c->in_scene = true; c->committed = false; c->dirty = false;
+    c->host.builder = c->opt.builder;           // latched: the builder decides where the mesh arrays are staged
+    c->host.mesh_on_device = c->opt.stream_upload && c->opt.builder == 0 && c->devs.size() == 1;
+    c->stream_ms = 0.f; c->stream_bytes = 0;
     return RT_OK;
 }
 
@@ -240,9 +248,19 @@ int rt_scene_mesh(rt_ctx* c, const float* v, const float* normals, int n_tris, c
     if (!c) return RT_E_INVALID;
     if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_mesh outside rt_scene_begin/commit");
     if (n_tris < 0 || !mat || !aabb || (n_tris > 0 && (!v || !normals))) return fail(c, RT_E_INVALID, "rt_scene_mesh: bad arguments");
+    if ((int64_t)c->host.mesh_tris + n_tris > (int64_t)(1 << 28)) return fail(c, RT_E_UNSUPPORTED, "too many primitives (limit 2^28)");
     c->host.mesh_base.push_back(c->host.n_meshtris());
-    c->host.mesh_v.insert(c->host.mesh_v.end(), v, v + 9 * (size_t)n_tris);
-    c->host.mesh_n.insert(c->host.mesh_n.end(), normals, normals + 3 * (size_t)n_tris);
+    if (c->host.mesh_on_device) {
+        auto t0 = std::chrono::steady_clock::now();
+        int rc = rt_device_stage_mesh(c->devs[0], v, normals, c->host.mesh_tris, n_tris, c->opt.upload_threads, c->err);
+        if (rc) return rc;
+        c->stream_ms += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        c->stream_bytes += (uint64_t)n_tris * 48;
+    } else {
+        c->host.mesh_v.insert(c->host.mesh_v.end(), v, v + 9 * (size_t)n_tris);
+        c->host.mesh_n.insert(c->host.mesh_n.end(), normals, normals + 3 * (size_t)n_tris);
+    }
+    c->host.mesh_tris += n_tris;
     c->host.mesh_mats.push_back(*mat);
     c->host.mesh_aabb.insert(c->host.mesh_aabb.end(), aabb, aabb + 6);
     return RT_OK;
@@ -257,22 +275,100 @@ int rt_scene_lights(rt_ctx* c, const float* pos_intensity, int n, const float am
     return RT_OK;
 }
 
-int rt_scene_commit(rt_ctx* c, const float scene_aabb[6]) {
-    if (!c) return RT_E_INVALID;
-    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_commit without rt_scene_begin");
+static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident) {
     if (scene_aabb) for (int k = 0; k < 6; ++k) c->host.aabb[k] = scene_aabb[k];
     else c->host.calc_aabb();
     float up = 0.f, bd = 0.f; uint64_t bytes = 0;
     for (auto& D : c->devs) {
         float u = 0.f, b = 0.f; uint64_t by = 0;
-        int rc = rt_device_commit(D, c->host, c->opt, c->err, &u, &b, &by);
+        int rc = rt_device_commit(D, c->host, c->opt, c->err, &u, &b, &by, raw_resident);
         if (rc) return rc;
         up += u; bd += b; bytes += by;
     }
-    c->stats.ms_commit_upload = up; c->stats.ms_commit_build = bd; c->stats.h2d_bytes = bytes;
+    c->stats.ms_commit_upload = up + c->stream_ms; c->stats.ms_commit_build = bd; c->stats.h2d_bytes = bytes + c->stream_bytes;
     c->stats.n_prims = (uint32_t)c->host.n_prims(); c->stats.n_nodes = c->devs[0].n_nodes;
+    c->stream_ms = 0.f; c->stream_bytes = 0;
     c->in_scene = false; c->committed = true;
     return RT_OK;
+}
+
+int rt_scene_commit(rt_ctx* c, const float scene_aabb[6]) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_commit without rt_scene_begin");
+    return commit_impl(c, scene_aabb, false);
+}
+
+// ---- dirty-tracking updates of a committed scene ----
+static int update_prolog(rt_ctx* c, const char* who) {
+    if (!c) return RT_E_INVALID;
+    if (c->in_scene) return fail(c, RT_E_STATE, std::string(who) + " inside rt_scene_begin/commit");
+    if (!c->committed && !c->dirty) return fail(c, RT_E_STATE, std::string(who) + ": no committed scene");
+    if (!c->dirty) { int rc = sync_all(c); if (rc) return rc; }          // frames in flight still read the old data
+    c->dirty = true; c->committed = false;
+    return RT_OK;
+}
+static int update_raw(rt_ctx* c, int what, int64_t first, int64_t n, const float* a, const float* b) {
+    auto t0 = std::chrono::steady_clock::now();
+    for (auto& D : c->devs) { int rc = rt_device_update_raw(D, what, first, n, a, b, c->opt.upload_threads, c->err); if (rc) return rc; }
+    c->stream_ms += std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->stream_bytes += (uint64_t)n * (what == 0 ? 48 : 16) * c->devs.size();
+    return RT_OK;
+}
+
+int rt_scene_update_mesh(rt_ctx* c, int mesh_index, const float* v, const float* normals, const float aabb[6]) {
+    int rc = update_prolog(c, "rt_scene_update_mesh");
+    if (rc) return rc;
+    RtHostScene& H = c->host;
+    if (mesh_index < 0 || mesh_index >= H.n_meshes() || !aabb) return fail(c, RT_E_INVALID, "rt_scene_update_mesh: bad arguments");
+    const int64_t first = H.mesh_base[mesh_index];
+    const int64_t n = (mesh_index + 1 < H.n_meshes() ? (int64_t)H.mesh_base[mesh_index + 1] : H.mesh_tris) - first;
+    if (n > 0 && (!v || !normals)) return fail(c, RT_E_INVALID, "rt_scene_update_mesh: bad arguments");
+    for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = aabb[k];
+    if (!H.mesh_on_device && n > 0) {                                      // host copies feed the host SAH builder / multi-device upload
+        std::memcpy(H.mesh_v.data() + 9 * (size_t)first, v, (size_t)n * 36);
+        std::memcpy(H.mesh_n.data() + 3 * (size_t)first, normals, (size_t)n * 12);
+    }
+    return update_raw(c, 0, first, n, v, normals);
+}
+
+int rt_scene_update_triangles(rt_ctx* c, int first, int n, const float* v, const float* normals) {
+    int rc = update_prolog(c, "rt_scene_update_triangles");
+    if (rc) return rc;
+    RtHostScene& H = c->host;
+    if (first < 0 || n < 0 || (int64_t)first + n > H.n_loose() || (n > 0 && (!v || !normals))) return fail(c, RT_E_INVALID, "rt_scene_update_triangles: bad range");
+    if (n == 0) return RT_OK;
+    std::memcpy(H.loose_v.data() + 9 * (size_t)first, v, (size_t)n * 36);
+    std::memcpy(H.loose_n.data() + 3 * (size_t)first, normals, (size_t)n * 12);
+    return update_raw(c, 0, (int64_t)H.n_meshtris() + first, n, v, normals);
+}
+
+int rt_scene_update_spheres(rt_ctx* c, int first, int n, const float* center_r2) {
+    int rc = update_prolog(c, "rt_scene_update_spheres");
+    if (rc) return rc;
+    RtHostScene& H = c->host;
+    if (first < 0 || n < 0 || (int64_t)first + n > H.n_spheres() || (n > 0 && !center_r2)) return fail(c, RT_E_INVALID, "rt_scene_update_spheres: bad range");
+    if (n == 0) return RT_OK;
+    std::memcpy(H.spheres.data() + 4 * (size_t)first, center_r2, (size_t)n * 16);
+    return update_raw(c, 1, first, n, center_r2, nullptr);
+}
+
+int rt_scene_update_lights(rt_ctx* c, const float* pos_intensity, int n, const float ambient[3]) {
+    int rc = update_prolog(c, "rt_scene_update_lights");
+    if (rc) return rc;
+    if (n < 0 || (n > 0 && !pos_intensity)) return fail(c, RT_E_INVALID, "rt_scene_update_lights: bad arguments");
+    c->host.lights.assign(pos_intensity, pos_intensity + 6 * (size_t)n);
+    if (ambient) for (int k = 0; k < 3; ++k) c->host.ambient[k] = ambient[k];
+    return RT_OK;
+}
+
+int rt_scene_recommit(rt_ctx* c, const float scene_aabb[6]) {
+    if (!c) return RT_E_INVALID;
+    if (c->in_scene) return fail(c, RT_E_STATE, "rt_scene_recommit inside rt_scene_begin/commit");
+    if (!c->dirty && !c->committed) return fail(c, RT_E_STATE, "rt_scene_recommit: no committed scene");
+    if (!c->dirty) { int rc = sync_all(c); if (rc) return rc; }
+    int rc = commit_impl(c, scene_aabb, true);
+    if (rc == RT_OK) c->dirty = false;
+    return rc;
 }
 
 int rt_scene_get_aabb(rt_ctx* c, float out[6]) {
@@ -478,6 +574,8 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "fuse_shade") { c->opt.fuse_shade = value != 0; }
     else if (k == "prefetch") { c->opt.prefetch = value != 0; }
     else if (k == "prefetch_max_mb") { c->opt.prefetch_max_mb = (int)value; }
+    else if (k == "upload_threads") { c->opt.upload_threads = (int)value; }
+    else if (k == "stream_upload") { c->opt.stream_upload = value != 0; }
     else if (k == "hints") { c->opt.hints = value != 0; }
     else if (k == "copy_waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "copy_waves must be 1..64"); c->opt.copy_waves = (int)value; }
     else if (k == "builder") { if (value != 0 && value != 1) return fail(c, RT_E_INVALID, "builder must be 0 (device LBVH) or 1 (host SAH)"); c->opt.builder = (int)value; }

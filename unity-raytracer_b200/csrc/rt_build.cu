@@ -5,6 +5,8 @@
 // Per-element logic lives in rt_build_steps.h (host/device) so tests can run it on the CPU.
 #include "rt_internal.h"
 #include "rt_sah.h"
+#include <thread>
+#include <cstring>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
@@ -85,8 +87,99 @@ __global__ void k_emit_nodes(int32_t n_int, RtTopo T, const int32_t* new_index, 
 
 }  // namespace
 
+// ---- pageable host -> device upload --------------------------------------------------------------------------------------
+// cudaMemcpyAsync from pageable memory is staged by the driver on ONE thread (measured 11.8 GB/s on this box: 4.1 ms for
+// cfg3's 48 MB, 86 % of a steady-state re-commit).  Here `threads` host threads copy 2 MiB chunks into their own two pinned
+// slots and queue the DMA of each chunk behind it, so the memcpys run in parallel with each other and with PCIe:
+// 4 threads 21 GB/s (2.2 ms); 8 threads no better — the box's host memcpy bandwidth (14 GB/s per thread, ~30 GB/s total) binds.
+void rt_upload_release(RtDevice& D) {
+    for (auto e : D.up_ev) cudaEventDestroy(e);
+    D.up_ev.clear();
+    if (D.up_ring) cudaFreeHost(D.up_ring);
+    D.up_ring = nullptr; D.up_slots = 0; D.up_slot_bytes = 0;
+}
+
+int rt_upload(RtDevice& D, void* dst, const void* src, size_t bytes, int threads, std::string& err) {
+    if (bytes == 0) return RT_OK;
+    cudaStream_t st = D.stream;
+    cudaPointerAttributes at{};
+    bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();                                        // unregistered host memory reports an error on old runtimes
+    constexpr size_t SLOT = 2u << 20;                          // 0.5 / 1 / 4 / 8 MiB measured slower (2.6 / 2.8 / 3.2 / 3.3 ms vs 2.2 ms for 48 MB)
+    if (threads > 16) threads = 16;
+    if (pinned || threads < 2 || bytes < 4 * SLOT) {
+        RT_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+        return RT_OK;
+    }
+    const int slots = 2 * threads;
+    if (D.up_slots < slots || D.up_slot_bytes != SLOT) {
+        RT_CUDA(cudaStreamSynchronize(st));
+        rt_upload_release(D);
+        RT_CUDA(cudaHostAlloc(&D.up_ring, (size_t)slots * SLOT, cudaHostAllocDefault));
+        D.up_slots = slots; D.up_slot_bytes = SLOT;
+        for (int i = 0; i < slots; ++i) { cudaEvent_t e; RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.up_ev.push_back(e); }
+    }
+    const size_t n_chunks = (bytes + SLOT - 1) / SLOT;
+    std::vector<cudaError_t> rc((size_t)threads, cudaSuccess);
+    auto work = [&](int t) {
+        cudaError_t e = cudaSetDevice(D.device);
+        int turn = 0;
+        for (size_t c = (size_t)t; c < n_chunks && e == cudaSuccess; c += (size_t)threads, ++turn) {
+            const int slot = 2 * t + (turn & 1);
+            char* bounce = (char*)D.up_ring + (size_t)slot * SLOT;
+            const size_t off = c * SLOT, len = bytes - off < SLOT ? bytes - off : SLOT;
+            e = cudaEventSynchronize(D.up_ev[slot]);       // the DMA that last read this slot (this or an earlier upload) is done
+            if (e != cudaSuccess) break;
+            std::memcpy(bounce, (const char*)src + off, len);
+            e = cudaMemcpyAsync((char*)dst + off, bounce, len, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaEventRecord(D.up_ev[slot], st);
+        }
+        rc[(size_t)t] = e;
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; ++t) pool.emplace_back(work, t);
+    work(0);
+    for (auto& th : pool) th.join();
+    for (cudaError_t e : rc) RT_CUDA(e);
+    return RT_OK;                                              // all DMAs are queued on D.stream; the bounce slots stay valid
+}
+
+int rt_device_stage_mesh(RtDevice& D, const float* v, const float* normals, int64_t first, int64_t n_tris, int threads, std::string& err) {
+    RT_CUDA(cudaSetDevice(D.device));
+    cudaStream_t st = D.stream;
+    RT_CUDA(D.raw_v.ensure_keep((size_t)(first + n_tris) * 36, (size_t)first * 36, st));
+    RT_CUDA(D.raw_n.ensure_keep((size_t)(first + n_tris) * 12, (size_t)first * 12, st));
+    if (n_tris > 0) {
+        int rc = rt_upload(D, (char*)D.raw_v.p + (size_t)first * 36, v, (size_t)n_tris * 36, threads, err);
+        if (rc == RT_OK) rc = rt_upload(D, (char*)D.raw_n.p + (size_t)first * 12, normals, (size_t)n_tris * 12, threads, err);
+        if (rc) return rc;
+        RT_CUDA(cudaStreamSynchronize(st));          // the caller's arrays are only valid during the call (pinned callers too)
+    }
+    return RT_OK;
+}
+
+// in-place replacement of a range of the device-resident raw arrays of a committed scene (rt_scene_update_*)
+int rt_device_update_raw(RtDevice& D, int what, int64_t first, int64_t n, const float* a, const float* b, int threads, std::string& err) {
+    RT_CUDA(cudaSetDevice(D.device));
+    if (n <= 0) return RT_OK;
+    int rc = RT_OK;
+    if (what == 0) {                                            // triangles: a = 9 floats each, b = 3 floats each
+        if ((size_t)(first + n) * 36 > D.raw_v.bytes || (size_t)(first + n) * 12 > D.raw_n.bytes) { err = "update beyond the committed arrays"; return RT_E_INVALID; }
+        rc = rt_upload(D, (char*)D.raw_v.p + (size_t)first * 36, a, (size_t)n * 36, threads, err);
+        if (rc == RT_OK) rc = rt_upload(D, (char*)D.raw_n.p + (size_t)first * 12, b, (size_t)n * 12, threads, err);
+    } else {                                                    // spheres: a = 4 floats each
+        if ((size_t)(first + n) * 16 > D.raw_s.bytes) { err = "update beyond the committed arrays"; return RT_E_INVALID; }
+        rc = rt_upload(D, (char*)D.raw_s.p + (size_t)first * 16, a, (size_t)n * 16, threads, err);
+    }
+    if (rc) return rc;
+    RT_CUDA(cudaStreamSynchronize(D.stream));
+    return RT_OK;
+}
+
+// raw_resident: the triangle / sphere arrays of this scene are already on the device (rt_scene_recommit after
+// rt_scene_update_*): only the small tables are uploaded before the BVH is rebuilt.
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
-                     float* ms_build, uint64_t* h2d_bytes) {
+                     float* ms_build, uint64_t* h2d_bytes, bool raw_resident) {
     RT_CUDA(cudaSetDevice(D.device));
     cudaStream_t st = D.stream;
     const int32_t n_mt = H.n_meshtris(), n_sp = H.n_spheres(), n_lo = H.n_loose(), n_me = H.n_meshes(), n_li = H.n_lights();
@@ -97,22 +190,32 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     RT_CUDA(cudaEventRecord(D.ev0, st));
     // ---- upload ----
     const size_t ntri = (size_t)n_mt + n_lo;
-    RT_CUDA(D.raw_v.ensure(ntri * 9 * 4)); RT_CUDA(D.raw_n.ensure(ntri * 3 * 4)); RT_CUDA(D.raw_s.ensure((size_t)n_sp * 16));
-    if (n_mt) {
-        RT_CUDA(cudaMemcpyAsync(D.raw_v.p, H.mesh_v.data(), (size_t)n_mt * 36, cudaMemcpyHostToDevice, st));
-        RT_CUDA(cudaMemcpyAsync(D.raw_n.p, H.mesh_n.data(), (size_t)n_mt * 12, cudaMemcpyHostToDevice, st));
+    const size_t keep_tris = raw_resident ? ntri : (H.mesh_on_device ? (size_t)n_mt : 0);   // streamed by rt_scene_mesh already
+    if (raw_resident && (D.raw_v.bytes < ntri * 36 || D.raw_n.bytes < ntri * 12 || (n_sp && D.raw_s.bytes < (size_t)n_sp * 16))) {
+        err = "rt_scene_recommit: no committed scene of this size on the device"; return RT_E_STATE;
     }
-    if (n_lo) {
-        RT_CUDA(cudaMemcpyAsync((char*)D.raw_v.p + (size_t)n_mt * 36, H.loose_v.data(), (size_t)n_lo * 36, cudaMemcpyHostToDevice, st));
-        RT_CUDA(cudaMemcpyAsync((char*)D.raw_n.p + (size_t)n_mt * 12, H.loose_n.data(), (size_t)n_lo * 12, cudaMemcpyHostToDevice, st));
+    RT_CUDA(D.raw_v.ensure_keep(ntri * 9 * 4, keep_tris * 36, st)); RT_CUDA(D.raw_n.ensure_keep(ntri * 3 * 4, keep_tris * 12, st));
+    if (!raw_resident) RT_CUDA(D.raw_s.ensure((size_t)n_sp * 16));
+    if (n_mt && !H.mesh_on_device && !raw_resident) {
+        int rc = rt_upload(D, D.raw_v.p, H.mesh_v.data(), (size_t)n_mt * 36, opt.upload_threads, err);
+        if (rc == RT_OK) rc = rt_upload(D, D.raw_n.p, H.mesh_n.data(), (size_t)n_mt * 12, opt.upload_threads, err);
+        if (rc) return rc;
     }
-    if (n_sp) RT_CUDA(cudaMemcpyAsync(D.raw_s.p, H.spheres.data(), (size_t)n_sp * 16, cudaMemcpyHostToDevice, st));
-    up += ntri * 48 + (uint64_t)n_sp * 16;
-    RtHostScene& Hm = const_cast<RtHostScene&>(H);
-    std::vector<float> mats = Hm.pack_materials();
-    D.has_mirror = Hm.has_mirror;
-    RT_CUDA(D.mats.ensure(mats.size() * 4));
-    if (!mats.empty()) RT_CUDA(cudaMemcpyAsync(D.mats.p, mats.data(), mats.size() * 4, cudaMemcpyHostToDevice, st));
+    if (n_lo && !raw_resident) {
+        int rc = rt_upload(D, (char*)D.raw_v.p + (size_t)n_mt * 36, H.loose_v.data(), (size_t)n_lo * 36, opt.upload_threads, err);
+        if (rc == RT_OK) rc = rt_upload(D, (char*)D.raw_n.p + (size_t)n_mt * 12, H.loose_n.data(), (size_t)n_lo * 12, opt.upload_threads, err);
+        if (rc) return rc;
+    }
+    if (n_sp && !raw_resident) RT_CUDA(cudaMemcpyAsync(D.raw_s.p, H.spheres.data(), (size_t)n_sp * 16, cudaMemcpyHostToDevice, st));
+    up += (ntri - keep_tris) * 48 + (raw_resident ? 0 : (uint64_t)n_sp * 16);
+    std::vector<float> mats;
+    if (!raw_resident) {                                       // materials cannot change through rt_scene_update_*
+        RtHostScene& Hm = const_cast<RtHostScene&>(H);
+        mats = Hm.pack_materials();
+        D.has_mirror = Hm.has_mirror;
+        RT_CUDA(D.mats.ensure(mats.size() * 4));
+        if (!mats.empty()) RT_CUDA(cudaMemcpyAsync(D.mats.p, mats.data(), mats.size() * 4, cudaMemcpyHostToDevice, st));
+    }
     std::vector<float> maabb((size_t)n_me * 8, 0.f);
     for (int m = 0; m < n_me; ++m) { for (int k = 0; k < 3; ++k) { maabb[8 * m + k] = H.mesh_aabb[6 * m + k]; maabb[8 * m + 4 + k] = H.mesh_aabb[6 * m + 3 + k]; } }
     RT_CUDA(D.mesh_aabb.ensure(maabb.size() * 4));
@@ -151,7 +254,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     if (n > 0) {
         RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_base.as<int32_t>(), n_me, n_mt, n_sp, n_lo};
         const int leaf_max = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 8 ? 8 : opt.leaf_max);
-        if (opt.builder == 1) {
+        if (H.builder == 1) {
             // ---- host binned-SAH build (rt_sah.h); the device only re-lays the primitives out in leaf order ----
             std::vector<RtSahBox> pb((size_t)n);
             float amax = 0.f;

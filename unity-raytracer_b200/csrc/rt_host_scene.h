@@ -24,10 +24,23 @@ struct RtHostScene {
     float ambient[3] = {0, 0, 0};
     float aabb[6] = {0, 0, 0, 0, 0, 0};
     bool has_mirror = false;
+    // Streaming commit (single device, device-built BVH): rt_scene_mesh copies the caller's arrays straight into the device's
+    // raw buffers and mesh_v / mesh_n stay empty — nothing on the host needs the mesh vertices (the mesh AABB is the caller's).
+    bool mesh_on_device = false;
+    int64_t mesh_tris = 0;                      // mesh triangles so far (== mesh_v.size() / 9 when staged on the host)
+    int builder = 0;                            // RtOptions::builder latched at rt_scene_begin
 
-    void clear() { *this = RtHostScene(); }
+    // keeps the capacity of the staging vectors: a scene that is re-committed every frame (RayTracingSetup.cs:120-128) must
+    // not pay for fresh pages each time (48 MB of first-touch page faults cost more than the copy itself)
+    void clear() {
+        mesh_v.clear(); mesh_n.clear(); mesh_base.clear(); mesh_aabb.clear(); mesh_mats.clear(); spheres.clear(); sphere_mats.clear();
+        loose_v.clear(); loose_n.clear(); loose_mats.clear(); lights.clear();
+        for (int k = 0; k < 3; ++k) ambient[k] = 0.f;
+        for (int k = 0; k < 6; ++k) aabb[k] = 0.f;
+        has_mirror = false; mesh_on_device = false; mesh_tris = 0; builder = 0;
+    }
     int32_t n_meshes() const { return (int32_t)mesh_mats.size(); }
-    int32_t n_meshtris() const { return (int32_t)(mesh_v.size() / 9); }
+    int32_t n_meshtris() const { return (int32_t)mesh_tris; }
     int32_t n_spheres() const { return (int32_t)(spheres.size() / 4); }
     int32_t n_loose() const { return (int32_t)(loose_v.size() / 9); }
     int64_t n_prims() const { return (int64_t)n_meshtris() + n_spheres() + n_loose(); }

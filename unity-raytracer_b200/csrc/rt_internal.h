@@ -19,6 +19,20 @@ struct DevBuf {
         if (e == cudaSuccess) bytes = n;
         return e;
     }
+    // like ensure, but the first `keep` bytes survive a reallocation (grown by half to amortise repeated appends)
+    cudaError_t ensure_keep(size_t n, size_t keep, cudaStream_t st) {
+        if (n <= bytes && p) return cudaSuccess;
+        if (!p || keep == 0) return ensure(n);
+        void* q = nullptr;
+        const size_t cap = n + n / 2;
+        cudaError_t e = cudaMalloc(&q, cap);
+        if (e != cudaSuccess) return e;
+        e = cudaMemcpyAsync(q, p, keep < bytes ? keep : bytes, cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { cudaFree(q); return e; }
+        cudaFree(p); p = q; bytes = cap;
+        return cudaSuccess;
+    }
     void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
     template <class T> T* as() const { return (T*)p; }
 };
@@ -39,6 +53,8 @@ struct RtOptions {
     int fuse_shade = 1;                // shading (+ pixel write at depth 0) inside the shadow-trace kernel when <= 32 lights
     int prefetch = 0;                  // bulk L2 prefetch of nodes + primitives at the start of every frame ...
     int prefetch_max_mb = 96;          // ... when they total at most this many MiB (L2 is 126 MB)
+    int upload_threads = 4;            // host threads that fill the pinned bounce buffers of a pageable upload (1 = plain cudaMemcpyAsync)
+    int stream_upload = 1;             // single device + builder 0: rt_scene_mesh uploads straight from the caller's arrays (no host staging)
     int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };
@@ -88,6 +104,8 @@ struct RtDevice {
     std::vector<int> kev_class;        // class of launch i; its events are kev_pool[2i], kev_pool[2i+1]
     // pipelined copy-out (rt_render with host buffers): one event per finished wave + the pixel rows it completed
     cudaStream_t copy_stream = nullptr;
+    // host->device staging ring of rt_upload (rt_build.cu): pinned bounce buffers filled by several host threads
+    void* up_ring = nullptr; size_t up_slot_bytes = 0; int up_slots = 0; std::vector<cudaEvent_t> up_ev;
     std::vector<cudaEvent_t> wave_ev;
     struct WaveMark { int row0, row1; };
     std::vector<WaveMark> wave_marks;
@@ -105,8 +123,15 @@ struct RtDevice {
     } while (0)
 
 // rt_build.cu
+// host -> device copy of caller memory that may be pageable: pinned sources go straight to the copy engine, pageable ones
+// through a ring of pinned bounce buffers filled by `threads` host threads (the driver's own pageable path is one thread)
+int rt_upload(RtDevice& D, void* dst, const void* src, size_t bytes, int threads, std::string& err);
+void rt_upload_release(RtDevice& D);
+// streaming commit: append n_tris mesh triangles (caller's arrays, read during the call only) at triangle offset `first`
+int rt_device_stage_mesh(RtDevice& D, const float* v, const float* normals, int64_t first, int64_t n_tris, int threads, std::string& err);
+int rt_device_update_raw(RtDevice& D, int what, int64_t first, int64_t n, const float* a, const float* b, int threads, std::string& err);
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
-                     float* ms_build, uint64_t* h2d_bytes);
+                     float* ms_build, uint64_t* h2d_bytes, bool raw_resident = false);
 // rt_render.cu
 struct RtFrameStats { uint64_t primary, shadow, mirror; uint32_t launches; float ms_kernel[RT_K_COUNT]; uint32_t launches_kernel[RT_K_COUNT]; };
 int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs, int split = 0);

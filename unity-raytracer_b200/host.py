@@ -18,7 +18,8 @@ RT_OUT_RGBA32F, RT_OUT_RGBA8, RT_OUT_HIT_ID, RT_OUT_HIT_T = 1, 2, 4, 8
 RT_OUT_ALL = 15
 
 ABI_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_begin", "rt_scene_spheres",
-               "rt_scene_triangles", "rt_scene_mesh", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_render",
+               "rt_scene_triangles", "rt_scene_mesh", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
+               "rt_scene_update_triangles", "rt_scene_update_spheres", "rt_scene_update_lights", "rt_scene_recommit", "rt_render",
                "rt_render_device", "rt_read_outputs", "rt_device_outputs", "rt_intersect", "rt_get_stats", "rt_set_stream",
                "rt_set_partition", "rt_alloc_outputs", "rt_export_outputs", "rt_import_outputs", "rt_set_option"]
 
@@ -88,6 +89,11 @@ def load_library():
     L.rt_scene_lights.argtypes = [vp, fp, C.c_int, fp]
     L.rt_scene_commit.argtypes = [vp, fp]
     L.rt_scene_get_aabb.argtypes = [vp, fp]
+    L.rt_scene_update_mesh.argtypes = [vp, C.c_int, fp, fp, fp]
+    L.rt_scene_update_triangles.argtypes = [vp, C.c_int, C.c_int, fp, fp]
+    L.rt_scene_update_spheres.argtypes = [vp, C.c_int, C.c_int, fp]
+    L.rt_scene_update_lights.argtypes = [vp, fp, C.c_int, fp]
+    L.rt_scene_recommit.argtypes = [vp, fp]
     L.rt_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, vp, vp, C.POINTER(Stats)]
     L.rt_render_device.argtypes = [vp, C.POINTER(RenderParams), C.c_int, C.POINTER(Stats)]
     L.rt_read_outputs.argtypes = [vp, vp, vp, vp, vp]
@@ -157,6 +163,28 @@ class RayTracer:
             self._chk(L.rt_scene_commit(h, _fptr(bb)))
         else:
             self._chk(L.rt_scene_commit(h, None))
+
+    # ---- dirty-tracking updates (rt_scene_update_* + rt_scene_recommit): only what moved is re-sent ----
+    def update_mesh(self, mesh_index, v, n, aabb):
+        v, n, aabb = (np.ascontiguousarray(a, dtype=np.float32) for a in (v, n, aabb))
+        self._chk(self.L.rt_scene_update_mesh(self.h, int(mesh_index), _fptr(v), _fptr(n), _fptr(aabb)))
+
+    def update_triangles(self, first, v, n):
+        v, n = np.ascontiguousarray(v, dtype=np.float32), np.ascontiguousarray(n, dtype=np.float32)
+        self._chk(self.L.rt_scene_update_triangles(self.h, int(first), int(v.shape[0]), _fptr(v), _fptr(n)))
+
+    def update_spheres(self, first, center_r2):
+        s = np.ascontiguousarray(center_r2, dtype=np.float32)
+        self._chk(self.L.rt_scene_update_spheres(self.h, int(first), int(s.shape[0]), _fptr(s)))
+
+    def update_lights(self, lights, ambient=None):
+        li = np.ascontiguousarray(lights, dtype=np.float32)
+        amb = None if ambient is None else np.ascontiguousarray(ambient, dtype=np.float32)
+        self._chk(self.L.rt_scene_update_lights(self.h, _fptr(li), int(li.shape[0]), _fptr(amb) if amb is not None else None))
+
+    def recommit(self, scene_aabb=None):
+        bb = None if scene_aabb is None else np.ascontiguousarray(scene_aabb, dtype=np.float32)
+        self._chk(self.L.rt_scene_recommit(self.h, _fptr(bb) if bb is not None else None))
 
     def scene_aabb(self):
         out = np.zeros(6, np.float32)
