@@ -341,6 +341,26 @@ def run_ours(args, rank, world, local_rank):
                     "issue": issue, "three_bounds": tb,
                     "note": "BVH traversal is bound by SM issue slots / dependent-load latency, not by HBM (the scene is L2-resident): the hbm "
                             "fraction is reported because the bench vocabulary is hbm|tensor; `issue` carries the binding bound (DESIGN.md §5)"}
+        # ---- commit path as a stage of its own: the reference rebuilds its Scene every frame ----
+        steady = None
+        if world == 1:
+            rt2 = rtb.RayTracer((local_rank,))                     # device LBVH builder = the per-frame (dynamic scene) path
+            rt2.set_scene(scene)                                   # first commit allocates
+            full = []
+            for _ in range(3):
+                t0 = time.perf_counter(); rt2.set_scene(scene); full.append(time.perf_counter() - t0)
+            c2 = rt2.stats()
+            re = []
+            for _ in range(3):
+                t0 = time.perf_counter(); rt2.update_lights(scene.lights, scene.ambient); rt2.recommit(); re.append(time.perf_counter() - t0)
+            s3 = rt2.render_device(params, want, sync_stats=True); s3 = rt2.render_device(params, want, sync_stats=True)
+            steady = {"builder": "lbvh (device)", "full_commit_wall_ms": 1e3 * sorted(full)[1], "mprims_per_s": scene.n_prims / sorted(full)[1] / 1e6,
+                      "ms_upload": c2["ms_commit_upload"], "ms_bvh_build": c2["ms_commit_build"], "h2d_bytes": c2["h2d_bytes"],
+                      "recommit_after_update_wall_ms": 1e3 * sorted(re)[1], "render_ms_with_this_bvh": s3["ms_render"],
+                      "what": "steady-state re-commit of the whole scene from pageable host arrays through the C-ABI (rt_scene_begin .. "
+                              "rt_scene_commit, buffers already allocated), and rt_scene_update_lights + rt_scene_recommit (BVH rebuilt from "
+                              "device-resident arrays)"}
+            rt2.close()
         cb = None
         if world == 1 and not args.no_cpu:
             cb, _ = cpu_baseline(scene, params, 12.0, os.cpu_count() or 1)
@@ -354,7 +374,8 @@ def run_ours(args, rank, world, local_rank):
                            "tile_order": "heavy-first from the previous frame's measured tile costs (warm-up frames establish it)"},
                 "ms_per_step_by_rank": ms_by_rank, "rays_rank0": rays_rank, "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
                 "commit": {"ms_upload": cstats["ms_commit_upload"], "ms_bvh_build": cstats["ms_commit_build"], "h2d_bytes": cstats["h2d_bytes"],
-                           "wall_ms": 1e3 * commit_wall, "n_prims": cstats["n_prims"], "n_nodes": cstats["n_nodes"], "builder": args.builder}}
+                           "wall_ms": 1e3 * commit_wall, "n_prims": cstats["n_prims"], "n_nodes": cstats["n_nodes"], "builder": args.builder,
+                           "steady_state": steady}}
         print(json.dumps(line), file=_OUT, flush=True)
     barrier()
     rt.close()

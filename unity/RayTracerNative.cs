@@ -51,6 +51,11 @@ namespace RayTracer
 		[DllImport(Lib)] static extern int rt_scene_mesh(IntPtr ctx, Triangle[] v, float3[] normals, int nTris, ref NativeMaterial material, ref AABB aabb);
 		[DllImport(Lib)] static extern int rt_scene_lights(IntPtr ctx, PointLightData[] posIntensity, int n, ref float3 ambientRadiance);
 		[DllImport(Lib)] static extern int rt_scene_commit(IntPtr ctx, ref AABB sceneAabb);
+		[DllImport(Lib)] static extern int rt_scene_update_mesh(IntPtr ctx, int meshIndex, Triangle[] v, float3[] normals, ref AABB aabb);
+		[DllImport(Lib)] static extern int rt_scene_update_triangles(IntPtr ctx, int first, int n, Triangle[] v, float3[] normals);
+		[DllImport(Lib)] static extern int rt_scene_update_spheres(IntPtr ctx, int first, int n, Sphere[] centerR2);
+		[DllImport(Lib)] static extern int rt_scene_update_lights(IntPtr ctx, PointLightData[] posIntensity, int n, ref float3 ambientRadiance);
+		[DllImport(Lib)] static extern int rt_scene_recommit(IntPtr ctx, ref AABB sceneAabb);
 		[DllImport(Lib)] static extern int rt_render(IntPtr ctx, ref NativeRenderParams p, Color[] outRgba32f, IntPtr outRgba8,
 		                                             IntPtr outHitId, IntPtr outHitT, IntPtr stats);
 
@@ -86,6 +91,27 @@ namespace RayTracer
 			Check(rt_scene_lights(ctx, scene.PointLights.ToArray(), scene.PointLights.Count, ref ambient));
 			var aabb = scene.AABB;                               // Scene.cs:15, computed by Scene.CalculateAABB()
 			Check(rt_scene_commit(ctx, ref aabb));
+		}
+
+		/// Dirty-tracking alternative to UploadScene for frames in which the object COUNTS did not change (the usual case: only
+		/// transforms moved).  meshMoved[i] = SceneMesh i's transform.hasChanged; spheres / loose triangles / lights are small
+		/// and are simply re-sent.  The BVH is rebuilt on the device from the resident arrays (0.7 ms per million primitives).
+		public static void UpdateScene(ref Scene scene, bool[] meshMoved)
+		{
+			var meshes = scene.MeshData.Meshes;
+			for (int i = 0; i < meshes.Count; i++)
+			{
+				if (!meshMoved[i]) continue;
+				var box = meshes[i].AABB;
+				Check(rt_scene_update_mesh(ctx, i, meshes[i].Triangles, meshes[i].TriangleNormals, ref box));
+			}
+			Check(rt_scene_update_spheres(ctx, 0, scene.SphereData.Spheres.Count, scene.SphereData.Spheres.ToArray()));
+			Check(rt_scene_update_triangles(ctx, 0, scene.TriangleData.Triangles.Count, scene.TriangleData.Triangles.ToArray(),
+			                                scene.TriangleData.Normals.ToArray()));
+			var ambient = scene.AmbientLight.Radiance;
+			Check(rt_scene_update_lights(ctx, scene.PointLights.ToArray(), scene.PointLights.Count, ref ambient));
+			var aabb = scene.AABB;
+			Check(rt_scene_recommit(ctx, ref aabb));
 		}
 
 		/// Replaces CastPixelRays(CameraData) (RayTracingSetup.cs:275-302): fills PixelColors (x + y * ResX, y = 0 top row).
