@@ -203,7 +203,8 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
             bool ha = amin <= amax, hb = bmin <= bmax;
             int32_t ra = f2i(n3.x), rb = f2i(n3.y);
             if (ha && hb) {
-                if (bmin < amin) { int32_t t = ra; ra = rb; rb = t; }
+                // closest hit: nearer child first; any hit: the child the ray stays inside longer (order cannot change the answer)
+                if (ANY ? (bmax - bmin) > (amax - amin) : bmin < amin) { int32_t t = ra; ra = rb; rb = t; }
                 stk.push(rb);
                 node = ra;
             } else if (ha) node = ra;
