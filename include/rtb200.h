@@ -158,6 +158,8 @@ int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_
  *                  visits per ray); takes effect at the next rt_scene_begin.  leaf_max (1..8, default 4), pad_scale, t_slack likewise.
  *   packet         1 = warp-coherent packet traversal for coherent warps (default), 0 = always the per-lane loop
  *   fuse_shade     1 = shading (and the pixel write at depth 0) inside the shadow-trace kernel when the scene has <= 32 lights (default)
+ *   backcull       1 = shadow queries of lights behind the surface are answered without traversal when that is exact for every
+ *                  material and light of the scene (default; decided at commit; the queries are still counted in rays_shadow)
  *   hints          1 = heavy-first tile order from the previous frame's measured tile costs (default)
  *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 2) and the 1|2 streams they alternate over
  *                  (2: the drain of one wave overlaps the start of the next)

@@ -60,6 +60,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder)
     S.aabb_min = mk3(H.aabb[0], H.aabb[1], H.aabb[2]); S.aabb_max = mk3(H.aabb[3], H.aabb[4], H.aabb[5]);
     S.ambient = mk3(H.ambient[0], H.ambient[1], H.ambient[2]);
     S.t_slack = (float)t_slack;
+    S.backcull = H.backcull_ok() ? 1 : 0;
     S.mats = E.mats.data(); S.mesh_aabb = E.mesh_aabb.data(); S.mesh_base = E.mesh_base.data(); S.lights = E.lights.data();
     E.n_nodes = 0;
     if (n == 0) return;

@@ -204,3 +204,32 @@ def test_tile_mapping_division_by_multiplication(emu, scenes):
                 acc[mine] = g["hit_t"][mine]; cnt += g["stats"]["rays_primary"]
             e.set_partition(0, 1, 32)
             assert cnt == rx * ry and np.array_equal(acc, full["hit_t"]), (rx, ry, world, band)
+
+
+@pytest.mark.parametrize("case", ["plain", "kd_inf", "neg_zero_ambient", "huge_light", "light_on_surface"])
+def test_backfacing_light_shadow_skip_is_exact(emu, oracle, scenes, case):
+    """rt_shadow_irrelevant: shadow queries of lights behind the surface are answered without traversal.  The reference
+    (RayTracingSetup.cs:333-355,384-391) adds kd*0*E + 0 for such a light when it is visible and nothing when it is occluded:
+    identical unless kd*0*E is not a zero or the colour is -0.0 — those scenes must fall back to the full query."""
+    s = scenes.SceneArrays()
+    kd = (np.inf, 0.5, 0.5) if case == "kd_inf" else (0.9, 0.5, 0.5)
+    ka = (0.0, 1.0, 1.0)
+    big = scenes.material(kd, ka, (0, 0, 0), (1, 1, 1), 20.0, 0)
+    # a wall facing the camera (normal -z): one light in front of it, one BEHIND it (back-facing, visible: nothing in between),
+    # one behind it and occluded by a second triangle
+    s.add_triangle((-30, -30, 40, 0, 30, 40, 30, -30, 40), (0, 0, -1), big)
+    s.add_triangle((-30, -30, 60, 0, 30, 60, 30, -30, 60), (0, 0, -1), scenes.material((0.2, 0.9, 0.2), (1, 1, 1)))
+    s.add_sphere((12, 0, 30), 16.0, scenes.material((0.3, 0.3, 0.9), (1, 1, 1), (0, 0, 0), (1, 1, 1), 8.0, 0))
+    s.add_light((0, 5, 0), 1e38 if case == "huge_light" else 2e5)
+    s.add_light((5, 0, 50), 1e5)                       # between the walls: behind the first, in front of the second
+    s.add_light((0, 0, 80), 1e5)                       # behind both
+    if case == "light_on_surface":
+        s.add_light((0, 0, 40), 1e5)                   # d2 -> 0 for the centre pixel: E = inf
+    s.ambient = np.array((-1.0, 15, 15) if case == "neg_zero_ambient" else (15, 15, 15), np.float32)   # -1 * 0 = -0.0
+    p = scenes.make_params(96, 64, 10.0, 8.0, 5.0, (0.1, 0.1, 0.1), 0, 1)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    e = emu.EmuTracer(); e.set_scene(s)
+    got = e.render(p)
+    assert np.array_equal(ref["hit_id"], got["hit_id"])
+    assert np.array_equal(ref["rgba32f"].view(np.uint32), got["rgba32f"].view(np.uint32))     # bit pattern: NaN and -0.0 included
+    assert got["stats"]["rays_shadow"] == ref["stats"][1]                                      # skipped queries are still counted

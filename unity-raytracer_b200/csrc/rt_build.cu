@@ -247,6 +247,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
         float d2 = dx * dx + dy * dy + dz * dz;
         S.coherent_spread2 = std::isfinite(d2) ? 0.0025f * d2 : 0.f;
     }
+    S.backcull = (opt.backcull != 0 && H.backcull_ok()) ? 1 : 0;
     S.mats = D.mats.as<float4>(); S.mesh_aabb = D.mesh_aabb.as<float4>(); S.mesh_base = D.mesh_base.as<int32_t>();
     S.lights = D.lights.as<float4>();
     D.n_nodes = 0;

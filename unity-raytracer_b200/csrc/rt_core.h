@@ -44,6 +44,7 @@ struct RtScene {
     f3 ambient;               // AmbientLight.Radiance
     float t_slack;            // multiplicative slack on the traversal cull distance (conservative)
     int32_t packet;           // 1: coherent warps traverse as one packet (rt_packet.cuh); 0: always per-lane
+    int32_t backcull;         // 1: shadow queries of lights behind the surface may be skipped (rt_shadow_irrelevant; set at commit)
     float coherent_spread2;   // packet mode needs the warp's ray origins within this squared distance of each other
 };
 
@@ -334,6 +335,16 @@ RT_HD void rt_surf_mirror(const RtSurf& sf, int32_t bounce, int32_t max_bounces,
     }
 }
 
+// A shadow query whose answer cannot change the pixel.  For a light behind the surface (dot(L, N) <= RT_SPEC_CUTOFF < 0) the
+// reference adds diffuse = kd * max(0, ldn) * E = kd * 0 * E and specular = 0 when the light is visible (RTS:350-355,384-391)
+// and nothing when it is occluded: the same colour, bit for bit, provided kd * 0 * E is a zero and the colour it is added to
+// is not -0.0.  rt_device_commit sets S.backcull only when that holds for every material and light of the scene (finite kd,
+// finite intensities below 1e18, no -0.0 channel in ambient * ka); d2 > 1e-20 then keeps E = I / d2 finite.  The query is
+// still counted (the reference issues it) and reported as occluded, so the shading loop skips the light.
+RT_HD bool rt_shadow_irrelevant(const RtScene& S, f3 Ldir, f3 N, float d2) {
+    return S.backcull != 0 && um_dot(Ldir, N) <= RT_SPEC_CUTOFF && d2 > 1e-20f;
+}
+
 // Shadow queries of one hit for lights [light_begin, light_begin + n) (n <= 32), one lane: bit i set = light
 // light_begin+i is occluded (RTS:331-345).  The kernels run the same loop warp-uniformly with packet traversal.
 template <class STK>
@@ -347,6 +358,7 @@ RT_HD uint32_t rt_shadow_mask(const RtScene& S, f3 O, f3 D, float t, int32_t slo
         f3 Ldir; float d2;
         rt_light_ray(S, P, light_begin + i, Ldir, d2);
         ++n_shadow;
+        if (rt_shadow_irrelevant(S, Ldir, N, d2)) { mask |= 1u << i; continue; }
         f3 inv = rt_rcp3(Ldir);
         if (rt_scene_gate(S, sO, inv)) {                                     // Scene.cs:54 inside the shadow query
             float st; int32_t ss;

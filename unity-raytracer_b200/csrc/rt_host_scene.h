@@ -61,6 +61,26 @@ struct RtHostScene {
         for (int k = 0; k < 3; ++k) { aabb[k] = mn[k]; aabb[3 + k] = mx[k]; }
     }
 
+    // preconditions of rt_shadow_irrelevant (rt_core.h), over every material and light of the scene: kd finite (kd * 0 is a
+    // zero), intensities finite and below 1e18 (E = I / d2 finite for d2 > 1e-20), no -0.0 channel in ambient * ka (adding the
+    // +0.0 contribution of an unoccluded back-facing light would flip its sign)
+    bool backcull_ok() const {
+        auto neg0 = [](float x) { return x == 0.0f && std::signbit(x); };
+        auto mat_ok = [&](const rt_material& m) {
+            for (int k = 0; k < 3; ++k) {
+                if (!std::isfinite(m.diffuse[k])) return false;
+                if (neg0(ambient[k] * m.ambient[k])) return false;
+            }
+            return true;
+        };
+        for (auto& m : mesh_mats) if (!mat_ok(m)) return false;
+        for (auto& m : sphere_mats) if (!mat_ok(m)) return false;
+        for (auto& m : loose_mats) if (!mat_ok(m)) return false;
+        for (size_t l = 0; l < lights.size() / 6; ++l)
+            for (int k = 3; k < 6; ++k) if (!std::isfinite(lights[6 * l + k]) || !(std::fabs(lights[6 * l + k]) < 1e18f)) return false;
+        return true;
+    }
+
     // all materials in material-id order: meshes, spheres, loose triangles; 4 x float4 each (layout: RtScene::mats)
     std::vector<float> pack_materials() {
         std::vector<float> out;

@@ -55,6 +55,7 @@ struct RtOptions {
     int prefetch_max_mb = 96;          // ... when they total at most this many MiB (L2 is 126 MB)
     int upload_threads = 4;            // host threads that fill the pinned bounce buffers of a pageable upload (1 = plain cudaMemcpyAsync)
     int stream_upload = 1;             // single device + builder 0: rt_scene_mesh uploads straight from the caller's arrays (no host staging)
+    int backcull = 1;                  // skip shadow traversals whose answer cannot change the pixel (rt_shadow_irrelevant), when exact
     int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };

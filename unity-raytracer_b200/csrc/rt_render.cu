@@ -210,9 +210,9 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
         const bool has = slot >= 0;
         uint32_t mask = 0;
         if (__any_sync(full, has)) {
-            f3 P = mk3(0.f, 0.f, 0.f), sO = P;
+            f3 P = mk3(0.f, 0.f, 0.f), sO = P, N = mk3(0.f, 0.f, 1.f);
             if (has) {
-                f3 N; int mat_id;
+                int mat_id;
                 item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
                 ht = RT_LD_STREAM(hit_t + q);
                 rt_surf_geom(S, O, D, ht, slot, P, N, mat_id);
@@ -221,13 +221,16 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
             for (int i = 0; i < n_l; ++i) {
                 f3 Ldir = mk3(0.f, 0.f, 1.f); float d2 = 0.f;
                 bool act = false;
-                if (has) { rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow; }
-                const f3 inv = rt_rcp3(Ldir);
-                if (has) act = rt_scene_gate(S, sO, inv);                                              // Scene.cs:54
                 bool occluded = false;
+                if (has) {
+                    rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow;
+                    occluded = rt_shadow_irrelevant(S, Ldir, N, d2);                                   // light behind the surface
+                }
+                const f3 inv = rt_rcp3(Ldir);
+                if (has && !occluded) act = rt_scene_gate(S, sO, inv);                                 // Scene.cs:54
                 float st; int ss;
                 if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
-                    if (__any_sync(full, act)) occluded = rt_traverse_packet<true>(S, sO, Ldir, inv, act, d2, stk, st, ss);
+                    if (__any_sync(full, act) && rt_traverse_packet<true>(S, sO, Ldir, inv, act, d2, stk, st, ss)) occluded = true;
                 } else if (act) occluded = rt_traverse<true>(S, sO, Ldir, inv, d2, stk, st, ss);
                 if (occluded) mask |= 1u << i;
             }
