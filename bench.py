@@ -368,7 +368,10 @@ def run_ours(args, rank, world, local_rank):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
-                "config": {"workload": f"{args.workload}: {desc}", "rays_per_step": rays_step, "l2": "flushed between timed steps (256 MiB memset), per-step CUDA events",
+                "config": {"workload": f"{args.workload}: {desc}", "rays_per_step": rays_step,
+                           "rays_note": f"rank 0: {st['rays_primary']} primary + {st['rays_shadow']} shadow + {st['rays_mirror']} mirror queries, counted as the reference "
+                                        f"issues them; {st.get('rays_shadow_skipped', 0)} of the shadow queries (light behind the surface, outcome cannot change the pixel) "
+                                        "are answered without traversal", "l2": "flushed between timed steps (256 MiB memset), per-step CUDA events",
                            "partition": f"{world} rank(s), interleaved {args.band_rows}-row bands, scene replicated", "gather": gather, "output": "RGBA32F full frame on GPU 0",
                            "options": args.opt, "bvh": f"builder={args.builder} (commit is outside the timed region and reported under `commit`)",
                            "tile_order": "heavy-first from the previous frame's measured tile costs (warm-up frames establish it)"},

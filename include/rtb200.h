@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define RTB200_ABI_VERSION 1
+#define RTB200_ABI_VERSION 2
 
 typedef struct rt_ctx rt_ctx;
 
@@ -74,6 +74,7 @@ typedef struct {
      * (CUDA events around every launch on the launching stream). Order: RT_K_* below. */
     float ms_kernel[8];
     uint32_t launches_kernel[8];
+    uint64_t rays_shadow_skipped;   /* of rays_shadow: queries for lights behind the surface answered without traversal (option "backcull") */
 } rt_stats;
 enum { RT_K_TRACE_PRIMARY = 0, RT_K_SHADE_PRIMARY = 1, RT_K_TRACE_QUEUE = 2, RT_K_SHADE_QUEUE = 3, RT_K_FOLD = 4, RT_K_FINALIZE = 5,
        RT_K_SHADOW_PRIMARY = 6, RT_K_SHADOW_QUEUE = 7, RT_K_COUNT = 8 };

@@ -27,13 +27,13 @@ def test_library_exports_every_declared_symbol(rtb):
     for f in header_functions():
         assert hasattr(L, f), f"librtb200.so does not export {f}"
     assert sorted(rtb.host.ABI_SYMBOLS) == header_functions()
-    assert L.rt_abi_version() == 1
+    assert L.rt_abi_version() == 2
 
 
 def test_struct_layouts_match_header(rtb, scenes):
     assert C.sizeof(rtb.host.RenderParams) == 88          # rt_render_params
     assert scenes.MAT_DTYPE.itemsize == 56                # rt_material
-    assert C.sizeof(rtb.host.Stats) == 8 * 3 + 4 * 4 + 8 * 2 + 4 * 4 + 4 * 8 + 4 * 8
+    assert C.sizeof(rtb.host.Stats) == 8 * 3 + 4 * 4 + 8 * 2 + 4 * 4 + 4 * 8 + 4 * 8 + 8
 
 
 def test_no_cpu_fallback_without_a_device(rtb):

@@ -19,6 +19,8 @@ struct rt_ctx {
     std::vector<RtFrameStats> fstats;
 };
 
+static_assert(sizeof(rt_render_params) == 88 && sizeof(rt_material) == 56 && sizeof(rt_stats) == 144, "C-ABI struct layout (include/rtb200.h)");
+
 static thread_local std::string g_err;   // rt_last_error(NULL): errors of rt_create
 
 namespace {
@@ -108,7 +110,7 @@ int validate_params(rt_ctx* c, const rt_render_params* p) {
 int finish_stats(rt_ctx* c) {
     if (!c->stats_pending) return RT_OK;
     std::string& err = c->err;
-    uint64_t pr = 0, sh = 0, mi = 0; uint32_t launches = 0; float ms = 0.f;
+    uint64_t pr = 0, sh = 0, mi = 0, sk = 0; uint32_t launches = 0; float ms = 0.f;
     for (size_t i = 0; i < c->devs.size(); ++i) {
         RtDevice& D = c->devs[i];
         RtFrameStats fs = c->fstats[i];
@@ -117,13 +119,13 @@ int finish_stats(rt_ctx* c) {
         RT_CUDA(cudaEventSynchronize(D.ev1));
         float m = 0.f; RT_CUDA(cudaEventElapsedTime(&m, D.ev0, D.ev1));
         ms = m > ms ? m : ms;
-        pr += fs.primary; sh += fs.shadow; mi += fs.mirror; launches += fs.launches;
+        pr += fs.primary; sh += fs.shadow; mi += fs.mirror; sk += fs.shadow_skipped; launches += fs.launches;
         for (int k = 0; k < RT_K_COUNT; ++k) {       // max over devices: they run concurrently
             if (i == 0 || fs.ms_kernel[k] > c->stats.ms_kernel[k]) c->stats.ms_kernel[k] = fs.ms_kernel[k];
             c->stats.launches_kernel[k] = (i == 0 ? 0 : c->stats.launches_kernel[k]) + fs.launches_kernel[k];
         }
     }
-    c->stats.rays_primary = pr; c->stats.rays_shadow = sh; c->stats.rays_mirror = mi;
+    c->stats.rays_primary = pr; c->stats.rays_shadow = sh; c->stats.rays_mirror = mi; c->stats.rays_shadow_skipped = sk;
     c->stats.ms_render = ms; c->stats.kernel_launches = launches;
     c->stats_pending = false;
     return RT_OK;

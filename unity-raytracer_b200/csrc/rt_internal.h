@@ -134,7 +134,7 @@ int rt_device_update_raw(RtDevice& D, int what, int64_t first, int64_t n, const 
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
                      float* ms_build, uint64_t* h2d_bytes, bool raw_resident = false);
 // rt_render.cu
-struct RtFrameStats { uint64_t primary, shadow, mirror; uint32_t launches; float ms_kernel[RT_K_COUNT]; uint32_t launches_kernel[RT_K_COUNT]; };
+struct RtFrameStats { uint64_t primary, shadow, mirror, shadow_skipped; uint32_t launches; float ms_kernel[RT_K_COUNT]; uint32_t launches_kernel[RT_K_COUNT]; };
 int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs, int split = 0);
 int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs, int n, int32_t* d_ids, float* d_t,
                         const RtOptions& opt, std::string& err);

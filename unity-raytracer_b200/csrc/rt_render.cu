@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
     const int lane = threadIdx.x & 31;
     const unsigned full = 0xffffffffu;
     const unsigned n = DEPTH0 ? (unsigned)n_tiles * 32u : *n_ptr;
-    unsigned my_shadow = 0, my_mirror = 0;
+    unsigned my_shadow = 0, my_mirror = 0, my_skipped = 0;
     for (;;) {
         int wt = warp_fetch(work, lane);
         if ((unsigned)wt * 32u >= n) break;
@@ -225,6 +225,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
                 if (has) {
                     rt_light_ray(S, P, light_begin + i, Ldir, d2); ++my_shadow;
                     occluded = rt_shadow_irrelevant(S, Ldir, N, d2);                                   // light behind the surface
+                    my_skipped += occluded ? 1u : 0u;
                 }
                 const f3 inv = rt_rcp3(Ldir);
                 if (has && !occluded) act = rt_scene_gate(S, sO, inv);                                 // Scene.cs:54
@@ -261,6 +262,8 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
     }
     my_shadow = __reduce_add_sync(full, my_shadow);
     if (lane == 0 && my_shadow) atomicAdd(stats + 1, (unsigned long long)my_shadow);
+    my_skipped = __reduce_add_sync(full, my_skipped);
+    if (lane == 0 && my_skipped) atomicAdd(stats + 3, (unsigned long long)my_skipped);
     if (FUSE && lane == 0 && my_mirror) atomicAdd(stats + 2, (unsigned long long)my_mirror);
 }
 
@@ -579,7 +582,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         primary = (uint64_t)V.res_x * (uint64_t)V.n_local_rows * (uint64_t)n_pass;
     }
     RT_CUDA(cudaEventRecord(D.ev1, D.stream));
-    if (fs) { fs->primary = primary; fs->shadow = 0; fs->mirror = 0; fs->launches = launches; }
+    if (fs) { fs->primary = primary; fs->shadow = 0; fs->mirror = 0; fs->shadow_skipped = 0; fs->launches = launches; }
     return RT_OK;
 }
 
@@ -609,7 +612,7 @@ int rt_device_read_stats(RtDevice& D, RtFrameStats* fs, std::string& err) {
         RT_CUDA(cudaMemcpyAsync(h, D.stats.p, sizeof(h), cudaMemcpyDeviceToHost, D.stream));
         RT_CUDA(cudaStreamSynchronize(D.stream));
     }
-    fs->shadow = h[1]; fs->mirror = h[2];
+    fs->shadow = h[1]; fs->mirror = h[2]; fs->shadow_skipped = h[3];
     for (int k = 0; k < RT_K_COUNT; ++k) { fs->ms_kernel[k] = 0.f; fs->launches_kernel[k] = 0; }
     for (size_t i = 0; i < D.kev_class.size(); ++i) {
         float m = 0.f;

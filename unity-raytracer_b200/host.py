@@ -37,7 +37,7 @@ class Stats(C.Structure):
                 ("ms_render", C.c_float), ("ms_d2h", C.c_float), ("ms_commit_upload", C.c_float), ("ms_commit_build", C.c_float),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("n_prims", C.c_uint32), ("n_nodes", C.c_uint32),
                 ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32),
-                ("ms_kernel", C.c_float * 8), ("launches_kernel", C.c_uint32 * 8)]
+                ("ms_kernel", C.c_float * 8), ("launches_kernel", C.c_uint32 * 8), ("rays_shadow_skipped", C.c_uint64)]
 
     KERNELS = ("trace_primary", "shade_primary", "trace_queue", "shade_queue", "fold", "finalize", "shadow_primary", "shadow_queue")
 
