@@ -38,12 +38,13 @@ __device__ __forceinline__ bool rt_warp_coherent(f3 O, f3 D, bool active, float 
 // (the slab planes are monotone under the FMA, so near <= far always holds and the result is the same interval).
 // Returns the next leaf reference (< 0), or RT_PACKET_DONE when the stack ran empty.
 #define RT_PACKET_DONE ((int32_t)0x80000000)
-// Child order when both are hit (ORD): 0 = nearer entry first by majority of the lanes (closest-hit queries: the cull distance
-// shrinks fastest); 4 = any-hit queries: the child MORE lanes still need first, ties by the longer ray interval inside the box
-// (the result of an any-hit query does not depend on the order, only how soon the lanes find their occluder: cfg3 shadow
-// kernel -2.8 %, cfg5 frame -6.5 % against nearest-first; farthest-first was 11 % slower).  1..3 are the rejected variants.
+// Child order when both are hit (ORD), by majority of the lanes that hit both: 0 = nearer entry first (closest-hit queries:
+// the cull distance shrinks fastest); 2 = any-hit queries: the child in which the ray stays LONGER first.  The result of an
+// any-hit query does not depend on the order, only how soon the lanes find their occluder: cfg3 shadow kernel -2.8 %, cfg5
+// frame -6.5 % against nearest-first.  Rejected: farthest-first (+11 %); "child more lanes still need first" (same gain on
+// a full frame but the heaviest tiles get longer: +10 % on the shadow kernel of a 1/8 partition).
 #ifndef RT_ANY_ORDER
-#define RT_ANY_ORDER 4
+#define RT_ANY_ORDER 2
 #endif
 template <int OCT, int ORD, class STK>
 __device__ __forceinline__ int32_t rt_packet_descend(const float4* __restrict__ nodes, float idx_, float idy_, float idz_,
@@ -86,13 +87,9 @@ __device__ __forceinline__ int32_t rt_packet_descend(const float4* __restrict__ 
         int32_t ra = f2i(n3.x), rb = f2i(n3.y);
         if (ma && mb) {
             unsigned both = ma & mb;
-            unsigned bnear = (ORD == 0 || ORD == 3) ? __ballot_sync(full, ha && hb && bmin < amin)
-                           : ORD == 4 ? __ballot_sync(full, ha && hb && (bmax - bmin) > (amax - amin))
-                           : ORD == 1 ? __ballot_sync(full, ha && hb && bmin > amin)
+            unsigned bnear = ORD == 0 ? __ballot_sync(full, ha && hb && bmin < amin)
                                       : __ballot_sync(full, ha && hb && (bmax - bmin) > (amax - amin));
-            bool swap_ab = 2 * __popc(bnear) > __popc(both);                                // majority vote on the order
-            if ((ORD == 3 || ORD == 4) && __popc(ma) != __popc(mb)) swap_ab = __popc(mb) > __popc(ma);     // the child more lanes need first
-            if (swap_ab) { int32_t t = ra; ra = rb; rb = t; }
+            if (2 * __popc(bnear) > __popc(both)) { int32_t t = ra; ra = rb; rb = t; }     // majority vote on the order
             stk.push(rb);
             node = ra;
         } else if (ma) node = ra;
