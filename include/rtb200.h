@@ -161,8 +161,10 @@ int rt_import_outputs(rt_ctx* ctx, const void* handles_4x64, int res_x, int res_
  *   fuse_shade     1 = shading (and the pixel write at depth 0) inside the shadow-trace kernel when the scene has <= 32 lights (default)
  *   backcull       1 = shadow queries of lights behind the surface are answered without traversal when that is exact for every
  *                  material and light of the scene (default; decided at commit; the queries are still counted in rays_shadow)
+ *   light_split    fused shadow kernel: tiles of cost class >= this are handed out as one work item per light (0 = off, -1 = auto,
+ *                  the default: class 6 on partitions of a quarter frame or less); needs hints
  *   hints          1 = heavy-first tile order from the previous frame's measured tile costs (default)
- *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 2) and the 1|2 streams they alternate over
+ *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 0 = auto: 2, or 1 on a quarter-frame partition or less) and the 1|2 streams they alternate over
  *                  (2: the drain of one wave overlaps the start of the next)
  *   copy_waves     number of waves rt_render splits a frame into so that the copy-out of one wave overlaps the kernels of the
  *                  next (default 8, 1 = off)

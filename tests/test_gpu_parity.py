@@ -350,3 +350,19 @@ def test_dirty_updates_plus_recommit_equal_full_commit(rtb, scenes, oracle, buil
     got = r.render(p)
     assert np.array_equal(want["hit_id"], got["hit_id"])
     r.close()
+
+
+def test_light_split_and_hints_do_not_change_the_frame(rtb, scenes):
+    """Scheduling only: heavy-first tile order (hints, active from the second frame on) and per-light work items for heavy
+    tiles (light_split, combined by the last item through atomics) must reproduce the first frame bit for bit."""
+    s, p = scenes.cfg3_scene(n=48), scenes.cfg3_params(960, 540)
+    base = rtb.RayTracer((0,)); base.set_option("hints", 0); base.set_scene(s)
+    want = base.render(p); base.close()
+    for ls in (1, 3, 6):
+        r = rtb.RayTracer((0,)); r.set_option("light_split", ls); r.set_scene(s)
+        for frame in range(3):
+            got = r.render(p)
+            for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+                assert np.array_equal(want[k], got[k]), (ls, frame, k)
+            assert got["stats"]["rays_shadow"] == want["stats"]["rays_shadow"]
+        r.close()

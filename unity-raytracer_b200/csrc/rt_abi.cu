@@ -36,7 +36,7 @@ void device_release(RtDevice& D) {
         b->release();
     rt_upload_release(D);
     for (auto& L : D.lanes) {
-        for (DevBuf* b : {&L.hit0_t, &L.hit0_slot, &L.hitq_t, &L.hitq_slot, &L.rays[0], &L.rays[1], &L.counters, &L.occl}) b->release();
+        for (DevBuf* b : {&L.hit0_t, &L.hit0_slot, &L.hitq_t, &L.hitq_slot, &L.rays[0], &L.rays[1], &L.counters, &L.occl, &L.split_occl, &L.split_acc}) b->release();
         for (auto& b : L.local) b.release();
         for (auto& b : L.link) b.release();
         if (L.done) cudaEventDestroy(L.done);
@@ -144,7 +144,7 @@ int render_device_impl(rt_ctx* c, const rt_render_params* p, int want, int split
     c->fstats.assign(c->devs.size(), RtFrameStats{});
     for (size_t i = 0; i < c->devs.size(); ++i) {
         RtView V = make_view(c, p, (int)i);
-        rc = rt_device_render(c->devs[i], V, want, c->opt, c->err, &c->fstats[i], split ? split : c->opt.waves);
+        rc = rt_device_render(c->devs[i], V, want, c->opt, c->err, &c->fstats[i], split ? split : (c->opt.waves > 0 ? c->opt.waves : (V.world >= 4 ? 1 : 2)));
         if (rc) return rc;
     }
     c->stats_pending = true;
@@ -571,7 +571,7 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "t_slack") { if (value < 1) return fail(c, RT_E_INVALID, "t_slack < 1"); c->opt.t_slack = value; }
     else if (k == "ctas_per_sm") { c->opt.ctas_per_sm = (int)value; }
     else if (k == "block") { c->opt.block = (int)value; }
-    else if (k == "waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "waves must be 1..64"); c->opt.waves = (int)value; }
+    else if (k == "waves") { if (value < 0 || value > 64) return fail(c, RT_E_INVALID, "waves must be 0 (auto) or 1..64"); c->opt.waves = (int)value; }
     else if (k == "lanes") { if (value != 1 && value != 2) return fail(c, RT_E_INVALID, "lanes must be 1 or 2"); c->opt.lanes = (int)value; }
     else if (k == "fuse_shade") { c->opt.fuse_shade = value != 0; }
     else if (k == "prefetch") { c->opt.prefetch = value != 0; }
@@ -579,6 +579,7 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "upload_threads") { c->opt.upload_threads = (int)value; }
     else if (k == "stream_upload") { c->opt.stream_upload = value != 0; }
     else if (k == "backcull") { c->opt.backcull = value != 0; }
+    else if (k == "light_split") { c->opt.light_split = (int)value; }
     else if (k == "hints") { c->opt.hints = value != 0; }
     else if (k == "copy_waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "copy_waves must be 1..64"); c->opt.copy_waves = (int)value; }
     else if (k == "builder") { if (value != 0 && value != 1) return fail(c, RT_E_INVALID, "builder must be 0 (device LBVH) or 1 (host SAH)"); c->opt.builder = (int)value; }

@@ -46,7 +46,8 @@ struct RtOptions {
     int ctas_per_sm = 0;               // 0 = occupancy query
     int packet = 1;                    // warp-coherent packet traversal for coherent warps
     int builder = 0;                   // 0 = device LBVH (fast commit), 1 = host binned-SAH (rt_sah.h; slower commit, fewer node visits)
-    int waves = 2;                     // rt_render_device: minimum number of waves per pass (2 lanes: tails overlap)
+    int waves = 0;                     // rt_render_device: minimum number of waves per pass; 0 = auto: 2 (two lanes: tails overlap),
+                                       // 1 on partitions of a quarter frame or less (smaller kernels only lengthen the critical path)
     int lanes = 2;                     // 1 = all waves on one stream; 2 = alternate waves over two streams (tail overlap)
     int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
                                        // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
@@ -56,6 +57,10 @@ struct RtOptions {
     int upload_threads = 4;            // host threads that fill the pinned bounce buffers of a pageable upload (1 = plain cudaMemcpyAsync)
     int stream_upload = 1;             // single device + builder 0: rt_scene_mesh uploads straight from the caller's arrays (no host staging)
     int backcull = 1;                  // skip shadow traversals whose answer cannot change the pixel (rt_shadow_irrelevant), when exact
+    int light_split = -1;              // fused depth-0 shadow kernel: tiles of cost class >= this become one work item per light on
+                                       // separate warps (needs hints).  0 = off, -1 = auto: class 6 (>= 128K cycles) on partitions of
+                                       // 1/4 frame or less, off otherwise — it shortens the heaviest tiles (1/8 partition: shadow
+                                       // kernel -5..11 %) but costs 4 % on a full frame (duplicated set-up, lost cache sharing)
     int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };
@@ -81,7 +86,7 @@ struct RtDevice {
     struct Lane {
         cudaStream_t own_stream = nullptr;   // lane 0 runs on D.stream, the others on their own stream
         cudaEvent_t done = nullptr;
-        DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, occl;
+        DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, occl, split_occl, split_acc;
         std::vector<DevBuf> local;          // [depth] float4 per entry
         std::vector<DevBuf> link;           // [depth>=1] float4 (km.xyz, parent index bits)
     };

@@ -70,7 +70,9 @@ __device__ __forceinline__ int warp_fetch(unsigned* counter, int lane) {
 // (longest-processing-time-first list scheduling), falling back to image order when no hints exist (first frame, changed
 // resolution / partition / wave layout).  Hints only reorder work: results are unaffected, stale hints are harmless.
 constexpr int RT_NCLS = 8;
-struct RtHintIn { const int* lists; const unsigned* counts; size_t stride; };     // lists[c * stride + i], counts[c]; null = image order
+// lists[c * stride + i], counts[c]; null = image order.  lsplit: cost classes >= lsplit are handed out as one item per light
+// (fused depth-0 shadow kernel only; RT_NCLS = off)
+struct RtHintIn { const int* lists; const unsigned* counts; size_t stride; int lsplit; };
 struct RtHintOut { int* lists; unsigned* counts; size_t stride; };                // null = do not record
 
 __device__ __forceinline__ int rt_cost_class(long long cycles) {
@@ -88,6 +90,30 @@ __device__ __forceinline__ int rt_hint_tile(const RtHintIn& h, int k, int lane) 
     if (src < 0) return k;                                 // inconsistent hints: cannot happen when the host validated them
     unsigned excl = __shfl_sync(0xffffffffu, incl - cnt, src);
     return h.lists[(size_t)(RT_NCLS - 1 - src) * h.stride + ((unsigned)k - excl)];
+}
+// Per-light items for heavy tiles.  On a small partition a trace kernel lasts as long as its heaviest tile (a dependent chain
+// that no amount of idle warps shortens), and the fused shadow kernel walks a tile's lights one after the other: cfg3's
+// heaviest tiles take 2 x 150 us.  The shadow queries of different lights are independent, so tiles of the classes >=
+// h.lsplit become n_l work items (tile, light) that run on n_l warps; each ORs its occlusion bit into a per-item word and the
+// LAST item of a tile to finish (per-tile arrival counter) shades and writes the pixel with the combined mask — exactly the
+// mask the single-warp loop would have built.  Overhead per extra item: regenerating the ray and the surface point (~100
+// instructions against thousands), so the split is applied regardless of the partition size.
+// Returns false when k is beyond the last item; light = -1: all lights in this item.
+__device__ __forceinline__ bool rt_hint_item_lights(const RtHintIn& h, int k, int lane, int n_tiles, int n_l, int& tile, int& light) {
+    light = -1;
+    if (!h.lists) { tile = k; return k < n_tiles; }
+    const int cls = RT_NCLS - 1 - lane;                                          // lane 0 holds the heaviest class
+    const unsigned mult = (lane < RT_NCLS && cls >= h.lsplit && n_l > 1) ? (unsigned)n_l : 1u;
+    const unsigned cnt = lane < RT_NCLS ? h.counts[cls] * mult : 0u;
+    unsigned incl = cnt;
+    for (int o = 1; o < RT_NCLS; o <<= 1) { unsigned v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+    const unsigned m = __ballot_sync(0xffffffffu, lane < RT_NCLS && (unsigned)k < incl);
+    const int src = __ffs(m) - 1;                                                // first class whose inclusive prefix exceeds k
+    if (src < 0) return false;                                                   // k >= number of items
+    unsigned j = (unsigned)k - __shfl_sync(0xffffffffu, incl - cnt, src);
+    if (__shfl_sync(0xffffffffu, mult, src) > 1u) { light = (int)(j % (unsigned)n_l); j /= (unsigned)n_l; }
+    tile = h.lists[(size_t)(RT_NCLS - 1 - src) * h.stride + j];
+    return true;
 }
 __device__ __forceinline__ void rt_hint_record(const RtHintOut& h, int tile, long long cycles, int lane) {
     if (!h.lists || lane != 0) return;
@@ -182,6 +208,8 @@ struct RtFuse {
     float4* rays_out; float4* link_out; unsigned* next_count;      // mirror-ray queue of the next depth (null at max depth)
     int fin;                           // 1: also finalize (depth 0 wave, no mirror depth above it)
     int pass, n_pass; float4* accum; RtOut out;
+    uint32_t* split_occl;              // per item: occlusion bits of a tile split by light (zero between uses)
+    unsigned long long* split_acc;     // per tile: (cycles << 6 | arrivals) of its per-light items (zero between uses)
 };
 
 // (A "mega" variant that also ran k_trace_primary's body here, camera ray to final colour in registers, was measured
@@ -198,10 +226,13 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
     const unsigned n = DEPTH0 ? (unsigned)n_tiles * 32u : *n_ptr;
     unsigned my_shadow = 0, my_mirror = 0, my_skipped = 0;
     for (;;) {
-        int wt = warp_fetch(work, lane);
-        if ((unsigned)wt * 32u >= n) break;
-        if (DEPTH0) wt = rt_hint_tile(hin, wt, lane);
-        const long long c0 = clock64();
+        int wt = warp_fetch(work, lane), one_light = -1;
+        if (DEPTH0 && FUSE) { if (!rt_hint_item_lights(hin, wt, lane, n_tiles, n_l, wt, one_light)) break; }
+        else {
+            if ((unsigned)wt * 32u >= n) break;
+            if (DEPTH0) wt = rt_hint_tile(hin, wt, lane);
+        }
+        long long c0 = clock64();
         const unsigned q = (unsigned)wt * 32u + lane;
         f3 O = mk3(0.f, 0.f, 0.f), D = mk3(0.f, 0.f, 1.f);
         float ht = 0.f;
@@ -218,7 +249,8 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
                 rt_surf_geom(S, O, D, ht, slot, P, N, mat_id);
                 sO = P + N * RT_SHADOW_EPS;                                                        // RTS:331
             }
-            for (int i = 0; i < n_l; ++i) {
+            const int i0 = one_light >= 0 ? one_light : 0, i1 = one_light >= 0 ? one_light + 1 : n_l;
+            for (int i = i0; i < i1; ++i) {
                 f3 Ldir = mk3(0.f, 0.f, 1.f); float d2 = 0.f;
                 bool act = false;
                 bool occluded = false;
@@ -237,6 +269,19 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
             }
         }
         if (!FUSE) { if (q < n) occl[q] = mask; if (DEPTH0) rt_hint_record(hout, wt, clock64() - c0, lane); continue; }
+        if (DEPTH0 && one_light >= 0) {                        // one of the n_l items of a tile split by light
+            if (mask) atomicOr(F.split_occl + q, mask);
+            __threadfence();
+            __syncwarp(full);
+            unsigned long long old = 0ull;
+            if (lane == 0) old = atomicAdd(F.split_acc + wt, ((unsigned long long)(clock64() - c0) << 6) | 1ull);
+            old = __shfl_sync(full, old, 0);
+            if ((int)(old & 63ull) != n_l - 1) continue;        // another item finishes the tile
+            __threadfence();
+            mask = atomicExch(F.split_occl + q, 0u);            // everybody's bits; leaves the word zero for the next use
+            if (lane == 0) F.split_acc[wt] = 0ull;
+            c0 -= (long long)(old >> 6);                        // the tile's cost = the sum over its items
+        }
         // ---- fused shading (k_shade's body) ----
         RtMirror mir; mir.emit = false;
         float4 col = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);                            // RTS:310-311
@@ -439,6 +484,12 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                 for (int d = 1; d <= maxd; ++d) RT_CUDA(L.link[d].ensure(W * 16));
             }
             RT_CUDA(L.occl.ensure(W * 4 * (size_t)(n_chunks < 1 ? 1 : n_chunks)));
+            if (opt.light_split != 0 && opt.fuse_shade && n_chunks == 1) {       // combine buffers of the per-light items: zero between uses
+                const void* p0 = L.split_occl.p; const void* p1 = L.split_acc.p;
+                RT_CUDA(L.split_occl.ensure(W * 4)); RT_CUDA(L.split_acc.ensure((size_t)wave_tiles * 8));
+                if (L.split_occl.p != p0) RT_CUDA(cudaMemsetAsync(L.split_occl.p, 0, L.split_occl.bytes, D.stream));
+                if (L.split_acc.p != p1) RT_CUDA(cudaMemsetAsync(L.split_acc.p, 0, L.split_acc.bytes, D.stream));
+            }
             if (li > 0) {
                 if (!L.own_stream) RT_CUDA(cudaStreamCreateWithFlags(&L.own_stream, cudaStreamNonBlocking));
                 if (!L.done) RT_CUDA(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
@@ -466,9 +517,11 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                 RT_CUDA(cudaStreamWaitEvent(D.lanes[1].own_stream, D.lanes[1].done, 0));
             }
         }
+        const int lsplit = opt.light_split >= 0 ? opt.light_split : (V.world >= 4 ? 6 : 0);
         auto hin_of = [&](RtDevice::Hints& hh, int tb, int wi) {
-            RtHintIn h{nullptr, nullptr, 0};
-            if (hint_in) h = RtHintIn{hh.lists[hb_in].as<int>() + tb, hh.counts[hb_in].as<unsigned>() + (size_t)wi * RT_NCLS, hstride};
+            RtHintIn h{nullptr, nullptr, 0, RT_NCLS};
+            if (hint_in) h = RtHintIn{hh.lists[hb_in].as<int>() + tb, hh.counts[hb_in].as<unsigned>() + (size_t)wi * RT_NCLS, hstride,
+                                      (&hh == &D.hint_shadow && lsplit > 0) ? lsplit : RT_NCLS};
             return h;
         };
         auto hout_of = [&](RtDevice::Hints& hh, int tb, int wi, bool on) {
@@ -524,12 +577,12 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                         }
                         if (fuse) {
                             RtFuse F{d, L.local[d].as<float4>(), rout, lout, C + d + 1, (d == 0 && maxd == 0) ? 1 : 0, pass, n_pass,
-                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out};
+                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out, L.split_occl.as<uint32_t>(), L.split_acc.as<unsigned long long>()};
                             if (F.fin && n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
                             if (d == 0) k_trace_shadow<true, true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
                                                                                                   hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0));
-                            else k_trace_shadow<false, true><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
+                            else k_trace_shadow<false, true><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                             continue;
                         }
@@ -540,7 +593,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
                             if (d == 0) k_trace_shadow<true, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
                                                                                                    hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0 && c == 0));
-                            else k_trace_shadow<false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0}, RtHintOut{nullptr, nullptr, 0});
+                            else k_trace_shadow<false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                         }
                         kbegin(d ? RT_K_SHADE_QUEUE : RT_K_SHADE_PRIMARY);
