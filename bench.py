@@ -293,6 +293,22 @@ def run_ours(args, rank, world, local_rank):
            "d2h_bytes_per_step": X * Y * 16, "ms_per_step": 1e3 * e2e_s / args.steps,
            "what": "rt_render() into a pinned host Color[] (RGBA32F, the reference's PixelColors format); scene committed once"}
 
+    # ---- N > 1: the frame the ranks assembled in rank 0's framebuffer must be the 1-GPU frame, bit for bit ----
+    gather_check = None
+    if world > 1 and not args.local_out:
+        barrier()
+        if rank == 0:
+            solo = rtb.RayTracer((local_rank,))
+            solo.set_option("builder", 1 if args.builder == "sah" else 0)
+            solo.set_scene(scene)
+            ref = solo.render(params, want)["rgba32f"]
+            solo.close()
+            same = bool(np.array_equal(ref.view(np.uint32), host_out["rgba32f"].view(np.uint32)))
+            gather_check = {"bit_identical_to_1gpu_frame": same, "bytes_compared": int(ref.nbytes)}
+            if not same:
+                raise SystemExit("bench.py: the gathered N-GPU frame differs from the 1-GPU frame")
+        barrier()
+
     # ---- roofline of the dominant kernel: per-kernel CUDA events on the launching stream over K more steps ----
     rt.set_option("kernel_timing", 1)
     ksum, kcnt = {}, {}
@@ -372,7 +388,7 @@ def run_ours(args, rank, world, local_rank):
                            "rays_note": f"rank 0: {st['rays_primary']} primary + {st['rays_shadow']} shadow + {st['rays_mirror']} mirror queries, counted as the reference "
                                         f"issues them; {st.get('rays_shadow_skipped', 0)} of the shadow queries (light behind the surface, outcome cannot change the pixel) "
                                         "are answered without traversal", "l2": "flushed between timed steps (256 MiB memset), per-step CUDA events",
-                           "partition": f"{world} rank(s), interleaved {args.band_rows}-row bands, scene replicated", "gather": gather, "output": "RGBA32F full frame on GPU 0",
+                           "partition": f"{world} rank(s), interleaved {args.band_rows}-row bands, scene replicated", "gather": gather, "gather_check": gather_check, "output": "RGBA32F full frame on GPU 0",
                            "options": args.opt, "bvh": f"builder={args.builder} (commit is outside the timed region and reported under `commit`)",
                            "tile_order": "heavy-first from the previous frame's measured tile costs (warm-up frames establish it)"},
                 "ms_per_step_by_rank": ms_by_rank, "rays_rank0": rays_rank, "clocks": clocks, "e2e": e2e, "gpu_launches": launches_step * args.steps, "roofline": roofline, "cpu_baseline": cb,
