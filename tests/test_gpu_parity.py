@@ -366,3 +366,57 @@ def test_light_split_and_hints_do_not_change_the_frame(rtb, scenes):
                 assert np.array_equal(want[k], got[k]), (ls, frame, k)
             assert got["stats"]["rays_shadow"] == want["stats"]["rays_shadow"]
         r.close()
+
+
+def test_cfg4_full_size(rtb, scenes, oracle):
+    """BASELINE config 4 at full size (125 meshes, 10 240 000 triangles, 7680x4320): (a) the second frame (heavy-first tile
+    order) equals the first, (b) the union of a 4-rank band partition (quarter-frame partitions: one wave, per-light items)
+    equals the 1-rank frame, (c) 2 048 random pixels equal the oracle (CPU BVH mode), (d) one shadow query per (hit, light)."""
+    s, p = scenes.cfg4_scene(), scenes.cfg4_params()
+    want = 2 | 4 | 8
+    r = rtb.RayTracer((0,)); r.set_scene(s)
+    f0 = r.render(p, want)
+    ids, t, rgba = f0["hit_id"].copy(), f0["hit_t"].copy(), f0["rgba8"].copy()
+    f1 = r.render(p, want)
+    assert np.array_equal(ids, f1["hit_id"]) and np.array_equal(t, f1["hit_t"]) and np.array_equal(rgba, f1["rgba8"])
+    st = f1["stats"]
+    hits = int((ids[:, 0] != 0).sum())
+    assert st["rays_primary"] == 7680 * 4320 and st["rays_shadow"] == 2 * hits and st["rays_mirror"] == 0
+    assert len(np.unique(ids[ids[:, 0] == 3, 2])) >= 50                      # most of the 125 meshes are visible
+    r.close()
+    rows = np.arange(4320)
+    for rank in range(4):
+        part = rtb.RayTracer((0,)); part.set_partition(rank, 4, 32); part.set_scene(s)
+        g = None
+        for frame in range(2):                                               # second frame: hints + per-light work items
+            g = part.render(p, 2 | 8, out=g)
+        mine = np.repeat(((rows // 32) % 4) == rank, 7680)
+        assert np.array_equal(g["rgba8"][mine], rgba[mine]) and np.array_equal(g["hit_t"][mine], t[mine]), rank
+        part.close()
+    px = np.random.default_rng(4).choice(7680 * 4320, 2048, replace=False)
+    ref = oracle.OracleScene(s).render(p, oracle.ACCELERATED, pixels=px)
+    assert np.array_equal(ref["hit_id"], ids[px]) and np.array_equal(ref["hit_t"], t[px])
+    assert np.abs(ref["rgba8"].astype(int) - rgba[px].astype(int)).max() <= 1
+
+
+def test_cfg5_full_size(rtb, scenes, oracle):
+    """BASELINE config 5 at full size (100 000 spheres + 5 000 000 triangles, 3840x2160, 4x4 spp, depth 4): (a) device LBVH and
+    host SAH BVH give the same frame, (b) 512 random pixels (16 samples each, mirrors included) equal the oracle,
+    (c) ray counts: primary = 16 per pixel, mirror rays present."""
+    s, p = scenes.cfg5_scene(), scenes.cfg5_params()
+    want = 2 | 4 | 8
+    frames = []
+    for builder in (0, 1):
+        r = rtb.RayTracer((0,)); r.set_option("builder", builder); r.set_scene(s)
+        f = r.render(p, want)
+        frames.append({k: f[k].copy() if k != "stats" else f[k] for k in f})
+        r.close()
+    for k in ("rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(frames[0][k], frames[1][k]), k
+    st = frames[0]["stats"]
+    assert st["rays_primary"] == 16 * 3840 * 2160 and st["rays_mirror"] > 0 and st["rays_shadow"] > st["rays_primary"]
+    assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == tuple(frames[1]["stats"][k] for k in ("rays_primary", "rays_shadow", "rays_mirror"))
+    px = np.random.default_rng(5).choice(3840 * 2160, 512, replace=False)
+    ref = oracle.OracleScene(s).render(p, oracle.ACCELERATED, pixels=px)
+    assert np.array_equal(ref["hit_id"][:, :2], frames[0]["hit_id"][px][:, :2]) and np.array_equal(ref["hit_t"], frames[0]["hit_t"][px])
+    assert np.abs(ref["rgba8"].astype(int) - frames[0]["rgba8"][px].astype(int)).max() <= 1
