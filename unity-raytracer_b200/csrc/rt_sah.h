@@ -14,6 +14,7 @@
 #include <thread>
 #include <future>
 #include <atomic>
+#include <array>
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
@@ -29,7 +30,7 @@ struct RtSahBuilder {
     std::vector<int32_t> order;               // leaf-slot order of scan keys
     std::vector<float> nodes;                 // 16 floats per node
     std::atomic<int32_t> n_nodes{0};
-    int spawn_depth = 0;
+    int spawn_depth = 0, threads_ = 1;
     static constexpr int NB = 16;             // bins per axis
 
     static inline float area(const float* lo, const float* hi) {
@@ -46,27 +47,77 @@ struct RtSahBuilder {
         const int32_t cnt = e - b;
         float lo[3], hi[3], clo[3], chi[3];
         reset(lo, hi); reset(clo, chi);
-        for (int32_t i = b; i < e; ++i) {
-            const RtSahBox& x = boxes[order[i]];
-            grow(lo, hi, x.lo, x.hi);
-            for (int k = 0; k < 3; ++k) { float c = 0.5f * (x.lo[k] + x.hi[k]); clo[k] = std::fmin(clo[k], c); chi[k] = std::fmax(chi[k], c); }
+        // Ranges near the root are swept by several threads (the subtree tasks have not fanned out yet: without this the top
+        // three levels cost as much as all the others together).  min/max and counts are order-independent, so the tree is
+        // the same as the serial one.
+        const int par = (depth < spawn_depth && cnt >= (1 << 16)) ? (threads_ >> depth > 1 ? threads_ >> depth : 1) : 1;
+        auto chunk = [&](int c, int32_t& cb, int32_t& ce) { cb = b + (int32_t)((int64_t)cnt * c / par); ce = b + (int32_t)((int64_t)cnt * (c + 1) / par); };
+        auto bounds_of = [&](int32_t cb, int32_t ce, float* l, float* h, float* cl, float* ch) {
+            reset(l, h); reset(cl, ch);
+            for (int32_t i = cb; i < ce; ++i) {
+                const RtSahBox& x = boxes[order[i]];
+                grow(l, h, x.lo, x.hi);
+                for (int k = 0; k < 3; ++k) { float c = 0.5f * (x.lo[k] + x.hi[k]); cl[k] = std::fmin(cl[k], c); ch[k] = std::fmax(ch[k], c); }
+            }
+        };
+        if (par == 1) bounds_of(b, e, lo, hi, clo, chi);
+        else {
+            std::vector<std::array<float, 12>> part((size_t)par);
+            std::vector<std::future<void>> fs;
+            for (int c = 0; c < par; ++c) {
+                int32_t cb, ce; chunk(c, cb, ce);
+                float* q = part[(size_t)c].data();
+                fs.push_back(std::async(std::launch::async, [=, &bounds_of]() { bounds_of(cb, ce, q, q + 3, q + 6, q + 9); }));
+            }
+            for (auto& f : fs) f.get();
+            for (int c = 0; c < par; ++c) { const float* q = part[(size_t)c].data(); grow(lo, hi, q, q + 3); grow(clo, chi, q + 6, q + 9); }
         }
         for (int k = 0; k < 3; ++k) { out_lo[k] = lo[k]; out_hi[k] = hi[k]; }
         if (cnt <= leaf_max) return ~(b * 8 + (cnt - 1));
         // ---- binned SAH over the three axes ----
-        int best_axis = -1, best_bin = -1; float best_cost = FLT_MAX;
+        struct Bins { int32_t bc[3][NB]; float blo[3][NB][3], bhi[3][NB][3]; };
+        float scale3[3]; bool axis_ok[3];
         for (int ax = 0; ax < 3; ++ax) {
             const float ext = chi[ax] - clo[ax];
-            if (!(ext > 0.f) || !std::isfinite(ext)) continue;
-            const float scale = (float)NB / ext;
-            int32_t bc[NB]; float blo[NB][3], bhi[NB][3];
-            for (int j = 0; j < NB; ++j) { bc[j] = 0; reset(blo[j], bhi[j]); }
-            for (int32_t i = b; i < e; ++i) {
+            axis_ok[ax] = (ext > 0.f) && std::isfinite(ext);
+            scale3[ax] = axis_ok[ax] ? (float)NB / ext : 0.f;
+        }
+        auto bin_range = [&](int32_t cb, int32_t ce, Bins& B) {
+            for (int ax = 0; ax < 3; ++ax) for (int j = 0; j < NB; ++j) { B.bc[ax][j] = 0; reset(B.blo[ax][j], B.bhi[ax][j]); }
+            for (int32_t i = cb; i < ce; ++i) {
                 const RtSahBox& x = boxes[order[i]];
-                int j = (int)((0.5f * (x.lo[ax] + x.hi[ax]) - clo[ax]) * scale);
-                j = j < 0 ? 0 : (j >= NB ? NB - 1 : j);
-                ++bc[j]; grow(blo[j], bhi[j], x.lo, x.hi);
+                for (int ax = 0; ax < 3; ++ax) {
+                    if (!axis_ok[ax]) continue;
+                    int j = (int)((0.5f * (x.lo[ax] + x.hi[ax]) - clo[ax]) * scale3[ax]);
+                    j = j < 0 ? 0 : (j >= NB ? NB - 1 : j);
+                    ++B.bc[ax][j]; grow(B.blo[ax][j], B.bhi[ax][j], x.lo, x.hi);
+                }
             }
+        };
+        Bins first;                                              // stack: one per node, no allocation on the serial path
+        std::vector<Bins> bins;
+        if (par == 1) bin_range(b, e, first);
+        else {
+            bins.resize((size_t)par);
+            std::vector<std::future<void>> fs;
+            for (int c = 0; c < par; ++c) {
+                int32_t cb, ce; chunk(c, cb, ce);
+                Bins* B = &bins[(size_t)c];
+                fs.push_back(std::async(std::launch::async, [=, &bin_range]() { bin_range(cb, ce, *B); }));
+            }
+            for (auto& f : fs) f.get();
+            first = bins[0];
+            for (int c = 1; c < par; ++c)
+                for (int ax = 0; ax < 3; ++ax) for (int j = 0; j < NB; ++j) {
+                    first.bc[ax][j] += bins[(size_t)c].bc[ax][j];
+                    grow(first.blo[ax][j], first.bhi[ax][j], bins[(size_t)c].blo[ax][j], bins[(size_t)c].bhi[ax][j]);
+                }
+        }
+        int best_axis = -1, best_bin = -1; float best_cost = FLT_MAX;
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!axis_ok[ax]) continue;
+            const int32_t* bc = first.bc[ax];
+            float (*blo)[3] = first.blo[ax]; float (*bhi)[3] = first.bhi[ax];
             float ra[NB]; int32_t rc[NB];
             float tlo[3], thi[3]; reset(tlo, thi); int32_t c = 0;
             for (int j = NB - 1; j >= 1; --j) { if (bc[j]) grow(tlo, thi, blo[j], bhi[j]); c += bc[j]; ra[j] = area(tlo, thi); rc[j] = c; }
@@ -122,8 +173,8 @@ struct RtSahBuilder {
         for (int32_t i = 0; i < n; ++i) order[i] = i;
         nodes.assign((size_t)16 * (n > 1 ? n - 1 : 1), 0.f);
         n_nodes = 0;
-        spawn_depth = 0;
-        for (int t = threads < 1 ? 1 : threads; t > 1; t >>= 1) ++spawn_depth;
+        spawn_depth = 0; threads_ = threads < 1 ? 1 : threads;
+        for (int t = threads_; t > 1; t >>= 1) ++spawn_depth;
         spawn_depth += 1;                                        // a few more tasks than threads, for balance
         if (n == 0) return -1;
         float lo[3], hi[3];
