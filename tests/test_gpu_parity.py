@@ -420,3 +420,23 @@ def test_cfg5_full_size(rtb, scenes, oracle):
     ref = oracle.OracleScene(s).render(p, oracle.ACCELERATED, pixels=px)
     assert np.array_equal(ref["hit_id"][:, :2], frames[0]["hit_id"][px][:, :2]) and np.array_equal(ref["hit_t"], frames[0]["hit_t"][px])
     assert np.abs(ref["rgba8"].astype(int) - frames[0]["rgba8"][px].astype(int)).max() <= 1
+
+
+def test_registered_host_buffer_gives_the_same_frame(rtb, scenes):
+    """rt_host_register page-locks a caller array that is reused across frames (the PixelColors array): same bytes as the
+    pageable and the pipelined paths, and unregistering leaves the array usable."""
+    s, p = scenes.cfg3_scene(n=32), scenes.cfg3_params(960, 544)
+    r = rtb.RayTracer((0,)); r.set_scene(s)
+    want = r.render(p)
+    out = r.alloc_host_outputs(p, 1 | 2)
+    r.host_register(out["rgba32f"]); r.host_register(out["rgba8"])
+    for frame in range(2):
+        out["rgba32f"][:] = -1; out["rgba8"][:] = 7
+        r.render(p, 1 | 2, out=out)
+        assert np.array_equal(want["rgba32f"], out["rgba32f"]) and np.array_equal(want["rgba8"], out["rgba8"])
+    r.host_unregister(out["rgba32f"]); r.host_unregister(out["rgba8"])
+    r.render(p, 1 | 2, out=out)
+    assert np.array_equal(want["rgba32f"], out["rgba32f"])
+    with pytest.raises(RuntimeError):
+        r.host_unregister(out["rgba8"])                     # not registered any more: CUDA error surfaces as a status code
+    r.close()

@@ -458,6 +458,25 @@ int rt_render(rt_ctx* c, const rt_render_params* p, float* rgba32f, uint8_t* rgb
     return RT_OK;
 }
 
+int rt_host_register(rt_ctx* c, void* ptr, size_t bytes) {
+    if (!c) return RT_E_INVALID;
+    if (!ptr || bytes == 0) return fail(c, RT_E_INVALID, "rt_host_register: bad arguments");
+    std::string& err = c->err;
+    RT_CUDA(cudaSetDevice(c->devs[0].device));
+    RT_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return RT_OK;
+}
+
+int rt_host_unregister(rt_ctx* c, void* ptr) {
+    if (!c) return RT_E_INVALID;
+    if (!ptr) return fail(c, RT_E_INVALID, "rt_host_unregister: bad arguments");
+    std::string& err = c->err;
+    int rc = sync_all(c);                                   // copies still in flight use the registration
+    if (rc) return rc;
+    RT_CUDA(cudaHostUnregister(ptr));
+    return RT_OK;
+}
+
 int rt_device_outputs(rt_ctx* c, void** rgba32f, void** rgba8, void** hit_id, void** hit_t) {
     if (!c) return RT_E_INVALID;
     RtDevice& D0 = c->devs[0];

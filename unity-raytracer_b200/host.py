@@ -21,7 +21,7 @@ ABI_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt
                "rt_scene_triangles", "rt_scene_mesh", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
                "rt_scene_update_triangles", "rt_scene_update_spheres", "rt_scene_update_lights", "rt_scene_recommit", "rt_render",
                "rt_render_device", "rt_read_outputs", "rt_device_outputs", "rt_intersect", "rt_get_stats", "rt_set_stream",
-               "rt_set_partition", "rt_alloc_outputs", "rt_export_outputs", "rt_import_outputs", "rt_set_option"]
+               "rt_set_partition", "rt_host_register", "rt_host_unregister", "rt_alloc_outputs", "rt_export_outputs", "rt_import_outputs", "rt_set_option"]
 
 
 class RenderParams(C.Structure):
@@ -106,6 +106,8 @@ def load_library():
     L.rt_export_outputs.argtypes = [vp, vp]
     L.rt_import_outputs.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int]
     L.rt_set_option.argtypes = [vp, C.c_char_p, C.c_double]
+    L.rt_host_register.argtypes = [vp, vp, C.c_size_t]
+    L.rt_host_unregister.argtypes = [vp, vp]
     _lib = L
     return L
 
@@ -185,6 +187,13 @@ class RayTracer:
     def recommit(self, scene_aabb=None):
         bb = None if scene_aabb is None else np.ascontiguousarray(scene_aabb, dtype=np.float32)
         self._chk(self.L.rt_scene_recommit(self.h, _fptr(bb) if bb is not None else None))
+
+    def host_register(self, arr):
+        """page-lock a numpy array that is reused across frames (rt_host_register)"""
+        self._chk(self.L.rt_host_register(self.h, arr.ctypes.data, arr.nbytes))
+
+    def host_unregister(self, arr):
+        self._chk(self.L.rt_host_unregister(self.h, arr.ctypes.data))
 
     def scene_aabb(self):
         out = np.zeros(6, np.float32)
