@@ -96,8 +96,9 @@ __device__ __forceinline__ int rt_hint_tile(const RtHintIn& h, int k, int lane) 
 // heaviest tiles take 2 x 150 us.  The shadow queries of different lights are independent, so tiles of the classes >=
 // h.lsplit become n_l work items (tile, light) that run on n_l warps; each ORs its occlusion bit into a per-item word and the
 // LAST item of a tile to finish (per-tile arrival counter) shades and writes the pixel with the combined mask — exactly the
-// mask the single-warp loop would have built.  Overhead per extra item: regenerating the ray and the surface point (~100
-// instructions against thousands), so the split is applied regardless of the partition size.
+// mask the single-warp loop would have built.  Each extra item regenerates the ray and the surface point and the lights of
+// a tile no longer share their cached nodes: 4 % on a full frame, so the host enables the split only on partitions of a
+// quarter frame or less (RtOptions::light_split), where the critical path is what counts (shadow kernel -5..11 %).
 // Returns false when k is beyond the last item; light = -1: all lights in this item.
 __device__ __forceinline__ bool rt_hint_item_lights(const RtHintIn& h, int k, int lane, int n_tiles, int n_l, int& tile, int& light) {
     light = -1;
