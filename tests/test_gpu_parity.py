@@ -199,10 +199,19 @@ def test_in_process_multi_device_equals_single(rtb, scenes):
         pytest.skip("needs 2 GPUs")
     s, p = scenes.random_soup(seed=5), scenes.soup_params(200, 150, 2, 1)
     one = rtb.RayTracer((0,)); one.set_scene(s); a = one.render(p); one.close()
-    two = rtb.RayTracer((0, 1)); two.set_partition(0, 1, 8); two.set_scene(s); b = two.render(p); two.close()
+    two = rtb.RayTracer((0, 1)); two.set_partition(0, 1, 8); two.set_scene(s); b = two.render(p)
     for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
         assert np.array_equal(a[k], b[k], equal_nan=True), k
     assert a["stats"]["rays_shadow"] == b["stats"]["rays_shadow"] and a["stats"]["rays_mirror"] == b["stats"]["rays_mirror"]
+    # dirty-tracking updates reach every device of the context
+    s2 = _moved_copy(s, (0.5, 0.25, -0.5))
+    one = rtb.RayTracer((0,)); one.set_scene(s2); a2 = one.render(p); one.close()
+    two.update_spheres(0, s2.spheres); two.update_triangles(0, s2.tris, s2.tri_normals)
+    two.update_mesh(0, s2.meshes[0][0], s2.meshes[0][1], s2.meshes[0][3]); two.update_lights(s2.lights, s2.ambient)
+    two.recommit()
+    b2 = two.render(p); two.close()
+    for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(a2[k], b2[k], equal_nan=True), k
 
 
 def test_render_full_size_properties(rt, scenes):
