@@ -155,7 +155,7 @@ RT_HD bool rt_scene_gate(const RtScene& S, f3 O, f3 inv) { return rt_ray_aabb_in
 // Visit counters of the instrumented development build (-DRT_COUNT_VISITS, tools/visit_counts.py): per query class
 // (closest-hit = 0, any-hit = 10): +0 rays, +1 node visits, +2 primitive tests of the per-lane traversal; +3 warps, +4 rays,
 // +5 warp-level node fetches, +6 lane-level node visits, +7 warp-level primitive fetches, +8 lane-level primitive tests of
-// the packet traversal.  Compiled out of the product build.
+// the packet traversal, +9 stack entries of the packet traversal dropped on pop (rt_packet_pop).  Compiled out of the product build.
 #if defined(RT_COUNT_VISITS) && defined(__CUDACC__)
 static __device__ unsigned long long g_rt_visits[20];
 #endif
@@ -167,7 +167,9 @@ static __device__ unsigned long long g_rt_visits[20];
 #ifdef RT_COUNT_VISITS
 #define RT_CNT_PARAM , int cbase
 #define RT_CNT_ARG(ANY) , ((ANY) ? 10 : 0)
+#define RT_CNT_FWD , cbase
 #else
+#define RT_CNT_FWD
 #define RT_CNT_PARAM
 #define RT_CNT_ARG(ANY)
 #endif

@@ -38,6 +38,31 @@ __device__ __forceinline__ bool rt_warp_coherent(f3 O, f3 D, bool active, float 
 // (the slab planes are monotone under the FMA, so near <= far always holds and the result is the same interval).
 // Returns the next leaf reference (< 0), or RT_PACKET_DONE when the stack ran empty.
 #define RT_PACKET_DONE ((int32_t)0x80000000)
+// Distance-culled pops (RT_POP_CULL, default on).  Every pushed reference carries, per lane, the lane's entry distance into
+// that box (+inf when the lane missed it).  Cull distances only shrink (closest hit found; any-hit lanes that have their
+// occluder drop to -1), so  entry > cull  now implies the lane's own box test would fail now: an entry no lane can reach is
+// dropped on pop without fetching the node or testing the leaf's primitives.  Conservative in the same sense as the box
+// test itself, hence the result is unchanged.  STK: push_packet(ref, dist), pop_packet(dist&), empty().
+#ifndef RT_POP_CULL
+#define RT_POP_CULL 1
+#endif
+template <class STK>
+__device__ __forceinline__ int32_t rt_packet_pop(STK& stk, float tcull RT_CNT_PARAM) {
+#if RT_POP_CULL
+    for (;;) {
+        if (stk.empty()) return RT_PACKET_DONE;
+        float d;
+        int32_t node = stk.pop_packet(d);
+        if (__any_sync(0xffffffffu, d <= tcull)) return node;
+#ifdef RT_COUNT_VISITS
+        if ((threadIdx.x & 31) == 0) RT_COUNT(cbase + 9, 1);
+#endif
+    }
+#else
+    if (stk.empty()) return RT_PACKET_DONE;
+    return stk.pop();
+#endif
+}
 // Child order when both are hit (ORD), by majority of the lanes that hit both: 0 = nearer entry first (closest-hit queries:
 // the cull distance shrinks fastest); 2 = any-hit queries: the child in which the ray stays LONGER first.  The result of an
 // any-hit query does not depend on the order, only how soon the lanes find their occluder: cfg3 shadow kernel -2.8 %, cfg5
@@ -89,14 +114,19 @@ __device__ __forceinline__ int32_t rt_packet_descend(const float4* __restrict__ 
             unsigned both = ma & mb;
             unsigned bnear = ORD == 0 ? __ballot_sync(full, ha && hb && bmin < amin)
                                       : __ballot_sync(full, ha && hb && (bmax - bmin) > (amax - amin));
-            if (2 * __popc(bnear) > __popc(both)) { int32_t t = ra; ra = rb; rb = t; }     // majority vote on the order
-            stk.push(rb);
-            node = ra;
+            const bool swap = 2 * __popc(bnear) > __popc(both);                              // majority vote on the order
+#if RT_POP_CULL
+            const float da = ha ? amin : INFINITY, db = hb ? bmin : INFINITY;
+            stk.push_packet(swap ? ra : rb, swap ? da : db);
+#else
+            stk.push(swap ? ra : rb);
+#endif
+            node = swap ? rb : ra;
         } else if (ma) node = ra;
         else if (mb) node = rb;
         else {
-            if (stk.empty()) return RT_PACKET_DONE;
-            node = stk.pop();
+            node = rt_packet_pop(stk, tcull RT_CNT_FWD);
+            if (node == RT_PACKET_DONE) return node;
         }
     }
     return node;
@@ -154,30 +184,38 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                 { unsigned live = __ballot_sync(full, tcull >= 0.0f);
                   if ((threadIdx.x & 31) == 0) { RT_COUNT((ANY ? 10 : 0) + 7, 1); RT_COUNT((ANY ? 10 : 0) + 8, __popc(live)); } }
 #endif
-                if (tcull < 0.0f) continue;                             // lane has no ray / is already occluded
-                float t; bool hit;
-                if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
-                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);
-                if (!hit) continue;
-                uint32_t key = (uint32_t)f2i(p0.w);
-                bool better = ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key));
-                if (!better) continue;
-                int32_t mesh = f2i(p2.w);
-                if (mesh >= 0) {                                        // Scene.cs:67
+                float t = 0.0f; bool hit = false;
+                if (tcull >= 0.0f) {                                    // else: lane has no ray / is already occluded
+                    if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
+                    else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);
+                }
+                const uint32_t key = (uint32_t)f2i(p0.w);
+                bool cand = hit && (ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key)));
+                if (!__any_sync(full, cand)) continue;                  // warp-uniform: nobody would accept this primitive
+                // Per-mesh AABB gate (Scene.cs:67) of a candidate.  The primitive, hence its mesh, is the same for all lanes, so
+                // the gate is evaluated by the WHOLE warp at once (each lane for its own ray, exact formula) and kept until the
+                // walk reaches a primitive of another mesh: once per query on a one-mesh scene.  Evaluating it lane by lane as
+                // each lane met its first candidate cost up to 32 divergent evaluations per query (ncu: ~5 % of the fused shadow
+                // kernel's instructions).  rcp(ray.Direction) is recomputed here — same bits as the caller's `inv` — which frees
+                // three registers across the loops.
+                const int32_t mesh = f2i(p2.w);
+                if (mesh >= 0) {
                     if (mesh != gate_mesh) {
                         gate_mesh = mesh;
                         float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
-                        gate_ok = rt_ray_aabb_inv(O, inv, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
+                        gate_ok = rt_ray_aabb_inv(O, rt_rcp3(D), mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z));
                     }
-                    if (!gate_ok) continue;
+                    cand = cand && gate_ok;
                 }
-                best_t = t; best_key = key; best_slot = slot;
-                if (ANY) { found = true; tcull = -1.0f; }
-                else tcull = t * S.t_slack;
+                if (cand) {
+                    best_t = t; best_key = key; best_slot = slot;
+                    if (ANY) { found = true; tcull = -1.0f; }
+                    else tcull = t * S.t_slack;
+                }
             }
         }
         if (ANY && __all_sync(full, tcull < 0.0f)) return found;        // every lane is occluded or has no ray
-        if (stk.empty()) return ANY ? found : best_slot >= 0;
-        node = stk.pop();
+        node = rt_packet_pop(stk, tcull RT_CNT_ARG(ANY));
+        if (node == RT_PACKET_DONE) return ANY ? found : best_slot >= 0;
     }
 }

@@ -25,7 +25,7 @@ namespace {
 #define RT_MIN_CTAS_PRIMARY 12
 #endif
 #ifndef RT_STK_CAP
-#define RT_STK_CAP 24
+#define RT_STK_CAP 12
 #endif
 constexpr int STK_CAP = RT_STK_CAP;   // shared-memory stack entries per thread
 constexpr int STK_OVF = 104;     // local-memory overflow entries (LBVH depth bound: 64 key bits + 32 index bits)
@@ -34,24 +34,51 @@ constexpr int STK_OVF = 104;     // local-memory overflow entries (LBVH depth bo
 // does not drag the whole stack object into local memory (ncu on the first version: one STL per push/pop for sp).
 // The shared-memory column is addressed through a precomputed 32-bit shared-window address with explicit st/ld.shared:
 // the generic-pointer form made the compiler rebuild the window base (S2R SR_CgaCtaId, LEA, 2 IMAD) on every push and pop.
+// An entry is TWO words per thread: the reference and, for the packet traversal (rt_packet.cuh), the lane's own entry
+// distance into the pushed box (+inf: this lane missed it) — one st/ld.shared.v2 per push/pop off a single address register
+// (a separate warp-shared reference column needed a second address, which the compiler rematerialised on every node step at
+// the 40/48-register occupancy cap: +8 instructions per step).  A popped entry that no lane can still reach (entry distance >
+// the lane's current cull distance; lanes that found their occluder have cull distance -1) is dropped without fetching it:
+// rt_packet_pop.  The per-lane traversal uses the reference word only.
+constexpr int RT_BLOCK = 128;         // threads per CTA of every kernel that owns a traversal stack
 struct SmemStack {
-    unsigned base; unsigned stride4; int sp; int* ovf;
-    __device__ __forceinline__ SmemStack(int* b, int s, int* o) : base((unsigned)__cvta_generic_to_shared(b)), stride4((unsigned)s * 4u), sp(0), ovf(o) {}
+    unsigned base; int sp; int* ovf; float* ovfd;
+    static constexpr unsigned stride = (unsigned)RT_BLOCK * 8u;
+    __device__ __forceinline__ SmemStack(int* b, int* o, float* od) : base((unsigned)__cvta_generic_to_shared(b)), sp(0), ovf(o), ovfd(od) {
+        // opaque to the compiler: at the register cap it otherwise REBUILDS the address (S2UR CgaCtaId, ULEA, S2R tid, LEA) on
+        // every node step instead of keeping one register live
+        asm volatile("" : "+r"(base));
+    }
     __device__ __forceinline__ void push(int v) {
-        if (sp < STK_CAP) asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (unsigned)sp * stride4), "r"(v) : "memory");
+        if (sp < STK_CAP) asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (unsigned)sp * stride), "r"(v) : "memory");
         else if (sp - STK_CAP < STK_OVF) ovf[sp - STK_CAP] = v;
         ++sp;
     }
     __device__ __forceinline__ int pop() {
         --sp;
         int v;
-        if (sp < STK_CAP) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + (unsigned)sp * stride4) : "memory");
+        if (sp < STK_CAP) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(base + (unsigned)sp * stride) : "memory");
         else v = ovf[sp - STK_CAP < STK_OVF ? sp - STK_CAP : STK_OVF - 1];
         return v;
     }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
+    __device__ __forceinline__ void push_packet(int v, float dist) {
+        if (sp < STK_CAP) asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(base + (unsigned)sp * stride), "r"(v), "r"(__float_as_int(dist)) : "memory");
+        else if (sp - STK_CAP < STK_OVF) { ovf[sp - STK_CAP] = v; ovfd[sp - STK_CAP] = dist; }
+        ++sp;
+    }
+    __device__ __forceinline__ int pop_packet(float& dist) {
+        --sp;
+        int v, d;
+        if (sp < STK_CAP) asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v), "=r"(d) : "r"(base + (unsigned)sp * stride) : "memory");
+        else { int i = sp - STK_CAP < STK_OVF ? sp - STK_CAP : STK_OVF - 1; v = ovf[i]; d = __float_as_int(ovfd[i]); }
+        dist = __int_as_float(d);
+        return v;
+    }
 };
-#define RT_DECL_STACK(name) int name##_ovf[STK_OVF]; SmemStack name(g_smem_stack + threadIdx.x, blockDim.x, name##_ovf)
+constexpr size_t RT_STACK_SMEM = (size_t)STK_CAP * RT_BLOCK * 8;
+#define RT_DECL_STACK(name) int name##_ovf[STK_OVF]; float name##_ovfd[STK_OVF]; \
+    SmemStack name(g_smem_stack + 2 * threadIdx.x, name##_ovf, name##_ovfd)
 
 extern __shared__ int g_smem_stack[];
 
@@ -75,8 +102,10 @@ constexpr int RT_NCLS = 8;
 struct RtHintIn { const int* lists; const unsigned* counts; size_t stride; int lsplit; };
 struct RtHintOut { int* lists; unsigned* counts; size_t stride; };                // null = do not record
 
-__device__ __forceinline__ int rt_cost_class(long long cycles) {
-    int c = 63 - __clzll((cycles >> 11) | 1);             // < 2K cycles: 0, 2-4K: 1, ... >= 256K: 7
+// (tile times are taken with the 32-bit cycle counter: a tile lasts < 1 ms, differences are wrap-safe, and the start value
+// occupies one register across the traversal instead of two)
+__device__ __forceinline__ int rt_cost_class(unsigned cycles) {
+    int c = 31 - __clz((int)((cycles >> 11) | 1u));             // < 2K cycles: 0, 2-4K: 1, ... >= 256K: 7
     return c > RT_NCLS - 1 ? RT_NCLS - 1 : c;
 }
 // k-th work item of the wave -> tile index within the wave, heaviest class first
@@ -116,7 +145,7 @@ __device__ __forceinline__ bool rt_hint_item_lights(const RtHintIn& h, int k, in
     tile = h.lists[(size_t)(RT_NCLS - 1 - src) * h.stride + j];
     return true;
 }
-__device__ __forceinline__ void rt_hint_record(const RtHintOut& h, int tile, long long cycles, int lane) {
+__device__ __forceinline__ void rt_hint_record(const RtHintOut& h, int tile, unsigned cycles, int lane) {
     if (!h.lists || lane != 0) return;
     int c = rt_cost_class(cycles);
     unsigned pos = atomicAdd(h.counts + c, 1u);
@@ -140,7 +169,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtSc
         int t = warp_fetch(work, lane);
         if (t >= n_tiles) break;
         t = rt_hint_tile(hin, t, lane);
-        const long long c0 = clock64();
+        const unsigned c0 = (unsigned)clock();
 #ifdef RT_TILE_TIMING
         unsigned long long dbg_t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
 #endif
@@ -157,7 +186,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtSc
         } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
         size_t q = (size_t)t * 32 + lane;
         RT_ST_STREAM(hit_t + q, bt); RT_ST_STREAM(hit_slot + q, valid ? bs : -2);
-        rt_hint_record(hout, t, clock64() - c0, lane);
+        rt_hint_record(hout, t, (unsigned)clock() - c0, lane);
 #ifdef RT_TILE_TIMING
         unsigned long long dbg_t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t1));
         if (lane == 0 && g_rt_tile_dbg) { g_rt_tile_dbg[2 * (size_t)(tile_begin + t)] = dbg_t0; g_rt_tile_dbg[2 * (size_t)(tile_begin + t) + 1] = dbg_t1 - dbg_t0; }
@@ -233,7 +262,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
             if ((unsigned)wt * 32u >= n) break;
             if (DEPTH0) wt = rt_hint_tile(hin, wt, lane);
         }
-        long long c0 = clock64();
+        unsigned c0 = (unsigned)clock();
         const unsigned q = (unsigned)wt * 32u + lane;
         f3 O = mk3(0.f, 0.f, 0.f), D = mk3(0.f, 0.f, 1.f);
         float ht = 0.f;
@@ -269,19 +298,19 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
                 if (occluded) mask |= 1u << i;
             }
         }
-        if (!FUSE) { if (q < n) occl[q] = mask; if (DEPTH0) rt_hint_record(hout, wt, clock64() - c0, lane); continue; }
+        if (!FUSE) { if (q < n) occl[q] = mask; if (DEPTH0) rt_hint_record(hout, wt, (unsigned)clock() - c0, lane); continue; }
         if (DEPTH0 && one_light >= 0) {                        // one of the n_l items of a tile split by light
             if (mask) atomicOr(F.split_occl + q, mask);
             __threadfence();
             __syncwarp(full);
             unsigned long long old = 0ull;
-            if (lane == 0) old = atomicAdd(F.split_acc + wt, ((unsigned long long)(clock64() - c0) << 6) | 1ull);
+            if (lane == 0) old = atomicAdd(F.split_acc + wt, ((unsigned long long)((unsigned)clock() - c0) << 6) | 1ull);
             old = __shfl_sync(full, old, 0);
             if ((int)(old & 63ull) != n_l - 1) continue;        // another item finishes the tile
             __threadfence();
             mask = atomicExch(F.split_occl + q, 0u);            // everybody's bits; leaves the word zero for the next use
             if (lane == 0) F.split_acc[wt] = 0ull;
-            c0 -= (long long)(old >> 6);                        // the tile's cost = the sum over its items
+            c0 -= (unsigned)(old >> 6);                         // the tile's cost = the sum over its items
         }
         // ---- fused shading (k_shade's body) ----
         RtMirror mir; mir.emit = false;
@@ -304,7 +333,11 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
             }
         }
         if (DEPTH0 && F.fin && slot >= -1) rt_finalize_value(S, V, tile_begin, q, F.pass, F.n_pass, col, has ? ht : FLT_MAX, slot, F.accum, F.out);
-        if (DEPTH0) rt_hint_record(hout, wt, clock64() - c0, lane);
+        if (DEPTH0) rt_hint_record(hout, wt, (unsigned)clock() - c0, lane);
+#ifdef RT_TILE_TIMING
+        // shadow-kernel tile costs (cycles; per-light items of a split tile add up) behind the primary kernel's records
+        if (DEPTH0 && lane == 0 && g_rt_tile_dbg) atomicAdd(g_rt_tile_dbg + 2 * (size_t)V.n_tiles + (size_t)(tile_begin + wt), (unsigned long long)((unsigned)clock() - c0));
+#endif
     }
     my_shadow = __reduce_add_sync(full, my_shadow);
     if (lane == 0 && my_shadow) atomicAdd(stats + 1, (unsigned long long)my_shadow);
@@ -429,8 +462,8 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
     uint64_t primary = 0;
     D.wave_marks.clear();
     if (V.n_tiles > 0 && V.res_x > 0) {
-        const int block = 128;
-        const size_t smem = (size_t)STK_CAP * block * sizeof(int);
+        const int block = RT_BLOCK;
+        const size_t smem = RT_STACK_SMEM;
         int wave_tiles = (opt.chunk_pixels / 32) < 1 ? 1 : (opt.chunk_pixels / 32);
         if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
         const int chunk_tiles = wave_tiles;                                 // capacity limit set by chunk_pixels
@@ -643,9 +676,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
 #ifdef RT_TILE_TIMING
 extern "C" int rt_debug_tile_times(int n_tiles, unsigned long long* host_out) {       // (start, duration) per tile of the last frame
     static unsigned long long* buf = nullptr; static int cap = 0;
-    if (host_out && buf) return (int)cudaMemcpy(host_out, buf, (size_t)(n_tiles < cap ? n_tiles : cap) * 16, cudaMemcpyDeviceToHost);
-    if (n_tiles > cap) { if (buf) cudaFree(buf); cudaMalloc(&buf, (size_t)n_tiles * 16); cap = n_tiles; }
-    cudaMemset(buf, 0, (size_t)cap * 16);
+    if (host_out && buf) return (int)cudaMemcpy(host_out, buf, (size_t)(n_tiles < cap ? n_tiles : cap) * 24, cudaMemcpyDeviceToHost);   // + shadow-kernel cycles per tile
+    if (n_tiles > cap) { if (buf) cudaFree(buf); cudaMalloc(&buf, (size_t)n_tiles * 24); cap = n_tiles; }
+    cudaMemset(buf, 0, (size_t)cap * 24);
     return (int)cudaMemcpyToSymbol(g_rt_tile_dbg, &buf, sizeof(buf));
 }
 #endif
@@ -681,8 +714,8 @@ int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs
                         const RtOptions& opt, std::string& err) {
     RT_CUDA(cudaSetDevice(D.device));
     if (n <= 0) return RT_OK;
-    const int block = 128;
-    const size_t smem = (size_t)STK_CAP * block * sizeof(int);
+    const int block = RT_BLOCK;
+    const size_t smem = RT_STACK_SMEM;
     int grid = (n + block - 1) / block;
     if (grid > D.sm_count * 16) grid = D.sm_count * 16;
     k_intersect<<<grid, block, smem, D.stream>>>(D.S, n, d_origins, d_dirs, d_ids, d_t);
