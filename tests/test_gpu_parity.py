@@ -94,6 +94,18 @@ def test_cfg3_reduced(rt, scenes, oracle):
     _check(compare_renders(sub, gsub))
 
 
+@pytest.mark.parametrize("phong", [20.0, 1.0, 64.0, 3.0, 0.0, 20.5, 100.0])
+def test_phong_exponent_paths(rt, scenes, oracle, phong):
+    """Blinn-Phong pow (RayTracingSetup.cs:399): whole exponents <= 64 take the device's exponentiation-by-squaring path
+    (rt_hd.h um_pow), everything else the library pow; both must give the oracle's float colours."""
+    s, p = scenes.cfg3_scene(n=40, phong=phong), scenes.cfg3_params(480, 270)
+    ref = oracle.OracleScene(s).render(p, oracle.ACCELERATED)
+    rt.set_scene(s)
+    cmp = compare_renders(ref, rt.render(p))
+    _check(cmp)
+    assert cmp["f32"] <= 2, cmp
+
+
 def test_edge_cases(rt, scenes):
     # empty scene: everything misses, background colour, FLT_MAX distance (Scene.cs:45-61)
     s = scenes.SceneArrays()

@@ -287,12 +287,12 @@ SEED = 12345
 ASPECT_HALF_H = 8.8889   # 16:9 with Dist 10, HalfV 5
 
 
-def cfg3_scene(n=224, radius=20.0):
+def cfg3_scene(n=224, radius=20.0, phong=20.0):
     """~1M-triangle displaced geodesic sphere (20*224^2 = 1 003 520) + ground quad, 2 lights."""
     s = SceneArrays()
     tris, w = displaced_icosphere(n, radius, (0, 0, 60), SEED)
     normals, aabb = mesh_from_world_tris(tris, w)
-    s.add_mesh(tris, normals, material((0.8, 0.8, 0.8), (1, 1, 1), (0, 0, 0), (1, 1, 1), 20.0, 0), aabb)
+    s.add_mesh(tris, normals, material((0.8, 0.8, 0.8), (1, 1, 1), (0, 0, 0), (1, 1, 1), phong, 0), aabb)
     add_ground(s, -radius - 2.0, 80.0, (0.0, 60.0))
     s.add_light((40, 40, 0), 2e5)
     s.add_light((-40, 40, 0), 2e5)
