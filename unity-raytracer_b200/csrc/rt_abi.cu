@@ -591,7 +591,8 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "ctas_per_sm") { c->opt.ctas_per_sm = (int)value; }
     else if (k == "block") { c->opt.block = (int)value; }
     else if (k == "waves") { if (value < 0 || value > 64) return fail(c, RT_E_INVALID, "waves must be 0 (auto) or 1..64"); c->opt.waves = (int)value; }
-    else if (k == "lanes") { if (value != 1 && value != 2) return fail(c, RT_E_INVALID, "lanes must be 1 or 2"); c->opt.lanes = (int)value; }
+    else if (k == "lanes") { if (value < 1 || value > RtDevice::RT_MAX_LANES) return fail(c, RT_E_INVALID, "lanes must be 1..8"); c->opt.lanes = (int)value; }
+    else if (k == "deep_lanes") { if (value < 1 || value > RtDevice::RT_MAX_LANES) return fail(c, RT_E_INVALID, "deep_lanes must be 1..8"); c->opt.deep_lanes = (int)value; }
     else if (k == "fuse_shade") { c->opt.fuse_shade = value != 0; }
     else if (k == "prefetch") { c->opt.prefetch = value != 0; }
     else if (k == "prefetch_max_mb") { c->opt.prefetch_max_mb = (int)value; }

@@ -48,7 +48,9 @@ struct RtOptions {
     int builder = 0;                   // 0 = device LBVH (fast commit), 1 = host binned-SAH (rt_sah.h; slower commit, fewer node visits)
     int waves = 0;                     // rt_render_device: minimum number of waves per pass; 0 = auto: 2 (two lanes: tails overlap),
                                        // 1 on partitions of a quarter frame or less (smaller kernels only lengthen the critical path)
-    int lanes = 2;                     // 1 = all waves on one stream; 2 = alternate waves over two streams (tail overlap)
+    int lanes = 2;                     // 1 = all waves on one stream; 2.. = consecutive waves rotate over this many streams (tail overlap)
+    int deep_lanes = 8;                // lanes of a frame with mirror depths AND >= 4 waves (spp passes): its queue kernels trace few,
+                                       // incoherent rays each and last as long as their longest ray, so many of them run side by side
     int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
                                        // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
     int fuse_shade = 1;                // shading (+ pixel write at depth 0) inside the shadow-trace kernel when <= 32 lights
@@ -83,6 +85,7 @@ struct RtDevice {
     // ---- frame work buffers (sized to the wave capacity W), one set per lane ----
     // A frame is cut into waves; consecutive waves alternate between two lanes (stream + buffer set) so that the drain
     // of one wave's persistent kernels is filled by the next wave's kernels instead of idling the SMs.
+    static constexpr int RT_MAX_LANES = 8;
     struct Lane {
         cudaStream_t own_stream = nullptr;   // lane 0 runs on D.stream, the others on their own stream
         cudaEvent_t done = nullptr;
@@ -90,7 +93,7 @@ struct RtDevice {
         std::vector<DevBuf> local;          // [depth] float4 per entry
         std::vector<DevBuf> link;           // [depth>=1] float4 (km.xyz, parent index bits)
     };
-    Lane lanes[2];
+    Lane lanes[RT_MAX_LANES];
     DevBuf accum, stats;
     // heavy-first tile order (rt_render.cu "cost hints"): per tile-indexed trace kernel, double-buffered class lists
     struct Hints { DevBuf lists[2], counts[2]; };

@@ -501,7 +501,14 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             wave_tb.push_back(V.n_tiles);
         }
         const int waves_per_pass = (int)wave_tb.size() - 1;
-        const int n_lanes = (opt.lanes > 1 && !opt.kernel_timing && waves_per_pass * n_pass > 1) ? 2 : 1;
+        int n_lanes = 1;
+        if (!opt.kernel_timing && waves_per_pass * n_pass > 1) {
+            n_lanes = opt.lanes;
+            if (V.max_bounces > 0 && waves_per_pass * n_pass >= 4 && opt.deep_lanes > n_lanes) n_lanes = opt.deep_lanes;
+            if (n_lanes > waves_per_pass * n_pass) n_lanes = waves_per_pass * n_pass;
+            if (n_lanes > RtDevice::RT_MAX_LANES) n_lanes = RtDevice::RT_MAX_LANES;
+            if (n_lanes < 1) n_lanes = 1;
+        }
         const size_t W = (size_t)wave_tiles * 32;
         const int maxd = V.max_bounces;
         const int n_chunks = (D.S.n_lights + 31) / 32;                      // shadow launches per depth
@@ -546,9 +553,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                 for (int k = 0; k < 2; ++k) { RT_CUDA(hh->lists[k].ensure(hstride * RT_NCLS * 4)); RT_CUDA(hh->counts[k].ensure((size_t)waves_per_pass * RT_NCLS * 4)); }
                 RT_CUDA(cudaMemsetAsync(hh->counts[hb_out].p, 0, (size_t)waves_per_pass * RT_NCLS * 4, D.stream));
             }
-            if (n_lanes > 1) {                                               // the lanes must see the cleared counters
-                RT_CUDA(cudaEventRecord(D.lanes[1].done, D.stream));
-                RT_CUDA(cudaStreamWaitEvent(D.lanes[1].own_stream, D.lanes[1].done, 0));
+            for (int li = 1; li < n_lanes; ++li) {                           // the lanes must see the cleared counters
+                RT_CUDA(cudaEventRecord(D.lanes[li].done, D.stream));
+                RT_CUDA(cudaStreamWaitEvent(D.lanes[li].own_stream, D.lanes[li].done, 0));
             }
         }
         const int lsplit = opt.light_split >= 0 ? opt.light_split : (V.world >= 4 ? 6 : 0);
