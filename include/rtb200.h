@@ -117,6 +117,12 @@ int rt_scene_update_triangles(rt_ctx* ctx, int first, int n, const float* vertic
 int rt_scene_update_spheres(rt_ctx* ctx, int first, int n, const float* center_r2);
 int rt_scene_update_lights(rt_ctx* ctx, const float* pos_intensity, int n, const float ambient_radiance[3]);
 int rt_scene_recommit(rt_ctx* ctx, const float scene_aabb[6]);
+/* Same contract as rt_scene_recommit, but the committed tree (either builder's) and its leaf order are KEPT and only the boxes
+ * are recomputed bottom-up from the moved primitives: the cheap path for deforming / slowly moving geometry, and the way to keep
+ * a host-built SAH tree on a dynamic scene (1M triangles: ~0.2 ms instead of a 0.3 s host build).  Results are identical to a
+ * fresh commit by construction (the query result does not depend on the tree, only on the boxes being conservative); frame
+ * time degrades as the geometry moves away from the layout the tree was built for, until the next commit / recommit. */
+int rt_scene_refit(rt_ctx* ctx, const float scene_aabb[6]);
 
 /* ---- render: replaces CastPixelRays(CameraData), RayTracingSetup.cs:198,275-302 ---------------------------- */
 /* out_rgba32f : X*Y*4 floats == UnityEngine.Color[] PixelColors (RTS:40,300; Rgb.Color = Value/255, alpha 1, Rgb.cs:13)

@@ -373,6 +373,47 @@ def test_dirty_updates_plus_recommit_equal_full_commit(rtb, scenes, oracle, buil
     r.close()
 
 
+@pytest.mark.parametrize("builder", [0, 1])
+def test_refit_equals_full_commit(rtb, scenes, oracle, builder):
+    """rt_scene_update_* + rt_scene_refit (tree kept, boxes recomputed bottom-up) = committing the moved scene from scratch = the
+    oracle, for both builders' trees, repeatedly, and for a deformation the old tree was not built for."""
+    s, p = scenes.cfg5_scene(n=12, n_spheres=500), scenes.cfg5_params(160, 90, 1, 2)
+    r = rtb.RayTracer((0,)); r.set_option("builder", builder); r.set_scene(s)
+    r.render(p)
+    n_nodes = r.stats()["n_nodes"]
+    rng = np.random.default_rng(5)
+    for step, shift in enumerate([(0.75, -0.5, 1.25), (-2.0, 1.0, 0.5)]):
+        s2 = _moved_copy(s, shift)
+        if step == 1:                                            # scramble: every sphere jumps somewhere else, the mesh is squashed
+            s2.spheres[:, :3] = rng.uniform(-30, 30, s2.spheres[:, :3].shape).astype(np.float32) + np.float32([0, 0, 60])
+            v = s2.meshes[0][0].copy(); v.reshape(-1, 3, 3)[:, :, 1] *= np.float32(0.5)
+            lo, hi = v.reshape(-1, 3).min(axis=0), v.reshape(-1, 3).max(axis=0)
+            s2.meshes[0] = (v, s2.meshes[0][1], s2.meshes[0][2], np.concatenate([lo, hi]).astype(np.float32))
+        ref = oracle.OracleScene(s2).render(p, oracle.ACCELERATED)
+        fresh = rtb.RayTracer((0,)); fresh.set_option("builder", builder); fresh.set_scene(s2)
+        want = fresh.render(p); fresh.close()
+        _check(compare_renders(ref, want))
+        r.update_spheres(0, s2.spheres)
+        r.update_triangles(0, s2.tris, s2.tri_normals)
+        r.update_mesh(0, s2.meshes[0][0], s2.meshes[0][1], s2.meshes[0][3])
+        r.update_lights(s2.lights, s2.ambient)
+        with pytest.raises(RuntimeError):
+            r.render(p)                                         # dirty until refit / recommit
+        r.refit()
+        got = r.render(p)
+        for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+            assert np.array_equal(want[k], got[k]), (step, k)
+        assert r.stats()["n_nodes"] == n_nodes                  # same tree
+    r.recommit()                                                # and a rebuild afterwards still works
+    got = r.render(p)
+    assert np.array_equal(want["hit_id"], got["hit_id"]) and np.array_equal(want["rgba32f"], got["rgba32f"])
+    r.close()
+    e = rtb.RayTracer((0,))
+    with pytest.raises(RuntimeError):
+        e.refit()                                               # nothing committed
+    e.close()
+
+
 def test_light_split_and_hints_do_not_change_the_frame(rtb, scenes):
     """Scheduling only: heavy-first tile order (hints, active from the second frame on) and per-light work items for heavy
     tiles (light_split, combined by the last item through atomics) must reproduce the first frame bit for bit."""

@@ -46,3 +46,18 @@ for rep in range(3):
     t2 = time.perf_counter()
     st = rt.stats()
     print(f"{cfg} {what} {1e3*(t1-t0):.2f} ms + recommit {1e3*(t2-t1):.2f} ms ({s.n_prims/(t2-t0)/1e6:.1f} Mprims/s rebuilt) | device: upload {st['ms_commit_upload']:.2f} build {st['ms_commit_build']:.2f}", flush=True)
+# refit path: the whole mesh moved a little (all vertices re-sent), tree kept, boxes recomputed; then the frame time with the refitted tree
+if s.meshes:
+    p = {"cfg3": sc.cfg3_params, "cfg4": sc.cfg4_params, "cfg5": sc.cfg5_params}[cfg]()
+    base = rt.render_device(p, H.RT_OUT_RGBA8, sync_stats=True)["ms_render"]
+    base = rt.render_device(p, H.RT_OUT_RGBA8, sync_stats=True)["ms_render"]
+    v0, n0, mat, aabb = s.meshes[0]
+    for rep, amp in enumerate((0.0, 0.01, 0.01, 0.05)):
+        rng = np.random.default_rng(rep)
+        v = (v0 + amp * rng.standard_normal(v0.shape).astype(np.float32)).astype(np.float32) if amp else v0
+        lo, hi = v.reshape(-1, 3).min(axis=0), v.reshape(-1, 3).max(axis=0)
+        t0 = time.perf_counter(); rt.update_mesh(0, v, n0, np.concatenate([lo, hi])); t1 = time.perf_counter()
+        rt.refit(); t2 = time.perf_counter()
+        st = rt.stats()
+        ms = [rt.render_device(p, H.RT_OUT_RGBA8, sync_stats=True)["ms_render"] for _ in range(3)][-1]
+        print(f"{cfg} jitter {amp}: update mesh 0 ({v.shape[0]} tris) {1e3*(t1-t0):.2f} ms + refit {1e3*(t2-t1):.2f} ms | device: build {st['ms_commit_build']:.3f} | frame {ms:.3f} ms (before: {base:.3f})", flush=True)

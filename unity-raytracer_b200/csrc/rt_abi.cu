@@ -277,13 +277,13 @@ int rt_scene_lights(rt_ctx* c, const float* pos_intensity, int n, const float am
     return RT_OK;
 }
 
-static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident) {
+static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, bool refit = false) {
     if (scene_aabb) for (int k = 0; k < 6; ++k) c->host.aabb[k] = scene_aabb[k];
     else c->host.calc_aabb();
     float up = 0.f, bd = 0.f; uint64_t bytes = 0;
     for (auto& D : c->devs) {
         float u = 0.f, b = 0.f; uint64_t by = 0;
-        int rc = rt_device_commit(D, c->host, c->opt, c->err, &u, &b, &by, raw_resident);
+        int rc = rt_device_commit(D, c->host, c->opt, c->err, &u, &b, &by, raw_resident, refit);
         if (rc) return rc;
         up += u; bd += b; bytes += by;
     }
@@ -369,6 +369,16 @@ int rt_scene_recommit(rt_ctx* c, const float scene_aabb[6]) {
     if (!c->dirty && !c->committed) return fail(c, RT_E_STATE, "rt_scene_recommit: no committed scene");
     if (!c->dirty) { int rc = sync_all(c); if (rc) return rc; }
     int rc = commit_impl(c, scene_aabb, true);
+    if (rc == RT_OK) c->dirty = false;
+    return rc;
+}
+
+int rt_scene_refit(rt_ctx* c, const float scene_aabb[6]) {
+    if (!c) return RT_E_INVALID;
+    if (c->in_scene) return fail(c, RT_E_STATE, "rt_scene_refit inside rt_scene_begin/commit");
+    if (!c->dirty && !c->committed) return fail(c, RT_E_STATE, "rt_scene_refit: no committed scene");
+    if (!c->dirty) { int rc = sync_all(c); if (rc) return rc; }
+    int rc = commit_impl(c, scene_aabb, true, true);
     if (rc == RT_OK) c->dirty = false;
     return rc;
 }

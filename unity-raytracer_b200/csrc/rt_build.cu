@@ -85,6 +85,45 @@ __global__ void k_emit_nodes(int32_t n_int, RtTopo T, const int32_t* new_index, 
         rt_emit_node(i, T, new_index, leaf_max, pad, leaf_lo, leaf_hi, int_lo, int_hi, nodes);
 }
 
+__global__ void k_node_parents(const float4* nodes, int32_t n_nodes, int32_t* parent) {
+    for (int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += gridDim.x * blockDim.x) rt_node_parents(nodes, i, parent);
+}
+
+// Refit of the emitted node array, bottom-up: a thread starts at every node whose children are both leaves and climbs; a
+// node with inner children is processed by the LAST of them to arrive (arrival counter), after a fence, so it reads finished
+// boxes (same scheme as k_refit on the Karras tree).  int_lo/int_hi hold the unpadded box per node; they are written with
+// st.cg and read with ld.cg by another thread.
+__global__ void k_refit_nodes(int32_t n_nodes, float pad, const int32_t* parent, const float4* leaf_lo, const float4* leaf_hi,
+                              float4* int_lo, float4* int_hi, int32_t* arrived, float4* nodes) {
+    for (int32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < n_nodes; s += gridDim.x * blockDim.x) {
+        float4 n3 = nodes[4 * (size_t)s + 3];
+        if (f2i(n3.x) >= 0 || f2i(n3.y) >= 0) continue;            // has an inner child: reached from below
+        int32_t i = s;
+        for (;;) {
+            float4* np = nodes + 4 * (size_t)i;
+            float4 r3 = np[3];
+            f3 alo, ahi, blo, bhi;
+            const int32_t ra = f2i(r3.x), rb = f2i(r3.y);
+            if (ra >= 0) { float4 a = ld_cg4(int_lo + ra), b = ld_cg4(int_hi + ra); alo = mk3(a.x, a.y, a.z); ahi = mk3(b.x, b.y, b.z); }
+            else rt_ref_box(ra, leaf_lo, leaf_hi, int_lo, int_hi, alo, ahi);
+            if (rb >= 0) { float4 a = ld_cg4(int_lo + rb), b = ld_cg4(int_hi + rb); blo = mk3(a.x, a.y, a.z); bhi = mk3(b.x, b.y, b.z); }
+            else rt_ref_box(rb, leaf_lo, leaf_hi, int_lo, int_hi, blo, bhi);
+            np[0] = make_float4(alo.x - pad, ahi.x + pad, alo.y - pad, ahi.y + pad);
+            np[1] = make_float4(blo.x - pad, bhi.x + pad, blo.y - pad, bhi.y + pad);
+            np[2] = make_float4(alo.z - pad, ahi.z + pad, blo.z - pad, bhi.z + pad);
+            __stcg(int_lo + i, make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f));
+            __stcg(int_hi + i, make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f));
+            const int32_t p = parent[i];
+            if (p < 0) break;
+            float4 p3 = nodes[4 * (size_t)p + 3];
+            const int32_t need = (f2i(p3.x) >= 0 ? 1 : 0) + (f2i(p3.y) >= 0 ? 1 : 0);
+            __threadfence();
+            if (atomicAdd(arrived + p, 1) + 1 < need) break;        // the other inner child is not done yet
+            i = p;
+        }
+    }
+}
+
 }  // namespace
 
 // ---- pageable host -> device upload --------------------------------------------------------------------------------------
@@ -179,7 +218,7 @@ int rt_device_update_raw(RtDevice& D, int what, int64_t first, int64_t n, const 
 // raw_resident: the triangle / sphere arrays of this scene are already on the device (rt_scene_recommit after
 // rt_scene_update_*): only the small tables are uploaded before the BVH is rebuilt.
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
-                     float* ms_build, uint64_t* h2d_bytes, bool raw_resident) {
+                     float* ms_build, uint64_t* h2d_bytes, bool raw_resident, bool refit) {
     RT_CUDA(cudaSetDevice(D.device));
     cudaStream_t st = D.stream;
     const int32_t n_mt = H.n_meshtris(), n_sp = H.n_spheres(), n_lo = H.n_loose(), n_me = H.n_meshes(), n_li = H.n_lights();
@@ -236,6 +275,10 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
 
     // ---- scene view (pointers filled below) ----
     RtScene& S = D.S;
+    const int32_t old_prims = D.bvh_prims, old_root = D.bvh_root;
+    const uint32_t old_nodes = D.n_nodes;
+    if (refit && (old_prims != n || n <= 0 || D.vals_alt.bytes < (size_t)n * 4)) { err = "rt_scene_refit: no committed tree over this many primitives"; return RT_E_STATE; }
+    D.bvh_prims = -1;
     S = RtScene{};
     S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_mt; S.n_spheres = n_sp; S.n_lights = n_li;
     S.aabb_min = mk3(H.aabb[0], H.aabb[1], H.aabb[2]); S.aabb_max = mk3(H.aabb[3], H.aabb[4], H.aabb[5]);
@@ -255,6 +298,43 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     if (n > 0) {
         RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_base.as<int32_t>(), n_me, n_mt, n_sp, n_lo};
         const int leaf_max = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 8 ? 8 : opt.leaf_max);
+        if (refit) {
+            // ---- refit: keep the tree (either builder's) and the slot order, recompute every box from the moved primitives ----
+            RT_CUDA(D.bounds.ensure(6 * 4));
+            uint32_t binit[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+            RT_CUDA(cudaMemcpyAsync(D.bounds.p, binit, sizeof(binit), cudaMemcpyHostToDevice, st));
+            k_bounds<<<grid_for(n) < D.sm_count * 4 ? grid_for(n) : D.sm_count * 4, BT, 0, st>>>(R, n, D.bounds.as<uint32_t>());
+            uint32_t bord[6];
+            RT_CUDA(cudaMemcpyAsync(bord, D.bounds.p, sizeof(bord), cudaMemcpyDeviceToHost, st));
+            RT_CUDA(D.leaf_lo.ensure((size_t)n * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)n * 16));
+            k_emit_slots<<<grid_for(n), BT, 0, st>>>(R, n, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
+            RT_CUDA(cudaStreamSynchronize(st));
+            float amax = 0.f;
+            for (int k = 0; k < 6; ++k) { float b = f_unord(bord[k]); if (std::isfinite(b)) amax = fmaxf(amax, fabsf(b)); }
+            const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
+            D.n_nodes = old_nodes;
+            if (old_nodes > 0) {
+                const int32_t nn = (int32_t)old_nodes;
+                RT_CUDA(D.int_lo.ensure((size_t)nn * 16)); RT_CUDA(D.int_hi.ensure((size_t)nn * 16));
+                RT_CUDA(D.flags.ensure((size_t)nn * 4)); RT_CUDA(D.node_parent.ensure((size_t)nn * 4));
+                if (!D.bvh_parents) {
+                    RT_CUDA(cudaMemsetAsync(D.node_parent.p, 0xff, (size_t)nn * 4, st));
+                    k_node_parents<<<grid_for(nn), BT, 0, st>>>(D.nodes.as<float4>(), nn, D.node_parent.as<int32_t>());
+                    D.bvh_parents = true;
+                }
+                RT_CUDA(cudaMemsetAsync(D.flags.p, 0, (size_t)nn * 4, st));
+                k_refit_nodes<<<grid_for(nn), BT, 0, st>>>(nn, pad, D.node_parent.as<int32_t>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>(),
+                                                          D.int_lo.as<float4>(), D.int_hi.as<float4>(), D.flags.as<int32_t>(), D.nodes.as<float4>());
+            }
+            RT_CUDA(cudaGetLastError());
+            S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
+            S.root = old_root;
+            D.bvh_prims = n; D.bvh_root = old_root;
+            RT_CUDA(cudaEventRecord(D.ev1, st));
+            RT_CUDA(cudaEventSynchronize(D.ev1));
+            if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
+            return RT_OK;
+        }
         if (H.builder == 1) {
             // ---- host binned-SAH build (rt_sah.h); the device only re-lays the primitives out in leaf order ----
             std::vector<RtSahBox> pb((size_t)n);
@@ -290,6 +370,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             RT_CUDA(cudaStreamSynchronize(st));                   // B.order / B.nodes go out of scope
             S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
             S.root = root;
+            D.bvh_prims = n; D.bvh_root = root; D.bvh_parents = false;
             RT_CUDA(cudaEventRecord(D.ev1, st));
             RT_CUDA(cudaEventSynchronize(D.ev1));
             if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
@@ -357,6 +438,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             S.nodes = D.nodes.as<float4>();
         }
         RT_CUDA(cudaGetLastError());
+        D.bvh_prims = n; D.bvh_root = S.root; D.bvh_parents = false;
     }
     RT_CUDA(cudaEventRecord(D.ev1, st));
     RT_CUDA(cudaEventSynchronize(D.ev1));

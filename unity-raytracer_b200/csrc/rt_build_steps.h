@@ -169,3 +169,22 @@ RT_HD void rt_emit_node(int32_t i, const RtTopo& T, const int32_t* new_index, in
     np[2] = make_float4(alo.z - pad, ahi.z + pad, blo.z - pad, bhi.z + pad);
     np[3] = make_float4(i2f(ra), i2f(rb), 0.f, 0.f);
 }
+
+// ---- refit of an emitted node array (rt_scene_refit): same tree, new boxes ----------------------------------------------
+// parent[c] = node that references inner node c (the root keeps -1)
+RT_HD void rt_node_parents(const float4* nodes, int32_t i, int32_t* parent) {
+    float4 n3 = nodes[4 * (size_t)i + 3];
+    int32_t ra = f2i(n3.x), rb = f2i(n3.y);
+    if (ra >= 0) parent[ra] = i;
+    if (rb >= 0) parent[rb] = i;
+}
+// box of a child reference: union of the slot boxes of a leaf, or the (already refitted) box of an inner node
+RT_HD void rt_ref_box(int32_t ref, const float4* leaf_lo, const float4* leaf_hi, const float4* int_lo, const float4* int_hi, f3& lo, f3& hi) {
+    if (ref >= 0) { float4 a = int_lo[ref], b = int_hi[ref]; lo = mk3(a.x, a.y, a.z); hi = mk3(b.x, b.y, b.z); return; }
+    int32_t r = ~ref, first = r >> 3, cnt = (r & 7) + 1;
+    lo = mk3(FLT_MAX, FLT_MAX, FLT_MAX); hi = mk3(-FLT_MAX, -FLT_MAX, -FLT_MAX);
+    for (int32_t k = 0; k < cnt; ++k) {
+        float4 a = leaf_lo[first + k], b = leaf_hi[first + k];
+        lo = mk3(fminf(lo.x, a.x), fminf(lo.y, a.y), fminf(lo.z, a.z)); hi = mk3(fmaxf(hi.x, b.x), fmaxf(hi.y, b.y), fmaxf(hi.z, b.z));
+    }
+}

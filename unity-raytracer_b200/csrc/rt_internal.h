@@ -80,6 +80,10 @@ struct RtDevice {
     RtScene S{};
     uint32_t n_nodes = 0;
     bool has_mirror = false;
+    // refit (rt_scene_refit): the committed tree is kept and only its boxes are recomputed
+    int32_t bvh_prims = -1, bvh_root = 0;   // primitive count / root ref of the tree in `nodes` (+ slot order in vals_alt); -1: none
+    bool bvh_parents = false;           // node_parent holds the parents of this tree
+    DevBuf node_parent;
     // ---- build scratch ----
     DevBuf keys, keys_alt, vals, vals_alt, cub_tmp, bounds, topo_i32, leaf_lo, leaf_hi, int_lo, int_hi, flags, new_index;
     // ---- frame work buffers (sized to the wave capacity W), one set per lane ----
@@ -140,7 +144,7 @@ void rt_upload_release(RtDevice& D);
 int rt_device_stage_mesh(RtDevice& D, const float* v, const float* normals, int64_t first, int64_t n_tris, int threads, std::string& err);
 int rt_device_update_raw(RtDevice& D, int what, int64_t first, int64_t n, const float* a, const float* b, int threads, std::string& err);
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
-                     float* ms_build, uint64_t* h2d_bytes, bool raw_resident = false);
+                     float* ms_build, uint64_t* h2d_bytes, bool raw_resident = false, bool refit = false);
 // rt_render.cu
 struct RtFrameStats { uint64_t primary, shadow, mirror, shadow_skipped; uint32_t launches; float ms_kernel[RT_K_COUNT]; uint32_t launches_kernel[RT_K_COUNT]; };
 int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs, int split = 0);

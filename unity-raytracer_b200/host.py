@@ -19,7 +19,7 @@ RT_OUT_ALL = 15
 
 ABI_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_begin", "rt_scene_spheres",
                "rt_scene_triangles", "rt_scene_mesh", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
-               "rt_scene_update_triangles", "rt_scene_update_spheres", "rt_scene_update_lights", "rt_scene_recommit", "rt_render",
+               "rt_scene_update_triangles", "rt_scene_update_spheres", "rt_scene_update_lights", "rt_scene_recommit", "rt_scene_refit", "rt_render",
                "rt_render_device", "rt_read_outputs", "rt_device_outputs", "rt_intersect", "rt_get_stats", "rt_set_stream",
                "rt_set_partition", "rt_host_register", "rt_host_unregister", "rt_alloc_outputs", "rt_export_outputs", "rt_import_outputs", "rt_set_option"]
 
@@ -94,6 +94,7 @@ def load_library():
     L.rt_scene_update_spheres.argtypes = [vp, C.c_int, C.c_int, fp]
     L.rt_scene_update_lights.argtypes = [vp, fp, C.c_int, fp]
     L.rt_scene_recommit.argtypes = [vp, fp]
+    L.rt_scene_refit.argtypes = [vp, fp]
     L.rt_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, vp, vp, C.POINTER(Stats)]
     L.rt_render_device.argtypes = [vp, C.POINTER(RenderParams), C.c_int, C.POINTER(Stats)]
     L.rt_read_outputs.argtypes = [vp, vp, vp, vp, vp]
@@ -187,6 +188,11 @@ class RayTracer:
     def recommit(self, scene_aabb=None):
         bb = None if scene_aabb is None else np.ascontiguousarray(scene_aabb, dtype=np.float32)
         self._chk(self.L.rt_scene_recommit(self.h, _fptr(bb) if bb is not None else None))
+
+    def refit(self, scene_aabb=None):
+        """rt_scene_refit: keep the committed tree, recompute its boxes from the updated primitives"""
+        bb = None if scene_aabb is None else np.ascontiguousarray(scene_aabb, dtype=np.float32)
+        self._chk(self.L.rt_scene_refit(self.h, _fptr(bb) if bb is not None else None))
 
     def host_register(self, arr):
         """page-lock a numpy array that is reused across frames (rt_host_register)"""

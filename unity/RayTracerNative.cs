@@ -56,6 +56,7 @@ namespace RayTracer
 		[DllImport(Lib)] static extern int rt_scene_update_spheres(IntPtr ctx, int first, int n, Sphere[] centerR2);
 		[DllImport(Lib)] static extern int rt_scene_update_lights(IntPtr ctx, PointLightData[] posIntensity, int n, ref float3 ambientRadiance);
 		[DllImport(Lib)] static extern int rt_scene_recommit(IntPtr ctx, ref AABB sceneAabb);
+		[DllImport(Lib)] static extern int rt_scene_refit(IntPtr ctx, ref AABB sceneAabb);
 		[DllImport(Lib)] static extern int rt_host_register(IntPtr ctx, IntPtr ptr, UIntPtr bytes);
 		[DllImport(Lib)] static extern int rt_host_unregister(IntPtr ctx, IntPtr ptr);
 		[DllImport(Lib)] static extern int rt_render(IntPtr ctx, ref NativeRenderParams p, Color[] outRgba32f, IntPtr outRgba8,
@@ -98,7 +99,9 @@ namespace RayTracer
 		/// Dirty-tracking alternative to UploadScene for frames in which the object COUNTS did not change (the usual case: only
 		/// transforms moved).  meshMoved[i] = SceneMesh i's transform.hasChanged; spheres / loose triangles / lights are small
 		/// and are simply re-sent.  The BVH is rebuilt on the device from the resident arrays (0.7 ms per million primitives).
-		public static void UpdateScene(ref Scene scene, bool[] meshMoved)
+		/// refitOnly: keep the tree and only recompute its boxes (rt_scene_refit) — for small per-frame motion; pass false
+		/// every so often (or after large motion) so that the tree is rebuilt for the new layout.
+		public static void UpdateScene(ref Scene scene, bool[] meshMoved, bool refitOnly = false)
 		{
 			var meshes = scene.MeshData.Meshes;
 			for (int i = 0; i < meshes.Count; i++)
@@ -113,7 +116,8 @@ namespace RayTracer
 			var ambient = scene.AmbientLight.Radiance;
 			Check(rt_scene_update_lights(ctx, scene.PointLights.ToArray(), scene.PointLights.Count, ref ambient));
 			var aabb = scene.AABB;
-			Check(rt_scene_recommit(ctx, ref aabb));
+			if (refitOnly) Check(rt_scene_refit(ctx, ref aabb));
+			else Check(rt_scene_recommit(ctx, ref aabb));
 		}
 
 		/// Replaces CastPixelRays(CameraData) (RayTracingSetup.cs:275-302): fills PixelColors (x + y * ResX, y = 0 top row).
