@@ -178,8 +178,10 @@ int rt_host_unregister(rt_ctx* ctx, void* ptr);
  *   light_split    fused shadow kernel: tiles of cost class >= this are handed out as one work item per light (0 = off, -1 = auto,
  *                  the default: class 6 on partitions of a quarter frame or less); needs hints
  *   hints          1 = heavy-first tile order from the previous frame's measured tile costs (default)
- *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 0 = auto: 2, or 1 on a quarter-frame partition or less) and the 1|2 streams they alternate over
- *                  (2: the drain of one wave overlaps the start of the next)
+ *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 0 = auto: 2, or 1 on a quarter-frame partition or less) and the 1..8 streams they rotate over
+ *                  (default 2: the drain of one wave overlaps the start of the next)
+ *   deep_lanes     lanes of a frame with mirror depths and >= 4 waves (spp passes), whose many small queue kernels then run side by side (1..8, default 8)
+ *   sah_term       host SAH builder: > 0 = SAH-driven leaf termination (node step cost / primitive test cost) for ranges of <= 8 primitives (default 0 = split down to leaf_max)
  *   copy_waves     number of waves rt_render splits a frame into so that the copy-out of one wave overlaps the kernels of the
  *                  next (default 8, 1 = off)
  *   chunk_pixels   upper bound of a wave in pixels (bounds the wave buffers)

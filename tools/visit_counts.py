@@ -17,7 +17,7 @@ else: s, p = sc.cfg5_scene(), sc.cfg5_params()
 L = H.load_library()
 L.rt_debug_visit_counts.argtypes = [C.c_void_p, C.c_int]
 names = ["lane_rays", "lane_node_visits", "lane_prim_tests", "packet_warps", "packet_rays", "packet_node_fetches", "packet_lane_node_visits",
-         "packet_prim_fetches", "packet_lane_prim_tests", "_"]
+         "packet_prim_fetches", "packet_lane_prim_tests", "packet_pops_culled"]
 out = {"workload": wl}
 for builder in (1, 0):
     for packet in (1, 0):

@@ -356,6 +356,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             }
             const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
             RtSahBuilder B;
+            B.term = (float)opt.sah_term;
             int threads = (int)std::thread::hardware_concurrency();
             const int32_t root = B.run(pb.data(), n, leaf_max, pad, threads < 1 ? 1 : threads);
             RT_CUDA(D.vals_alt.ensure((size_t)n * 4));

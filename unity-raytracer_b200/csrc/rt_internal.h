@@ -40,6 +40,8 @@ struct DevBuf {
 struct RtOptions {
     int chunk_pixels = 1 << 23;        // work items (pixel samples) per wave; multiple of 32
     int leaf_max = 4;                  // LBVH subtrees with <= leaf_max primitives become one leaf (<= 8)
+    double sah_term = 0.0;             // host SAH builder: > 0 = ranges of <= 8 primitives are split by an exact sweep and only while the
+                                       // SAH says so (node step cost / primitive test cost = this ratio); 0 = split down to leaf_max
     double pad_scale = 1.0 / 65536.0;  // node-box padding = max |coordinate| * pad_scale
     double t_slack = 1.000125;         // multiplicative slack on the traversal cull distance
     int block = 128;

@@ -27,6 +27,7 @@ struct RtSahBuilder {
     const RtSahBox* boxes = nullptr;          // per scan key
     int32_t n = 0, leaf_max = 4;
     float pad = 0.f;
+    float term = 0.f;                         // > 0: SAH termination for small ranges (RtOptions::sah_term)
     std::vector<int32_t> order;               // leaf-slot order of scan keys
     std::vector<float> nodes;                 // 16 floats per node
     std::atomic<int32_t> n_nodes{0};
@@ -73,7 +74,42 @@ struct RtSahBuilder {
             for (int c = 0; c < par; ++c) { const float* q = part[(size_t)c].data(); grow(lo, hi, q, q + 3); grow(clo, chi, q + 6, q + 9); }
         }
         for (int k = 0; k < 3; ++k) { out_lo[k] = lo[k]; out_hi[k] = hi[k]; }
-        if (cnt <= leaf_max) return ~(b * 8 + (cnt - 1));
+        if (term <= 0.f ? cnt <= leaf_max : cnt == 1) return ~(b * 8 + (cnt - 1));
+        if (term > 0.f && cnt <= 8) {
+            // ---- small range: exact sweep over the sorted centroids of each axis; leaf unless a split pays ----
+            int32_t best_ax = -1, best_k = 0; float best = FLT_MAX;
+            int32_t tmp[8], keep[3][8];
+            for (int ax = 0; ax < 3; ++ax) {
+                for (int32_t i = 0; i < cnt; ++i) tmp[i] = order[b + i];
+                std::sort(tmp, tmp + cnt, [&](int32_t x, int32_t y) {
+                    const float cx = boxes[x].lo[ax] + boxes[x].hi[ax], cy = boxes[y].lo[ax] + boxes[y].hi[ax];
+                    return cx < cy || (cx == cy && x < y);
+                });
+                for (int32_t i = 0; i < cnt; ++i) keep[ax][i] = tmp[i];
+                float ra[8]; float tlo[3], thi[3]; reset(tlo, thi);
+                for (int32_t i = cnt - 1; i >= 1; --i) { grow(tlo, thi, boxes[tmp[i]].lo, boxes[tmp[i]].hi); ra[i] = area(tlo, thi); }
+                reset(tlo, thi);
+                for (int32_t k = 1; k < cnt; ++k) {
+                    grow(tlo, thi, boxes[tmp[k - 1]].lo, boxes[tmp[k - 1]].hi);
+                    const float cost = area(tlo, thi) * (float)k + ra[k] * (float)(cnt - k);
+                    if (cost < best) { best = cost; best_ax = ax; best_k = k; }
+                }
+            }
+            const float pa = area(lo, hi);
+            if (cnt <= leaf_max && (best_ax < 0 || !((float)cnt * pa > term * pa + best))) return ~(b * 8 + (cnt - 1));
+            if (best_ax < 0) { best_ax = 0; best_k = cnt / 2; }
+            for (int32_t i = 0; i < cnt; ++i) order[b + i] = keep[best_ax][i];
+            const int32_t mid2 = b + best_k;
+            const int32_t me2 = n_nodes.fetch_add(1);
+            float llo[3], lhi[3], rlo[3], rhi[3];
+            const int32_t rl = build(b, mid2, depth + 1, llo, lhi), rr = build(mid2, e, depth + 1, rlo, rhi);
+            float* np = nodes.data() + 16 * (size_t)me2;
+            np[0] = llo[0] - pad; np[1] = lhi[0] + pad; np[2] = llo[1] - pad; np[3] = lhi[1] + pad;
+            np[4] = rlo[0] - pad; np[5] = rhi[0] + pad; np[6] = rlo[1] - pad; np[7] = rhi[1] + pad;
+            np[8] = llo[2] - pad; np[9] = lhi[2] + pad; np[10] = rlo[2] - pad; np[11] = rhi[2] + pad;
+            std::memcpy(np + 12, &rl, 4); std::memcpy(np + 13, &rr, 4); np[14] = 0.f; np[15] = 0.f;
+            return me2;
+        }
         // ---- binned SAH over the three axes ----
         struct Bins { int32_t bc[3][NB]; float blo[3][NB][3], bhi[3][NB][3]; };
         float scale3[3]; bool axis_ok[3];
