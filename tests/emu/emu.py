@@ -26,6 +26,8 @@ def lib():
         L.emu_scene_mesh.argtypes = [vp, fp, fp, C.c_int, vp, fp]
         L.emu_scene_lights.argtypes = [vp, fp, C.c_int, fp]
         L.emu_scene_commit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double, C.c_int]
+        L.emu_scene_clear.argtypes = [vp]
+        L.emu_scene_refit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double]
         L.emu_get_aabb.argtypes = [vp, fp]
         L.emu_n_nodes.argtypes = [vp]
         L.emu_max_stack.argtypes = [vp]
@@ -54,8 +56,10 @@ class EmuTracer:
         except Exception:
             pass
 
-    def set_scene(self, sa):
+    def set_scene(self, sa, refit=False):
         L, h = self.L, self.h
+        if refit:
+            L.emu_scene_clear(h)
         f32 = lambda a: np.ascontiguousarray(a, dtype=np.float32)
         if sa.spheres.shape[0]:
             s, m = f32(sa.spheres), np.ascontiguousarray(sa.sphere_mats)
@@ -69,6 +73,9 @@ class EmuTracer:
         li, amb = f32(sa.lights), f32(sa.ambient)
         L.emu_scene_lights(h, _fp(li), li.shape[0], _fp(amb))
         bb = _fp(f32(sa.scene_aabb)) if sa.scene_aabb is not None else None
+        if refit:
+            assert L.emu_scene_refit(h, bb, self.opts[0], self.opts[1], self.opts[2]) == 0
+            return
         L.emu_scene_commit(h, bb, self.opts[0], self.opts[1], self.opts[2], self.opts[3])
 
     def scene_aabb(self):

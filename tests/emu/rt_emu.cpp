@@ -27,12 +27,14 @@ struct Emu {
     std::vector<float> raw_v, raw_n; std::vector<float4> raw_s;
     std::vector<int32_t> mesh_base;
     std::vector<float4> nodes, prims, pinfo, mats, mesh_aabb, lights;
+    std::vector<int32_t> order;               // slot -> scan key of the committed tree (the device keeps it in vals_alt)
+    int32_t root = 0;
     RtScene S{};
     int n_nodes = 0, max_stack = 0;
     bool has_mirror = false;
 };
 
-void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder) {
+void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder, bool refit = false) {
     RtHostScene& H = E.host;
     const int n_mt = H.n_meshtris(), n_sp = H.n_spheres(), n_lo = H.n_loose(), n_me = H.n_meshes(), n_li = H.n_lights();
     const int n = (int)H.n_prims();
@@ -62,7 +64,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder)
     S.t_slack = (float)t_slack;
     S.backcull = H.backcull_ok() ? 1 : 0;
     S.mats = E.mats.data(); S.mesh_aabb = E.mesh_aabb.data(); S.mesh_base = E.mesh_base.data(); S.lights = E.lights.data();
-    E.n_nodes = 0;
+    if (!refit) E.n_nodes = 0;
     if (n == 0) return;
     RtRaw R{E.raw_v.data(), E.raw_n.data(), E.raw_s.data(), E.mesh_base.data(), n_me, n_mt, n_sp, n_lo};
     leaf_max = leaf_max < 1 ? 1 : (leaf_max > 8 ? 8 : leaf_max);
@@ -76,6 +78,39 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder)
     const float pad = (float)(amax * pad_scale) + 1e-30f;
     f3 bmin = mk3(b[0], b[1], b[2]);
     f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
+    if (refit) {                                                   // rt_scene_refit: k_emit_slots + k_node_parents + k_refit_nodes, serialised
+        E.prims.assign((size_t)3 * n, float4{}); E.pinfo.assign(n, float4{});
+        std::vector<float4> leaf_lo(n), leaf_hi(n);
+        for (int s = 0; s < n; ++s) rt_emit_slot(R, s, E.order[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
+        const int nn = E.n_nodes;
+        std::vector<int32_t> parent(nn, -1), arrived(nn, 0);
+        for (int i = 0; i < nn; ++i) rt_node_parents(E.nodes.data(), i, parent.data());
+        std::vector<float4> int_lo(nn), int_hi(nn);
+        for (int s0 = 0; s0 < nn; ++s0) {
+            float4 n3 = E.nodes[4 * (size_t)s0 + 3];
+            if (f2i(n3.x) >= 0 || f2i(n3.y) >= 0) continue;
+            int i = s0;
+            for (;;) {
+                float4* np = E.nodes.data() + 4 * (size_t)i;
+                f3 alo, ahi, blo, bhi;
+                rt_ref_box(f2i(np[3].x), leaf_lo.data(), leaf_hi.data(), int_lo.data(), int_hi.data(), alo, ahi);
+                rt_ref_box(f2i(np[3].y), leaf_lo.data(), leaf_hi.data(), int_lo.data(), int_hi.data(), blo, bhi);
+                np[0] = make_float4(alo.x - pad, ahi.x + pad, alo.y - pad, ahi.y + pad);
+                np[1] = make_float4(blo.x - pad, bhi.x + pad, blo.y - pad, bhi.y + pad);
+                np[2] = make_float4(alo.z - pad, ahi.z + pad, blo.z - pad, bhi.z + pad);
+                int_lo[i] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.f);
+                int_hi[i] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.f);
+                const int p = parent[i];
+                if (p < 0) break;
+                float4 p3 = E.nodes[4 * (size_t)p + 3];
+                const int need = (f2i(p3.x) >= 0 ? 1 : 0) + (f2i(p3.y) >= 0 ? 1 : 0);
+                if (++arrived[p] < need) break;
+                i = p;
+            }
+        }
+        S.prims = E.prims.data(); S.pinfo = E.pinfo.data(); S.nodes = E.nodes.data(); S.root = E.root;
+        return;
+    }
     if (builder == 1) {                                            // host binned-SAH path of rt_device_commit
         std::vector<RtSahBox> pb(n);
         for (int i = 0; i < n; ++i) { f3 lo, hi; rt_prim_box(R, i, lo, hi); pb[i] = RtSahBox{{lo.x, lo.y, lo.z}, {hi.x, hi.y, hi.z}}; }
@@ -88,6 +123,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder)
         E.nodes.assign(std::max<size_t>(4, B.nodes.size() / 4), float4{});
         memcpy(E.nodes.data(), B.nodes.data(), B.nodes.size() * 4);
         S.prims = E.prims.data(); S.pinfo = E.pinfo.data(); S.nodes = E.nodes.data(); S.root = root;
+        E.order = B.order; E.root = root;
         return;
     }
     std::vector<uint64_t> keys(n); std::vector<int32_t> vals(n);
@@ -99,7 +135,8 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder)
     std::vector<float4> leaf_lo(n), leaf_hi(n);
     for (int s = 0; s < n; ++s) rt_emit_slot(R, s, vals[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
     S.prims = E.prims.data(); S.pinfo = E.pinfo.data();
-    if (n <= leaf_max) { S.root = ~(n - 1); E.nodes.assign(4, float4{}); S.nodes = E.nodes.data(); return; }
+    E.order = vals;
+    if (n <= leaf_max) { S.root = ~(n - 1); E.root = S.root; E.nodes.assign(4, float4{}); S.nodes = E.nodes.data(); return; }
     const int ni = n - 1;
     std::vector<int32_t> tp((size_t)5 * ni + n, 0);
     RtTopo T{tp.data(), tp.data() + ni, tp.data() + 2 * (size_t)ni, tp.data() + 3 * (size_t)ni, tp.data() + 4 * (size_t)ni, tp.data() + 5 * (size_t)ni};
@@ -123,7 +160,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder)
     E.n_nodes = run;
     E.nodes.assign((size_t)4 * run, float4{});
     for (int i = 0; i < ni; ++i) rt_emit_node(i, T, new_index.data(), leaf_max, pad, leaf_lo.data(), leaf_hi.data(), int_lo.data(), int_hi.data(), E.nodes.data());
-    S.root = 0; S.nodes = E.nodes.data();
+    S.root = 0; S.nodes = E.nodes.data(); E.root = 0;
 }
 
 RtView make_view(const rt_render_params* p, int rank, int world, int band_rows) {
@@ -168,6 +205,15 @@ int emu_scene_commit(void* e, const float* aabb, int leaf_max, double pad_scale,
     Emu* E = (Emu*)e;
     if (aabb) for (int k = 0; k < 6; ++k) E->host.aabb[k] = aabb[k]; else E->host.calc_aabb();
     commit(*E, leaf_max, pad_scale, t_slack, builder);
+    return 0;
+}
+// rt_scene_update_* + rt_scene_refit: the scene is fed again (same counts) after emu_scene_clear; the tree and slot order are kept
+void emu_scene_clear(void* e) { Emu* E = (Emu*)e; E->host.clear(); E->host.mesh_tris = 0; }
+int emu_scene_refit(void* e, const float* aabb, int leaf_max, double pad_scale, double t_slack) {
+    Emu* E = (Emu*)e;
+    if ((int64_t)E->order.size() != E->host.n_prims()) return -1;
+    if (aabb) for (int k = 0; k < 6; ++k) E->host.aabb[k] = aabb[k]; else E->host.calc_aabb();
+    commit(*E, leaf_max, pad_scale, t_slack, 0, true);
     return 0;
 }
 void emu_get_aabb(void* e, float* out) { for (int k = 0; k < 6; ++k) out[k] = ((Emu*)e)->host.aabb[k]; }

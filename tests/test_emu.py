@@ -46,6 +46,30 @@ def test_bvh_equals_linear_scan(emu, oracle, scenes, leaf_max, builder):
     assert e.max_stack() < 64
 
 
+@pytest.mark.parametrize("builder", [0, 1])
+def test_refit_keeps_the_tree_and_the_result(emu, oracle, scenes, builder):
+    """rt_scene_refit's logic (rt_node_parents + bottom-up rt_ref_box over the emitted node array, rt_build_steps.h): after
+    the primitives moved — here: scrambled, the worst case for the old tree — the refitted tree still answers every query like
+    the reference's scan of the moved scene."""
+    import copy
+    s, p = scenes.random_soup(seed=7), scenes.soup_params(64, 48, 3, 1)
+    e = emu.EmuTracer(leaf_max=4, builder=builder); e.set_scene(s)
+    _strict(compare_renders(oracle.OracleScene(s).render(p, oracle.FAITHFUL), e.render(p)))
+    n_nodes = e.n_nodes()
+    rng = np.random.default_rng(2)
+    m = copy.deepcopy(s)
+    m.spheres[:, :3] += rng.uniform(-6, 6, m.spheres[:, :3].shape).astype(np.float32)
+    m.tris += np.tile(rng.uniform(-6, 6, (m.tris.shape[0], 3)).astype(np.float32), 3)
+    for k, (v, n, mat, aabb) in enumerate(m.meshes):
+        v = (v + np.tile(rng.uniform(-3, 3, (v.shape[0], 3)).astype(np.float32), 3)).astype(np.float32)
+        lo, hi = v.reshape(-1, 3).min(axis=0), v.reshape(-1, 3).max(axis=0)
+        m.meshes[k] = (v, n, mat, np.concatenate([lo, hi]).astype(np.float32))
+    m.scene_aabb = None
+    e.set_scene(m, refit=True)
+    assert e.n_nodes() == n_nodes
+    _strict(compare_renders(oracle.OracleScene(m).render(p, oracle.FAITHFUL), e.render(p)))
+
+
 def test_spp_grid_extension(emu, oracle, scenes):
     s, p = scenes.random_soup(seed=3), scenes.soup_params(48, 32, 2, 2)
     e = emu.EmuTracer(); e.set_scene(s)
