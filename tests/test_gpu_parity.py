@@ -221,9 +221,16 @@ def test_in_process_multi_device_equals_single(rtb, scenes):
     two.update_spheres(0, s2.spheres); two.update_triangles(0, s2.tris, s2.tri_normals)
     two.update_mesh(0, s2.meshes[0][0], s2.meshes[0][1], s2.meshes[0][3]); two.update_lights(s2.lights, s2.ambient)
     two.recommit()
-    b2 = two.render(p); two.close()
+    b2 = two.render(p)
     for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
         assert np.array_equal(a2[k], b2[k], equal_nan=True), k
+    # ... and so does a refit (tree kept on every device): back to the first layout
+    two.update_spheres(0, s.spheres); two.update_triangles(0, s.tris, s.tri_normals)
+    two.update_mesh(0, s.meshes[0][0], s.meshes[0][1], s.meshes[0][3]); two.update_lights(s.lights, s.ambient)
+    two.refit()
+    b3 = two.render(p); two.close()
+    for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(a[k], b3[k], equal_nan=True), k
 
 
 def test_render_full_size_properties(rt, scenes):
