@@ -44,10 +44,19 @@ if len(sys.argv) > 3 and sys.argv[2] == "--json":
         return v * mult * scale
     alias = {"k_trace_shadow<1, 1>": "k_shadow_primary", "k_trace_shadow<1, 0>": "k_shadow_primary", "k_trace_shadow<0, 1>": "k_shadow_queue",
              "k_trace_shadow<0, 0>": "k_shadow_queue", "k_trace_shadow<1>": "k_shadow_primary", "k_trace_shadow<0>": "k_shadow_queue"}
+    # per kernel: the mean over its launches in the report (the two waves of a frame differ a lot); utilisation and lanes
+    # weighted by duration / instructions
+    acc = {}
     for nm, r in zip(names, R):
-        nm = nm.strip()
-        wl[alias.get(nm, nm)] = {"dram_bytes_per_launch": val(r, "dram__bytes_read.sum") + val(r, "dram__bytes_write.sum"),
-                  "issue_slot_util_pct": val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
-                  "warp_instructions": val(r, "smsp__inst_executed.sum"), "active_lanes": val(r, "smsp__thread_inst_executed_per_inst_executed.ratio"),
-                  "duration_ms_under_ncu": val(r, "gpu__time_duration.sum"), "source": "profiles/" + os.path.basename(rep).replace(".ncu-rep", ".md")}
+        nm = alias.get(nm.strip(), nm.strip())
+        a = acc.setdefault(nm, {"n": 0, "dram": 0.0, "inst": 0.0, "ms": 0.0, "util_ms": 0.0, "lanes_inst": 0.0})
+        ms, inst = val(r, "gpu__time_duration.sum"), val(r, "smsp__inst_executed.sum")
+        a["n"] += 1; a["dram"] += val(r, "dram__bytes_read.sum") + val(r, "dram__bytes_write.sum"); a["inst"] += inst; a["ms"] += ms
+        a["util_ms"] += val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active") * ms
+        a["lanes_inst"] += val(r, "smsp__thread_inst_executed_per_inst_executed.ratio") * inst
+    for nm, a in acc.items():
+        wl[nm] = {"dram_bytes_per_launch": a["dram"] / a["n"], "issue_slot_util_pct": a["util_ms"] / a["ms"],
+                  "warp_instructions": a["inst"] / a["n"], "active_lanes": a["lanes_inst"] / a["inst"],
+                  "duration_ms_under_ncu": a["ms"] / a["n"], "launches_averaged": a["n"],
+                  "source": "profiles/" + os.path.basename(rep).replace(".ncu-rep", ".md")}
     json.dump(db, open(out, "w"), indent=1)
