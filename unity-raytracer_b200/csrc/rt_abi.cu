@@ -446,6 +446,20 @@ static int read_outputs_pipelined(rt_ctx* c, float* rgba32f, uint8_t* rgba8, int
             RT_CUDA(cudaMemcpyAsync(dst[k] + off, src[k] + off, len, cudaMemcpyDeviceToHost, D.copy_stream));
             bytes += len;
         }
+#ifdef RT_WAVE_TRACE
+        {   // development aid (-DRT_WAVE_TRACE): when each wave finished rendering / copying, relative to the frame's first event
+            static std::vector<cudaEvent_t> cev;
+            while (cev.size() <= w) { cudaEvent_t e; cudaEventCreate(&e); cev.push_back(e); }
+            cudaEventRecord(cev[w], D.copy_stream);
+            if (w + 1 == D.wave_marks.size()) {
+                cudaStreamSynchronize(D.copy_stream); cudaStreamSynchronize(D.stream);
+                if (getenv("RTB200_WAVE_TRACE")) for (size_t k = 0; k <= w; ++k) {
+                    float tr = 0.f, tc = 0.f; cudaEventElapsedTime(&tr, D.ev0, D.wave_ev[k]); cudaEventElapsedTime(&tc, D.ev0, cev[k]);
+                    fprintf(stderr, "wave %zu rows %d..%d rendered at %.3f ms, copied at %.3f ms\n", k, D.wave_marks[k].row0, D.wave_marks[k].row1, tr, tc);
+                }
+            }
+        }
+#endif
     }
     RT_CUDA(cudaStreamSynchronize(D.copy_stream));
     RT_CUDA(cudaStreamSynchronize(D.stream));

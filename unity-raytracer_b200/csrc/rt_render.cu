@@ -660,7 +660,11 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                     if (n_pass > 1 && n_lanes > 1 && pass < n_pass - 1) RT_CUDA(cudaEventRecord(D.fin_ev[wi], st));
                     if (mark && pass == n_pass - 1) {
                         const size_t i = D.wave_marks.size();
+                        #ifdef RT_WAVE_TRACE
+                        while (D.wave_ev.size() <= i) { cudaEvent_t e; RT_CUDA(cudaEventCreate(&e)); D.wave_ev.push_back(e); }
+#else
                         while (D.wave_ev.size() <= i) { cudaEvent_t e; RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.wave_ev.push_back(e); }
+#endif
                         RT_CUDA(cudaEventRecord(D.wave_ev[i], st));
                         const int r0 = (tb / V.tiles_x) * 4, r1 = ((tb + nt) / V.tiles_x) * 4;
                         D.wave_marks.push_back(RtDevice::WaveMark{r0, r1 < V.res_y ? r1 : V.res_y});
