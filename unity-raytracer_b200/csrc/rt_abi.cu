@@ -626,6 +626,7 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "backcull") { c->opt.backcull = value != 0; }
     else if (k == "light_split") { c->opt.light_split = (int)value; }
     else if (k == "hints") { c->opt.hints = value != 0; }
+    else if (k == "copy_plan") { if (value < 0) return fail(c, RT_E_INVALID, "copy_plan < 0"); c->opt.copy_plan = (long long)value; }
     else if (k == "copy_waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "copy_waves must be 1..64"); c->opt.copy_waves = (int)value; }
     else if (k == "builder") { if (value != 0 && value != 1) return fail(c, RT_E_INVALID, "builder must be 0 (device LBVH) or 1 (host SAH)"); c->opt.builder = (int)value; }
     else if (k == "kernel_timing") { c->opt.kernel_timing = value != 0; }

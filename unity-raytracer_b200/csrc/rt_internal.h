@@ -53,6 +53,7 @@ struct RtOptions {
     int lanes = 2;                     // 1 = all waves on one stream; 2.. = consecutive waves rotate over this many streams (tail overlap)
     int deep_lanes = 8;                // lanes of a frame with mirror depths AND >= 4 waves (spp passes): its queue kernels trace few,
                                        // incoherent rays each and last as long as their longest ray, so many of them run side by side
+    long long copy_plan = 0;           // development: wave plan of the pipelined copy-out as decimal digits (sixteenths of the rows per wave, sum 16); 0 = 1244221
     int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
                                        // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
     int fuse_shade = 1;                // shading (+ pixel write at depth 0) inside the shadow-trace kernel when <= 32 lights

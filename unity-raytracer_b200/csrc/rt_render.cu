@@ -489,11 +489,17 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         {
             const int tile_rows = V.n_tiles / V.tiles_x;
             const int cap_rows = chunk_tiles / V.tiles_x;
-            static const int plan16[7] = {1, 2, 4, 4, 2, 2, 1};
-            if (mark && n_split == 8 && tile_rows >= 64 && cap_rows >= tile_rows / 4 + 2) {
+            int plan16[16] = {1, 2, 4, 4, 2, 2, 1}, n_plan = 7, plan_max = 4;
+            if (opt.copy_plan > 0) {                                 // decimal digits = sixteenths of the rows per wave (must sum to 16)
+                int digits[16], nd = 0, sum = 0, mx = 0;
+                for (long long v = opt.copy_plan; v > 0 && nd < 16; v /= 10) { digits[nd++] = (int)(v % 10); }
+                for (int k = 0; k < nd; ++k) { sum += digits[k]; mx = digits[k] > mx ? digits[k] : mx; }
+                if (sum == 16 && nd >= 2) { n_plan = nd; plan_max = mx; for (int k = 0; k < nd; ++k) plan16[k] = digits[nd - 1 - k]; }
+            }
+            if (mark && n_split == 8 && tile_rows >= 64 && cap_rows >= tile_rows * plan_max / 16 + 2) {
                 int acc = 0;
-                for (int k = 0; k < 7; ++k) { wave_tb.push_back((int)((long long)tile_rows * acc / 16) * V.tiles_x); acc += plan16[k]; }
-                wave_tiles = ((tile_rows * 4 + 15) / 16 + 1) * V.tiles_x;            // capacity: the largest wave
+                for (int k = 0; k < n_plan; ++k) { if (plan16[k] > 0) wave_tb.push_back((int)((long long)tile_rows * acc / 16) * V.tiles_x); acc += plan16[k]; }
+                wave_tiles = ((tile_rows * plan_max + 15) / 16 + 1) * V.tiles_x;     // capacity: the largest wave
                 if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
             } else {
                 for (int tb = 0; tb < V.n_tiles; tb += wave_tiles) wave_tb.push_back(tb);
@@ -504,7 +510,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         int n_lanes = 1;
         if (!opt.kernel_timing && waves_per_pass * n_pass > 1) {
             n_lanes = opt.lanes;
-            if (V.max_bounces > 0 && waves_per_pass * n_pass >= 4 && opt.deep_lanes > n_lanes) n_lanes = opt.deep_lanes;
+            // (not for the pipelined copy-out of a single pass: there the waves must FINISH one after the other, early ones early,
+            // so that their copies can start — with all of them side by side cfg2's rt_render went from 2.9 to 3.2 ms)
+            if (V.max_bounces > 0 && waves_per_pass * n_pass >= 4 && opt.deep_lanes > n_lanes && (!mark || n_pass > 1)) n_lanes = opt.deep_lanes;
             if (n_lanes > waves_per_pass * n_pass) n_lanes = waves_per_pass * n_pass;
             if (n_lanes > RtDevice::RT_MAX_LANES) n_lanes = RtDevice::RT_MAX_LANES;
             if (n_lanes < 1) n_lanes = 1;
