@@ -156,6 +156,25 @@ def test_small_waves_equal_one_wave(rt, scenes):
         assert np.array_equal(a[k], b[k], equal_nan=True), k
 
 
+@pytest.mark.parametrize("lanes,deep", [(1, 1), (2, 2), (3, 8), (8, 8)])
+def test_lane_count_does_not_change_the_frame(rtb, scenes, lanes, deep):
+    """Waves rotate over 1..8 lanes (streams + buffer sets; 8 for frames with mirror depths and spp passes): the per-pixel
+    accumulation order of the spp passes and every result stay the same, through rt_render_device and through rt_render."""
+    s, p = scenes.random_soup(seed=9), scenes.soup_params(160, 96, 4, 2)          # depth 4, 2x2 spp: 4 passes
+    r = rtb.RayTracer((0,)); r.set_scene(s)
+    r.set_option("lanes", 1); r.set_option("deep_lanes", 1); r.set_option("chunk_pixels", 160 * 96)
+    a = r.render(p)
+    r.set_option("lanes", lanes); r.set_option("deep_lanes", deep)
+    for chunk in (160 * 96, 2048):                                                 # 1 wave per pass / 8 waves per pass
+        r.set_option("chunk_pixels", chunk)
+        for _ in range(2):                                                        # second frame: hints active
+            b = r.render(p)
+            for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+                assert np.array_equal(a[k], b[k], equal_nan=True), (chunk, k)
+        assert a["stats"]["rays_mirror"] == b["stats"]["rays_mirror"] and a["stats"]["rays_shadow"] == b["stats"]["rays_shadow"]
+    r.close()
+
+
 def test_host_sah_builder_parity(rtb, scenes, oracle):
     """option builder=1 (host binned-SAH BVH, csrc/rt_sah.h): same results as the reference's scan."""
     r = rtb.RayTracer((0,)); r.set_option("builder", 1)
