@@ -181,6 +181,8 @@ int rt_host_unregister(rt_ctx* ctx, void* ptr);
  *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 0 = auto: 2, or 1 on a quarter-frame partition or less) and the 1..8 streams they rotate over
  *                  (default 2: the drain of one wave overlaps the start of the next)
  *   deep_lanes     lanes of a frame with mirror depths and >= 4 waves (spp passes), whose many small queue kernels then run side by side (1..8, default 8)
+ *   presplit, presplit_depth   host SAH builder: > 0 = triangles whose box half-area exceeds this multiple of their area enter the tree as up to
+ *                  2^depth clipped pieces (reference pre-splitting; measured slower for packet traversal, default 0 = off)
  *   sah_term       host SAH builder: > 0 = SAH-driven leaf termination (node step cost / primitive test cost) for ranges of <= 8 primitives (default 0 = split down to leaf_max)
  *   copy_waves     number of waves rt_render splits a frame into so that the copy-out of one wave overlaps the kernels of the
  *                  next (default 8, 1 = off)

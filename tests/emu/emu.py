@@ -28,6 +28,8 @@ def lib():
         L.emu_scene_commit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double, C.c_int]
         L.emu_scene_clear.argtypes = [vp]
         L.emu_scene_refit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double]
+        L.emu_set_presplit.argtypes = [vp, C.c_double, C.c_int]
+        L.emu_n_slots.argtypes = [vp]
         L.emu_get_aabb.argtypes = [vp, fp]
         L.emu_n_nodes.argtypes = [vp]
         L.emu_max_stack.argtypes = [vp]
@@ -82,6 +84,12 @@ class EmuTracer:
         out = np.zeros(6, np.float32)
         self.L.emu_get_aabb(self.h, _fp(out))
         return out
+
+    def set_presplit(self, ratio, depth=3):
+        self.L.emu_set_presplit(self.h, float(ratio), int(depth))
+
+    def n_slots(self):
+        return self.L.emu_n_slots(self.h)
 
     def n_nodes(self):
         return self.L.emu_n_nodes(self.h)

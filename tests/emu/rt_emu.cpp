@@ -29,6 +29,7 @@ struct Emu {
     std::vector<float4> nodes, prims, pinfo, mats, mesh_aabb, lights;
     std::vector<int32_t> order;               // slot -> scan key of the committed tree (the device keeps it in vals_alt)
     int32_t root = 0;
+    double presplit = 0.0; int presplit_depth = 3;   // RtOptions::presplit / presplit_depth
     RtScene S{};
     int n_nodes = 0, max_stack = 0;
     bool has_mirror = false;
@@ -79,9 +80,10 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
     f3 bmin = mk3(b[0], b[1], b[2]);
     f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
     if (refit) {                                                   // rt_scene_refit: k_emit_slots + k_node_parents + k_refit_nodes, serialised
-        E.prims.assign((size_t)3 * n, float4{}); E.pinfo.assign(n, float4{});
-        std::vector<float4> leaf_lo(n), leaf_hi(n);
-        for (int s = 0; s < n; ++s) rt_emit_slot(R, s, E.order[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
+        const int ns = (int)E.order.size();                         // slots (>= n for a pre-split tree)
+        E.prims.assign((size_t)3 * ns, float4{}); E.pinfo.assign(ns, float4{});
+        std::vector<float4> leaf_lo(ns), leaf_hi(ns);
+        for (int s = 0; s < ns; ++s) rt_emit_slot(R, s, E.order[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
         const int nn = E.n_nodes;
         std::vector<int32_t> parent(nn, -1), arrived(nn, 0);
         for (int i = 0; i < nn; ++i) rt_node_parents(E.nodes.data(), i, parent.data());
@@ -115,10 +117,22 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
         std::vector<RtSahBox> pb(n);
         for (int i = 0; i < n; ++i) { f3 lo, hi; rt_prim_box(R, i, lo, hi); pb[i] = RtSahBox{{lo.x, lo.y, lo.z}, {hi.x, hi.y, hi.z}}; }
         RtSahBuilder B;
-        int root = B.run(pb.data(), n, leaf_max, pad, 4);
-        E.prims.assign((size_t)3 * n, float4{}); E.pinfo.assign(n, float4{});
-        std::vector<float4> leaf_lo(n), leaf_hi(n);
-        for (int s = 0; s < n; ++s) rt_emit_slot(R, s, B.order[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
+        std::vector<RtSahBox> rb; std::vector<int32_t> rk;
+        int ns = n;
+        if (E.presplit > 0.0) {                                     // reference pre-splitting, as rt_device_commit does it
+            auto tri = [&](int32_t key) -> const float* {
+                if (key < n_mt) return H.mesh_v.data() + 9 * (size_t)key;
+                if (key >= n_mt + n_sp) return H.loose_v.data() + 9 * (size_t)(key - n_mt - n_sp);
+                return nullptr;
+            };
+            RtPresplit::run(pb.data(), n, tri, E.presplit, E.presplit_depth, 3, rb, rk);
+            ns = (int)rb.size();
+        }
+        int root = B.run(rk.empty() ? pb.data() : rb.data(), ns, leaf_max, pad, 4);
+        if (!rk.empty()) for (int s = 0; s < ns; ++s) B.order[s] = rk[B.order[s]];
+        E.prims.assign((size_t)3 * ns, float4{}); E.pinfo.assign(ns, float4{});
+        std::vector<float4> leaf_lo(ns), leaf_hi(ns);
+        for (int s = 0; s < ns; ++s) rt_emit_slot(R, s, B.order[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
         E.n_nodes = (int)(B.nodes.size() / 16);
         E.nodes.assign(std::max<size_t>(4, B.nodes.size() / 4), float4{});
         memcpy(E.nodes.data(), B.nodes.data(), B.nodes.size() * 4);
@@ -211,11 +225,13 @@ int emu_scene_commit(void* e, const float* aabb, int leaf_max, double pad_scale,
 void emu_scene_clear(void* e) { Emu* E = (Emu*)e; E->host.clear(); E->host.mesh_tris = 0; }
 int emu_scene_refit(void* e, const float* aabb, int leaf_max, double pad_scale, double t_slack) {
     Emu* E = (Emu*)e;
-    if ((int64_t)E->order.size() != E->host.n_prims()) return -1;
+    if ((int64_t)E->order.size() < E->host.n_prims() || E->host.n_prims() <= 0) return -1;
     if (aabb) for (int k = 0; k < 6; ++k) E->host.aabb[k] = aabb[k]; else E->host.calc_aabb();
     commit(*E, leaf_max, pad_scale, t_slack, 0, true);
     return 0;
 }
+void emu_set_presplit(void* e, double ratio, int depth) { ((Emu*)e)->presplit = ratio; ((Emu*)e)->presplit_depth = depth; }
+int emu_n_slots(void* e) { return (int)((Emu*)e)->order.size(); }
 void emu_get_aabb(void* e, float* out) { for (int k = 0; k < 6; ++k) out[k] = ((Emu*)e)->host.aabb[k]; }
 int emu_n_nodes(void* e) { return ((Emu*)e)->n_nodes; }
 int emu_max_stack(void* e) { return ((Emu*)e)->max_stack; }

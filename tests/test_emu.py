@@ -70,6 +70,26 @@ def test_refit_keeps_the_tree_and_the_result(emu, oracle, scenes, builder):
     _strict(compare_renders(oracle.OracleScene(m).render(p, oracle.FAITHFUL), e.render(p)))
 
 
+@pytest.mark.parametrize("ratio,depth", [(2.5, 3), (1.0, 5)])
+def test_presplit_references_keep_the_result(emu, oracle, scenes, ratio, depth):
+    """Reference pre-splitting of the host SAH builder (rt_sah.h RtPresplit): thin diagonal triangles enter the tree as several
+    clipped pieces, so a triangle sits in several leaves — the query result (argmin over (t, scan key), any-hit) must not
+    change, nor must a refit of the split tree."""
+    import copy
+    for s, p in ((scenes.random_soup(seed=7), scenes.soup_params(64, 48, 3, 1)), (scenes.cfg3_scene(n=8), scenes.cfg3_params(96, 54))):
+        plain = emu.EmuTracer(leaf_max=4, builder=1); plain.set_scene(s)
+        e = emu.EmuTracer(leaf_max=4, builder=1); e.set_presplit(ratio, depth); e.set_scene(s)
+        assert e.n_slots() > plain.n_slots() == s.n_prims                  # something was split
+        ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+        _strict(compare_renders(ref, e.render(p)))
+        m = copy.deepcopy(s)
+        m.tris += np.float32(0.25)
+        m.meshes = [(v + np.float32(0.25), n, mat, aabb + np.float32(0.25)) for (v, n, mat, aabb) in m.meshes]
+        m.scene_aabb = None
+        e.set_scene(m, refit=True)
+        _strict(compare_renders(oracle.OracleScene(m).render(p, oracle.FAITHFUL), e.render(p)))
+
+
 def test_spp_grid_extension(emu, oracle, scenes):
     s, p = scenes.random_soup(seed=3), scenes.soup_params(48, 32, 2, 2)
     e = emu.EmuTracer(); e.set_scene(s)

@@ -189,6 +189,19 @@ def test_host_sah_builder_parity(rtb, scenes, oracle):
         got = r.render(p)
         _check(compare_renders(ref, got))
         assert (got["stats"]["rays_primary"], got["stats"]["rays_shadow"], got["stats"]["rays_mirror"]) == ref["stats"]
+        # builder options that change the tree, never the result: SAH leaf termination, reference pre-splitting (a triangle
+        # then sits in several leaves; more slots than primitives), and a refit of such a tree
+        n_nodes = r.stats()["n_nodes"]
+        r.set_option("sah_term", 1.0); r.set_option("presplit", 2.5); r.set_option("presplit_depth", 3)
+        r.set_scene(s)
+        assert r.stats()["n_nodes"] > n_nodes
+        g2 = r.render(p)
+        for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+            assert np.array_equal(got[k], g2[k], equal_nan=True), k
+        r.update_lights(s.lights, s.ambient); r.refit()
+        g3 = r.render(p)
+        for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+            assert np.array_equal(got[k], g3[k], equal_nan=True), k
     finally:
         r.close()
 

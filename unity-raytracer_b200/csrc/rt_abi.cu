@@ -610,6 +610,8 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     std::string k(key);
     if (k == "chunk_pixels") { if (value < 32) return fail(c, RT_E_INVALID, "chunk_pixels < 32"); c->opt.chunk_pixels = ((int)value / 32) * 32; }
     else if (k == "leaf_max") { if (value < 1 || value > 8) return fail(c, RT_E_INVALID, "leaf_max must be 1..8"); c->opt.leaf_max = (int)value; }
+    else if (k == "presplit") { if (value < 0) return fail(c, RT_E_INVALID, "presplit < 0"); c->opt.presplit = value; }
+    else if (k == "presplit_depth") { if (value < 0 || value > 6) return fail(c, RT_E_INVALID, "presplit_depth must be 0..6"); c->opt.presplit_depth = (int)value; }
     else if (k == "sah_term") { if (value < 0) return fail(c, RT_E_INVALID, "sah_term < 0"); c->opt.sah_term = value; }
     else if (k == "pad_scale") { if (value < 0) return fail(c, RT_E_INVALID, "pad_scale < 0"); c->opt.pad_scale = value; }
     else if (k == "t_slack") { if (value < 1) return fail(c, RT_E_INVALID, "t_slack < 1"); c->opt.t_slack = value; }

@@ -275,9 +275,9 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
 
     // ---- scene view (pointers filled below) ----
     RtScene& S = D.S;
-    const int32_t old_prims = D.bvh_prims, old_root = D.bvh_root;
+    const int32_t old_prims = D.bvh_prims, old_root = D.bvh_root, old_slots = D.bvh_slots;
     const uint32_t old_nodes = D.n_nodes;
-    if (refit && (old_prims != n || n <= 0 || D.vals_alt.bytes < (size_t)n * 4)) { err = "rt_scene_refit: no committed tree over this many primitives"; return RT_E_STATE; }
+    if (refit && (old_prims != n || n <= 0 || old_slots < n || D.vals_alt.bytes < (size_t)old_slots * 4)) { err = "rt_scene_refit: no committed tree over this many primitives"; return RT_E_STATE; }
     D.bvh_prims = -1;
     S = RtScene{};
     S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_mt; S.n_spheres = n_sp; S.n_lights = n_li;
@@ -306,8 +306,9 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             k_bounds<<<grid_for(n) < D.sm_count * 4 ? grid_for(n) : D.sm_count * 4, BT, 0, st>>>(R, n, D.bounds.as<uint32_t>());
             uint32_t bord[6];
             RT_CUDA(cudaMemcpyAsync(bord, D.bounds.p, sizeof(bord), cudaMemcpyDeviceToHost, st));
-            RT_CUDA(D.leaf_lo.ensure((size_t)n * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)n * 16));
-            k_emit_slots<<<grid_for(n), BT, 0, st>>>(R, n, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
+            // (slots of a pre-split tree get the whole triangle's box again: conservative, the clipping is lost until the next commit)
+            RT_CUDA(D.leaf_lo.ensure((size_t)old_slots * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)old_slots * 16));
+            k_emit_slots<<<grid_for(old_slots), BT, 0, st>>>(R, old_slots, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
             RT_CUDA(cudaStreamSynchronize(st));
             float amax = 0.f;
             for (int k = 0; k < 6; ++k) { float b = f_unord(bord[k]); if (std::isfinite(b)) amax = fmaxf(amax, fabsf(b)); }
@@ -329,7 +330,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             RT_CUDA(cudaGetLastError());
             S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
             S.root = old_root;
-            D.bvh_prims = n; D.bvh_root = old_root;
+            D.bvh_prims = n; D.bvh_slots = old_slots; D.bvh_root = old_root;
             RT_CUDA(cudaEventRecord(D.ev1, st));
             RT_CUDA(cudaEventSynchronize(D.ev1));
             if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
@@ -358,20 +359,36 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             RtSahBuilder B;
             B.term = (float)opt.sah_term;
             int threads = (int)std::thread::hardware_concurrency();
-            const int32_t root = B.run(pb.data(), n, leaf_max, pad, threads < 1 ? 1 : threads);
-            RT_CUDA(D.vals_alt.ensure((size_t)n * 4));
-            RT_CUDA(cudaMemcpyAsync(D.vals_alt.p, B.order.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+            // reference pre-splitting (rt_sah.h RtPresplit): thin diagonal triangles enter the builder as several clipped pieces
+            std::vector<RtSahBox> rb; std::vector<int32_t> rk;
+            const RtSahBox* items = pb.data();
+            int32_t ns = n;                                           // leaf slots = BVH references (>= n with pre-splitting)
+            if (opt.presplit > 0.0) {
+                auto tri = [&](int32_t key) -> const float* {
+                    if (key < n_mt) return H.mesh_v.data() + 9 * (size_t)key;
+                    if (key >= n_mt + n_sp) return H.loose_v.data() + 9 * (size_t)(key - n_mt - n_sp);
+                    return nullptr;
+                };
+                RtPresplit::run(pb.data(), n, tri, opt.presplit, opt.presplit_depth < 0 ? 0 : (opt.presplit_depth > 6 ? 6 : opt.presplit_depth),
+                                threads < 1 ? 1 : threads, rb, rk);
+                if (rb.size() > (size_t)(1 << 28) - 8) { err = "too many BVH references after pre-splitting"; return RT_E_UNSUPPORTED; }
+                items = rb.data(); ns = (int32_t)rb.size();
+            }
+            const int32_t root = B.run(items, ns, leaf_max, pad, threads < 1 ? 1 : threads);
+            if (!rk.empty()) for (int32_t s2 = 0; s2 < ns; ++s2) B.order[(size_t)s2] = rk[(size_t)B.order[(size_t)s2]];      // slot -> scan key
+            RT_CUDA(D.vals_alt.ensure((size_t)ns * 4));
+            RT_CUDA(cudaMemcpyAsync(D.vals_alt.p, B.order.data(), (size_t)ns * 4, cudaMemcpyHostToDevice, st));
             D.n_nodes = (uint32_t)(B.nodes.size() / 16);
             RT_CUDA(D.nodes.ensure(B.nodes.size() * 4 + 64));
             if (!B.nodes.empty()) RT_CUDA(cudaMemcpyAsync(D.nodes.p, B.nodes.data(), B.nodes.size() * 4, cudaMemcpyHostToDevice, st));
-            RT_CUDA(D.prims.ensure((size_t)n * 48)); RT_CUDA(D.pinfo.ensure((size_t)n * 16));
-            RT_CUDA(D.leaf_lo.ensure((size_t)n * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)n * 16));
-            k_emit_slots<<<grid_for(n), BT, 0, st>>>(R, n, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
+            RT_CUDA(D.prims.ensure((size_t)ns * 48)); RT_CUDA(D.pinfo.ensure((size_t)ns * 16));
+            RT_CUDA(D.leaf_lo.ensure((size_t)ns * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)ns * 16));
+            k_emit_slots<<<grid_for(ns), BT, 0, st>>>(R, ns, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
             RT_CUDA(cudaGetLastError());
             RT_CUDA(cudaStreamSynchronize(st));                   // B.order / B.nodes go out of scope
             S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
             S.root = root;
-            D.bvh_prims = n; D.bvh_root = root; D.bvh_parents = false;
+            D.bvh_prims = n; D.bvh_slots = ns; D.bvh_root = root; D.bvh_parents = false;
             RT_CUDA(cudaEventRecord(D.ev1, st));
             RT_CUDA(cudaEventSynchronize(D.ev1));
             if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
@@ -439,7 +456,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             S.nodes = D.nodes.as<float4>();
         }
         RT_CUDA(cudaGetLastError());
-        D.bvh_prims = n; D.bvh_root = S.root; D.bvh_parents = false;
+        D.bvh_prims = n; D.bvh_slots = n; D.bvh_root = S.root; D.bvh_parents = false;
     }
     RT_CUDA(cudaEventRecord(D.ev1, st));
     RT_CUDA(cudaEventSynchronize(D.ev1));

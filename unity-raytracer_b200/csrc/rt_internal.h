@@ -40,6 +40,9 @@ struct DevBuf {
 struct RtOptions {
     int chunk_pixels = 1 << 23;        // work items (pixel samples) per wave; multiple of 32
     int leaf_max = 4;                  // LBVH subtrees with <= leaf_max primitives become one leaf (<= 8)
+    double presplit = 0.0;             // host SAH builder: > 0 = triangles whose box half-area exceeds this multiple of their own area enter the
+                                       // builder as clipped pieces (rt_sah.h RtPresplit); 0 = off
+    int presplit_depth = 3;            // at most 2^depth pieces per triangle
     double sah_term = 0.0;             // host SAH builder: > 0 = ranges of <= 8 primitives are split by an exact sweep and only while the
                                        // SAH says so (node step cost / primitive test cost = this ratio); 0 = split down to leaf_max
     double pad_scale = 1.0 / 65536.0;  // node-box padding = max |coordinate| * pad_scale
@@ -84,7 +87,7 @@ struct RtDevice {
     uint32_t n_nodes = 0;
     bool has_mirror = false;
     // refit (rt_scene_refit): the committed tree is kept and only its boxes are recomputed
-    int32_t bvh_prims = -1, bvh_root = 0;   // primitive count / root ref of the tree in `nodes` (+ slot order in vals_alt); -1: none
+    int32_t bvh_prims = -1, bvh_slots = 0, bvh_root = 0;   // primitive count / root ref of the tree in `nodes` (+ slot order in vals_alt); -1: none
     bool bvh_parents = false;           // node_parent holds the parents of this tree
     DevBuf node_parent;
     // ---- build scratch ----

@@ -219,3 +219,96 @@ struct RtSahBuilder {
         return root;                                             // the first fetch_add happened at the root: root == 0
     }
 };
+
+// ---- reference pre-splitting ("early split clipping", Ernst & Greiner 2007) for the host SAH builder --------------------
+// A thin triangle that lies diagonally in space has an axis-aligned box far larger than itself (cfg3's displaced shell:
+// 0.1-wide facets that run up to 0.8 along the radius): the leaf boxes of neighbours overlap massively and every ray near
+// the surface visits many leaves for nothing.  Such a triangle is cut by axis-aligned planes (midpoint of the longest box
+// axis) into up to 2^max_depth convex pieces; each piece becomes its own BVH *reference* with the box of the clipped
+// polygon, all references carrying the same triangle.  The query result cannot change: a leaf stores the whole triangle
+// (exact test as ever), duplicates of a triangle in several leaves give the same (t, scan key), and the piece boxes cover
+// the triangle.  Boxes are computed in double, rounded outward and still padded by the builder.
+// split while  box half-area / polygon area > ratio  (1 = an axis-aligned rectangle, 2 = an axis-aligned right triangle).
+struct RtPresplit {
+    struct P3 { double x[3]; };
+    static int clip(const P3* in, int n, int ax, double c, bool keep_low, P3* out) {        // Sutherland-Hodgman against x[ax] = c
+        int m = 0;
+        for (int i = 0; i < n; ++i) {
+            const P3& a = in[i]; const P3& b = in[(i + 1) % n];
+            const double da = keep_low ? c - a.x[ax] : a.x[ax] - c, db = keep_low ? c - b.x[ax] : b.x[ax] - c;   // >= 0: inside
+            if (da >= 0) out[m++] = a;
+            if ((da > 0 && db < 0) || (da < 0 && db > 0)) {
+                const double t = da / (da - db);
+                P3 p; for (int k = 0; k < 3; ++k) p.x[k] = a.x[k] + t * (b.x[k] - a.x[k]);
+                p.x[ax] = c;
+                out[m++] = p;
+            }
+        }
+        return m;
+    }
+    static double area(const P3* p, int n) {                                               // polygon area (fan)
+        double sx = 0, sy = 0, sz = 0;
+        for (int i = 1; i + 1 < n; ++i) {
+            const double ux = p[i].x[0] - p[0].x[0], uy = p[i].x[1] - p[0].x[1], uz = p[i].x[2] - p[0].x[2];
+            const double vx = p[i + 1].x[0] - p[0].x[0], vy = p[i + 1].x[1] - p[0].x[1], vz = p[i + 1].x[2] - p[0].x[2];
+            sx += uy * vz - uz * vy; sy += uz * vx - ux * vz; sz += ux * vy - uy * vx;
+        }
+        return 0.5 * std::sqrt(sx * sx + sy * sy + sz * sz);
+    }
+    static void emit(const P3* p, int n, const RtSahBox& clipto, int32_t key, std::vector<RtSahBox>& rb, std::vector<int32_t>& rk) {
+        RtSahBox b;
+        for (int k = 0; k < 3; ++k) {
+            double lo = p[0].x[k], hi = p[0].x[k];
+            for (int i = 1; i < n; ++i) { lo = std::fmin(lo, p[i].x[k]); hi = std::fmax(hi, p[i].x[k]); }
+            float flo = (float)lo, fhi = (float)hi;
+            if ((double)flo > lo) flo = std::nextafterf(flo, -FLT_MAX);
+            if ((double)fhi < hi) fhi = std::nextafterf(fhi, FLT_MAX);
+            b.lo[k] = std::fmax(flo, clipto.lo[k]); b.hi[k] = std::fmin(fhi, clipto.hi[k]);      // never beyond the triangle's own box
+        }
+        rb.push_back(b); rk.push_back(key);
+    }
+    static void split(const P3* p, int n, const RtSahBox& full, int32_t key, int depth, int max_depth, double ratio,
+                      std::vector<RtSahBox>& rb, std::vector<int32_t>& rk) {
+        double lo[3], hi[3];
+        for (int k = 0; k < 3; ++k) { lo[k] = hi[k] = p[0].x[k]; for (int i = 1; i < n; ++i) { lo[k] = std::fmin(lo[k], p[i].x[k]); hi[k] = std::fmax(hi[k], p[i].x[k]); } }
+        const double dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        const double ha = dx * dy + dy * dz + dz * dx, pa = area(p, n);
+        int ax = dx >= dy ? (dx >= dz ? 0 : 2) : (dy >= dz ? 1 : 2);
+        const double ext = hi[ax] - lo[ax];
+        if (depth >= max_depth || !(ha > ratio * pa) || !(ext > 0) || !std::isfinite(ha)) { emit(p, n, full, key, rb, rk); return; }
+        const double c = 0.5 * (lo[ax] + hi[ax]);
+        P3 a[12], b[12];
+        const int na = clip(p, n, ax, c, true, a), nb = clip(p, n, ax, c, false, b);
+        if (na < 3 || nb < 3 || na > 10 || nb > 10) { emit(p, n, full, key, rb, rk); return; }    // degenerate cut: keep the piece whole
+        split(a, na, full, key, depth + 1, max_depth, ratio, rb, rk);
+        split(b, nb, full, key, depth + 1, max_depth, ratio, rb, rk);
+    }
+    // pb: box per scan key; tri(key): the 9 vertex floats of a triangle key, nullptr for a sphere (never split).
+    // References come out in key order (pieces of one triangle adjacent), independent of the thread count.
+    template <class TRI>
+    static void run(const RtSahBox* pb, int32_t n, TRI tri, double ratio, int max_depth, int threads,
+                    std::vector<RtSahBox>& rb, std::vector<int32_t>& rk) {
+        threads = threads < 1 ? 1 : (threads > 64 ? 64 : threads);
+        if (n < (1 << 14)) threads = 1;
+        std::vector<std::vector<RtSahBox>> tb((size_t)threads); std::vector<std::vector<int32_t>> tk((size_t)threads);
+        auto work = [&](int t) {
+            const int32_t k0 = (int32_t)((int64_t)n * t / threads), k1 = (int32_t)((int64_t)n * (t + 1) / threads);
+            tb[(size_t)t].reserve((size_t)(k1 - k0) * 2); tk[(size_t)t].reserve((size_t)(k1 - k0) * 2);
+            for (int32_t key = k0; key < k1; ++key) {
+                const float* v = tri(key);
+                bool ok = v != nullptr;
+                for (int k = 0; ok && k < 9; ++k) ok = std::isfinite(v[k]);
+                if (!ok) { tb[(size_t)t].push_back(pb[key]); tk[(size_t)t].push_back(key); continue; }
+                P3 p[3];
+                for (int i = 0; i < 3; ++i) for (int k = 0; k < 3; ++k) p[i].x[k] = (double)v[3 * i + k];
+                split(p, 3, pb[key], key, 0, max_depth, ratio, tb[(size_t)t], tk[(size_t)t]);
+            }
+        };
+        std::vector<std::thread> pool;
+        for (int t = 1; t < threads; ++t) pool.emplace_back(work, t);
+        work(0);
+        for (auto& th : pool) th.join();
+        rb.clear(); rk.clear();
+        for (int t = 0; t < threads; ++t) { rb.insert(rb.end(), tb[(size_t)t].begin(), tb[(size_t)t].end()); rk.insert(rk.end(), tk[(size_t)t].begin(), tk[(size_t)t].end()); }
+    }
+};
