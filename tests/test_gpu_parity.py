@@ -66,6 +66,32 @@ def test_random_soup_vs_faithful_scan(rt, scenes, oracle, seed, spp):
     assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == ref["stats"]
 
 
+def test_many_lights_and_unfused_shading(rtb, scenes, oracle):
+    """The light loop (RayTracingSetup.cs:333-355) beyond the fused kernel's 32-light limit: 40 lights go through the separate
+    occlusion-mask + shading kernels, checked against the faithful scan; with 2 lights the unfused and the fused kernels,
+    and backcull off, must give the fused frame bit for bit."""
+    s, p = scenes.random_soup(seed=13, n_tris=600, n_spheres=60), scenes.soup_params(80, 48, 2, 1)
+    rng = np.random.default_rng(2)
+    two = scenes.random_soup(seed=13, n_tris=600, n_spheres=60)
+    for i in range(38):
+        s.add_light(tuple(rng.uniform(-45, 45, 3)), float(rng.uniform(2e3, 2e4)))
+    assert s.lights.shape[0] == 40
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    r = rtb.RayTracer((0,)); r.set_scene(s)
+    got = r.render(p)
+    _check(compare_renders(ref, got))
+    st = got["stats"]
+    assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == ref["stats"]
+    r.set_scene(two)
+    fused = r.render(p)
+    for key in ("fuse_shade", "backcull"):
+        q = rtb.RayTracer((0,)); q.set_option(key, 0); q.set_scene(two)
+        other = q.render(p); q.close()
+        for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+            assert np.array_equal(fused[k], other[k]), (key, k)
+    r.close()
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)
