@@ -92,6 +92,50 @@ def test_many_lights_and_unfused_shading(rtb, scenes, oracle):
     r.close()
 
 
+def test_reference_driver_interface_and_device_resident_api(rtb, scenes, oracle):
+    """The reference's own call order (RayTracingSetup.Update, RayTracingSetup.cs:171-199): set ImagePlane / BackgroundColor /
+    MaxReflectionBounces, UpdateScene(), CastPixelRays(CameraData) -> PixelColors (Color[] index x + y*X).  Then the
+    device-resident calls under it: rt_render_device + rt_read_outputs, the device pointers of rt_device_outputs (read back
+    through torch, no library copy), and a caller-owned stream (rt_set_stream) give the same frame."""
+    import torch
+    s, p = scenes.rt_unity(mirror_sphere=True), scenes.rt_unity_params(200, 112, 3)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    setup = rtb.RayTracingSetup((0,))
+    setup.ImagePlane = rtb.ImagePlane(rtb.Resolution(200, 112), p["dist"], p["half_h"], p["half_v"])
+    setup.BackgroundColor = tuple(p["background_rgb"])
+    setup.MaxReflectionBounces = 3
+    setup.UpdateScene(s)
+    cam = rtb.CameraData(p["pos"], p["fwd"], p["right"], p["up"])
+    colors = setup.CastPixelRays(cam)
+    assert colors is setup.PixelColors and colors.shape == (200 * 112, 4)
+    assert np.array_equal(colors, ref["rgba32f"], equal_nan=True)
+    r = setup._rt
+    st = r.render_device(p, rtb.host.RT_OUT_ALL, sync_stats=True)
+    assert (st["rays_primary"], st["rays_shadow"], st["rays_mirror"]) == ref["stats"]
+    back = r.read_outputs(p)
+    _check(compare_renders(ref, back))
+    ptrs = r.device_outputs()
+    assert all(ptrs)
+    n = 200 * 112
+
+    class _Dev:                                             # __cuda_array_interface__ view of a library-owned device buffer
+        def __init__(self, ptr, shape, typestr):
+            self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+    f32 = torch.as_tensor(_Dev(ptrs[0], (n, 4), "<f4"), device="cuda:0").cpu().numpy()
+    ids = torch.as_tensor(_Dev(ptrs[2], (n, 3), "<i4"), device="cuda:0").cpu().numpy()
+    assert np.array_equal(f32, ref["rgba32f"], equal_nan=True) and np.array_equal(ids, back["hit_id"])
+    stream = torch.cuda.Stream(device=0)
+    r.set_stream(stream.cuda_stream)
+    r.render_device(scenes.rt_unity_params(200, 112, 0), rtb.host.RT_OUT_ALL)      # a different frame in between
+    r.render_device(p, rtb.host.RT_OUT_ALL)
+    stream.synchronize()
+    again = r.read_outputs(p)
+    for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+        assert np.array_equal(back[k], again[k], equal_nan=True), k
+    r.set_stream(None)
+    r.close()
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)
