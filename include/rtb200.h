@@ -111,7 +111,8 @@ int rt_scene_get_aabb(rt_ctx* ctx, float out_aabb[6]);
  * the shim re-send only what changed.  Counts and materials stay as committed; the arrays replace the object's data in place
  * (same layouts as rt_scene_mesh / rt_scene_triangles / rt_scene_spheres / rt_scene_lights; mesh_index and first are the
  * reference's MeshIndex / Index).  After one or more updates rt_scene_recommit rebuilds the BVH from the device-resident
- * arrays (scene_aabb as for rt_scene_commit); rendering between an update and the recommit returns RT_E_STATE. */
+ * arrays (scene_aabb as for rt_scene_commit); rendering between an update and the recommit returns RT_E_STATE.  An update
+ * rejected for its arguments (RT_E_INVALID) changes nothing and leaves a clean scene clean. */
 int rt_scene_update_mesh(rt_ctx* ctx, int mesh_index, const float* vertices, const float* normals, const float aabb[6]);
 int rt_scene_update_triangles(rt_ctx* ctx, int first, int n, const float* vertices, const float* normals);
 int rt_scene_update_spheres(rt_ctx* ctx, int first, int n, const float* center_r2);

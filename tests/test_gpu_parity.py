@@ -136,6 +136,40 @@ def test_reference_driver_interface_and_device_resident_api(rtb, scenes, oracle)
     r.close()
 
 
+def test_error_codes_leave_the_context_usable(rtb, scenes):
+    """Every misuse returns its documented code (include/rtb200.h RT_E_*) with a message in rt_last_error, launches nothing,
+    and the context renders the next valid frame unchanged."""
+    E = rtb.host.RtError
+    INVALID, STATE = -1, -4                                            # include/rtb200.h:31-35
+    r = rtb.RayTracer((0,))
+    s, p = scenes.rt_unity(), scenes.rt_unity_params(64, 40, 2)
+
+    def fails(code, text, fn, *a):
+        with pytest.raises(E) as ei:
+            fn(*a)
+        assert ei.value.code == code and text in str(ei.value), (ei.value.code, str(ei.value))
+
+    fails(STATE, "before rt_scene_commit", r.render, p)
+    fails(STATE, "before rt_scene_commit", r.intersect, [(0, 0, 0)], [(0, 0, 1)])
+    fails(STATE, "no committed scene", r.recommit)
+    fails(INVALID, "unknown option", r.set_option, "no_such_option", 1)
+    fails(INVALID, "lanes must be 1..8", r.set_option, "lanes", 9)
+    fails(INVALID, "leaf_max must be 1..8", r.set_option, "leaf_max", 0)
+    fails(INVALID, "bad arguments", r.set_partition, 2, 2)
+    r.set_scene(s)
+    want = r.render(p)
+    fails(INVALID, "negative resolution", r.render_device, dict(p, res_x=-1))
+    fails(INVALID, "spp_grid above 64", r.render, dict(p, spp_grid=65))
+    fails(INVALID, "bad range", r.update_spheres, s.spheres.shape[0], s.spheres[:1])
+    fails(INVALID, "bad arguments", r.update_mesh, 7, s.meshes[0][0], s.meshes[0][1], s.meshes[0][3])
+    r.render_device(p, rtb.host.RT_OUT_RGBA8)
+    fails(STATE, "was not rendered", r.read_outputs, p, rtb.host.RT_OUT_HIT_T)
+    got = r.render(p)                                                  # failed updates left the scene clean and unchanged
+    for k in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+        assert np.array_equal(want[k], got[k]), k
+    r.close()
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)

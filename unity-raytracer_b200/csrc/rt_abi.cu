@@ -305,6 +305,10 @@ static int update_prolog(rt_ctx* c, const char* who) {
     if (!c) return RT_E_INVALID;
     if (c->in_scene) return fail(c, RT_E_STATE, std::string(who) + " inside rt_scene_begin/commit");
     if (!c->committed && !c->dirty) return fail(c, RT_E_STATE, std::string(who) + ": no committed scene");
+    return RT_OK;
+}
+// called once the arguments are known to be good: a rejected update leaves the scene clean
+static int update_mark(rt_ctx* c) {
     if (!c->dirty) { int rc = sync_all(c); if (rc) return rc; }          // frames in flight still read the old data
     c->dirty = true; c->committed = false;
     return RT_OK;
@@ -325,6 +329,7 @@ int rt_scene_update_mesh(rt_ctx* c, int mesh_index, const float* v, const float*
     const int64_t first = H.mesh_base[mesh_index];
     const int64_t n = (mesh_index + 1 < H.n_meshes() ? (int64_t)H.mesh_base[mesh_index + 1] : H.mesh_tris) - first;
     if (n > 0 && (!v || !normals)) return fail(c, RT_E_INVALID, "rt_scene_update_mesh: bad arguments");
+    if ((rc = update_mark(c))) return rc;
     for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = aabb[k];
     if (!H.mesh_on_device && n > 0) {                                      // host copies feed the host SAH builder / multi-device upload
         std::memcpy(H.mesh_v.data() + 9 * (size_t)first, v, (size_t)n * 36);
@@ -339,6 +344,7 @@ int rt_scene_update_triangles(rt_ctx* c, int first, int n, const float* v, const
     RtHostScene& H = c->host;
     if (first < 0 || n < 0 || (int64_t)first + n > H.n_loose() || (n > 0 && (!v || !normals))) return fail(c, RT_E_INVALID, "rt_scene_update_triangles: bad range");
     if (n == 0) return RT_OK;
+    if ((rc = update_mark(c))) return rc;
     std::memcpy(H.loose_v.data() + 9 * (size_t)first, v, (size_t)n * 36);
     std::memcpy(H.loose_n.data() + 3 * (size_t)first, normals, (size_t)n * 12);
     return update_raw(c, 0, (int64_t)H.n_meshtris() + first, n, v, normals);
@@ -350,6 +356,7 @@ int rt_scene_update_spheres(rt_ctx* c, int first, int n, const float* center_r2)
     RtHostScene& H = c->host;
     if (first < 0 || n < 0 || (int64_t)first + n > H.n_spheres() || (n > 0 && !center_r2)) return fail(c, RT_E_INVALID, "rt_scene_update_spheres: bad range");
     if (n == 0) return RT_OK;
+    if ((rc = update_mark(c))) return rc;
     std::memcpy(H.spheres.data() + 4 * (size_t)first, center_r2, (size_t)n * 16);
     return update_raw(c, 1, first, n, center_r2, nullptr);
 }
@@ -358,6 +365,7 @@ int rt_scene_update_lights(rt_ctx* c, const float* pos_intensity, int n, const f
     int rc = update_prolog(c, "rt_scene_update_lights");
     if (rc) return rc;
     if (n < 0 || (n > 0 && !pos_intensity)) return fail(c, RT_E_INVALID, "rt_scene_update_lights: bad arguments");
+    if ((rc = update_mark(c))) return rc;
     c->host.lights.assign(pos_intensity, pos_intensity + 6 * (size_t)n);
     if (ambient) for (int k = 0; k < 3; ++k) c->host.ambient[k] = ambient[k];
     return RT_OK;
