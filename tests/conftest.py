@@ -53,3 +53,29 @@ def compare_renders(ref, got, check_float=True):
         a, b = ref["rgba32f"], got["rgba32f"]
         out["f32"] = int(((a != b) & ~(np.isnan(a) & np.isnan(b))).any(axis=1).sum())
     return out
+
+
+def degenerate_scene(scenes, nan=False):
+    """A soup plus the inputs the reference's scan takes without complaint: zero-area triangles, repeated primitives, a
+    sphere with r2 = 0, the camera inside a huge sphere, a triangle edge-on to the centre ray, coordinates near 1e19 and
+    (nan=True) NaN / infinite vertices and centres — whatever Scene.cs:43-122 answers for them is the required answer."""
+    s = scenes.random_soup(seed=21, n_tris=300, n_spheres=40)
+    m = scenes.material()
+    flat = np.array((0, 0, -1), np.float32)
+    for tri in ((1, 1, 12, 1, 1, 12, 1, 1, 12), (-5, 0, 15, 0, 0, 15, 5, 0, 15)):          # a point, a collinear triangle
+        s.add_triangle(np.array(tri, np.float32), flat, m)
+    t = np.array((-3, -3, 18, 3, -3, 18, 0, 3, 18), np.float32)
+    for _ in range(5):
+        s.add_triangle(t, scenes.triangle_normal(t)[0], m)
+    for _ in range(3):
+        s.add_sphere((4, 4, 22), 9.0, m)
+    s.add_sphere((0, 0, 10), 0.0, m)
+    s.add_sphere((0, 0, 0), 1e6, m)
+    t = np.array((0, -2, 5, 0, 2, 5, 0, 0, 30), np.float32)
+    s.add_triangle(t, scenes.triangle_normal(t)[0], m)
+    s.add_triangle(np.array((-1e18, -1e18, 1e19, 1e18, -1e18, 1e19, 0, 1e18, 1e19), np.float32), flat, m)
+    if nan:
+        s.add_triangle(np.array((np.nan, 0, 9, 1, 0, 9, 0, 1, 9), np.float32), flat, m)
+        s.add_triangle(np.array((np.inf, 0, 9, 1, 0, 9, 0, 1, 9), np.float32), flat, m)
+        s.add_sphere((np.nan, 0, 9), 1.0, m)
+    return s

@@ -277,3 +277,16 @@ def test_backfacing_light_shadow_skip_is_exact(emu, oracle, scenes, case):
     assert np.array_equal(ref["hit_id"], got["hit_id"])
     assert np.array_equal(ref["rgba32f"].view(np.uint32), got["rgba32f"].view(np.uint32))     # bit pattern: NaN and -0.0 included
     assert got["stats"]["rays_shadow"] == ref["stats"][1]                                      # skipped queries are still counted
+
+
+@pytest.mark.parametrize("nan", [False, True])
+def test_degenerate_geometry_matches_the_scan(emu, oracle, scenes, nan):
+    """conftest.degenerate_scene: both builders, leaf sizes 1 and 4, against the faithful scan."""
+    from conftest import degenerate_scene
+    s, p = degenerate_scene(scenes, nan), scenes.soup_params(64, 40, 2, 1)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    for builder in (0, 1):
+        for leaf_max in (1, 4):
+            e = emu.EmuTracer(leaf_max=leaf_max, builder=builder); e.set_scene(s)
+            cmp = compare_renders(ref, e.render(p))
+            assert cmp["id"] == 0 and cmp["t"] == 0 and cmp["u8_gt0"] == 0 and cmp["f32"] == 0, (builder, leaf_max, cmp)

@@ -170,6 +170,20 @@ def test_error_codes_leave_the_context_usable(rtb, scenes):
     r.close()
 
 
+def test_degenerate_geometry_matches_the_scan(rtb, scenes, oracle):
+    """conftest.degenerate_scene (zero-area / repeated / huge / NaN / infinite primitives, camera inside a sphere): device LBVH
+    and host SAH builder, packet and per-lane traversal, against the faithful scan."""
+    from conftest import degenerate_scene
+    for nan in (False, True):
+        s, p = degenerate_scene(scenes, nan), scenes.soup_params(96, 64, 2, 1)
+        ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+        for builder, packet in ((0, 1), (0, 0), (1, 1)):
+            r = rtb.RayTracer((0,)); r.set_option("builder", builder); r.set_option("packet", packet); r.set_scene(s)
+            got = r.render(p); r.close()
+            _check(compare_renders(ref, got))
+            assert (got["stats"]["rays_primary"], got["stats"]["rays_shadow"], got["stats"]["rays_mirror"]) == ref["stats"], (nan, builder, packet)
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)
