@@ -79,3 +79,21 @@ def degenerate_scene(scenes, nan=False):
         s.add_triangle(np.array((np.inf, 0, 9, 1, 0, 9, 0, 1, 9), np.float32), flat, m)
         s.add_sphere((np.nan, 0, 9), 1.0, m)
     return s
+
+
+def camera_set():
+    """CameraData as Unity hands it over (transform.position / forward / right / up, CameraData.cs:5-10): looking down every
+    axis, an oblique rotation off the origin, and a basis that is neither unit length nor orthogonal (the reference uses the
+    vectors as given, RayTracingSetup.cs:282-300)."""
+    def rot(axis, deg):
+        a = np.asarray(axis, np.float64); a /= np.linalg.norm(a)
+        c, s = np.cos(np.radians(deg)), np.sin(np.radians(deg))
+        K = np.array(((0, -a[2], a[1]), (a[2], 0, -a[0]), (-a[1], a[0], 0)))
+        return np.eye(3) * c + s * K + (1 - c) * np.outer(a, a)
+    cams = []
+    for R, pos in ((rot((0, 1, 0), 180), (0, 0, 60)), (rot((0, 1, 0), 90), (-60, 0, 20)), (rot((0, 1, 0), -90), (60, 0, 20)),
+                   (rot((1, 0, 0), 90), (0, 60, 20)), (rot((1, 0, 0), -90), (0, -60, 20)), (rot((1, 2, 3), 37), (7, -11, -25))):
+        R = R.astype(np.float32)
+        cams.append(dict(pos=tuple(np.float32(x) for x in pos), right=tuple(R[:, 0]), up=tuple(R[:, 1]), fwd=tuple(R[:, 2])))
+    cams.append(dict(pos=(3.0, -2.0, -30.0), fwd=(0.1, 0.05, 1.7), right=(0.8, 0.1, 0.0), up=(0.2, 1.3, -0.1)))
+    return cams

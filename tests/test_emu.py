@@ -290,3 +290,15 @@ def test_degenerate_geometry_matches_the_scan(emu, oracle, scenes, nan):
             e = emu.EmuTracer(leaf_max=leaf_max, builder=builder); e.set_scene(s)
             cmp = compare_renders(ref, e.render(p))
             assert cmp["id"] == 0 and cmp["t"] == 0 and cmp["u8_gt0"] == 0 and cmp["f32"] == 0, (builder, leaf_max, cmp)
+
+
+def test_cameras_off_axis(emu, oracle, scenes):
+    """conftest.camera_set: every view direction / octant and a sheared basis, soup with mirrors, against the faithful scan."""
+    from conftest import camera_set
+    s = scenes.random_soup(seed=4, n_tris=500, n_spheres=60)
+    e = emu.EmuTracer(); e.set_scene(s)
+    ora = oracle.OracleScene(s)
+    for i, cam in enumerate(camera_set()):
+        p = scenes.make_params(56, 40, 10.0, 8.0, 6.0, (0.1, 0.2, 0.3), 2, 1, cam=cam)
+        cmp = compare_renders(ora.render(p, oracle.FAITHFUL), e.render(p))
+        assert cmp["id"] == 0 and cmp["t"] == 0 and cmp["u8_gt0"] == 0 and cmp["f32"] == 0, (i, cmp)

@@ -184,6 +184,32 @@ def test_degenerate_geometry_matches_the_scan(rtb, scenes, oracle):
             assert (got["stats"]["rays_primary"], got["stats"]["rays_shadow"], got["stats"]["rays_mirror"]) == ref["stats"], (nan, builder, packet)
 
 
+def test_cameras_off_axis(rt, scenes, oracle):
+    """conftest.camera_set (every view axis, an oblique rotation, a sheared non-unit basis): a soup with mirrors against the
+    faithful scan, and the reduced config-3 mesh (packet traversal in every octant) against the accelerated oracle."""
+    from conftest import camera_set
+    s = scenes.random_soup(seed=4, n_tris=500, n_spheres=60)
+    ora = oracle.OracleScene(s)
+    rt.set_scene(s)
+    for i, cam in enumerate(camera_set()):
+        p = scenes.make_params(112, 80, 10.0, 8.0, 6.0, (0.1, 0.2, 0.3), 2, 1, cam=cam)
+        ref = ora.render(p, oracle.FAITHFUL)
+        got = rt.render(p)
+        _check(compare_renders(ref, got))
+        assert (got["stats"]["rays_primary"], got["stats"]["rays_shadow"], got["stats"]["rays_mirror"]) == ref["stats"], i
+    s = scenes.cfg3_scene(n=48)
+    ora = oracle.OracleScene(s)
+    rt.set_scene(s)
+    hits = 0
+    for i, cam in enumerate(camera_set()):
+        p = scenes.make_params(320, 180, 10.0, 8.0, 4.5, (0.1, 0.1, 0.2), 0, 1, cam=cam)
+        ref = ora.render(p, oracle.ACCELERATED)
+        got = rt.render(p)
+        _check(compare_renders(ref, got))
+        hits += int((got["hit_id"][:, 0] != 0).sum())
+    assert hits > 7 * 320 * 180 // 20                       # the views do look at the mesh
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)
