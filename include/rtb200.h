@@ -55,7 +55,7 @@ typedef struct {
     int32_t res_x, res_y;                    /* Resolution.X, .Y */
     float dist, half_h, half_v;              /* DistanceToCamera, HalfHorizontalLength, HalfVerticalLength */
     float background_rgb[3];                 /* 0..1; multiplied by 255 inside (Rgb.cs:15-18) */
-    int32_t max_reflection_bounces;          /* RTS:23 */
+    int32_t max_reflection_bounces;          /* RTS:23; above 64 in a scene that has mirror materials: RT_E_UNSUPPORTED */
     int32_t spp_grid;                        /* 1 = reference behaviour (one ray at the pixel centre, RTS:291-292);
                                                 g>1 = g*g stratified sample centres, averaged in fixed (j,i) order */
 } rt_render_params;                          /* 88 bytes */

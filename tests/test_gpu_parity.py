@@ -210,6 +210,38 @@ def test_cameras_off_axis(rt, scenes, oracle):
     assert hits > 7 * 320 * 180 // 20                       # the views do look at the mesh
 
 
+def test_deep_mirror_recursion(rtb, scenes, oracle):
+    """Two parallel mirror walls around the camera: the reflection chain (RayTracingSetup.cs:357-372) runs to the
+    bounce limit on most pixels.  Depths 30 and 64 against the faithful scan; 65 is refused (a clamp would change the
+    picture) unless the scene has no mirror material, where the depth cannot matter."""
+    s = scenes.SceneArrays()
+    mir = scenes.material(diffuse=(0.2, 0.1, 0.1), ambient=(0.1, 0.1, 0.1), mirror=(0.97, 0.95, 0.9), specular=(0.3, 0.3, 0.3), phong=8.0, is_mirror=1)
+    for z, side in ((20.0, 1.0), (-20.0, -1.0)):                             # two parallel mirror walls, 8000 x 8000
+        for tri in ((-4e3, -4e3, z, 4e3, -4e3, z, 4e3, 4e3, z), (-4e3, -4e3, z, 4e3, 4e3, z, -4e3, 4e3, z)):
+            s.add_triangle(np.array(tri, np.float32), np.array((0, 0, -side), np.float32), mir)
+    s.add_sphere((6, 2, 4), 2.0, scenes.material(diffuse=(0.8, 0.3, 0.2), ambient=(0.2, 0.2, 0.2), specular=(0.5, 0.5, 0.5), phong=20.0))
+    t = np.array((-9, -6, 2, -3, -6, 5, -6, 4, 3), np.float32)
+    s.add_triangle(t, scenes.triangle_normal(t)[0], scenes.material(diffuse=(0.2, 0.7, 0.3), ambient=(0.1, 0.1, 0.1)))
+    s.add_light((0, 8, 0), 3e3); s.add_light((5, -7, 1), 2e3); s.ambient[:] = (30, 30, 30)
+    ora = oracle.OracleScene(s)
+    r = rtb.RayTracer((0,)); r.set_scene(s)
+    for depth in (30, 64):
+        p = scenes.make_params(96, 64, 10.0, 8.0, 5.0, (0.05, 0.05, 0.1), depth, 1)
+        ref = ora.render(p, oracle.FAITHFUL)
+        got = r.render(p)
+        _check(compare_renders(ref, got))
+        assert (got["stats"]["rays_primary"], got["stats"]["rays_shadow"], got["stats"]["rays_mirror"]) == ref["stats"]
+        assert got["stats"]["rays_mirror"] > depth * 96 * 64 // 2            # the chains really are that long
+    with pytest.raises(rtb.host.RtError) as ei:
+        r.render(dict(p, max_reflection_bounces=65))
+    assert ei.value.code == -5 and "above 64" in str(ei.value)
+    plain = scenes.rt_unity()                                                # no mirror material: any depth is the same frame
+    r.set_scene(plain)
+    a = r.render(scenes.rt_unity_params(64, 40, 1000)); b = r.render(scenes.rt_unity_params(64, 40, 0))
+    assert np.array_equal(a["rgba32f"], b["rgba32f"])
+    r.close()
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)

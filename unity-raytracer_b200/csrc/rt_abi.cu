@@ -104,6 +104,9 @@ int validate_params(rt_ctx* c, const rt_render_params* p) {
     if (p->res_x < 0 || p->res_y < 0) return fail(c, RT_E_INVALID, "negative resolution");
     if ((int64_t)p->res_x * p->res_y > (int64_t)1 << 30) return fail(c, RT_E_UNSUPPORTED, "resolution above 2^30 pixels");
     if (p->spp_grid > 64) return fail(c, RT_E_INVALID, "spp_grid above 64");
+    // the reference recurses without a bound (RTS:357-372); a silent clamp would change the picture, so say so instead
+    if (p->max_reflection_bounces > RT_MAX_DEPTH && !c->devs.empty() && c->devs[0].has_mirror)
+        return fail(c, RT_E_UNSUPPORTED, "max_reflection_bounces above 64 in a scene with mirrors");
     return RT_OK;
 }
 
