@@ -242,6 +242,49 @@ def test_deep_mirror_recursion(rtb, scenes, oracle):
     r.close()
 
 
+def test_two_contexts_commit_and_render_concurrently(rtb, scenes, oracle):
+    """Contexts share no state: one host thread re-commits scenes into context B (alternating two different scenes) while
+    another renders context A and vice versa — the pipelined frame loop of bench.py's `frame_loop`.  Every frame must equal
+    the frame of its scene rendered alone."""
+    import threading
+    sa, sb = scenes.cfg3_scene(n=40), scenes.random_soup(seed=17, n_tris=3000, n_spheres=300)
+    pa, pb = scenes.cfg3_params(480, 270), scenes.soup_params(320, 200, 3, 1)
+    solo = rtb.RayTracer((0,))
+    want = {}
+    for key, (s, p) in (("a", (sa, pa)), ("b", (sb, pb))):
+        solo.set_scene(s); want[key] = solo.render(p)
+    solo.close()
+    _check(compare_renders(oracle.OracleScene(sb).render(pb, oracle.FAITHFUL), want["b"]))
+    ctx = [rtb.RayTracer((0,)), rtb.RayTracer((0,))]
+    frames = 12
+    ready = [threading.Semaphore(0), threading.Semaphore(0)]
+    free = [threading.Semaphore(1), threading.Semaphore(1)]
+    plan = [("a", sa, pa) if (k // 2) % 2 == 0 else ("b", sb, pb) for k in range(frames)]
+    errors = []
+
+    def committer():
+        try:
+            for k in range(frames):
+                free[k & 1].acquire(); ctx[k & 1].set_scene(plan[k][1]); ready[k & 1].release()
+        except Exception as e:                                      # noqa: BLE001
+            errors.append(e)
+            for sem in ready:
+                sem.release()
+    th = threading.Thread(target=committer); th.start()
+    for k in range(frames):
+        ready[k & 1].acquire()
+        if errors:
+            break
+        got = ctx[k & 1].render(plan[k][2])
+        free[k & 1].release()
+        for key in ("hit_id", "hit_t", "rgba8", "rgba32f"):
+            assert np.array_equal(want[plan[k][0]][key], got[key], equal_nan=True), (k, key)
+    th.join()
+    assert not errors, errors
+    for c in ctx:
+        c.close()
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)
