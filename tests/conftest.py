@@ -97,3 +97,26 @@ def camera_set():
         cams.append(dict(pos=tuple(np.float32(x) for x in pos), right=tuple(R[:, 0]), up=tuple(R[:, 1]), fwd=tuple(R[:, 2])))
     cams.append(dict(pos=(3.0, -2.0, -30.0), fwd=(0.1, 0.05, 1.7), right=(0.8, 0.1, 0.0), up=(0.2, 1.3, -0.1)))
     return cams
+
+
+def many_lights_scene(scenes, n_lights=40):
+    """a soup lit by n_lights point lights (RayTracingSetup.cs:333-355 loops over all of them)"""
+    s = scenes.random_soup(seed=13, n_tris=600, n_spheres=60)
+    rng = np.random.default_rng(2)
+    for _ in range(n_lights - s.lights.shape[0]):
+        s.add_light(tuple(rng.uniform(-45, 45, 3)), float(rng.uniform(2e3, 2e4)))
+    return s
+
+
+def mirror_walls_scene(scenes):
+    """two parallel 8000 x 8000 mirror walls around the camera: reflection chains (RayTracingSetup.cs:357-372) run to the limit"""
+    s = scenes.SceneArrays()
+    mir = scenes.material(diffuse=(0.2, 0.1, 0.1), ambient=(0.1, 0.1, 0.1), mirror=(0.97, 0.95, 0.9), specular=(0.3, 0.3, 0.3), phong=8.0, is_mirror=1)
+    for z, side in ((20.0, 1.0), (-20.0, -1.0)):
+        for tri in ((-4e3, -4e3, z, 4e3, -4e3, z, 4e3, 4e3, z), (-4e3, -4e3, z, 4e3, 4e3, z, -4e3, 4e3, z)):
+            s.add_triangle(np.array(tri, np.float32), np.array((0, 0, -side), np.float32), mir)
+    s.add_sphere((6, 2, 4), 2.0, scenes.material(diffuse=(0.8, 0.3, 0.2), ambient=(0.2, 0.2, 0.2), specular=(0.5, 0.5, 0.5), phong=20.0))
+    t = np.array((-9, -6, 2, -3, -6, 5, -6, 4, 3), np.float32)
+    s.add_triangle(t, scenes.triangle_normal(t)[0], scenes.material(diffuse=(0.2, 0.7, 0.3), ambient=(0.1, 0.1, 0.1)))
+    s.add_light((0, 8, 0), 3e3); s.add_light((5, -7, 1), 2e3); s.ambient[:] = (30, 30, 30)
+    return s

@@ -70,11 +70,9 @@ def test_many_lights_and_unfused_shading(rtb, scenes, oracle):
     """The light loop (RayTracingSetup.cs:333-355) beyond the fused kernel's 32-light limit: 40 lights go through the separate
     occlusion-mask + shading kernels, checked against the faithful scan; with 2 lights the unfused and the fused kernels,
     and backcull off, must give the fused frame bit for bit."""
-    s, p = scenes.random_soup(seed=13, n_tris=600, n_spheres=60), scenes.soup_params(80, 48, 2, 1)
-    rng = np.random.default_rng(2)
+    from conftest import many_lights_scene
+    s, p = many_lights_scene(scenes), scenes.soup_params(80, 48, 2, 1)
     two = scenes.random_soup(seed=13, n_tris=600, n_spheres=60)
-    for i in range(38):
-        s.add_light(tuple(rng.uniform(-45, 45, 3)), float(rng.uniform(2e3, 2e4)))
     assert s.lights.shape[0] == 40
     ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
     r = rtb.RayTracer((0,)); r.set_scene(s)
@@ -214,15 +212,8 @@ def test_deep_mirror_recursion(rtb, scenes, oracle):
     """Two parallel mirror walls around the camera: the reflection chain (RayTracingSetup.cs:357-372) runs to the
     bounce limit on most pixels.  Depths 30 and 64 against the faithful scan; 65 is refused (a clamp would change the
     picture) unless the scene has no mirror material, where the depth cannot matter."""
-    s = scenes.SceneArrays()
-    mir = scenes.material(diffuse=(0.2, 0.1, 0.1), ambient=(0.1, 0.1, 0.1), mirror=(0.97, 0.95, 0.9), specular=(0.3, 0.3, 0.3), phong=8.0, is_mirror=1)
-    for z, side in ((20.0, 1.0), (-20.0, -1.0)):                             # two parallel mirror walls, 8000 x 8000
-        for tri in ((-4e3, -4e3, z, 4e3, -4e3, z, 4e3, 4e3, z), (-4e3, -4e3, z, 4e3, 4e3, z, -4e3, 4e3, z)):
-            s.add_triangle(np.array(tri, np.float32), np.array((0, 0, -side), np.float32), mir)
-    s.add_sphere((6, 2, 4), 2.0, scenes.material(diffuse=(0.8, 0.3, 0.2), ambient=(0.2, 0.2, 0.2), specular=(0.5, 0.5, 0.5), phong=20.0))
-    t = np.array((-9, -6, 2, -3, -6, 5, -6, 4, 3), np.float32)
-    s.add_triangle(t, scenes.triangle_normal(t)[0], scenes.material(diffuse=(0.2, 0.7, 0.3), ambient=(0.1, 0.1, 0.1)))
-    s.add_light((0, 8, 0), 3e3); s.add_light((5, -7, 1), 2e3); s.ambient[:] = (30, 30, 30)
+    from conftest import mirror_walls_scene
+    s = mirror_walls_scene(scenes)
     ora = oracle.OracleScene(s)
     r = rtb.RayTracer((0,)); r.set_scene(s)
     for depth in (30, 64):

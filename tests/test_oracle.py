@@ -138,7 +138,8 @@ def test_inline_invariants(oracle, scenes):
         assert abs(float(d[0]) ** 2 + float(d[1]) ** 2 + float(d[2]) ** 2 - 1.0) < 1e-5
 
 
-@pytest.mark.parametrize("name", ["cfg1_rt_unity_50x50", "cfg2_mirror_96x54_d4", "soup7_64x48_d3", "soup3_48x32_d2_spp2"])
+@pytest.mark.parametrize("name", ["cfg1_rt_unity_50x50", "cfg2_mirror_96x54_d4", "soup7_64x48_d3", "soup3_48x32_d2_spp2", "degenerate_nan_64x40_d2",
+                                  "soup4_oblique_camera_56x40_d2", "soup4_sheared_camera_56x40_d2", "soup13_40_lights_48x32_d2", "mirror_walls_48x32_d64"])
 def test_golden_fixtures(oracle, scenes, name):
     """Frozen oracle outputs (tests/golden/make_golden.py).  u8/ids/t bit-exact; float colour bit-exact too (same libm)."""
     from golden import make_golden as G
