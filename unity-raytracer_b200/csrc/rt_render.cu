@@ -10,6 +10,9 @@
 // All traversal kernels are persistent: 148 x k resident CTAs fetch 32-item batches (one 8x4 pixel tile = one warp) from
 // a global counter; the traversal stack lives in shared memory, strided so a warp's accesses are conflict-free.
 // Compiled with -fmad=false: see rt_hd.h.
+#include <mutex>
+#include <utility>
+#include <vector>
 #include "rt_internal.h"
 #include "rt_packet.cuh"
 
@@ -418,15 +421,23 @@ __global__ void k_prefetch_l2(const char* __restrict__ a, size_t na, const char*
     for (size_t o = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 128u; o < nb; o += stride) asm volatile("prefetch.global.L2 [%0];" ::"l"(b + o));
 }
 
-// resident CTAs per SM of a persistent kernel (occupancy query, cached per kernel: the query costs ~10 us of host time and
-// a frame on a 1/8 partition lasts only 0.5 ms)
+// resident CTAs per SM of a persistent kernel (occupancy query, cached per kernel FUNCTION — instantiations of one template
+// share their pointer type, so the key is the pointer, not K; the query costs ~10 us of host time and a frame on a 1/8
+// partition lasts only 0.5 ms).  Contexts on different host threads may get here at once.
 template <class K>
 int persistent_grid(K kernel, int block, size_t smem, int sm_count, int ctas_per_sm) {
-    static int cached = 0;                                    // one instance of this template per kernel
-    if (cached < 1) {
-        int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
-        cached = per_sm;
+    static std::mutex mu;
+    static std::vector<std::pair<const void*, int>> seen;
+    int cached = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        for (auto& e : seen) if (e.first == (const void*)kernel) cached = e.second;
+        if (cached < 1) {
+            int per_sm = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+            cached = per_sm;
+            seen.emplace_back((const void*)kernel, cached);
+        }
     }
     int per_sm = cached;
     if (ctas_per_sm > 0 && ctas_per_sm < per_sm) per_sm = ctas_per_sm;
