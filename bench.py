@@ -408,7 +408,7 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
-def frame_loop(rtb, scene, params, dev, frames=10):
+def frame_loop(rtb, scene, params, dev, frames=30):
     """The reference's Update() is UpdateScene() then CastPixelRays() (RayTracingSetup.cs:171-199): whole scene re-sent from
     pageable host arrays, frame returned in host memory (RGBA32F).  (a) one context, back to back; (b) two contexts on the
     same GPU, scene k+1 committed by a second host thread while frame k renders (one frame of latency for the caller)."""

@@ -11,7 +11,19 @@ frames = int(sys.argv[2]) if len(sys.argv) > 2 else 12
 s = {"cfg3": sc.cfg3_scene, "cfg4": sc.cfg4_scene, "cfg5": sc.cfg5_scene}[cfg]()
 p = {"cfg3": sc.cfg3_params, "cfg4": sc.cfg4_params, "cfg5": sc.cfg5_params}[cfg]()
 want = H.RT_OUT_RGBA32F
+opts = dict(a.split("=") for a in sys.argv[3:])
+pinned = int(opts.pop("pinned", 0))
+if pinned:                                                    # caller arrays page-locked (a shim that keeps NativeArrays pinned)
+    import torch
+    def pin(a):
+        tt = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+        keep.append(tt)
+        return tt.numpy()
+    keep = []
+    s.meshes = [(pin(v), pin(n), m, ab) for (v, n, m, ab) in s.meshes]
 ctx = [rtb.RayTracer((0,)), rtb.RayTracer((0,))]
+for c in ctx:
+    for k, v in opts.items(): c.set_option(k, float(v))
 outs = [rtb.RayTracer.alloc_host_outputs(p, want, pinned=True) for _ in range(2)]
 for c, o in zip(ctx, outs):
     c.set_scene(s); c.render(p, want, out=o); c.render(p, want, out=o)
@@ -22,6 +34,13 @@ for k in range(frames):
     ctx[0].set_scene(s); ctx[0].render(p, want, out=outs[0])
 seq = (time.perf_counter() - t0) / frames
 assert np.array_equal(ref, outs[0]["rgba32f"], equal_nan=True)
+t0 = time.perf_counter()
+for k in range(frames): ctx[0].set_scene(s)
+only_commit = (time.perf_counter() - t0) / frames
+t0 = time.perf_counter()
+for k in range(frames): ctx[0].render(p, want, out=outs[0])
+only_render = (time.perf_counter() - t0) / frames
+print(f"{cfg}: commit alone {1e3*only_commit:.2f} ms, render alone {1e3*only_render:.2f} ms", flush=True)
 # (b) two contexts: commit of scene k+1 on a second thread while frame k renders
 ready = [threading.Semaphore(0), threading.Semaphore(0)]      # scene committed into ctx[i]
 free = [threading.Semaphore(1), threading.Semaphore(1)]       # ctx[i] rendered, may take the next scene
