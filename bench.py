@@ -409,38 +409,53 @@ def run_ours(args, rank, world, local_rank):
 
 
 def frame_loop(rtb, scene, params, dev, frames=30):
-    """The reference's Update() is UpdateScene() then CastPixelRays() (RayTracingSetup.cs:171-199): whole scene re-sent from
-    pageable host arrays, frame returned in host memory (RGBA32F).  (a) one context, back to back; (b) two contexts on the
-    same GPU, scene k+1 committed by a second host thread while frame k renders (one frame of latency for the caller)."""
+    """The reference's Update() is UpdateScene() then CastPixelRays() (RayTracingSetup.cs:171-199): scene re-sent from pageable
+    host arrays, frame returned in host memory (RGBA32F).  Two ways to re-send: "full" = rt_scene_begin .. rt_scene_commit
+    (device LBVH rebuilt), "refit" = rt_scene_update_mesh of every mesh + rt_scene_refit (host-built SAH tree kept).  Each
+    (a) on one context, back to back, and (b) on two contexts of the same GPU, scene k+1 sent by a second host thread while
+    frame k renders (one frame of latency for the caller)."""
     import threading
     want = rtb.host.RT_OUT_RGBA32F
-    ctx = [rtb.RayTracer((dev,)), rtb.RayTracer((dev,))]
-    outs = [rtb.RayTracer.alloc_host_outputs(params, want, pinned=True) for _ in range(2)]
-    for c, o in zip(ctx, outs):
-        c.set_scene(scene); c.render(params, want, out=o); c.render(params, want, out=o)
-    ref = outs[0]["rgba32f"].copy()
-    t0 = time.perf_counter()
-    for _ in range(frames):
-        ctx[0].set_scene(scene); ctx[0].render(params, want, out=outs[0])
-    seq = (time.perf_counter() - t0) / frames
-    ready = [threading.Semaphore(0), threading.Semaphore(0)]
-    free = [threading.Semaphore(1), threading.Semaphore(1)]
+    res = {"frames": frames,
+           "what": "wall ms per frame of scene re-send (pageable arrays) + rt_render (host RGBA32F out); pipelined = scene k+1 sent "
+                   "into a second context by a second host thread while frame k renders"}
+    for mode in ("full", "refit"):
+        ctx = [rtb.RayTracer((dev,)), rtb.RayTracer((dev,))]
+        outs = [rtb.RayTracer.alloc_host_outputs(params, want, pinned=True) for _ in range(2)]
 
-    def committer():
+        def send(c):
+            if mode == "full":
+                c.set_scene(scene)
+            else:
+                for i, (v, n, _m, ab) in enumerate(scene.meshes):
+                    c.update_mesh(i, v, n, ab)
+                c.refit()
+        for c, o in zip(ctx, outs):
+            if mode == "refit":
+                c.set_option("builder", 1)
+            c.set_scene(scene); c.render(params, want, out=o); c.render(params, want, out=o)
+        ref = outs[0]["rgba32f"].copy()
+        t0 = time.perf_counter()
+        for _ in range(frames):
+            send(ctx[0]); ctx[0].render(params, want, out=outs[0])
+        seq = (time.perf_counter() - t0) / frames
+        ready = [threading.Semaphore(0), threading.Semaphore(0)]
+        free = [threading.Semaphore(1), threading.Semaphore(1)]
+
+        def sender():
+            for k in range(frames):
+                free[k & 1].acquire(); send(ctx[k & 1]); ready[k & 1].release()
+        th = threading.Thread(target=sender)
+        t0 = time.perf_counter(); th.start()
         for k in range(frames):
-            free[k & 1].acquire(); ctx[k & 1].set_scene(scene); ready[k & 1].release()
-    th = threading.Thread(target=committer)
-    t0 = time.perf_counter(); th.start()
-    for k in range(frames):
-        ready[k & 1].acquire(); ctx[k & 1].render(params, want, out=outs[k & 1]); free[k & 1].release()
-    th.join()
-    pipe = (time.perf_counter() - t0) / frames
-    same = bool(np.array_equal(ref, outs[0]["rgba32f"], equal_nan=True) and np.array_equal(ref, outs[1]["rgba32f"], equal_nan=True))
-    for c in ctx:
-        c.close()
-    return {"one_context_commit_then_render_ms": 1e3 * seq, "two_contexts_pipelined_ms": 1e3 * pipe, "frames_identical": same, "frames": frames,
-            "what": "wall ms per frame of commit (whole scene, pageable arrays) + rt_render (host RGBA32F out); pipelined = scene k+1 "
-                    "committed into a second context by a second host thread while frame k renders"}
+            ready[k & 1].acquire(); ctx[k & 1].render(params, want, out=outs[k & 1]); free[k & 1].release()
+        th.join()
+        pipe = (time.perf_counter() - t0) / frames
+        same = bool(np.array_equal(ref, outs[0]["rgba32f"], equal_nan=True) and np.array_equal(ref, outs[1]["rgba32f"], equal_nan=True))
+        for c in ctx:
+            c.close()
+        res[mode] = {"one_context_ms": 1e3 * seq, "two_contexts_pipelined_ms": 1e3 * pipe, "frames_identical": same}
+    return res
 
 
 def main():

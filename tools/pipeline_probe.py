@@ -13,6 +13,7 @@ p = {"cfg3": sc.cfg3_params, "cfg4": sc.cfg4_params, "cfg5": sc.cfg5_params}[cfg
 want = H.RT_OUT_RGBA32F
 opts = dict(a.split("=") for a in sys.argv[3:])
 pinned = int(opts.pop("pinned", 0))
+refit = int(opts.pop("refit", 0))                             # 1: per-frame update = rt_scene_update_mesh of every mesh + rt_scene_refit (tree kept)
 if pinned:                                                    # caller arrays page-locked (a shim that keeps NativeArrays pinned)
     import torch
     def pin(a):
@@ -25,17 +26,24 @@ ctx = [rtb.RayTracer((0,)), rtb.RayTracer((0,))]
 for c in ctx:
     for k, v in opts.items(): c.set_option(k, float(v))
 outs = [rtb.RayTracer.alloc_host_outputs(p, want, pinned=True) for _ in range(2)]
+def commit(c):
+    if not refit:
+        c.set_scene(s)
+        return
+    for i, (v, n, m, ab) in enumerate(s.meshes):
+        c.update_mesh(i, v, n, ab)
+    c.refit()
 for c, o in zip(ctx, outs):
     c.set_scene(s); c.render(p, want, out=o); c.render(p, want, out=o)
 ref = outs[0]["rgba32f"].copy()
 # (a) one context, back to back
 t0 = time.perf_counter()
 for k in range(frames):
-    ctx[0].set_scene(s); ctx[0].render(p, want, out=outs[0])
+    commit(ctx[0]); ctx[0].render(p, want, out=outs[0])
 seq = (time.perf_counter() - t0) / frames
 assert np.array_equal(ref, outs[0]["rgba32f"], equal_nan=True)
 t0 = time.perf_counter()
-for k in range(frames): ctx[0].set_scene(s)
+for k in range(frames): commit(ctx[0])
 only_commit = (time.perf_counter() - t0) / frames
 t0 = time.perf_counter()
 for k in range(frames): ctx[0].render(p, want, out=outs[0])
@@ -47,7 +55,7 @@ free = [threading.Semaphore(1), threading.Semaphore(1)]       # ctx[i] rendered,
 def committer():
     for k in range(frames):
         i = k & 1
-        free[i].acquire(); ctx[i].set_scene(s); ready[i].release()
+        free[i].acquire(); commit(ctx[i]); ready[i].release()
 th = threading.Thread(target=committer)
 t0 = time.perf_counter(); th.start()
 ok = True

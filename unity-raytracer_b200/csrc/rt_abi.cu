@@ -281,6 +281,18 @@ int rt_scene_lights(rt_ctx* c, const float* pos_intensity, int n, const float am
 }
 
 static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, bool refit = false) {
+    if (c->host.mesh_stale && !refit && c->opt.builder == 1 && !c->host.mesh_on_device) {   // host rebuild after device-only mesh updates
+        RtDevice& D = c->devs[0];
+        std::string& err = c->err;
+        const size_t n_mt = (size_t)c->host.n_meshtris();
+        if (c->host.mesh_v.size() < 9 * n_mt || c->host.mesh_n.size() < 3 * n_mt || D.raw_v.bytes < n_mt * 36 || D.raw_n.bytes < n_mt * 12)
+            return fail(c, RT_E_STATE, "mesh arrays of the committed scene are gone");
+        RT_CUDA(cudaSetDevice(D.device));
+        RT_CUDA(cudaMemcpyAsync(c->host.mesh_v.data(), D.raw_v.p, n_mt * 36, cudaMemcpyDeviceToHost, D.stream));
+        RT_CUDA(cudaMemcpyAsync(c->host.mesh_n.data(), D.raw_n.p, n_mt * 12, cudaMemcpyDeviceToHost, D.stream));
+        RT_CUDA(cudaStreamSynchronize(D.stream));
+        c->host.mesh_stale = false;
+    }
     if (scene_aabb) for (int k = 0; k < 6; ++k) c->host.aabb[k] = scene_aabb[k];
     else c->host.calc_aabb();
     float up = 0.f, bd = 0.f; uint64_t bytes = 0;
@@ -334,10 +346,9 @@ int rt_scene_update_mesh(rt_ctx* c, int mesh_index, const float* v, const float*
     if (n > 0 && (!v || !normals)) return fail(c, RT_E_INVALID, "rt_scene_update_mesh: bad arguments");
     if ((rc = update_mark(c))) return rc;
     for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = aabb[k];
-    if (!H.mesh_on_device && n > 0) {                                      // host copies feed the host SAH builder / multi-device upload
-        std::memcpy(H.mesh_v.data() + 9 * (size_t)first, v, (size_t)n * 36);
-        std::memcpy(H.mesh_n.data() + 3 * (size_t)first, normals, (size_t)n * 12);
-    }
+    // the host copies feed the host SAH builder only; keeping them current would cost a second pass over the caller's arrays
+    // on every update (host memory bandwidth is what binds an update), so they are refreshed from the device when needed
+    if (!H.mesh_on_device && n > 0) H.mesh_stale = true;
     return update_raw(c, 0, first, n, v, normals);
 }
 

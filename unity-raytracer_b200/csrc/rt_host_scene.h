@@ -27,6 +27,9 @@ struct RtHostScene {
     // Streaming commit (single device, device-built BVH): rt_scene_mesh copies the caller's arrays straight into the device's
     // raw buffers and mesh_v / mesh_n stay empty — nothing on the host needs the mesh vertices (the mesh AABB is the caller's).
     bool mesh_on_device = false;
+    // rt_scene_update_mesh sends new vertices to the devices only; mesh_v / mesh_n (read by the host SAH builder alone) are
+    // then out of date and are fetched back from device 0 if a host rebuild ever needs them (rt_abi.cu commit_impl)
+    bool mesh_stale = false;
     int64_t mesh_tris = 0;                      // mesh triangles so far (== mesh_v.size() / 9 when staged on the host)
     int builder = 0;                            // RtOptions::builder latched at rt_scene_begin
 
@@ -37,7 +40,7 @@ struct RtHostScene {
         loose_v.clear(); loose_n.clear(); loose_mats.clear(); lights.clear();
         for (int k = 0; k < 3; ++k) ambient[k] = 0.f;
         for (int k = 0; k < 6; ++k) aabb[k] = 0.f;
-        has_mirror = false; mesh_on_device = false; mesh_tris = 0; builder = 0;
+        has_mirror = false; mesh_on_device = false; mesh_stale = false; mesh_tris = 0; builder = 0;
     }
     int32_t n_meshes() const { return (int32_t)mesh_mats.size(); }
     int32_t n_meshtris() const { return (int32_t)mesh_tris; }
