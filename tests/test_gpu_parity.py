@@ -473,6 +473,14 @@ def test_in_process_multi_device_equals_single(rtb, scenes):
     b3 = two.render(p); two.close()
     for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
         assert np.array_equal(a[k], b3[k], equal_nan=True), k
+    # host SAH builder on two devices: mesh updates go to the devices only, the host rebuild fetches the vertices back
+    two = rtb.RayTracer((0, 1)); two.set_option("builder", 1); two.set_partition(0, 1, 8); two.set_scene(s)
+    two.update_spheres(0, s2.spheres); two.update_triangles(0, s2.tris, s2.tri_normals)
+    two.update_mesh(0, s2.meshes[0][0], s2.meshes[0][1], s2.meshes[0][3]); two.update_lights(s2.lights, s2.ambient)
+    two.refit(); b4 = two.render(p)
+    two.recommit(); b5 = two.render(p); two.close()
+    for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(a2[k], b4[k], equal_nan=True) and np.array_equal(a2[k], b5[k], equal_nan=True), k
 
 
 def test_render_full_size_properties(rt, scenes):
