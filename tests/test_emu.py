@@ -302,3 +302,18 @@ def test_cameras_off_axis(emu, oracle, scenes):
         p = scenes.make_params(56, 40, 10.0, 8.0, 6.0, (0.1, 0.2, 0.3), 2, 1, cam=cam)
         cmp = compare_renders(ora.render(p, oracle.FAITHFUL), e.render(p))
         assert cmp["id"] == 0 and cmp["t"] == 0 and cmp["u8_gt0"] == 0 and cmp["f32"] == 0, (i, cmp)
+
+
+def test_golden_fixtures_in_the_emulator(emu, scenes):
+    """every committed golden vector (tests/golden/*.npz, edge cases included) through the device headers compiled for the CPU:
+    ids and t bit-exact, u8 within 1 LSB — the check the GPU suite runs (test_golden_fixtures_on_gpu), without a GPU."""
+    import os
+    from golden import make_golden as G
+    for name, mk in G.CASES.items():
+        s, p = mk(scenes)
+        g = np.load(os.path.join(os.path.dirname(os.path.abspath(G.__file__)), name + ".npz"))
+        e = emu.EmuTracer(); e.set_scene(s)
+        got = e.render(p)
+        assert np.array_equal(got["hit_id"][:, :2], g["hit_id"][:, :2]), name
+        assert np.array_equal(got["hit_t"], g["hit_t"]), name
+        assert np.abs(got["rgba8"].astype(int) - g["rgba8"].astype(int)).max() <= 1, name
