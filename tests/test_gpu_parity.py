@@ -276,6 +276,33 @@ def test_two_contexts_commit_and_render_concurrently(rtb, scenes, oracle):
         c.close()
 
 
+def test_pipelined_driver_returns_the_previous_scene(rtb, scenes):
+    """PipelinedRayTracingSetup.Update(scene k, cam): frame of scene k-1 (scene 0 on the first call) while scene k is being
+    committed on the worker thread; Flush() shows the last one.  Each frame equals that scene rendered alone."""
+    seq = [scenes.rt_unity(mirror_sphere=True), scenes.random_soup(seed=17, n_tris=3000, n_spheres=300), scenes.cfg3_scene(n=32),
+           scenes.rt_unity(), scenes.random_soup(seed=18, n_tris=500, n_spheres=50)]
+    p = scenes.make_params(240, 136, 10.0, 16.0, 9.0, (0.1, 0.1, 0.2), 3, 1)
+    cam = rtb.CameraData(p["pos"], p["fwd"], p["right"], p["up"])
+
+    def configure(d):
+        d.ImagePlane = rtb.ImagePlane(rtb.Resolution(240, 136), p["dist"], p["half_h"], p["half_v"])
+        d.BackgroundColor, d.MaxReflectionBounces = tuple(p["background_rgb"]), 3
+    solo = rtb.RayTracingSetup((0,)); configure(solo)
+    want = []
+    for s in seq:
+        solo.UpdateScene(s); want.append(solo.CastPixelRays(cam).copy())
+    solo.close()
+    assert not np.array_equal(want[0], want[1])
+    pipe = rtb.PipelinedRayTracingSetup((0,)); configure(pipe)
+    for rep in range(2):                                     # second round: both contexts re-committed with other scenes
+        for k, s in enumerate(seq):
+            got = pipe.Update(s, cam)
+            shown = 0 if (rep == 0 and k == 0) else (k - 1) % len(seq)
+            assert np.array_equal(got, want[shown], equal_nan=True), (rep, k)
+    assert np.array_equal(pipe.Flush(cam), want[-1], equal_nan=True)
+    pipe.close()
+
+
 def test_intersect_random_rays(rt, scenes, oracle):
     s = scenes.random_soup(seed=11)
     rng = np.random.default_rng(5)

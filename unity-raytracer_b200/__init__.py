@@ -9,5 +9,5 @@ the mirror of the reference's RayTracingSetup interface), scenes.py (the referen
 """
 from . import scenes            # noqa: F401
 from . import host              # noqa: F401
-from .host import RayTracer, RayTracingSetup, CameraData, ImagePlane, Resolution, load_library, LIB_PATH  # noqa: F401
+from .host import RayTracer, RayTracingSetup, PipelinedRayTracingSetup, CameraData, ImagePlane, Resolution, load_library, LIB_PATH  # noqa: F401
 from .build import build        # noqa: F401

@@ -338,3 +338,72 @@ class RayTracingSetup:
         out = self._rt.render(self.params(cameraData), RT_OUT_RGBA32F)
         self.PixelColors = out["rgba32f"]
         return self.PixelColors
+
+    def close(self):
+        self._rt.close()
+
+
+class PipelinedRayTracingSetup(RayTracingSetup):
+    """RayTracingSetup.Update() (RayTracingSetup.cs:171-199) for callers that accept ONE frame of latency: two contexts on the
+    same devices; Update(scene, cam) hands `scene` to a worker thread that commits it into the idle context while this thread
+    renders the scene handed over by the previous Update with `cam`.  The first Update has nothing older to show, so it
+    commits and renders `scene` itself.  Contexts share no state (include/rtb200.h, conventions), so the two calls overlap:
+    the host-bound upload runs under the device-bound frame (bench.py `frame_loop`)."""
+
+    def __init__(self, devices=(0,)):
+        import threading
+        super().__init__(devices)
+        self._ctx = [self._rt, RayTracer(devices)]
+        self._front = None                      # index of the context holding the newest committed scene
+        self._pending = None                    # (thread, index, error list) of the commit in flight
+        self._threading = threading
+
+    def set_option(self, key, value):
+        for c in self._ctx:
+            c.set_option(key, value)
+
+    def _join(self):
+        if self._pending is not None:
+            th, idx, err = self._pending
+            th.join()
+            self._pending = None
+            if err:
+                raise err[0]
+            self._front = idx
+
+    def Update(self, scene_arrays, cameraData):
+        self._join()
+        if self._front is None:                 # first frame: nothing to overlap with
+            self._ctx[0].set_scene(scene_arrays)
+            self._front = 0
+            self.Scene = scene_arrays
+        else:
+            idx, err = 1 - self._front, []
+
+            def work(c=self._ctx[idx], s=scene_arrays, e=err):
+                try:
+                    c.set_scene(s)
+                except Exception as ex:         # noqa: BLE001 - re-raised on the caller's thread by _join
+                    e.append(ex)
+            th = self._threading.Thread(target=work)
+            th.start()
+            self._pending = (th, idx, err)
+        out = self._ctx[self._front].render(self.params(cameraData), RT_OUT_RGBA32F)
+        self.PixelColors = out["rgba32f"]
+        if self._pending is not None:
+            self.Scene = scene_arrays
+        return self.PixelColors
+
+    def Flush(self, cameraData):
+        """renders the scene handed over by the last Update (ends the one-frame latency, e.g. before a screenshot)"""
+        self._join()
+        out = self._ctx[self._front].render(self.params(cameraData), RT_OUT_RGBA32F)
+        self.PixelColors = out["rgba32f"]
+        return self.PixelColors
+
+    def close(self):
+        try:
+            self._join()
+        finally:
+            for c in self._ctx:
+                c.close()
