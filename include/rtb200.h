@@ -81,8 +81,11 @@ enum { RT_K_TRACE_PRIMARY = 0, RT_K_SHADE_PRIMARY = 1, RT_K_TRACE_QUEUE = 2, RT_
        RT_K_SHADOW_PRIMARY = 6, RT_K_SHADOW_QUEUE = 7, RT_K_COUNT = 8 };
 
 /* ---- lifetime ---------------------------------------------------------------------------------------------- */
-/* n_devices in {1,2,4,8}: in-process multi-GPU (screen-space row bands interleaved over the devices, scene replicated,
- * framebuffer bands written straight into device_ids[0]'s buffers over NVLink peer mappings). */
+/* n_devices in 1..16 (one box: typically 1, 2, 4 or 8); device_ids NULL = devices 0..n_devices-1.  n_devices > 1 is in-process
+ * multi-GPU: screen-space row bands interleaved over the devices (any count works, the band owner is band % n_devices), scene
+ * replicated.  rt_render_device gathers the frame on device_ids[0] (every device stores its bands straight into that device's
+ * buffers over NVLink peer mappings); rt_render copies every device's bands to the caller's host arrays over that device's own
+ * PCIe link.  Devices that cannot reach device_ids[0] as a peer: RT_E_UNSUPPORTED. */
 int rt_create(rt_ctx** out, const int* device_ids, int n_devices);
 void rt_destroy(rt_ctx* ctx);
 const char* rt_last_error(const rt_ctx* ctx);        /* valid until the next call on the same ctx; ctx may be NULL */

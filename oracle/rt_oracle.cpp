@@ -222,8 +222,22 @@ struct Scene {
         int type, index, mesh; key_decode(key, type, index, mesh);
         AABB b;
         if (type == T_SPHERE) {
+            // RaySphereIntersection (RMath.cs:81-108) computes disc = uoc*uoc - (lengthsq(oc) - r2) in binary32: two numbers of
+            // size |oc|^2 cancel down to ~r2, so `disc < 0 -> miss` accepts rays that pass the centre at up to
+            // sqrt(r2 + ~23 * 2^-24 * |oc|^2) (measured: 9.5 * 2^-24; a sphere of radius 0.1 seen from 100 away is "hit" out to
+            // 1.21 r).  That is the reference's answer, so the box must hold those rays: r_box^2 = r2 + 2^-19 * Rmax^2, Rmax =
+            // distance from the centre to the farthest corner of the box all ray origins lie in (obox).
             const Sph& s = spheres[index];
-            float r = std::sqrt(s.r2) * 1.0001f + 1e-6f;
+            double rr = (double)s.r2;
+            if (obox_valid) {
+                double m2 = 0.0;
+                for (int k = 0; k < 3; ++k) {
+                    double d = std::fmax(std::fabs((double)idx(s.c, k) - idx(obox.mn, k)), std::fabs((double)idx(s.c, k) - idx(obox.mx, k)));
+                    m2 += d * d;
+                }
+                rr += std::ldexp(m2, -19);
+            }
+            float r = (rr >= 0.0 && rr < 1e37) ? (float)std::sqrt(rr) * 1.0001f + 1e-6f : std::sqrt(s.r2) * 1.0001f + 1e-6f;
             b.mn = s.c - bc(r); b.mx = s.c + bc(r);
         } else {
             const Tri& t = (type == T_MESHTRI) ? meshes[mesh].tris[index] : tris[index];
@@ -236,12 +250,53 @@ struct Scene {
     }
 
     float pad = 0.f;
+    // box of every ray origin the BVH must serve: the primitive bounds (shadow / mirror rays start on surfaces) united with
+    // the explicit origins (camera, ora_intersect rays) seen so far; see prim_box
+    AABB obox{bc(0.f), bc(0.f)}; bool obox_valid = false;
+    AABB extra{bc(0.f), bc(0.f)}; bool extra_valid = false;
+
+    bool origin_covered(const f3& o) const {
+        if (spheres.empty() || !bvh_built) return true;
+        for (int k = 0; k < 3; ++k) {
+            float v = idx(o, k);
+            if (!std::isfinite(v)) return true;                   // nothing to cover: such a ray hits nothing
+            if (v < idx(obox.mn, k) || v > idx(obox.mx, k)) return false;
+        }
+        return true;
+    }
+    // makes the accelerated mode valid for rays starting at o (rebuilds the BVH when the sphere boxes were too small for it)
+    void cover_origin(const f3& o) {
+        if (origin_covered(o)) return;
+        if (!extra_valid) { extra.mn = o; extra.mx = o; extra_valid = true; }
+        extra.mn = mk(std::fmin(extra.mn.x, o.x), std::fmin(extra.mn.y, o.y), std::fmin(extra.mn.z, o.z));
+        extra.mx = mk(std::fmax(extra.mx.x, o.x), std::fmax(extra.mx.y, o.y), std::fmax(extra.mx.z, o.z));
+        build_bvh();
+    }
 
     void build_bvh() {
         mesh_base.clear(); n_meshtris = 0;
         for (auto& m : meshes) { mesh_base.push_back(n_meshtris); n_meshtris += (uint32_t)m.tris.size(); }
         mesh_base.push_back(n_meshtris);
         uint32_t n = n_prims();
+        {   // origin box = un-inflated bounds of everything (+ margin) united with the explicit origins
+            obox_valid = false;
+            AABB b{bc(FLT_MAX), bc(-FLT_MAX)};
+            for (uint32_t i = 0; i < n; ++i) {
+                AABB pb = prim_box(i);
+                b.mn = mk(std::fmin(b.mn.x, pb.mn.x), std::fmin(b.mn.y, pb.mn.y), std::fmin(b.mn.z, pb.mn.z));
+                b.mx = mk(std::fmax(b.mx.x, pb.mx.x), std::fmax(b.mx.y, pb.mx.y), std::fmax(b.mx.z, pb.mx.z));
+            }
+            if (extra_valid) {
+                b.mn = mk(std::fmin(b.mn.x, extra.mn.x), std::fmin(b.mn.y, extra.mn.y), std::fmin(b.mn.z, extra.mn.z));
+                b.mx = mk(std::fmax(b.mx.x, extra.mx.x), std::fmax(b.mx.y, extra.mx.y), std::fmax(b.mx.z, extra.mx.z));
+            }
+            float am = 0.f;
+            for (int k = 0; k < 3; ++k) { if (std::isfinite(idx(b.mn, k))) am = std::fmax(am, std::fabs(idx(b.mn, k))); if (std::isfinite(idx(b.mx, k))) am = std::fmax(am, std::fabs(idx(b.mx, k))); }
+            const float m = 1e-2f * (1.f + am), L = 1e18f;
+            auto cl = [&](float v) { return std::fmin(std::fmax(v, -L), L); };
+            obox.mn = mk(cl(b.mn.x - m), cl(b.mn.y - m), cl(b.mn.z - m)); obox.mx = mk(cl(b.mx.x + m), cl(b.mx.y + m), cl(b.mx.z + m));
+            obox_valid = n > 0 && obox.mn.x <= obox.mx.x && obox.mn.y <= obox.mx.y && obox.mn.z <= obox.mx.z;
+        }
         order.resize(n);
         std::vector<AABB> boxes(n);
         std::vector<f3> cent(n);
@@ -297,11 +352,13 @@ struct Scene {
     }
 
     // conservative slab test for BVH nodes: returns entry distance, or +inf when missed.
-    static inline float node_entry(const f3& o, const f3& inv, const AABB& b, float tbest) {
+    // dl: every plane moved outward by this much for this ray — the rounding of (plane - o) and of the reference's own
+    // fl(O - v0) grows with |o|, a fixed padding does not (a camera 1e4 scene extents away; rt_core.h rt_far_pad)
+    static inline float node_entry(const f3& o, const f3& inv, const AABB& b, float tbest, float dl) {
         float t0 = 0.f, t1 = tbest;
         for (int i = 0; i < 3; ++i) {
-            float a = (idx(b.mn, i) - idx(o, i)) * idx(inv, i);
-            float c = (idx(b.mx, i) - idx(o, i)) * idx(inv, i);
+            float a = ((idx(b.mn, i) - dl) - idx(o, i)) * idx(inv, i);
+            float c = ((idx(b.mx, i) + dl) - idx(o, i)) * idx(inv, i);
             float lo = std::fmin(a, c), hi = std::fmax(a, c);     // fmin/fmax ignore a NaN operand
             t0 = std::fmax(t0, lo); t1 = std::fmin(t1, hi);
         }
@@ -321,20 +378,22 @@ struct Scene {
         float cull = FLT_MAX;
         if (any_tmax2 >= 0.f) cull = std::sqrt(any_tmax2) * 1.001f + pad;
         int stack[256]; int sp = 0;
-        if (node_entry(ray.o, inv, nodes[0].box, cull) == INFINITY) return h;
+        float dl = std::fmax(std::fmax(std::fabs(ray.o.x), std::fabs(ray.o.y)), std::fabs(ray.o.z)) * 0x1p-17f;
+        if (!(dl == dl)) dl = INFINITY;
+        if (node_entry(ray.o, inv, nodes[0].box, cull, dl) == INFINITY) return h;
         stack[sp++] = 0;
         while (sp) {
             const BNode& nd = nodes[stack[--sp]];
             float lim = std::fmin(cull, best * 1.001f + pad);
             if (nd.count == 0) {                       // children tested before the push, nearer child popped first
-                float el = node_entry(ray.o, inv, nodes[nd.left].box, lim), er = node_entry(ray.o, inv, nodes[nd.right].box, lim);
+                float el = node_entry(ray.o, inv, nodes[nd.left].box, lim, dl), er = node_entry(ray.o, inv, nodes[nd.right].box, lim, dl);
                 if (el != INFINITY && er != INFINITY) {
                     if (el <= er) { stack[sp++] = nd.right; stack[sp++] = nd.left; } else { stack[sp++] = nd.left; stack[sp++] = nd.right; }
                 } else if (el != INFINITY) stack[sp++] = nd.left;
                 else if (er != INFINITY) stack[sp++] = nd.right;
                 continue;
             }
-            if (node_entry(ray.o, inv, nd.box, lim) == INFINITY) continue;     // best may have shrunk since the push
+            if (node_entry(ray.o, inv, nd.box, lim, dl) == INFINITY) continue;     // best may have shrunk since the push
             for (int i = 0; i < nd.count; ++i) {
                 uint32_t key = order[nd.first + i];
                 int type, index, mesh; key_decode(key, type, index, mesh);
@@ -565,6 +624,7 @@ int ora_intersect(void* s_, const float* o, const float* d, int n, int mode, int
     Scene* s = (Scene*)s_;
     if (!s->committed || (mode == 1 && !s->bvh_built)) return -1;
     std::vector<int8_t> gc(s->meshes.size());
+    if (mode == 1) for (int i = 0; i < n; ++i) s->cover_origin(mk(o[3 * i], o[3 * i + 1], o[3 * i + 2]));
     for (int i = 0; i < n; ++i) {
         Ray r{mk(o[3 * i], o[3 * i + 1], o[3 * i + 2]), mk(d[3 * i], d[3 * i + 1], d[3 * i + 2])};
         Hit h = mode == 0 ? s->intersect_faithful(r) : s->intersect_accel(r, gc);
@@ -577,6 +637,7 @@ int ora_intersect(void* s_, const float* o, const float* d, int n, int mode, int
 int ora_shade_ray(void* s_, const Params* p, const float* o, const float* d, int mode, float* rgb_value) {
     Scene* s = (Scene*)s_;
     if (!s->committed || (mode == 1 && !s->bvh_built)) return -1;
+    if (mode == 1) s->cover_origin(mk(o[0], o[1], o[2]));
     Tracer tr(*s, *p, mode);
     f3 c = tr.shade(Ray{mk(o[0], o[1], o[2]), mk(d[0], d[1], d[2])}, 0, nullptr);
     rgb_value[0] = c.x; rgb_value[1] = c.y; rgb_value[2] = c.z;
@@ -607,6 +668,7 @@ int ora_render(void* s_, const Params* p, int mode, int n_threads, const int64_t
     Scene* s = (Scene*)s_;
     if (!s->committed || (mode == 1 && !s->bvh_built)) return -1;
     if (p->res_x < 0 || p->res_y < 0) return -2;
+    if (mode == 1) s->cover_origin(mk(p->pos[0], p->pos[1], p->pos[2]));
     int64_t total = pixels ? n_pixels : (int64_t)p->res_x * p->res_y;
     Outputs o{rgba32f, rgba8, hit_id, hit_t};
     if (n_threads < 1) n_threads = (int)std::thread::hardware_concurrency();

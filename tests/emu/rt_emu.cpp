@@ -33,6 +33,8 @@ struct Emu {
     RtScene S{};
     int n_nodes = 0, max_stack = 0;
     bool has_mirror = false;
+    float obox[6] = {0, 0, 0, 0, 0, 0};        // RtDevice::obox
+    int opt_leaf_max = 4, opt_builder = 0; double opt_pad_scale = 1.0 / 65536.0, opt_t_slack = 1.000125;   // of the last commit
 };
 
 void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder, bool refit = false) {
@@ -67,16 +69,20 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
     S.mats = E.mats.data(); S.mesh_aabb = E.mesh_aabb.data(); S.mesh_base = E.mesh_base.data(); S.lights = E.lights.data();
     if (!refit) E.n_nodes = 0;
     if (n == 0) return;
-    RtRaw R{E.raw_v.data(), E.raw_n.data(), E.raw_s.data(), E.mesh_base.data(), n_me, n_mt, n_sp, n_lo};
+    RtRaw R{E.raw_v.data(), E.raw_n.data(), E.raw_s.data(), E.mesh_base.data(), n_me, n_mt, n_sp, n_lo, mk3(0.f, 0.f, 0.f), mk3(0.f, 0.f, 0.f), 0.0f};
     leaf_max = leaf_max < 1 ? 1 : (leaf_max > 8 ? 8 : leaf_max);
     float b[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
-    for (int i = 0; i < n; ++i) {
+    for (int i = 0; i < n; ++i) {                                  // k_bounds: un-inflated sphere boxes (R.sphere_k = 0)
         f3 lo, hi; rt_prim_box(R, i, lo, hi);
         b[0] = fminf(b[0], lo.x); b[1] = fminf(b[1], lo.y); b[2] = fminf(b[2], lo.z);
         b[3] = fmaxf(b[3], hi.x); b[4] = fmaxf(b[4], hi.y); b[5] = fmaxf(b[5], hi.z);
     }
     float amax = 0.f; for (int k = 0; k < 6; ++k) if (std::isfinite(b[k])) amax = fmaxf(amax, fabsf(b[k]));
     const float pad = (float)(amax * pad_scale) + 1e-30f;
+    S.origin_reach = rt_origin_reach(pad);
+    H.origin_box(b, amax, E.obox);                                 // rt_device_commit's set_obox
+    R.obox_lo = mk3(E.obox[0], E.obox[1], E.obox[2]); R.obox_hi = mk3(E.obox[3], E.obox[4], E.obox[5]); R.sphere_k = RT_SPHERE_K;
+    S.n_slots = refit ? (int)E.order.size() : n;
     f3 bmin = mk3(b[0], b[1], b[2]);
     f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
     if (refit) {                                                   // rt_scene_refit: k_emit_slots + k_node_parents + k_refit_nodes, serialised
@@ -137,6 +143,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
         E.nodes.assign(std::max<size_t>(4, B.nodes.size() / 4), float4{});
         memcpy(E.nodes.data(), B.nodes.data(), B.nodes.size() * 4);
         S.prims = E.prims.data(); S.pinfo = E.pinfo.data(); S.nodes = E.nodes.data(); S.root = root;
+        S.n_slots = ns;
         E.order = B.order; E.root = root;
         return;
     }
@@ -190,6 +197,13 @@ RtView make_view(const rt_render_params* p, int rank, int world, int band_rows) 
     return V;
 }
 
+// rt_abi.cu cover_camera: a camera outside the committed origin box -> remember it and recompute the sphere boxes (refit)
+void cover_origin(Emu& E, const float* pos) {
+    if (E.S.n_spheres <= 0 || E.S.n_prims <= 0) return;
+    if (!E.host.cover_camera(pos, E.obox)) return;
+    commit(E, E.opt_leaf_max, E.opt_pad_scale, E.opt_t_slack, 0, true);
+}
+
 }  // namespace
 
 extern "C" {
@@ -218,6 +232,7 @@ int emu_scene_lights(void* e, const float* pi, int n, const float* amb) {
 int emu_scene_commit(void* e, const float* aabb, int leaf_max, double pad_scale, double t_slack, int builder) {
     Emu* E = (Emu*)e;
     if (aabb) for (int k = 0; k < 6; ++k) E->host.aabb[k] = aabb[k]; else E->host.calc_aabb();
+    E->opt_leaf_max = leaf_max; E->opt_pad_scale = pad_scale; E->opt_t_slack = t_slack; E->opt_builder = builder;
     commit(*E, leaf_max, pad_scale, t_slack, builder);
     return 0;
 }
@@ -249,10 +264,21 @@ int emu_ray_triangle(const float* o, const float* d, const float* v, float tmax,
 int emu_intersect(void* e, const float* o, const float* d, int n, int32_t* out_id, float* out_t) {
     Emu* E = (Emu*)e; const RtScene& S = E->S;
     VecStack stk;
+    if (S.n_spheres > 0 && n > 0) {                                 // rt_intersect: the explicit origins join the origin box
+        float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+        for (int i = 0; i < n; ++i) for (int k = 0; k < 3; ++k) { const float v = o[3 * i + k]; if (std::isfinite(v)) { lo[k] = fminf(lo[k], v); hi[k] = fmaxf(hi[k], v); } }
+        for (int k = 0; k < 3; ++k) if (!(lo[k] <= hi[k])) { lo[k] = 0.f; hi[k] = 0.f; }
+        cover_origin(*E, lo); cover_origin(*E, hi);
+    }
     for (int i = 0; i < n; ++i) {
         f3 O = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
         float bt = FLT_MAX; int bs = -1;
-        { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } }
+        { f3 inv = rt_rcp3(D);
+          if (rt_scene_gate(S, O, inv)) {                              // k_intersect
+              const float dd = um_dot(D, D);
+              if (S.n_spheres > 0 && !(fabsf(dd - 1.0f) <= 0x1p-20f)) rt_scan_all(S, O, D, inv, bt, bs);
+              else { stk.sp = 0; rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+          } }
         int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
         out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
     }
@@ -264,7 +290,9 @@ int emu_intersect(void* e, const float* o, const float* d, int n, int32_t* out_i
 int emu_render(void* e, const rt_render_params* p, int rank, int world, int band_rows, int chunk_pixels,
                float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t, uint64_t* stats3) {
     Emu* E = (Emu*)e; const RtScene& S = E->S;
+    cover_origin(*E, p->pos);
     RtView V = make_view(p, rank, world, band_rows);
+    rt_view_far_origin(V, S.origin_reach);
     int maxd = (E->has_mirror && V.max_bounces > 0) ? (V.max_bounces > 64 ? 64 : V.max_bounces) : 0;
     V.max_bounces = maxd;
     uint64_t n_shadow = 0, n_mirror = 0;
@@ -287,7 +315,8 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
             for (int t = 0; t < nt; ++t) for (int lane = 0; lane < 32; ++lane) {           // k_trace_primary
                 int x, y; bool valid = rt_item_to_pixel(V, tb + t, lane, x, y);
                 float bt = FLT_MAX; int bs = -1;
-                if (valid) { f3 O, D; rt_primary_ray(V, x, y, si, sj, O, D); { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } } }
+                if (valid) { f3 O, D; rt_primary_ray(V, x, y, si, sj, O, D); { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0;
+                    if (V.far_origin) rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); else rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } } }
                 size_t q = (size_t)t * 32 + lane; hit0_t[q] = bt; hit0_slot[q] = valid ? bs : -2;
             }
             for (int d = 0; d <= maxd; ++d) {

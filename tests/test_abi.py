@@ -62,3 +62,27 @@ def test_product_package_does_not_reference_the_oracle():
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert "librt_oracle" not in txt and "import oracle" not in txt and "from oracle" not in txt, f
                 assert "librt_emu" not in txt, f
+
+
+def build_abi_smoke(out_dir):
+    """tests/abi_smoke.c as a strict C99 translation unit against include/rtb200.h, linked to the product library"""
+    import subprocess
+    exe = os.path.join(out_dir, "abi_smoke")
+    lib_dir = os.path.join(ROOT, "unity-raytracer_b200")
+    subprocess.check_call(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "abi_smoke.c"), "-o", exe, "-L", lib_dir, "-lrtb200", "-lm",
+                           "-Wl,-rpath," + lib_dir])
+    return exe
+
+
+def test_header_is_plain_c_and_the_c_caller_fails_loudly_without_a_device(rtb, tmp_path):
+    """the boundary is bound from C (a managed [DllImport] sees exactly this view). Without a GPU the C caller
+    must get RT_E_CUDA from rt_create, never a CPU path; with one, the GPU suite runs the full smoke (test_gpu_parity.py)."""
+    import subprocess
+    import torch
+    rtb.load_library()
+    exe = build_abi_smoke(str(tmp_path))
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present: the full C smoke test runs in the gpu suite")
+    r = subprocess.run([exe, "--no-gpu"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr

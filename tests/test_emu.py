@@ -317,3 +317,99 @@ def test_golden_fixtures_in_the_emulator(emu, scenes):
         assert np.array_equal(got["hit_id"][:, :2], g["hit_id"][:, :2]), name
         assert np.array_equal(got["hit_t"], g["hit_t"]), name
         assert np.abs(got["rgba8"].astype(int) - g["rgba8"].astype(int)).max() <= 1, name
+
+
+def far_camera_case(scenes, distance):
+    """an axis-aligned cube (thin node boxes: a face seen edge-on is a zero-thickness slab) plus a few spheres, seen
+    from `distance` away through a very narrow image plane, so that the slab test's rounding (|O/d| * 2^-24) exceeds the
+    node padding (max|coordinate| * 2^-16)."""
+    s = scenes.SceneArrays()
+    h = 5.0
+    corners = np.array([(x, y, z) for x in (-h, h) for y in (-h, h) for z in (-h, h)], np.float32) + np.array((1.0, -2.0, 3.0), np.float32)
+    quads = ((0, 1, 3, 2), (4, 6, 7, 5), (0, 4, 5, 1), (2, 3, 7, 6), (0, 2, 6, 4), (1, 5, 7, 3))
+    tris = []
+    for a, b, c, d in quads:
+        tris.append(np.concatenate([corners[a], corners[b], corners[c]])); tris.append(np.concatenate([corners[a], corners[c], corners[d]]))
+    tris = np.asarray(tris, np.float32)
+    nrm, box = scenes.mesh_from_world_tris(tris)
+    s.add_mesh(tris, nrm, scenes.material(diffuse=(0.2, 0.8, 0.7), ambient=(1, 1, 1), specular=(0.4, 0.4, 0.4), phong=12.0), box)
+    s.add_sphere((9.0, 4.0, 1.0), 4.0, scenes.material(diffuse=(0.9, 0.2, 0.2), ambient=(1, 1, 1)))
+    s.add_sphere((-8.0, -6.0, 6.0), 2.25, scenes.material(diffuse=(0.2, 0.2, 0.9), ambient=(1, 1, 1), mirror=(0.8, 0.8, 0.8), is_mirror=1))
+    s.add_light((30.0, 40.0, -20.0), 4e4); s.ambient[:] = (12, 12, 12)
+    # looking along an oblique direction so that no ray direction component is zero, from far away
+    fwd = np.array((0.36, -0.48, 0.8), np.float64); fwd /= np.linalg.norm(fwd)
+    right = np.cross((0, 1, 0), fwd); right /= np.linalg.norm(right)
+    up = np.cross(fwd, right)
+    pos = np.array((1.0, -2.0, 3.0)) - fwd * distance
+    cam = dict(pos=tuple(np.float32(pos)), fwd=tuple(np.float32(fwd)), right=tuple(np.float32(right)), up=tuple(np.float32(up)))
+    # the plane at distance `distance` spans ~ +-16 world units: the scene fills the frame
+    p = scenes.make_params(64, 48, float(distance), 16.0, 12.0, background=(0.1, 0.1, 0.2), bounces=2, cam=cam)
+    return s, p
+
+
+@pytest.mark.parametrize("builder", [0, 1])
+@pytest.mark.parametrize("distance", [2e3, 2e4, 2e5, 3e6])
+def test_far_camera_keeps_the_scan_result(emu, oracle, scenes, builder, distance):
+    """A camera 1e2 .. 1e5 scene extents away: the BVH walk must still return what the reference's scan returns
+    (rt_origin_slack, rt_core.h); primary rays of such a view take the per-lane loop on the GPU (RtView::far_origin)."""
+    s, p = far_camera_case(scenes, distance)
+    e = emu.EmuTracer(leaf_max=1, builder=builder); e.set_scene(s)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    got = e.render(p)
+    _strict(compare_renders(ref, got))
+    assert (ref["hit_id"][:, 0] != 0).sum() > 100          # the fixture does see geometry
+
+
+def grazing_sphere_rays(rng, centers, radii, origin_box, n_per=64):
+    """normalised binary32 rays from random origins that pass each sphere centre at 0.98 .. 1.3 radii — where the reference's
+    cancelling discriminant (RMath.cs:88-93) decides differently from the exact geometry"""
+    O, D = [], []
+    for c, r in zip(centers, radii):
+        o = rng.uniform(origin_box[0], origin_box[1], (n_per, 3))
+        v = c - o
+        vh = v / np.linalg.norm(v, axis=1, keepdims=True)
+        a = rng.normal(size=(n_per, 3)); a -= (a * vh).sum(1, keepdims=True) * vh; a /= np.linalg.norm(a, axis=1, keepdims=True)
+        tgt = c + a * (r * rng.uniform(0.98, 1.3, (n_per, 1)))
+        d = (tgt - o).astype(np.float32)
+        O.append(o.astype(np.float32)); D.append(d)
+    O, D = np.concatenate(O), np.concatenate(D)
+    dd = (D[:, 0] * D[:, 0] + D[:, 1] * D[:, 1]) + D[:, 2] * D[:, 2]                         # math.normalize = rsqrt(dot) * x
+    D = (np.float32(1) / np.sqrt(dd))[:, None] * D
+    return O, D.astype(np.float32)
+
+
+@pytest.mark.parametrize("builder", [0, 1])
+def test_sphere_silhouettes_match_the_scan(emu, oracle, scenes, builder):
+    """Small spheres seen from far away: rays that geometrically MISS a sphere by up to ~20 % of its radius are hits for the
+    reference's binary32 discriminant.  The sphere boxes are inflated for exactly that (rt_sphere_box_radius), otherwise the
+    BVH would cull what the scan hits.  Explicit rays (rt_intersect's path) from inside and far outside the scene, and the
+    accelerated oracle, against the faithful scan."""
+    rng = np.random.default_rng(11)
+    s = scenes.SceneArrays()
+    m = scenes.material(diffuse=(0.7, 0.7, 0.7), ambient=(1, 1, 1))
+    n_s = 400
+    centers = rng.uniform(-40, 40, (n_s, 3)) + np.array((0, 0, 100.0))
+    radii = rng.uniform(0.1, 0.4, n_s)
+    for c, r in zip(centers, radii):
+        s.add_sphere(tuple(np.float32(c)), float(np.float32(r * r)), m)
+    t = np.array((-60, -45, 160, 60, -45, 160, 0, 60, 160), np.float32)
+    s.add_triangle(t, scenes.triangle_normal(t)[0], m)
+    s.add_light((0, 80, 0), 1e5)
+    centers = s.spheres[:, :3].astype(np.float64); radii = np.sqrt(s.spheres[:, 3].astype(np.float64))
+    ref_scene = oracle.OracleScene(s)
+    e = emu.EmuTracer(leaf_max=2, builder=builder); e.set_scene(s)
+    n_diff_geom = 0
+    for box in (((-1, -1, -1), (1, 1, 1)), ((-40, -40, 60), (40, 40, 140)), ((-900, -900, -2000), (900, 900, -1000))):
+        O, D = grazing_sphere_rays(rng, centers, radii, np.asarray(box, np.float64), 48)
+        rid, rt_ = ref_scene.intersect(O, D, oracle.FAITHFUL)
+        gid, gt = e.intersect(O, D)
+        assert np.array_equal(rid[:, :2], gid[:, :2]) and np.array_equal(rt_, gt), (box, int((rid[:, :2] != gid[:, :2]).any(axis=1).sum()))
+        aid, at = ref_scene.intersect(O, D, oracle.ACCELERATED)
+        assert np.array_equal(rid[:, :2], aid[:, :2]) and np.array_equal(rt_, at), box
+        # how many of the reference's hits are geometric misses by more than the node padding?
+        k = np.repeat(np.arange(n_s), 48)
+        oc = O.astype(np.float64) - centers[k]
+        u = (D.astype(np.float64) * oc).sum(1)
+        perp = np.sqrt(np.maximum((oc ** 2).sum(1) - u * u, 0))
+        n_diff_geom += int(((rid[:, 0] == 1) & (rid[:, 1] == k) & (perp > radii[k] + 0.01)).sum())
+    assert n_diff_geom > 50, n_diff_geom          # the fixture does exercise the inflated region

@@ -786,3 +786,97 @@ def test_registered_host_buffer_gives_the_same_frame(rtb, scenes):
     with pytest.raises(RuntimeError):
         r.host_unregister(out["rgba8"])                     # not registered any more: CUDA error surfaces as a status code
     r.close()
+
+
+# ---- round 2 -------------------------------------------------------------------------------------------------------------
+def test_c_smoke_test_of_the_boundary(rtb, tmp_path):
+    """tests/abi_smoke.c: the header compiled as strict C99 and the whole call sequence of a C caller (create -> scene ->
+    commit -> rt_render / rt_intersect -> KAT-1..4 -> destroy), SURVEY §8(b)."""
+    import subprocess
+    from test_abi import build_abi_smoke
+    exe = build_abi_smoke(str(tmp_path))
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0 and "abi_smoke ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_lights_appearing_after_a_frame_without_lights(rtb, scenes, oracle):
+    """a frame with 0 point lights launches no shadow kernel, so it records no tile costs for it; the
+    next frame (lights switched on through rt_scene_update_lights, same layout otherwise) must not take those empty class
+    lists for hints — the fused kernel would hand out no tile at all and leave the frame unwritten."""
+    import copy
+    s = scenes.random_soup(seed=5, n_tris=900, n_spheres=80)
+    p = scenes.soup_params(192, 128, 0, 1)
+    lit = copy.deepcopy(s)
+    dark = copy.deepcopy(s); dark.lights = dark.lights[:0]
+    for builder in (0, 1):
+        r = rtb.RayTracer((0,)); r.set_option("builder", builder)
+        r.set_scene(dark)
+        ref_dark = oracle.OracleScene(dark).render(p, oracle.FAITHFUL)
+        for _ in range(2):
+            _check(compare_renders(ref_dark, r.render(p)))
+        r.update_lights(lit.lights, lit.ambient); r.recommit()
+        ref_lit = oracle.OracleScene(lit).render(p, oracle.FAITHFUL)
+        for _ in range(3):                                  # first frame without hints, then with the hints it recorded
+            got = r.render(p)
+            _check(compare_renders(ref_lit, got))
+            assert got["stats"]["rays_shadow"] == ref_lit["stats"][1] > 0
+        r.set_option("hints", 0)
+        _check(compare_renders(ref_lit, r.render(p)))
+        r.update_lights(dark.lights, dark.ambient); r.refit()               # and back, through the refit path
+        r.set_option("hints", 1)
+        for _ in range(2):
+            _check(compare_renders(ref_dark, r.render(p)))
+        r.close()
+
+
+@pytest.mark.parametrize("distance", [2e3, 2e5, 3e6])
+def test_far_camera_keeps_the_scan_result(rtb, scenes, oracle, distance):
+    """a camera 1e2 .. 1e5 scene extents away (k_trace_primary<FAR>, sphere boxes inflated for the camera's
+    distance through the automatic refit): same fixture as tests/test_emu.py, here on the GPU, both builders and both loops."""
+    from test_emu import far_camera_case
+    s, p = far_camera_case(scenes, distance)
+    ref = oracle.OracleScene(s).render(p, oracle.FAITHFUL)
+    assert (ref["hit_id"][:, 0] != 0).sum() > 100
+    for builder, packet in ((0, 1), (1, 1), (1, 0)):
+        r = rtb.RayTracer((0,)); r.set_option("builder", builder); r.set_option("packet", packet)
+        r.set_scene(s)
+        for _ in range(2):
+            _check(compare_renders(ref, r.render(p)))
+        r.close()
+
+
+def test_sphere_silhouettes_match_the_scan(rtb, scenes, oracle):
+    """Small spheres far from the ray origin: the reference's binary32 discriminant hits them out to ~1.2 radii
+    (rt_build_steps.h rt_sphere_box_radius).  Explicit rays through rt_intersect, from inside and far outside the scene,
+    and a rendered frame whose camera sits outside the scene (automatic refit of the sphere boxes), vs the faithful scan."""
+    from test_emu import grazing_sphere_rays
+    rng = np.random.default_rng(11)
+    s = scenes.SceneArrays()
+    m = scenes.material(diffuse=(0.7, 0.7, 0.7), ambient=(1, 1, 1), mirror=(0.5, 0.5, 0.5), is_mirror=1)
+    n_s = 1500
+    centers = rng.uniform(-40, 40, (n_s, 3)) + np.array((0, 0, 100.0))
+    radii = rng.uniform(0.1, 0.4, n_s)
+    for c, r in zip(centers, radii):
+        s.add_sphere(tuple(np.float32(c)), float(np.float32(r * r)), m)
+    t = np.array((-60, -45, 160, 60, -45, 160, 0, 60, 160), np.float32)
+    s.add_triangle(t, scenes.triangle_normal(t)[0], m)
+    s.add_light((0, 80, 0), 1e5); s.add_light((-70, 10, 60), 1e5); s.ambient[:] = (20, 20, 20)
+    centers = s.spheres[:, :3].astype(np.float64); radii = np.sqrt(s.spheres[:, 3].astype(np.float64))
+    ref_scene = oracle.OracleScene(s)
+    p = scenes.make_params(256, 192, 10.0, 4.5, 3.4, background=(0.1, 0.1, 0.1), bounces=2)     # camera at the origin, outside the sphere cloud
+    ref = ref_scene.render(p, oracle.FAITHFUL)
+    for builder in (0, 1):
+        r = rtb.RayTracer((0,)); r.set_option("builder", builder); r.set_scene(s)
+        for box in (((-1, -1, -1), (1, 1, 1)), ((-40, -40, 60), (40, 40, 140)), ((-900, -900, -2000), (900, 900, -1000))):
+            O, D = grazing_sphere_rays(rng, centers, radii, np.asarray(box, np.float64), 16)
+            rid, rt_ = ref_scene.intersect(O, D, oracle.FAITHFUL)
+            gid, gt = r.intersect(O, D)
+            assert np.array_equal(rid[:, :2], gid[:, :2]) and np.array_equal(rt_, gt), (builder, box, int((rid[:, :2] != gid[:, :2]).any(axis=1).sum()))
+        for _ in range(2):
+            _check(compare_renders(ref, r.render(p)))
+        # a direction that is not normalised: the reference's sphere test then describes another shape; rt_intersect scans
+        O = np.zeros((64, 3), np.float32); D = (centers[:64] * 1.7).astype(np.float32)
+        rid, rt_ = ref_scene.intersect(O, D, oracle.FAITHFUL)
+        gid, gt = r.intersect(O, D)
+        assert np.array_equal(rid[:, :2], gid[:, :2]) and np.array_equal(rt_, gt, equal_nan=True)
+        r.close()

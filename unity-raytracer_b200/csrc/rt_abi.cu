@@ -23,6 +23,8 @@ static_assert(sizeof(rt_render_params) == 88 && sizeof(rt_material) == 56 && siz
 
 static thread_local std::string g_err;   // rt_last_error(NULL): errors of rt_create
 
+extern "C" { static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, bool refit); }
+
 namespace {
 
 int fail(rt_ctx* c, int code, const std::string& msg) { if (c) c->err = msg; else g_err = msg; return code; }
@@ -96,6 +98,7 @@ RtView make_view(const rt_ctx* c, const rt_render_params* p, int dev_index) {
     const int nd = (int)c->devs.size();
     V.rank = c->ext_rank * nd + dev_index; V.world = c->ext_world * nd; V.band_rows = c->band_rows;
     rt_view_finish(V);
+    rt_view_far_origin(V, c->devs[(size_t)dev_index].S.origin_reach);
     return V;
 }
 
@@ -134,10 +137,30 @@ int finish_stats(rt_ctx* c) {
     return RT_OK;
 }
 
+int sync_all(rt_ctx* c);
+
+// Sphere boxes are inflated for ray origins inside the origin box of the last commit (rt_build_steps.h rt_sphere_box_radius).
+// A camera outside it makes the context remember the position (with some room to move: an orbiting camera settles after a
+// few frames) and recompute the boxes through the refit path — same tree, same result, new sphere boxes.
+int cover_origin(rt_ctx* c, const float pos[3]) {
+    const RtDevice& D0 = c->devs[0];
+    if (D0.S.n_spheres <= 0 || D0.S.n_prims <= 0) return RT_OK;
+    RtHostScene& H = c->host;
+    if (!H.cover_camera(pos, D0.obox)) return RT_OK;
+    int rc = sync_all(c);
+    if (rc) return rc;
+    float keep[6]; for (int k = 0; k < 6; ++k) keep[k] = H.aabb[k];
+    const float up = c->stats.ms_commit_upload, bd = c->stats.ms_commit_build; const uint64_t hb = c->stats.h2d_bytes;
+    rc = commit_impl(c, keep, true, true);
+    c->stats.ms_commit_upload = up; c->stats.ms_commit_build = bd; c->stats.h2d_bytes = hb;     // keep the caller's commit figures
+    return rc;
+}
+
 int render_device_impl(rt_ctx* c, const rt_render_params* p, int want, int split = 0) {
     int rc = validate_params(c, p);
     if (rc) return rc;
     if (!c->committed) return fail(c, RT_E_STATE, "rt_render before rt_scene_commit");
+    if ((rc = cover_origin(c, p->pos))) return rc;
     c->last_res_x = p->res_x; c->last_res_y = p->res_y; c->last_want = want;
     c->stats.rays_primary = c->stats.rays_shadow = c->stats.rays_mirror = 0;
     c->stats.ms_render = 0.f; c->stats.kernel_launches = 0; c->stats.ms_d2h = 0.f; c->stats.d2h_bytes = 0;
@@ -280,8 +303,8 @@ int rt_scene_lights(rt_ctx* c, const float* pos_intensity, int n, const float am
     return RT_OK;
 }
 
-static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, bool refit = false) {
-    if (c->host.mesh_stale && !refit && c->opt.builder == 1 && !c->host.mesh_on_device) {   // host rebuild after device-only mesh updates
+static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, bool refit) {
+    if (c->host.mesh_stale && !refit && c->host.builder == 1 && !c->host.mesh_on_device) {   // (the builder latched at rt_scene_begin, as rt_device_commit uses)   // host rebuild after device-only mesh updates
         RtDevice& D = c->devs[0];
         std::string& err = c->err;
         const size_t n_mt = (size_t)c->host.n_meshtris();
@@ -312,7 +335,7 @@ static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, 
 int rt_scene_commit(rt_ctx* c, const float scene_aabb[6]) {
     if (!c) return RT_E_INVALID;
     if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_commit without rt_scene_begin");
-    return commit_impl(c, scene_aabb, false);
+    return commit_impl(c, scene_aabb, false, false);
 }
 
 // ---- dirty-tracking updates of a committed scene ----
@@ -390,7 +413,7 @@ int rt_scene_recommit(rt_ctx* c, const float scene_aabb[6]) {
     if (c->in_scene) return fail(c, RT_E_STATE, "rt_scene_recommit inside rt_scene_begin/commit");
     if (!c->dirty && !c->committed) return fail(c, RT_E_STATE, "rt_scene_recommit: no committed scene");
     if (!c->dirty) { int rc = sync_all(c); if (rc) return rc; }
-    int rc = commit_impl(c, scene_aabb, true);
+    int rc = commit_impl(c, scene_aabb, true, false);
     if (rc == RT_OK) c->dirty = false;
     return rc;
 }
@@ -546,6 +569,15 @@ int rt_intersect(rt_ctx* c, const float* origins, const float* dirs, int n, int3
     if (!c->committed) return fail(c, RT_E_STATE, "rt_intersect before rt_scene_commit");
     if (n < 0 || (n > 0 && (!origins || !dirs || !out_id || !out_t))) return fail(c, RT_E_INVALID, "rt_intersect: bad arguments");
     if (n == 0) return RT_OK;
+    if (c->devs[0].S.n_spheres > 0) {                          // explicit origins belong to the origin box too (both corners: it is convex)
+        float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+        for (int i = 0; i < n; ++i)
+            for (int k = 0; k < 3; ++k) { const float v = origins[3 * (size_t)i + k]; if (std::isfinite(v)) { lo[k] = fminf(lo[k], v); hi[k] = fmaxf(hi[k], v); } }
+        for (int k = 0; k < 3; ++k) if (!(lo[k] <= hi[k])) { lo[k] = 0.f; hi[k] = 0.f; }
+        int rc0 = cover_origin(c, lo);
+        if (rc0 == RT_OK) rc0 = cover_origin(c, hi);
+        if (rc0) return rc0;
+    }
     std::string& err = c->err;
     RtDevice& D = c->devs[0];
     RT_CUDA(cudaSetDevice(D.device));
@@ -569,8 +601,9 @@ int rt_intersect(rt_ctx* c, const float* origins, const float* dirs, int n, int3
 int rt_set_stream(rt_ctx* c, void* cuda_stream) {
     if (!c) return RT_E_INVALID;
     RtDevice& D = c->devs[0];
-    cudaSetDevice(D.device);
-    cudaStreamSynchronize(D.stream);
+    std::string& err = c->err;
+    RT_CUDA(cudaSetDevice(D.device));
+    RT_CUDA(cudaStreamSynchronize(D.stream));                 // work queued on the old stream reads buffers the next call may touch
     D.stream = cuda_stream ? (cudaStream_t)cuda_stream : D.own_stream;
     return RT_OK;
 }

@@ -275,6 +275,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
 
     // ---- scene view (pointers filled below) ----
     RtScene& S = D.S;
+    D.hint_ready = false;                      // tile-cost hints describe the previous scene's frames
     const int32_t old_prims = D.bvh_prims, old_root = D.bvh_root, old_slots = D.bvh_slots;
     const uint32_t old_nodes = D.n_nodes;
     if (refit && (old_prims != n || n <= 0 || old_slots < n || D.vals_alt.bytes < (size_t)old_slots * 4)) { err = "rt_scene_refit: no committed tree over this many primitives"; return RT_E_STATE; }
@@ -296,7 +297,14 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     D.n_nodes = 0;
     RT_CUDA(cudaEventRecord(D.ev0, st));
     if (n > 0) {
-        RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_base.as<int32_t>(), n_me, n_mt, n_sp, n_lo};
+        RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_base.as<int32_t>(), n_me, n_mt, n_sp, n_lo,
+                mk3(0.f, 0.f, 0.f), mk3(0.f, 0.f, 0.f), 0.0f};   // sphere boxes un-inflated until the origin box is known (set_obox)
+        auto set_obox = [&](const float b6[6], float amax_) {
+            H.origin_box(b6, amax_, D.obox);
+            R.obox_lo = mk3(D.obox[0], D.obox[1], D.obox[2]); R.obox_hi = mk3(D.obox[3], D.obox[4], D.obox[5]);
+            R.sphere_k = RT_SPHERE_K;
+        };
+        S.n_slots = n;
         const int leaf_max = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 8 ? 8 : opt.leaf_max);
         if (refit) {
             // ---- refit: keep the tree (either builder's) and the slot order, recompute every box from the moved primitives ----
@@ -308,11 +316,14 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             RT_CUDA(cudaMemcpyAsync(bord, D.bounds.p, sizeof(bord), cudaMemcpyDeviceToHost, st));
             // (slots of a pre-split tree get the whole triangle's box again: conservative, the clipping is lost until the next commit)
             RT_CUDA(D.leaf_lo.ensure((size_t)old_slots * 16)); RT_CUDA(D.leaf_hi.ensure((size_t)old_slots * 16));
-            k_emit_slots<<<grid_for(old_slots), BT, 0, st>>>(R, old_slots, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
             RT_CUDA(cudaStreamSynchronize(st));
-            float amax = 0.f;
-            for (int k = 0; k < 6; ++k) { float b = f_unord(bord[k]); if (std::isfinite(b)) amax = fmaxf(amax, fabsf(b)); }
+            float amax = 0.f, b6[6];
+            for (int k = 0; k < 6; ++k) { b6[k] = f_unord(bord[k]); if (std::isfinite(b6[k])) amax = fmaxf(amax, fabsf(b6[k])); }
             const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
+            S.origin_reach = rt_origin_reach(pad);
+            set_obox(b6, amax);
+            S.n_slots = old_slots;
+            k_emit_slots<<<grid_for(old_slots), BT, 0, st>>>(R, old_slots, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
             D.n_nodes = old_nodes;
             if (old_nodes > 0) {
                 const int32_t nn = (int32_t)old_nodes;
@@ -340,11 +351,19 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             // ---- host binned-SAH build (rt_sah.h); the device only re-lays the primitives out in leaf order ----
             std::vector<RtSahBox> pb((size_t)n);
             float amax = 0.f;
+            if (n_sp > 0) {                                        // origin box first: the un-inflated bounds of everything
+                float b6[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, am = 0.f;
+                auto grow = [&](float v, int k) { b6[k] = fminf(b6[k], v); b6[3 + k] = fmaxf(b6[3 + k], v); if (std::isfinite(v)) am = fmaxf(am, fabsf(v)); };
+                for (size_t i = 0; i < (size_t)n_mt * 9; ++i) grow(H.mesh_v[i], (int)(i % 3));
+                for (size_t i = 0; i < (size_t)n_lo * 9; ++i) grow(H.loose_v[i], (int)(i % 3));
+                for (int32_t i = 0; i < n_sp; ++i) { const float* sp = H.spheres.data() + 4 * (size_t)i; const float r = sqrtf(sp[3]); for (int k = 0; k < 3; ++k) { grow(sp[k] - r, k); grow(sp[k] + r, k); } }
+                set_obox(b6, am);
+            }
             for (int32_t key = 0; key < n; ++key) {
                 RtSahBox& x = pb[key];
                 if (key >= n_mt && key < n_mt + n_sp) {
                     const float* sp = H.spheres.data() + 4 * (size_t)(key - n_mt);
-                    const float r = sqrtf(sp[3]);
+                    const float r = rt_sphere_box_radius(R, make_float4(sp[0], sp[1], sp[2], sp[3]));
                     for (int k = 0; k < 3; ++k) { x.lo[k] = sp[k] - r; x.hi[k] = sp[k] + r; }
                 } else {
                     const float* v = key < n_mt ? H.mesh_v.data() + 9 * (size_t)key : H.loose_v.data() + 9 * (size_t)(key - n_mt - n_sp);
@@ -356,6 +375,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
                 }
             }
             const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
+            S.origin_reach = rt_origin_reach(pad);
             RtSahBuilder B;
             B.term = (float)opt.sah_term;
             int threads = (int)std::thread::hardware_concurrency();
@@ -375,6 +395,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
                 items = rb.data(); ns = (int32_t)rb.size();
             }
             const int32_t root = B.run(items, ns, leaf_max, pad, threads < 1 ? 1 : threads);
+            if (B.max_depth.load() + 2 > RT_STACK_ENTRIES) { err = "host SAH tree deeper than the traversal stack"; return RT_E_UNSUPPORTED; }
             if (!rk.empty()) for (int32_t s2 = 0; s2 < ns; ++s2) B.order[(size_t)s2] = rk[(size_t)B.order[(size_t)s2]];      // slot -> scan key
             RT_CUDA(D.vals_alt.ensure((size_t)ns * 4));
             RT_CUDA(cudaMemcpyAsync(D.vals_alt.p, B.order.data(), (size_t)ns * 4, cudaMemcpyHostToDevice, st));
@@ -388,6 +409,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             RT_CUDA(cudaStreamSynchronize(st));                   // B.order / B.nodes go out of scope
             S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
             S.root = root;
+            S.n_slots = ns;
             D.bvh_prims = n; D.bvh_slots = ns; D.bvh_root = root; D.bvh_parents = false;
             RT_CUDA(cudaEventRecord(D.ev1, st));
             RT_CUDA(cudaEventSynchronize(D.ev1));
@@ -406,6 +428,8 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
         float b[6]; for (int k = 0; k < 6; ++k) b[k] = f_unord(bord[k]);
         float amax = 0.f; for (int k = 0; k < 6; ++k) if (std::isfinite(b[k])) amax = fmaxf(amax, fabsf(b[k]));
         const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
+        S.origin_reach = rt_origin_reach(pad);
+        set_obox(b, amax);
         f3 bmin = mk3(b[0], b[1], b[2]);
         f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
         // morton + sort

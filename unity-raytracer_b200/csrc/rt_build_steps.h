@@ -14,7 +14,35 @@ struct RtRaw {                    // raw uploaded arrays, in the reference's sca
     const float4* spheres;        // (Center, RadiusSquared)
     const int32_t* mesh_base;     // [n_meshes+1]
     int32_t n_meshes, n_meshtris, n_spheres, n_loose;
+    // Sphere boxes (rt_sphere_box_radius): every ray origin the committed tree must serve lies in [obox_lo, obox_hi]
+    // (the primitive bounds, where shadow and mirror rays start, united with the camera positions seen so far);
+    // sphere_k = 0 switches the inflation off (the pass that computes the primitive bounds themselves).
+    f3 obox_lo, obox_hi;
+    float sphere_k;
 };
+
+// Box half-width of a sphere.  RMath.RaySphereIntersection (RMath.cs:81-108) evaluates
+//     disc = uoc*uoc - (lengthsq(oc) - r2),  oc = O - C,  uoc = dot(D, oc)
+// in binary32, where uoc^2 and lengthsq(oc) are both ~|oc|^2 and cancel down to ~r2: the computed disc differs from the exact
+// r2 - dist(ray, C)^2 by up to  (12 u from the products/sums + 2 u from fl(O - C) + 9 u from |D|^2 = 1 +- 9 u of a normalised
+// direction) * |oc|^2,  u = 2^-24  (measured on random grazing rays: up to 9.5 u).  `disc < 0 -> miss` therefore ACCEPTS rays
+// that pass the centre at up to sqrt(r2 + 23 u |oc|^2): seen from 100 units away a sphere of radius 0.1 is hit out to 1.21 r.
+// That is the reference's answer, so the BVH may not cull those rays: the box uses  r_box = sqrt(r2 + RT_SPHERE_K * Rmax^2),
+// Rmax = distance from C to the farthest corner of the origin box, RT_SPHERE_K = 32 u = 2^-19 (mirror directions
+// 2N(V.N) - V are not renormalised, RayTracingSetup.cs:371, and carry a few u more).  Directions are assumed normalised in
+// binary32; rt_intersect handles others by a scan.
+#define RT_SPHERE_K 0x1p-19f
+RT_HD float rt_sphere_box_radius(const RtRaw& R, float4 s) {
+    float r = rt_sqrt(s.w);
+    if (R.sphere_k > 0.0f) {
+        const double dx = fmax(fabs((double)s.x - R.obox_lo.x), fabs((double)s.x - R.obox_hi.x));
+        const double dy = fmax(fabs((double)s.y - R.obox_lo.y), fabs((double)s.y - R.obox_hi.y));
+        const double dz = fmax(fabs((double)s.z - R.obox_lo.z), fabs((double)s.z - R.obox_hi.z));
+        const double rr = (double)s.w + (double)R.sphere_k * (dx * dx + dy * dy + dz * dz);
+        if (rr >= 0.0 && rr < 1e37) r = (float)(sqrt(rr) * 1.000001);       // else: NaN / negative / huge input, box as before
+    }
+    return r;
+}
 
 RT_HD int32_t rt_raw_nprims(const RtRaw& R) { return R.n_meshtris + R.n_spheres + R.n_loose; }
 
@@ -35,7 +63,7 @@ RT_HD void rt_prim_box(const RtRaw& R, int32_t key, f3& lo, f3& hi) {
     int32_t kind, raw, mesh, mat; rt_key_decode(R, key, kind, raw, mesh, mat);
     if (kind == 1) {
         float4 s = R.spheres[raw];
-        float r = rt_sqrt(s.w);
+        float r = rt_sphere_box_radius(R, s);
         lo = mk3(s.x - r, s.y - r, s.z - r); hi = mk3(s.x + r, s.y + r, s.z + r);
     } else {
         const float* v = R.tri_v + 9 * (size_t)raw;

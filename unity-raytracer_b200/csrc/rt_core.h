@@ -40,12 +40,15 @@ struct RtScene {
     const float4* lights;     // 2 x float4 per light: (Position,0) (Intensity,0)
     int32_t root;             // 0 (internal root) or a leaf ref when n_prims <= leaf_max
     int32_t n_prims, n_meshes, n_meshtris, n_spheres, n_lights;
+    int32_t n_slots;          // leaf slots = n_prims, or more when the host builder pre-split references (a triangle then sits in several slots)
     f3 aabb_min, aabb_max;    // Scene.AABB (Scene.cs:15) as given / computed per Scene.cs:17-41
     f3 ambient;               // AmbientLight.Radiance
     float t_slack;            // multiplicative slack on the traversal cull distance (conservative)
     int32_t packet;           // 1: coherent warps traverse as one packet (rt_packet.cuh); 0: always per-lane
     int32_t backcull;         // 1: shadow queries of lights behind the surface may be skipped (rt_shadow_irrelevant; set at commit)
     float coherent_spread2;   // packet mode needs the warp's ray origins within this squared distance of each other
+    float origin_reach;       // ray origins within this distance of the world origin are covered by the node padding alone
+                              // (= RT_FAR_ORIGIN_FACTOR * pad * 2^16, see rt_far_pad); set at commit
 };
 
 struct RtView {
@@ -62,6 +65,8 @@ struct RtView {
     int32_t band_shift;       // log2(band_rows) when it is a power of two, else -1
     int32_t n_local_rows;     // rows owned by this rank
     int32_t n_tiles;          // tiles_x * ceil(n_local_rows / 4); one tile = 8x4 pixels = one warp
+    int32_t far_origin;       // 1: the camera lies so far outside the geometry that the node padding no longer covers the rounding
+                              // of the slab test (rt_far_pad): primary rays take the FAR form of the per-lane loop
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -175,14 +180,30 @@ static __device__ unsigned long long g_rt_visits[20];
 #endif
 
 RT_HD float rt_safe_inv(float d, float inv) { return fabsf(d) > 1e-30f ? inv : copysignf(1e30f, d); }
+// Ray origins far outside the geometry.  The node test computes fma(plane, 1/d, -fl(O/d)); its rounding, and the rounding
+// of fl(O - v0) through which the reference's own triangle test sees the geometry (equivalent to displacing a triangle by
+// ~10 u |O - v0| across the ray, u = 2^-24), are covered by the node padding (max|coordinate| * 2^-16, rt_build) only while
+// the origin lies within RT_FAR_ORIGIN_FACTOR times max|coordinate| of the world origin — always true for shadow and mirror
+// rays, which start on surfaces.  A camera farther out (RtView::far_origin) sends its primary rays through the FAR form of
+// rt_traverse, which moves every slab plane outward by rt_far_pad(O) = 32 u * max|O| for that ray: thin boxes (a cube face
+// seen edge-on) are then never culled although the reference's exact test hits the primitive inside.  (Spheres need more than
+// that, at any distance: rt_sphere_box_radius, rt_build_steps.h.)
+#define RT_FAR_ORIGIN_FACTOR 16.0f
+RT_HD float rt_far_pad(f3 O) {
+    float d = fmaxf(fmaxf(fabsf(O.x), fabsf(O.y)), fabsf(O.z)) * 0x1p-19f;
+    return d == d ? d : INFINITY;
+}
 
-template <bool ANY, class STK>
+template <bool ANY, bool FAR = false, class STK>
 RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& stk, float& best_t, int32_t& best_slot) {
     best_t = FLT_MAX; best_slot = -1;
     stk.sp = 0;                       // an any-hit query returns early and leaves entries behind
     if (S.n_prims <= 0) return false;
     float idx_ = rt_safe_inv(D.x, inv.x), idy_ = rt_safe_inv(D.y, inv.y), idz_ = rt_safe_inv(D.z, inv.z);
     float oodx = O.x * idx_, oody = O.y * idy_, oodz = O.z * idz_;
+    // FAR: every slab plane moved outward by dl in space = by dl * |1/d| along the ray (inf * 0 cannot occur: |1/d| > 0)
+    const float dl = FAR ? rt_far_pad(O) : 0.0f;
+    const float ex = dl * fabsf(idx_), ey = dl * fabsf(idy_), ez = dl * fabsf(idz_);
     uint32_t best_key = 0xffffffffu;
     float tcull = ANY ? rt_sqrt(any_d2) * S.t_slack : INFINITY;
     int32_t gate_mesh = -1; bool gate_ok = true;
@@ -199,10 +220,18 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
             float bx0 = rt_fma(n1.x, idx_, -oodx), bx1 = rt_fma(n1.y, idx_, -oodx);
             float by0 = rt_fma(n1.z, idy_, -oody), by1 = rt_fma(n1.w, idy_, -oody);
             float bz0 = rt_fma(n2.z, idz_, -oodz), bz1 = rt_fma(n2.w, idz_, -oodz);
-            float amin = fmaxf(fmaxf(fminf(ax0, ax1), fminf(ay0, ay1)), fmaxf(fminf(az0, az1), 0.0f));
-            float amax = fminf(fminf(fmaxf(ax0, ax1), fmaxf(ay0, ay1)), fminf(fmaxf(az0, az1), tcull));
-            float bmin = fmaxf(fmaxf(fminf(bx0, bx1), fminf(by0, by1)), fmaxf(fminf(bz0, bz1), 0.0f));
-            float bmax = fminf(fminf(fmaxf(bx0, bx1), fmaxf(by0, by1)), fminf(fmaxf(bz0, bz1), tcull));
+            float amin, amax, bmin, bmax;
+            if (FAR) {
+                amin = fmaxf(fmaxf(fminf(ax0, ax1) - ex, fminf(ay0, ay1) - ey), fmaxf(fminf(az0, az1) - ez, 0.0f));
+                amax = fminf(fminf(fmaxf(ax0, ax1) + ex, fmaxf(ay0, ay1) + ey), fminf(fmaxf(az0, az1) + ez, tcull));
+                bmin = fmaxf(fmaxf(fminf(bx0, bx1) - ex, fminf(by0, by1) - ey), fmaxf(fminf(bz0, bz1) - ez, 0.0f));
+                bmax = fminf(fminf(fmaxf(bx0, bx1) + ex, fmaxf(by0, by1) + ey), fminf(fmaxf(bz0, bz1) + ez, tcull));
+            } else {
+                amin = fmaxf(fmaxf(fminf(ax0, ax1), fminf(ay0, ay1)), fmaxf(fminf(az0, az1), 0.0f));
+                amax = fminf(fminf(fmaxf(ax0, ax1), fmaxf(ay0, ay1)), fminf(fmaxf(az0, az1), tcull));
+                bmin = fmaxf(fmaxf(fminf(bx0, bx1), fminf(by0, by1)), fmaxf(fminf(bz0, bz1), 0.0f));
+                bmax = fminf(fminf(fmaxf(bx0, bx1), fmaxf(by0, by1)), fminf(fmaxf(bz0, bz1), tcull));
+            }
             bool ha = amin <= amax, hb = bmin <= bmax;
             int32_t ra = f2i(n3.x), rb = f2i(n3.y);
             if (ha && hb) {
@@ -250,6 +279,31 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
         if (stk.empty()) return best_slot >= 0;
         node = stk.pop();
     }
+}
+
+// The same query without the tree: every slot tested, argmin over (t, scan key), per-mesh gate on acceptance.  For explicit
+// rays whose direction is not normalised (rt_intersect): the reference's sphere test then no longer describes the sphere the
+// boxes were built for, so nothing may be culled.
+RT_HD bool rt_scan_all(const RtScene& S, f3 O, f3 D, f3 inv, float& best_t, int32_t& best_slot) {
+    best_t = FLT_MAX; best_slot = -1;
+    uint32_t best_key = 0xffffffffu;
+    for (int32_t slot = 0; slot < S.n_slots; ++slot) {
+        const float4* pp = S.prims + 3 * (size_t)slot;
+        float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+        float t; bool hit;
+        if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
+        else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), INFINITY, t);
+        if (!hit) continue;
+        const uint32_t key = (uint32_t)f2i(p0.w);
+        if (!(t < best_t || (t == best_t && key < best_key))) continue;
+        const int32_t mesh = f2i(p2.w);
+        if (mesh >= 0) {                                            // Scene.cs:67
+            float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
+            if (!rt_ray_aabb_inv(O, inv, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z))) continue;
+        }
+        best_t = t; best_key = key; best_slot = slot;
+    }
+    return best_slot >= 0;
 }
 
 // slot -> ObjectId {Type, Index, MeshIndex} (ObjectId.cs:7-9)
@@ -408,6 +462,12 @@ RT_HD void rt_view_finish(RtView& V) {
     V.band_shift = -1;
     for (int32_t k = 0; k < 31; ++k) if (V.band_rows == (1 << k)) V.band_shift = k;
 }
+// sets V.far_origin for a committed scene (see rt_far_pad)
+RT_HD void rt_view_far_origin(RtView& V, float origin_reach) {
+    const float o = fmaxf(fmaxf(fabsf(V.pos.x), fabsf(V.pos.y)), fabsf(V.pos.z));
+    V.far_origin = (o <= origin_reach) ? 0 : 1;                              // NaN positions count as far
+}
+RT_HD float rt_origin_reach(float pad) { return RT_FAR_ORIGIN_FACTOR * 65536.0f * pad; }
 // local work item (tile, lane) -> pixel. One tile is an 8x4 pixel block (one warp) of the rank's local image.
 // tile / tiles_x by multiplication: q' = mulhi(tile, floor(2^32/d)) is q or q-1 for every 32-bit tile; one fix-up step.
 RT_HD bool rt_item_to_pixel(const RtView& V, int32_t tile, int32_t lane, int32_t& x, int32_t& y) {

@@ -32,6 +32,38 @@ struct RtHostScene {
     bool mesh_stale = false;
     int64_t mesh_tris = 0;                      // mesh triangles so far (== mesh_v.size() / 9 when staged on the host)
     int builder = 0;                            // RtOptions::builder latched at rt_scene_begin
+    // camera positions the context has rendered from (viewer state, survives clear()): part of the origin box the sphere
+    // boxes are inflated for (rt_build_steps.h rt_sphere_box_radius)
+    bool cam_valid = false;
+    float cam_box[6] = {0, 0, 0, 0, 0, 0};
+
+    // Origin box of a commit (RtRaw::obox_*): the un-inflated primitive bounds b[6] — shadow and mirror rays start on surfaces,
+    // RayTracingSetup.cs:331,370 — with a small margin, united with the camera positions the context has rendered from.
+    void origin_box(const float b[6], float amax, float out[6]) const {
+        const float m = 1e-3f * (1.0f + amax), L = 1e18f;
+        for (int k = 0; k < 3; ++k) {
+            float lo = b[k] - m, hi = b[3 + k] + m;
+            if (!(lo <= hi)) { lo = 0.f; hi = 0.f; }             // empty / NaN bounds
+            if (cam_valid) { lo = fminf(lo, cam_box[k]); hi = fmaxf(hi, cam_box[3 + k]); }
+            out[k] = fminf(fmaxf(lo, -L), L); out[3 + k] = fminf(fmaxf(hi, -L), L);
+        }
+    }
+    // A camera at `pos` outside the committed origin box `obox`: remember it, with room to move (an orbiting camera settles
+    // after a few frames).  Returns true when the sphere boxes have to be recomputed (refit) for the grown box.
+    bool cover_camera(const float pos[3], const float obox[6]) {
+        bool inside = true, finite = true;
+        for (int k = 0; k < 3; ++k) { finite = finite && std::isfinite(pos[k]); inside = inside && pos[k] >= obox[k] && pos[k] <= obox[3 + k]; }
+        if (inside || !finite) return false;
+        for (int k = 0; k < 3; ++k) {
+            float lo = cam_valid ? fminf(cam_box[k], pos[k]) : pos[k], hi = cam_valid ? fmaxf(cam_box[3 + k], pos[k]) : pos[k];
+            const float room = 0.25f * fmaxf(fmaxf(hi, obox[3 + k]) - fminf(lo, obox[k]), 0.f);
+            if (pos[k] < obox[k]) lo = pos[k] - room;
+            if (pos[k] > obox[3 + k]) hi = pos[k] + room;
+            cam_box[k] = lo; cam_box[3 + k] = hi;
+        }
+        cam_valid = true;
+        return true;
+    }
 
     // keeps the capacity of the staging vectors: a scene that is re-committed every frame (RayTracingSetup.cs:120-128) must
     // not pay for fresh pages each time (48 MB of first-touch page faults cost more than the copy itself)

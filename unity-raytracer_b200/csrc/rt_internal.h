@@ -74,6 +74,8 @@ struct RtOptions {
 };
 
 enum { RT_MAX_DEPTH = 64 };           // max_reflection_bounces is clamped to this
+enum { RT_STACK_ENTRIES = 116 };      // traversal stack entries per thread (rt_render.cu: 12 in shared memory + 104 in local memory);
+                                      // bounds the depth of any tree the builders may emit (LBVH: 96 key bits; SAH: rt_sah.h MAX_SAH_DEPTH)
 
 struct RtDevice {
     int device = -1;
@@ -86,6 +88,7 @@ struct RtDevice {
     RtScene S{};
     uint32_t n_nodes = 0;
     bool has_mirror = false;
+    float obox[6] = {0, 0, 0, 0, 0, 0};  // origin box the committed sphere boxes were inflated for (rt_sphere_box_radius)
     // refit (rt_scene_refit): the committed tree is kept and only its boxes are recomputed
     int32_t bvh_prims = -1, bvh_slots = 0, bvh_root = 0;   // primitive count / root ref of the tree in `nodes` (+ slot order in vals_alt); -1: none
     bool bvh_parents = false;           // node_parent holds the parents of this tree
@@ -109,7 +112,10 @@ struct RtDevice {
     struct Hints { DevBuf lists[2], counts[2]; };
     Hints hint_primary, hint_shadow;
     int hint_cur = 0; bool hint_ready = false;
-    long long hint_sig[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool hint_shadow_ready = false;          // the frame that recorded the hints launched its depth-0 shadow kernel(s) (it had lights)
+    static constexpr int HINT_SIG = 12;
+    long long hint_sig[HINT_SIG] = {0};
+    bool split_dirty = false;                // a frame was abandoned half-way: the per-light combine buffers may be non-zero
     std::vector<cudaEvent_t> fin_ev;        // spp passes: finalize of (pass p, wave i) follows finalize of (pass p-1, wave i)
     // ---- outputs: full-frame buffers. Owned on the gather device; other devices/ranks hold peer pointers ----
     DevBuf own_rgba32f, own_rgba8, own_hit_id, own_hit_t;

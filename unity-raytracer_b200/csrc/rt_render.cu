@@ -32,6 +32,7 @@ namespace {
 #endif
 constexpr int STK_CAP = RT_STK_CAP;   // shared-memory stack entries per thread
 constexpr int STK_OVF = 104;     // local-memory overflow entries (LBVH depth bound: 64 key bits + 32 index bits)
+static_assert(RT_STK_CAP != 12 || STK_CAP + STK_OVF == RT_STACK_ENTRIES, "rt_internal.h RT_STACK_ENTRIES is what the builders are checked against");
 
 // sp lives in a register; the (rarely used) overflow array is a separate local object so that indexing it dynamically
 // does not drag the whole stack object into local memory (ncu on the first version: one STL per push/pop for sp).
@@ -163,6 +164,9 @@ constexpr int C_TOTAL = C_WORK + 8 * (RT_MAX_DEPTH + 2);
 #ifdef RT_TILE_TIMING
 __device__ unsigned long long* g_rt_tile_dbg = nullptr;      // per tile: (start ns, duration ns); development aid only
 #endif
+// FAR (RtView::far_origin, a camera many scene extents away): per-lane loop with ray-dependent node padding (rt_far_pad) —
+// a kernel of its own so that its registers do not count against the packet loop's
+template <bool FAR>
 __global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                         float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work,
                                                         RtHintIn hin, RtHintOut hout) {
@@ -184,7 +188,8 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtSc
         if (valid) rt_primary_ray(V, x, y, si, sj, O, D);
         const f3 inv = rt_rcp3(D);
         if (valid) active = rt_scene_gate(S, O, inv);                                               // Scene.cs:54
-        if (S.packet) {                   // rays of one 8x4 pixel tile share the origin and are almost parallel
+        if (FAR) { if (active) rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+        else if (S.packet) {              // rays of one 8x4 pixel tile share the origin and are almost parallel
             if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
         } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
         size_t q = (size_t)t * 32 + lane;
@@ -406,7 +411,13 @@ __global__ void __launch_bounds__(128) k_intersect(RtScene S, int n, const float
         f3 O = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
         float bt = FLT_MAX; int bs = -1;
         const f3 inv = rt_rcp3(D);
-        if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); }
+        if (rt_scene_gate(S, O, inv)) {
+            // explicit rays come from anywhere: always the ray-padded walk.  A direction that is not normalised in binary32
+            // breaks what the sphere boxes assume (rt_sphere_box_radius), so such a ray scans the primitives like the reference.
+            const float dd = um_dot(D, D);
+            if (S.n_spheres > 0 && !(fabsf(dd - 1.0f) <= 0x1p-20f)) rt_scan_all(S, O, D, inv, bt, bs);
+            else { stk.sp = 0; rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+        }
         int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
         out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
     }
@@ -458,14 +469,18 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
     cudaStream_t st = D.stream;                 // stream of the wave being enqueued (one of the lanes')
     uint32_t launches = 0;
     D.kev_class.clear();
+    cudaError_t kev_err = cudaSuccess;          // first failure of the timing events (checked once after the launches)
     auto kbegin = [&](int cls) {
-        if (!opt.kernel_timing) return;
+        if (!opt.kernel_timing || kev_err != cudaSuccess) return;
         size_t i = D.kev_class.size();
-        while (D.kev_pool.size() < 2 * (i + 1)) { cudaEvent_t e; cudaEventCreate(&e); D.kev_pool.push_back(e); }
+        while (D.kev_pool.size() < 2 * (i + 1)) { cudaEvent_t e; if ((kev_err = cudaEventCreate(&e)) != cudaSuccess) return; D.kev_pool.push_back(e); }
         D.kev_class.push_back(cls);
-        cudaEventRecord(D.kev_pool[2 * i], st);
+        kev_err = cudaEventRecord(D.kev_pool[2 * i], st);
     };
-    auto kend = [&]() { if (opt.kernel_timing) cudaEventRecord(D.kev_pool[2 * (D.kev_class.size() - 1) + 1], st); };
+    auto kend = [&]() {
+        if (!opt.kernel_timing || kev_err != cudaSuccess || D.kev_class.empty()) return;
+        kev_err = cudaEventRecord(D.kev_pool[2 * (D.kev_class.size() - 1) + 1], st);
+    };
     RT_CUDA(D.stats.ensure(4 * 8));
     RT_CUDA(cudaMemsetAsync(D.stats.p, 0, 4 * 8, D.stream));
     RT_CUDA(cudaEventRecord(D.ev0, D.stream));
@@ -544,26 +559,39 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                 for (int d = 1; d <= maxd; ++d) RT_CUDA(L.link[d].ensure(W * 16));
             }
             RT_CUDA(L.occl.ensure(W * 4 * (size_t)(n_chunks < 1 ? 1 : n_chunks)));
-            if (opt.light_split != 0 && opt.fuse_shade && n_chunks == 1) {       // combine buffers of the per-light items: zero between uses
-                const void* p0 = L.split_occl.p; const void* p1 = L.split_acc.p;
-                RT_CUDA(L.split_occl.ensure(W * 4)); RT_CUDA(L.split_acc.ensure((size_t)wave_tiles * 8));
-                if (L.split_occl.p != p0) RT_CUDA(cudaMemsetAsync(L.split_occl.p, 0, L.split_occl.bytes, D.stream));
-                if (L.split_acc.p != p1) RT_CUDA(cudaMemsetAsync(L.split_acc.p, 0, L.split_acc.bytes, D.stream));
-            }
             if (li > 0) {
                 if (!L.own_stream) RT_CUDA(cudaStreamCreateWithFlags(&L.own_stream, cudaStreamNonBlocking));
                 if (!L.done) RT_CUDA(cudaEventCreateWithFlags(&L.done, cudaEventDisableTiming));
                 RT_CUDA(cudaStreamWaitEvent(L.own_stream, D.ev0, 0));        // after everything queued before this frame
             }
+            if (opt.light_split != 0 && opt.fuse_shade && n_chunks == 1) {
+                // Combine buffers of the per-light items.  Invariant: all zero between frames (the last item of a tile leaves
+                // its words zero).  They are zeroed when (re)allocated and after a frame that did not run to its end, on the
+                // stream of the lane that uses them, so the order against that lane's kernels never depends on another lane.
+                const void* p0 = L.split_occl.p; const void* p1 = L.split_acc.p;
+                RT_CUDA(L.split_occl.ensure(W * 4)); RT_CUDA(L.split_acc.ensure((size_t)wave_tiles * 8));
+                cudaStream_t ls = li ? L.own_stream : D.stream;
+                if (L.split_occl.p != p0 || D.split_dirty) RT_CUDA(cudaMemsetAsync(L.split_occl.p, 0, L.split_occl.bytes, ls));
+                if (L.split_acc.p != p1 || D.split_dirty) RT_CUDA(cudaMemsetAsync(L.split_acc.p, 0, L.split_acc.bytes, ls));
+            }
         }
+        D.split_dirty = true;                                               // until this frame's launches are all queued
         if (n_pass > 1) {
             RT_CUDA(D.accum.ensure((size_t)V.n_tiles * 32 * 16));
             while (n_lanes > 1 && (int)D.fin_ev.size() < waves_per_pass) { cudaEvent_t e; RT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); D.fin_ev.push_back(e); }
         }
         // ---- cost hints of the previous frame (same layout only) / recording for the next ----
-        const long long sig[8] = {V.n_tiles, (long long)wave_tiles * 64 + waves_per_pass, V.res_x, V.res_y, V.rank, V.world, V.band_rows, (long long)D.S.n_prims};
+        // Hints are used only when the previous frame RECORDED them under the same layout: tiles, wave plan, resolution,
+        // partition, scene size, and what the shadow pass looks like (a frame without lights launches no shadow kernel and
+        // leaves that kernel's class counts at zero — with them the fused kernel would hand out no tile at all).
+        const bool fuse = opt.fuse_shade && n_chunks == 1;                  // shade (+ finalize) inside the shadow kernel
+        long long plan_hash = 1469598103934665603ll;
+        for (int tbk : wave_tb) plan_hash = (plan_hash ^ tbk) * 1099511628211ll;
+        const long long sig[RtDevice::HINT_SIG] = {V.n_tiles, (long long)wave_tiles * 64 + waves_per_pass, V.res_x, V.res_y, V.rank, V.world, V.band_rows,
+                                                   (long long)D.S.n_prims, D.S.n_lights, fuse ? 1 : 0, plan_hash, n_pass};
         bool hint_in = opt.hints && D.hint_ready;
-        for (int k = 0; k < 8; ++k) hint_in = hint_in && D.hint_sig[k] == sig[k];
+        for (int k = 0; k < RtDevice::HINT_SIG; ++k) hint_in = hint_in && D.hint_sig[k] == sig[k];
+        const bool hint_in_shadow = hint_in && D.hint_shadow_ready;
         const bool hint_rec = opt.hints != 0;
         const int hb_in = D.hint_cur, hb_out = 1 - D.hint_cur;
         const size_t hstride = (size_t)V.n_tiles;
@@ -580,8 +608,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         const int lsplit = opt.light_split >= 0 ? opt.light_split : (V.world >= 4 ? 6 : 0);
         auto hin_of = [&](RtDevice::Hints& hh, int tb, int wi) {
             RtHintIn h{nullptr, nullptr, 0, RT_NCLS};
-            if (hint_in) h = RtHintIn{hh.lists[hb_in].as<int>() + tb, hh.counts[hb_in].as<unsigned>() + (size_t)wi * RT_NCLS, hstride,
-                                      (&hh == &D.hint_shadow && lsplit > 0) ? lsplit : RT_NCLS};
+            const bool shadow = &hh == &D.hint_shadow;
+            if (shadow ? hint_in_shadow : hint_in) h = RtHintIn{hh.lists[hb_in].as<int>() + tb, hh.counts[hb_in].as<unsigned>() + (size_t)wi * RT_NCLS, hstride,
+                                                                (shadow && lsplit > 0) ? lsplit : RT_NCLS};
             return h;
         };
         auto hout_of = [&](RtDevice::Hints& hh, int tb, int wi, bool on) {
@@ -589,9 +618,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             if (hint_rec && on) h = RtHintOut{hh.lists[hb_out].as<int>() + tb, hh.counts[hb_out].as<unsigned>() + (size_t)wi * RT_NCLS, hstride};
             return h;
         };
-        const int g_trace = persistent_grid(k_trace_primary, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_trace = V.far_origin ? persistent_grid(k_trace_primary<true>, block, smem, D.sm_count, opt.ctas_per_sm)
+                                         : persistent_grid(k_trace_primary<false>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_traceq = persistent_grid(k_trace_queue, block, smem, D.sm_count, opt.ctas_per_sm);
-        const bool fuse = opt.fuse_shade && n_chunks == 1;                  // shade (+ finalize) inside the shadow kernel
         const int g_shadow0 = fuse ? persistent_grid(k_trace_shadow<true, true>, block, smem, D.sm_count, opt.ctas_per_sm)
                                    : persistent_grid(k_trace_shadow<true, false>, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_shadown = fuse ? persistent_grid(k_trace_shadow<false, true>, block, smem, D.sm_count, opt.ctas_per_sm)
@@ -619,8 +648,10 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                     RT_CUDA(cudaMemsetAsync(C, 0, C_TOTAL * 4, st));
                     {
                     kbegin(RT_K_TRACE_PRIMARY);
-                    k_trace_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
-                                                                   hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
+                    if (V.far_origin) k_trace_primary<true><<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
+                                                                                           hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
+                    else k_trace_primary<false><<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
+                                                                              hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
                     kend(); ++launches;
                     }
                     for (int d = 0; d <= maxd; ++d) {
@@ -694,8 +725,10 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             RT_CUDA(cudaStreamWaitEvent(D.stream, D.lanes[li].done, 0));
         }
         RT_CUDA(cudaGetLastError());
-        if (hint_rec) { D.hint_cur = hb_out; D.hint_ready = true; for (int k = 0; k < 8; ++k) D.hint_sig[k] = sig[k]; }
+        RT_CUDA(kev_err);
+        if (hint_rec) { D.hint_cur = hb_out; D.hint_ready = true; D.hint_shadow_ready = n_chunks > 0; for (int k = 0; k < RtDevice::HINT_SIG; ++k) D.hint_sig[k] = sig[k]; }
         else D.hint_ready = false;
+        D.split_dirty = false;
         primary = (uint64_t)V.res_x * (uint64_t)V.n_local_rows * (uint64_t)n_pass;
     }
     RT_CUDA(cudaEventRecord(D.ev1, D.stream));

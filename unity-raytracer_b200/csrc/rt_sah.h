@@ -33,6 +33,8 @@ struct RtSahBuilder {
     std::atomic<int32_t> n_nodes{0};
     int spawn_depth = 0, threads_ = 1;
     static constexpr int NB = 16;             // bins per axis
+    static constexpr int MAX_SAH_DEPTH = 64;  // deeper ranges are halved by count (see build)
+    std::atomic<int> max_depth{0};            // deepest leaf of the last run (checked against the stack bound at commit)
 
     static inline float area(const float* lo, const float* hi) {
         float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
@@ -74,6 +76,7 @@ struct RtSahBuilder {
             for (int c = 0; c < par; ++c) { const float* q = part[(size_t)c].data(); grow(lo, hi, q, q + 3); grow(clo, chi, q + 6, q + 9); }
         }
         for (int k = 0; k < 3; ++k) { out_lo[k] = lo[k]; out_hi[k] = hi[k]; }
+        { int seen = max_depth.load(std::memory_order_relaxed); while (depth > seen && !max_depth.compare_exchange_weak(seen, depth, std::memory_order_relaxed)) {} }
         if (term <= 0.f ? cnt <= leaf_max : cnt == 1) return ~(b * 8 + (cnt - 1));
         if (term > 0.f && cnt <= 8) {
             // ---- small range: exact sweep over the sorted centroids of each axis; leaf unless a split pays ----
@@ -167,8 +170,13 @@ struct RtSahBuilder {
             }
         }
         int32_t mid;
+        // Depth bound.  The traversal stack (rt_render.cu SmemStack) holds 12 + 104 entries and an entry is pushed at most once
+        // per level, so a tree deeper than that would silently drop subtrees.  Binned splits on geometrically distributed
+        // primitives can peel one bin per level without end; from MAX_SAH_DEPTH on the range is halved by count instead, which
+        // ends after log2(2^28) = 28 more levels (+ 8 for the exact sweep of small ranges): 64 + 28 + 8 = 100 < 116.
+        if (depth >= MAX_SAH_DEPTH) best_axis = -1;
         if (best_axis < 0) {
-            mid = b + cnt / 2;                                   // all centroids coincide: split by count
+            mid = b + cnt / 2;                                   // all centroids coincide (or depth bound): split by count
         } else {
             const int ax = best_axis;
             const float scale = (float)NB / (chi[ax] - clo[ax]);
@@ -208,7 +216,7 @@ struct RtSahBuilder {
         order.resize(n);
         for (int32_t i = 0; i < n; ++i) order[i] = i;
         nodes.assign((size_t)16 * (n > 1 ? n - 1 : 1), 0.f);
-        n_nodes = 0;
+        n_nodes = 0; max_depth = 0;
         spawn_depth = 0; threads_ = threads < 1 ? 1 : threads;
         for (int t = threads_; t > 1; t >>= 1) ++spawn_depth;
         spawn_depth += 1;                                        // a few more tasks than threads, for balance
