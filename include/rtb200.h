@@ -134,7 +134,11 @@ int rt_scene_refit(rt_ctx* ctx, const float scene_aabb[6]);
  * out_hit_id  : X*Y*3 int32 {Type, Index, MeshIndex} of the PRIMARY hit (IntersectionResult.ObjectId, ObjectId.cs:7-9);
  *               MeshIndex is -1 unless Type == RT_TYPE_MESH_TRIANGLE; miss = {0,-1,-1}
  * out_hit_t   : X*Y floats, IntersectionResult.Distance of the primary hit, FLT_MAX on a miss (Scene.cs:45)
- * pixel index = x + y*res_x, y = 0 is the top row (RTS:243-246). Any output may be NULL. */
+ * pixel index = x + y*res_x, y = 0 is the top row (RTS:243-246). Any output may be NULL.
+ * Several devices (rt_create with n_devices > 1): every device copies the bands it rendered to the caller's arrays over its
+ * own PCIe link, wave by wave while it still renders — a 4K Color[] frame is 2.3 ms of ONE link.  A ctx that holds a
+ * partition of the frame (rt_set_partition, one process per GPU) writes ONLY its own bands: all ranks pass the same
+ * full-frame arrays (shared memory) and the frame is complete when every rank has returned. */
 int rt_render(rt_ctx* ctx, const rt_render_params* params, float* out_rgba32f, uint8_t* out_rgba8,
               int32_t* out_hit_id, float* out_hit_t, rt_stats* stats);
 
@@ -142,7 +146,8 @@ int rt_render(rt_ctx* ctx, const rt_render_params* params, float* out_rgba32f, u
  * `want` is a bit mask of RT_OUT_*. Asynchronous with respect to the host only if rt_set_stream gave a stream. */
 enum { RT_OUT_RGBA32F = 1, RT_OUT_RGBA8 = 2, RT_OUT_HIT_ID = 4, RT_OUT_HIT_T = 8 };
 int rt_render_device(rt_ctx* ctx, const rt_render_params* params, int want, rt_stats* stats);
-/* copy the device framebuffers of the last rt_render_device out to host memory (any pointer may be NULL) */
+/* copy the device framebuffers of the last rt_render_device out to host memory (any pointer may be NULL); RT_E_STATE after
+ * an rt_render of a multi-device / partitioned ctx, which gathers nothing on the device */
 int rt_read_outputs(rt_ctx* ctx, float* out_rgba32f, uint8_t* out_rgba8, int32_t* out_hit_id, float* out_hit_t);
 /* raw device pointers of those framebuffers (NULL when not allocated): for zero-copy consumers / NCCL gathers */
 int rt_device_outputs(rt_ctx* ctx, void** rgba32f, void** rgba8, void** hit_id, void** hit_t);
@@ -189,7 +194,8 @@ int rt_host_unregister(rt_ctx* ctx, void* ptr);
  *                  2^depth clipped pieces (reference pre-splitting; measured slower for packet traversal, default 0 = off)
  *   sah_term       host SAH builder: > 0 = SAH-driven leaf termination (node step cost / primitive test cost) for ranges of <= 8 primitives (default 0 = split down to leaf_max)
  *   copy_waves     number of waves rt_render splits a frame into so that the copy-out of one wave overlaps the kernels of the
- *                  next (default 8, 1 = off)
+ *                  next (default 8, 1 = off); copy_waves_part: the same for a device that renders a band partition (0 = auto:
+ *                  4 on a half frame, 2 below)
  *   chunk_pixels   upper bound of a wave in pixels (bounds the wave buffers)
  *   ctas_per_sm    cap on the resident CTAs per SM of the persistent kernels (0 = occupancy limit)
  *   prefetch, prefetch_max_mb   bulk L2 prefetch of nodes + primitives at the start of a frame when they fit (default off)

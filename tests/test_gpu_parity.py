@@ -880,3 +880,30 @@ def test_sphere_silhouettes_match_the_scan(rtb, scenes, oracle):
         gid, gt = r.intersect(O, D)
         assert np.array_equal(rid[:, :2], gid[:, :2]) and np.array_equal(rt_, gt, equal_nan=True)
         r.close()
+
+
+@pytest.mark.parametrize("world,band_rows,res", [(2, 32, (640, 360)), (4, 32, (512, 777)), (8, 16, (300, 1100)), (3, 8, (129, 431))])
+def test_ranks_copy_their_bands_into_one_host_frame(rtb, scenes, world, band_rows, res):
+    """rt_render on a partition: the rank renders into its own framebuffer and copies ONLY its bands, wave by wave, straight
+    into the caller's full-frame arrays (one shared host frame for all ranks — bench.py's N-GPU e2e path, where it is a POSIX
+    shared-memory segment).  After every rank has rendered into the same arrays they hold the 1-rank frame, bit for bit, for
+    every output, whatever the wave count; rows of other ranks are never touched."""
+    s = scenes.random_soup(seed=5)
+    p = scenes.soup_params(res[0], res[1], 2, 1)
+    full = rtb.RayTracer((0,)); full.set_scene(s); ref = full.render(p); full.close()
+    for waves in (0, 1, 3):
+        frame = rtb.RayTracer.alloc_host_outputs(p)
+        frame["rgba32f"][:] = -7.0; frame["hit_t"][:] = -7.0; frame["hit_id"][:] = -7; frame["rgba8"][:] = 7
+        for r in range(world):
+            part = rtb.RayTracer((0,)); part.set_partition(r, world, band_rows); part.set_option("copy_waves_part", waves)
+            part.set_scene(s)
+            before = {k: frame[k].copy() for k in ("rgba32f", "rgba8", "hit_id", "hit_t")}
+            part.render(p, out=frame)
+            rows = np.arange(res[1]); mine = np.repeat(((rows // band_rows) % world) == r, res[0])
+            for k in before:
+                assert np.array_equal(frame[k][~mine], before[k][~mine], equal_nan=True), (world, r, k, "foreign rows written")
+            with pytest.raises(rtb.host.RtError):            # nothing was gathered: rt_read_outputs must say so
+                part.read_outputs(p)
+            part.close()
+        for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+            assert np.array_equal(frame[k], ref[k], equal_nan=True), (world, waves, k)

@@ -3,6 +3,7 @@
 #include "rt_internal.h"
 #include <new>
 #include <chrono>
+#include <thread>
 
 struct rt_ctx {
     std::vector<RtDevice> devs;
@@ -15,6 +16,7 @@ struct rt_ctx {
     int ext_rank = 0, ext_world = 1, band_rows = 32;
     int last_res_x = 0, last_res_y = 0, last_want = 0;
     bool stats_pending = false;
+    bool last_local = false;                                // the last render wrote per-device framebuffers (rt_render), not the gather target
     float stream_ms = 0.f; uint64_t stream_bytes = 0;      // streaming commit: time / bytes spent inside rt_scene_mesh
     std::vector<RtFrameStats> fstats;
 };
@@ -48,8 +50,7 @@ void device_release(RtDevice& D) {
     for (auto* hh : {&D.hint_primary, &D.hint_shadow}) for (int k = 0; k < 2; ++k) { hh->lists[k].release(); hh->counts[k].release(); }
     for (cudaEvent_t e : D.fin_ev) cudaEventDestroy(e);
     D.fin_ev.clear();
-    void* imp[4] = {D.o_rgba32f, D.o_rgba8, D.o_hit_id, D.o_hit_t};
-    for (int k = 0; k < 4; ++k) if (D.imported[k] && imp[k]) cudaIpcCloseMemHandle(imp[k]);
+    for (int k = 0; k < 4; ++k) if (D.imported[k] && D.imp[k]) { cudaIpcCloseMemHandle(D.imp[k]); D.imp[k] = nullptr; D.imported[k] = false; }
     for (cudaEvent_t e : D.kev_pool) cudaEventDestroy(e);
     D.kev_pool.clear();
     if (D.ev0) cudaEventDestroy(D.ev0);
@@ -66,22 +67,25 @@ size_t out_bytes(int k, int rx, int ry) {
     return k == 0 ? px * 16 : (k == 1 ? px * 4 : (k == 2 ? px * 12 : px * 4));
 }
 
-// allocate (on device 0) the full-frame outputs named in `want`; point every device at them (peer mappings in-process)
-int ensure_outputs(rt_ctx* c, int rx, int ry, int want) {
+// Where the next render writes.  gather (rt_render_device): the full-frame buffers of device 0 (or the ones imported from
+// rank 0's process), every device pointing at them — peer stores over NVLink.  local (rt_render, host outputs): every device
+// its OWN full-frame-indexed buffers, of which it fills only its bands and copies them out over its own PCIe link.
+int ensure_outputs(rt_ctx* c, int rx, int ry, int want, bool local) {
     std::string& err = c->err;
-    RtDevice& D0 = c->devs[0];
-    RT_CUDA(cudaSetDevice(D0.device));
-    DevBuf* own[4] = {&D0.own_rgba32f, &D0.own_rgba8, &D0.own_hit_id, &D0.own_hit_t};
-    void** ptr[4] = {&D0.o_rgba32f, &D0.o_rgba8, &D0.o_hit_id, &D0.o_hit_t};
-    for (int k = 0; k < 4; ++k) {
-        if (!(want & (1 << k)) || D0.imported[k]) continue;
-        RT_CUDA(own[k]->ensure(out_bytes(k, rx, ry)));
-        *ptr[k] = own[k]->p;
-    }
-    D0.out_res_x = rx; D0.out_res_y = ry;
-    for (size_t i = 1; i < c->devs.size(); ++i) {
+    for (size_t i = 0; i < c->devs.size(); ++i) {
         RtDevice& D = c->devs[i];
-        D.o_rgba32f = D0.o_rgba32f; D.o_rgba8 = D0.o_rgba8; D.o_hit_id = D0.o_hit_id; D.o_hit_t = D0.o_hit_t;
+        RtDevice& D0 = c->devs[0];
+        DevBuf* own[4] = {&D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t};
+        void** ptr[4] = {&D.o_rgba32f, &D.o_rgba8, &D.o_hit_id, &D.o_hit_t};
+        void* first[4] = {D0.o_rgba32f, D0.o_rgba8, D0.o_hit_id, D0.o_hit_t};
+        for (int k = 0; k < 4; ++k) {
+            if (!(want & (1 << k))) continue;
+            if (!local && i > 0) { *ptr[k] = first[k]; continue; }
+            if (!local && D.imported[k]) { *ptr[k] = D.imp[k]; continue; }
+            RT_CUDA(cudaSetDevice(D.device));
+            RT_CUDA(own[k]->ensure(out_bytes(k, rx, ry)));
+            *ptr[k] = own[k]->p;
+        }
         D.out_res_x = rx; D.out_res_y = ry;
     }
     return RT_OK;
@@ -156,23 +160,108 @@ int cover_origin(rt_ctx* c, const float pos[3]) {
     return rc;
 }
 
-int render_device_impl(rt_ctx* c, const rt_render_params* p, int want, int split = 0) {
+// host destinations of rt_render (NULL members: not wanted); null pointer = rt_render_device
+struct HostDst { char* p[4]; };
+
+// rt_render: host buffers out.  Every device renders its bands into its own framebuffer in waves of whole pixel rows and
+// copies wave k out on its copy stream — over its OWN PCIe link, straight into the caller's arrays — while wave k+1
+// renders.  The 4K Color[] frame is 132.7 MB, i.e. 2.3 ms of one PCIe Gen5 link, as long as the render itself: one device
+// hides the render behind the copy; N devices divide the copy by N (a frame gathered on one GPU first would leave through
+// that GPU's single link and take the same 2.3 ms however many GPUs rendered it).
+// A wave is a range of LOCAL rows of the device's band partition; a band is contiguous in the frame.
+int copy_rows_out(RtDevice& D, const RtView& V, int lr0, int lr1, char* const dst[4], std::string& err, uint64_t& bytes) {
+    char* src[4] = {(char*)D.o_rgba32f, (char*)D.o_rgba8, (char*)D.o_hit_id, (char*)D.o_hit_t};
+    const size_t bpp[4] = {16, 4, 12, 4};
+    const size_t rx = (size_t)V.res_x;
+    for (int r = lr0; r < lr1;) {
+        int y0, n;
+        if (V.world == 1) { y0 = r; n = lr1 - r; }
+        else {
+            const int lb = r / V.band_rows, in_band = r % V.band_rows;
+            y0 = (lb * V.world + V.rank) * V.band_rows + in_band;
+            n = V.band_rows - in_band;
+            if (n > lr1 - r) n = lr1 - r;
+        }
+        if (y0 + n > V.res_y) n = V.res_y - y0;
+        if (n <= 0) break;
+        for (int k = 0; k < 4; ++k) {
+            if (!dst[k]) continue;
+            const size_t off = (size_t)y0 * rx * bpp[k], len = (size_t)n * rx * bpp[k];
+            RT_CUDA(cudaMemcpyAsync(dst[k] + off, src[k] + off, len, cudaMemcpyDeviceToHost, D.copy_stream));
+            bytes += len;
+        }
+        r += n;
+    }
+    return RT_OK;
+}
+
+// queued right behind the device's launches (same host thread): waits for each wave's event on the device's copy stream
+int enqueue_copy_out(rt_ctx* c, size_t i, const RtView& V, const HostDst& dst, std::string& err, uint64_t& bytes) {
+    RtDevice& D = c->devs[i];
+    RT_CUDA(cudaSetDevice(D.device));
+    if (!D.copy_stream) RT_CUDA(cudaStreamCreateWithFlags(&D.copy_stream, cudaStreamNonBlocking));
+    if (D.wave_marks.empty()) {                                  // not split: everything after the frame
+        RT_CUDA(cudaStreamWaitEvent(D.copy_stream, D.ev1, 0));
+        return copy_rows_out(D, V, 0, V.n_local_rows, dst.p, err, bytes);
+    }
+    for (size_t w = 0; w < D.wave_marks.size(); ++w) {
+        RT_CUDA(cudaStreamWaitEvent(D.copy_stream, D.wave_ev[w], 0));
+        int rc = copy_rows_out(D, V, D.wave_marks[w].row0, D.wave_marks[w].row1, dst.p, err, bytes);
+        if (rc) return rc;
+#ifdef RT_WAVE_TRACE
+        {   // development aid (-DRT_WAVE_TRACE): when each wave finished rendering / copying, relative to the frame's first event
+            static std::vector<cudaEvent_t> cev;
+            while (cev.size() <= w) { cudaEvent_t e; cudaEventCreate(&e); cev.push_back(e); }
+            cudaEventRecord(cev[w], D.copy_stream);
+            if (w + 1 == D.wave_marks.size()) {
+                cudaStreamSynchronize(D.copy_stream); cudaStreamSynchronize(D.stream);
+                if (getenv("RTB200_WAVE_TRACE")) for (size_t k = 0; k <= w; ++k) {
+                    float tr = 0.f, tc = 0.f; cudaEventElapsedTime(&tr, D.ev0, D.wave_ev[k]); cudaEventElapsedTime(&tc, D.ev0, cev[k]);
+                    fprintf(stderr, "dev %zu wave %zu rows %d..%d rendered at %.3f ms, copied at %.3f ms\n", i, k, D.wave_marks[k].row0, D.wave_marks[k].row1, tr, tc);
+                }
+            }
+        }
+#endif
+    }
+    return RT_OK;
+}
+
+int render_device_impl(rt_ctx* c, const rt_render_params* p, int want, int split = 0, const HostDst* host = nullptr) {
     int rc = validate_params(c, p);
     if (rc) return rc;
     if (!c->committed) return fail(c, RT_E_STATE, "rt_render before rt_scene_commit");
     if ((rc = cover_origin(c, p->pos))) return rc;
+    const bool local = host != nullptr;
     c->last_res_x = p->res_x; c->last_res_y = p->res_y; c->last_want = want;
     c->stats.rays_primary = c->stats.rays_shadow = c->stats.rays_mirror = 0;
     c->stats.ms_render = 0.f; c->stats.kernel_launches = 0; c->stats.ms_d2h = 0.f; c->stats.d2h_bytes = 0;
     if ((int64_t)p->res_x * p->res_y == 0) { c->stats_pending = false; return RT_OK; }     // 0x0 ImagePlane: a no-op
-    rc = ensure_outputs(c, p->res_x, p->res_y, want);
+    rc = ensure_outputs(c, p->res_x, p->res_y, want, local);
     if (rc) return rc;
-    c->fstats.assign(c->devs.size(), RtFrameStats{});
-    for (size_t i = 0; i < c->devs.size(); ++i) {
+    c->last_local = local;
+    const size_t nd = c->devs.size();
+    c->fstats.assign(nd, RtFrameStats{});
+    std::vector<uint64_t> bytes(nd, 0);
+    auto one = [&](size_t i, std::string& err) -> int {
         RtView V = make_view(c, p, (int)i);
-        rc = rt_device_render(c->devs[i], V, want, c->opt, c->err, &c->fstats[i], split ? split : (c->opt.waves > 0 ? c->opt.waves : (V.world >= 4 ? 1 : 2)));
-        if (rc) return rc;
+        int r = rt_device_render(c->devs[i], V, want, c->opt, err, &c->fstats[i], split ? split : (c->opt.waves > 0 ? c->opt.waves : (V.world >= 4 ? 1 : 2)));
+        if (r == RT_OK && host) r = enqueue_copy_out(c, i, V, *host, err, bytes[i]);
+        return r;
+    };
+    if (nd == 1) rc = one(0, c->err);
+    else {
+        // one host thread per device: queueing a frame's launches takes ~0.1 ms of host time, which run one device after the
+        // other would start the last of 8 devices most of a frame late
+        std::vector<std::string> errs(nd);
+        std::vector<int> rcs(nd, RT_OK);
+        std::vector<std::thread> pool;
+        for (size_t i = 1; i < nd; ++i) pool.emplace_back([&, i]() { rcs[i] = one(i, errs[i]); });
+        rcs[0] = one(0, errs[0]);
+        for (auto& t : pool) t.join();
+        for (size_t i = 0; i < nd && rc == RT_OK; ++i) if (rcs[i]) { rc = rcs[i]; c->err = errs[i]; }
     }
+    if (rc) return rc;
+    for (uint64_t b : bytes) c->stats.d2h_bytes += b;
     c->stats_pending = true;
     return RT_OK;
 }
@@ -452,6 +541,8 @@ int rt_read_outputs(rt_ctx* c, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, 
     if (rc) return rc;
     RtDevice& D0 = c->devs[0];
     RT_CUDA(cudaSetDevice(D0.device));
+    if (c->last_local && (c->devs.size() > 1 || c->ext_world > 1))
+        return fail(c, RT_E_STATE, "rt_read_outputs after rt_render of a partition: the frame was not gathered (use rt_render_device)");
     void* dst[4] = {rgba32f, rgba8, hit_id, hit_t};
     void* src[4] = {D0.o_rgba32f, D0.o_rgba8, D0.o_hit_id, D0.o_hit_t};
     auto t0 = std::chrono::steady_clock::now();
@@ -468,61 +559,25 @@ int rt_read_outputs(rt_ctx* c, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, 
     return RT_OK;
 }
 
-// rt_render with one device: the frame is rendered in `copy_waves` waves of whole pixel rows and the copy-out of wave k
-// (on a second stream, after the wave's event) overlaps the kernels of wave k+1.  The 4K Color[] frame is 132.7 MB, i.e.
-// ~2.4 ms over PCIe Gen5 — as long as the render itself — so without the overlap the call would take twice as long.
-static int read_outputs_pipelined(rt_ctx* c, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t) {
-    std::string& err = c->err;
-    RtDevice& D = c->devs[0];
-    RT_CUDA(cudaSetDevice(D.device));
-    if (!D.copy_stream) RT_CUDA(cudaStreamCreateWithFlags(&D.copy_stream, cudaStreamNonBlocking));
-    const size_t rx = (size_t)c->last_res_x;
-    char* dst[4] = {(char*)rgba32f, (char*)rgba8, (char*)hit_id, (char*)hit_t};
-    char* src[4] = {(char*)D.o_rgba32f, (char*)D.o_rgba8, (char*)D.o_hit_id, (char*)D.o_hit_t};
-    const size_t bpp[4] = {16, 4, 12, 4};
-    auto t0 = std::chrono::steady_clock::now();
-    uint64_t bytes = 0;
-    for (size_t w = 0; w < D.wave_marks.size(); ++w) {
-        RT_CUDA(cudaStreamWaitEvent(D.copy_stream, D.wave_ev[w], 0));
-        const size_t r0 = (size_t)D.wave_marks[w].row0, r1 = (size_t)D.wave_marks[w].row1;
-        for (int k = 0; k < 4; ++k) {
-            if (!dst[k] || r1 <= r0) continue;
-            const size_t off = r0 * rx * bpp[k], len = (r1 - r0) * rx * bpp[k];
-            RT_CUDA(cudaMemcpyAsync(dst[k] + off, src[k] + off, len, cudaMemcpyDeviceToHost, D.copy_stream));
-            bytes += len;
-        }
-#ifdef RT_WAVE_TRACE
-        {   // development aid (-DRT_WAVE_TRACE): when each wave finished rendering / copying, relative to the frame's first event
-            static std::vector<cudaEvent_t> cev;
-            while (cev.size() <= w) { cudaEvent_t e; cudaEventCreate(&e); cev.push_back(e); }
-            cudaEventRecord(cev[w], D.copy_stream);
-            if (w + 1 == D.wave_marks.size()) {
-                cudaStreamSynchronize(D.copy_stream); cudaStreamSynchronize(D.stream);
-                if (getenv("RTB200_WAVE_TRACE")) for (size_t k = 0; k <= w; ++k) {
-                    float tr = 0.f, tc = 0.f; cudaEventElapsedTime(&tr, D.ev0, D.wave_ev[k]); cudaEventElapsedTime(&tc, D.ev0, cev[k]);
-                    fprintf(stderr, "wave %zu rows %d..%d rendered at %.3f ms, copied at %.3f ms\n", k, D.wave_marks[k].row0, D.wave_marks[k].row1, tr, tc);
-                }
-            }
-        }
-#endif
-    }
-    RT_CUDA(cudaStreamSynchronize(D.copy_stream));
-    RT_CUDA(cudaStreamSynchronize(D.stream));
-    c->stats.ms_d2h = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
-    c->stats.d2h_bytes = bytes;
-    return RT_OK;
-}
-
 int rt_render(rt_ctx* c, const rt_render_params* p, float* rgba32f, uint8_t* rgba8, int32_t* hit_id, float* hit_t, rt_stats* stats) {
     if (!c) return RT_E_INVALID;
     int want = (rgba32f ? RT_OUT_RGBA32F : 0) | (rgba8 ? RT_OUT_RGBA8 : 0) | (hit_id ? RT_OUT_HIT_ID : 0) | (hit_t ? RT_OUT_HIT_T : 0);
-    const bool pipelined = want && c->devs.size() == 1 && c->ext_world == 1 && c->opt.copy_waves > 1 && p && p->res_y >= 64 &&
-                           !c->devs[0].imported[0] && !c->devs[0].imported[1] && !c->devs[0].imported[2] && !c->devs[0].imported[3];
-    int rc = render_device_impl(c, p, want, pipelined ? -c->opt.copy_waves : 0);
+    const int world = c->ext_world * (int)c->devs.size();
+    int cw = world == 1 ? c->opt.copy_waves : (c->opt.copy_waves_part > 0 ? c->opt.copy_waves_part : (world == 2 ? 4 : 2));
+    const bool pipelined = want && cw > 1 && p && p->res_y / world >= 64;
+    const HostDst dst{{(char*)rgba32f, (char*)rgba8, (char*)hit_id, (char*)hit_t}};
+    auto t0 = std::chrono::steady_clock::now();
+    int rc = render_device_impl(c, p, want, pipelined ? -cw : 0, &dst);
     if (rc) return rc;
-    if (pipelined && !c->devs[0].wave_marks.empty()) rc = read_outputs_pipelined(c, rgba32f, rgba8, hit_id, hit_t);
-    else rc = rt_read_outputs(c, rgba32f, rgba8, hit_id, hit_t);
-    if (rc) return rc;
+    if (p && (int64_t)p->res_x * p->res_y > 0) {
+        std::string& err = c->err;
+        for (auto& D : c->devs) {
+            RT_CUDA(cudaSetDevice(D.device));
+            if (D.copy_stream) RT_CUDA(cudaStreamSynchronize(D.copy_stream));
+            RT_CUDA(cudaStreamSynchronize(D.stream));
+        }
+        c->stats.ms_d2h = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();   // launches + copies, wall
+    }
     if (stats) { rc = rt_get_stats(c, stats); if (rc) return rc; }
     return RT_OK;
 }
@@ -618,7 +673,7 @@ int rt_set_partition(rt_ctx* c, int rank, int world, int band_rows) {
 int rt_alloc_outputs(rt_ctx* c, int res_x, int res_y, int want) {
     if (!c) return RT_E_INVALID;
     if (res_x < 0 || res_y < 0) return fail(c, RT_E_INVALID, "negative resolution");
-    return ensure_outputs(c, res_x, res_y, want);
+    return ensure_outputs(c, res_x, res_y, want, false);
 }
 
 int rt_export_outputs(rt_ctx* c, void* handles) {
@@ -627,7 +682,7 @@ int rt_export_outputs(rt_ctx* c, void* handles) {
     RtDevice& D0 = c->devs[0];
     RT_CUDA(cudaSetDevice(D0.device));
     memset(handles, 0, 4 * sizeof(cudaIpcMemHandle_t));
-    void* ptr[4] = {D0.o_rgba32f, D0.o_rgba8, D0.o_hit_id, D0.o_hit_t};
+    void* ptr[4] = {D0.own_rgba32f.p, D0.own_rgba8.p, D0.own_hit_id.p, D0.own_hit_t.p};
     for (int k = 0; k < 4; ++k) {
         if (!ptr[k] || D0.imported[k]) continue;
         cudaIpcMemHandle_t h;
@@ -647,10 +702,10 @@ int rt_import_outputs(rt_ctx* c, const void* handles, int res_x, int res_y, int 
         if (!(want & (1 << k))) continue;
         cudaIpcMemHandle_t h;
         memcpy(&h, (const char*)handles + k * sizeof(h), sizeof(h));
-        if (D0.imported[k] && *ptr[k]) { cudaIpcCloseMemHandle(*ptr[k]); *ptr[k] = nullptr; D0.imported[k] = false; }
+        if (D0.imported[k] && D0.imp[k]) { cudaIpcCloseMemHandle(D0.imp[k]); D0.imp[k] = nullptr; *ptr[k] = nullptr; D0.imported[k] = false; }
         void* p = nullptr;
         RT_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
-        *ptr[k] = p; D0.imported[k] = true;
+        *ptr[k] = p; D0.imp[k] = p; D0.imported[k] = true;
     }
     D0.out_res_x = res_x; D0.out_res_y = res_y;
     for (size_t i = 1; i < c->devs.size(); ++i) {
@@ -684,6 +739,7 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "light_split") { c->opt.light_split = (int)value; }
     else if (k == "hints") { c->opt.hints = value != 0; }
     else if (k == "copy_plan") { if (value < 0) return fail(c, RT_E_INVALID, "copy_plan < 0"); c->opt.copy_plan = (long long)value; }
+    else if (k == "copy_waves_part") { if (value < 0 || value > 64) return fail(c, RT_E_INVALID, "copy_waves_part must be 0 (auto) or 1..64"); c->opt.copy_waves_part = (int)value; }
     else if (k == "copy_waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "copy_waves must be 1..64"); c->opt.copy_waves = (int)value; }
     else if (k == "builder") { if (value != 0 && value != 1) return fail(c, RT_E_INVALID, "builder must be 0 (device LBVH) or 1 (host SAH)"); c->opt.builder = (int)value; }
     else if (k == "kernel_timing") { c->opt.kernel_timing = value != 0; }

@@ -57,8 +57,10 @@ struct RtOptions {
     int deep_lanes = 8;                // lanes of a frame with mirror depths AND >= 4 waves (spp passes): its queue kernels trace few,
                                        // incoherent rays each and last as long as their longest ray, so many of them run side by side
     long long copy_plan = 0;           // development: wave plan of the pipelined copy-out as decimal digits (sixteenths of the rows per wave, sum 16); 0 = 1244221
-    int copy_waves = 8;                // rt_render (host outputs, 1 device): frame split into this many waves so that the
-                                       // device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
+    int copy_waves = 8;                // rt_render (host outputs): a device that renders the whole frame splits it into this many waves
+                                       // so that the device->host copy of wave k overlaps the kernels of wave k+1 (1 = no overlap)
+    int copy_waves_part = 0;           // the same for a device that renders a band partition (several devices / ranks, each copying its
+                                       // own bands out over its own PCIe link); 0 = auto: 4 waves on a half frame, 2 below
     int fuse_shade = 1;                // shading (+ pixel write at depth 0) inside the shadow-trace kernel when <= 32 lights
     int prefetch = 0;                  // bulk L2 prefetch of nodes + primitives at the start of every frame ...
     int prefetch_max_mb = 96;          // ... when they total at most this many MiB (L2 is 126 MB)
@@ -119,8 +121,9 @@ struct RtDevice {
     std::vector<cudaEvent_t> fin_ev;        // spp passes: finalize of (pass p, wave i) follows finalize of (pass p-1, wave i)
     // ---- outputs: full-frame buffers. Owned on the gather device; other devices/ranks hold peer pointers ----
     DevBuf own_rgba32f, own_rgba8, own_hit_id, own_hit_t;
-    void* o_rgba32f = nullptr; void* o_rgba8 = nullptr; void* o_hit_id = nullptr; void* o_hit_t = nullptr;
+    void* o_rgba32f = nullptr; void* o_rgba8 = nullptr; void* o_hit_id = nullptr; void* o_hit_t = nullptr;   // targets of the NEXT render
     bool imported[4] = {false, false, false, false};
+    void* imp[4] = {nullptr, nullptr, nullptr, nullptr};   // gather targets imported from another process (rt_import_outputs)
     int out_res_x = 0, out_res_y = 0;
     // partition
     int rank = 0, world = 1;

@@ -493,7 +493,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         int wave_tiles = (opt.chunk_pixels / 32) < 1 ? 1 : (opt.chunk_pixels / 32);
         if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
         const int chunk_tiles = wave_tiles;                                 // capacity limit set by chunk_pixels
-        bool mark = split < 0 && V.world == 1;
+        bool mark = split < 0;
         const int n_split = split < 0 ? -split : split;
         if (n_split > 1) {
             // waves of whole tile rows (4 pixel rows each): a finished wave is a contiguous block of the (1-rank) frame
@@ -717,7 +717,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
 #endif
                         RT_CUDA(cudaEventRecord(D.wave_ev[i], st));
                         const int r0 = (tb / V.tiles_x) * 4, r1 = ((tb + nt) / V.tiles_x) * 4;
-                        D.wave_marks.push_back(RtDevice::WaveMark{r0, r1 < V.res_y ? r1 : V.res_y});
+                        D.wave_marks.push_back(RtDevice::WaveMark{r0, r1 < V.n_local_rows ? r1 : V.n_local_rows});   // LOCAL rows of this partition
                     }
                 }
         for (int li = 1; li < n_lanes; ++li) {                               // join the lanes back into the caller's stream
