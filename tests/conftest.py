@@ -52,7 +52,20 @@ def compare_renders(ref, got, check_float=True):
     if check_float:
         a, b = ref["rgba32f"], got["rgba32f"]
         out["f32"] = int(((a != b) & ~(np.isnan(a) & np.isnan(b))).any(axis=1).sum())
+        out["f32_far"] = float_far(a, b)
     return out
+
+
+def float_far(a, b, ulps=8):
+    """pixels whose float colour differs by MORE than a last-bits difference of one term (|a - b| > ulps * 2^-24 * max|.|):
+    the only legitimate source of a float mismatch is the Blinn-Phong pow() (CUDA's double pow vs glibc's, <= 1 ulp of a
+    double apart, which can flip the rounding of (float)pow and then moves the pixel by an ulp or two of the sum)"""
+    a, b = a.astype(np.float64), b.astype(np.float64)
+    with np.errstate(invalid="ignore"):
+        tol = ulps * 2.0 ** -24 * np.maximum(np.maximum(np.abs(a), np.abs(b)), 1e-30)
+        bad = (np.abs(a - b) > tol) & ~(np.isnan(a) & np.isnan(b)) & ~((a == b))
+        bad |= np.isnan(a) != np.isnan(b)
+    return int(bad.any(axis=1).sum())
 
 
 def degenerate_scene(scenes, nan=False):
