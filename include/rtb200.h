@@ -155,6 +155,20 @@ int rt_device_outputs(rt_ctx* ctx, void** rgba32f, void** rgba8, void** hit_id, 
 /* Scene.IntersectRay(Ray) for n explicit rays (Scene.cs:43-122): out_id 3 int32 each, out_t 1 float each. */
 int rt_intersect(rt_ctx* ctx, const float* origins, const float* directions, int n, int32_t* out_id, float* out_t);
 
+/* rt_intersect without any device allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, same results as rt_intersect, but the rays and results are staged in a file-scope device array of the library
+ * (RT_INTERSECT_STATIC_MAX rays x 40 bytes = 2.5 MiB, held by every GPU that loads librtb200.so until the process exits) instead
+ * of per-call cudaMalloc'ed buffers; the call makes no cudaMalloc / cudaFree / allocating library call.  n above
+ * RT_INTERSECT_STATIC_MAX: RT_E_INVALID (split the batch).  Every call on a device shares that one array, which keeps the last
+ * call's contents (nothing in it needs clearing: each call overwrites what it reads back): calls that overlap on the same GPU —
+ * two contexts, or two host threads — race and must be serialised by the caller.  Single device (device_ids[0]).  Because it may not
+ * re-fit the sphere boxes (that allocates), a ray whose origin lies outside the origin box of the last commit (scene bounds united
+ * with the camera positions rendered from so far) in a scene that has spheres takes the reference's linear scan over all primitives:
+ * identical result, O(primitives) time. */
+#define RT_INTERSECT_STATIC_MAX 65536
+int rt_intersect_static(rt_ctx* ctx, const float* origins, const float* directions, int n, int32_t* out_id, float* out_t);
+
 int rt_get_stats(rt_ctx* ctx, rt_stats* stats);
 
 /* ---- one-process-per-GPU plumbing (torchrun / NCCL launches) ------------------------------------------------- */

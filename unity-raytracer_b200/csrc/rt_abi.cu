@@ -653,6 +653,18 @@ int rt_intersect(rt_ctx* c, const float* origins, const float* dirs, int n, int3
     return rc;
 }
 
+// no counterpart in the reference (include/rtb200.h): rt_intersect with its staging in a static device array, no allocation
+int rt_intersect_static(rt_ctx* c, const float* origins, const float* dirs, int n, int32_t* out_id, float* out_t) {
+    if (!c) return RT_E_INVALID;
+    if (!c->committed) return fail(c, RT_E_STATE, "rt_intersect_static before rt_scene_commit");
+    if (n < 0 || (n > 0 && (!origins || !dirs || !out_id || !out_t))) return fail(c, RT_E_INVALID, "rt_intersect_static: bad arguments");
+    if (n > RT_INTERSECT_STATIC_MAX)
+        return fail(c, RT_E_INVALID, "rt_intersect_static: n = " + std::to_string(n) + " exceeds RT_INTERSECT_STATIC_MAX = " + std::to_string(RT_INTERSECT_STATIC_MAX) +
+                                         " rays (the static scratch array); split the batch or use rt_intersect");
+    if (n == 0) return RT_OK;
+    return rt_device_intersect_static(c->devs[0], origins, dirs, n, out_id, out_t, c->err);
+}
+
 int rt_set_stream(rt_ctx* c, void* cuda_stream) {
     if (!c) return RT_E_INVALID;
     RtDevice& D = c->devs[0];

@@ -166,3 +166,5 @@ int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& op
 int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs, int n, int32_t* d_ids, float* d_t,
                         const RtOptions& opt, std::string& err);
 int rt_device_read_stats(RtDevice& D, RtFrameStats* fs, std::string& err);
+// allocation-free rt_intersect: host arrays in and out, staging in a file-scope device array of rt_render.cu
+int rt_device_intersect_static(RtDevice& D, const float* h_origins, const float* h_dirs, int n, int32_t* h_ids, float* h_t, std::string& err);

@@ -785,3 +785,82 @@ int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs
     RT_CUDA(cudaGetLastError());
     return RT_OK;
 }
+
+// ---- rt_intersect_static: the allocation-free form of rt_intersect (include/rtb200.h) ---------------------------------------
+// rt_intersect stages its rays and results in four cudaMalloc'ed buffers per call.  Callers that must not allocate (code under
+// CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the same query with that staging in a
+// file-scope device array: RT_INTERSECT_STATIC_MAX rays x 40 B = 2.5 MiB, held by every GPU that loads the library until
+// the process exits.  Layout (offsets in bytes, all multiples of 256): origins [0, 12 MAX), directions [12 MAX, 24 MAX),
+// ids [24 MAX, 36 MAX), distances [36 MAX, 40 MAX).  Nothing in it has to start at zero: the kernel overwrites ids[i] and t[i]
+// for every i < n before they are copied out, and reads only the o[i], d[i] the same call uploaded; what a previous call left
+// beyond n is never read.  Every call of every context on a device shares the ONE array: calls that overlap on the GPU
+// (two contexts, or one context on two host threads) race.
+// In host code the array's NAME is a host-side stand-in, not a device address: the address comes from cudaGetSymbolAddress,
+// asked once per device with that device current.
+__device__ __align__(256) static unsigned char g_intersect_static[(size_t)RT_INTERSECT_STATIC_MAX * 40];
+
+namespace {
+
+// k_intersect with one difference: this entry point may not refit the sphere boxes for origins outside the origin box of the
+// last commit (rt_abi.cu cover_origin allocates), so such a ray — like one whose direction is not normalised — takes the
+// reference's own linear scan (Scene.cs:43-122), which needs no boxes at all.  Same primitive tests, same (t, key) argmin.
+__global__ void __launch_bounds__(128) k_intersect_static(RtScene S, int n, f3 obox_lo, f3 obox_hi, const float* __restrict__ o,
+                                                           const float* __restrict__ d, int32_t* __restrict__ out_id, float* __restrict__ out_t) {
+    RT_DECL_STACK(stk);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        f3 O = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), D = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+        float bt = FLT_MAX; int bs = -1;
+        const f3 inv = rt_rcp3(D);
+        if (rt_scene_gate(S, O, inv)) {
+            const float dd = um_dot(D, D);
+            const bool covered = O.x >= obox_lo.x && O.x <= obox_hi.x && O.y >= obox_lo.y && O.y <= obox_hi.y && O.z >= obox_lo.z && O.z <= obox_hi.z;
+            if (S.n_spheres > 0 && (!covered || !(fabsf(dd - 1.0f) <= 0x1p-20f))) rt_scan_all(S, O, D, inv, bt, bs);
+            else { stk.sp = 0; rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+        }
+        int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
+        out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
+    }
+}
+
+// device address of g_intersect_static on the CURRENT device, looked up once per device
+int intersect_static_base(int device, unsigned char** out, std::string& err) {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static unsigned char* base[MAX_DEV] = {};
+    if (device < 0 || device >= MAX_DEV) { err = "rt_intersect_static: device ordinal out of range"; return RT_E_UNSUPPORTED; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!base[device]) {
+        void* p = nullptr;
+        RT_CUDA(cudaGetSymbolAddress(&p, g_intersect_static));
+        if (!p) { err = "cudaGetSymbolAddress returned a null address"; return RT_E_CUDA; }
+        base[device] = (unsigned char*)p;
+    }
+    *out = base[device];
+    return RT_OK;
+}
+
+}  // namespace
+
+// host arrays in, host arrays out; no cudaMalloc / cudaFree / allocating library routine on this path
+int rt_device_intersect_static(RtDevice& D, const float* h_origins, const float* h_dirs, int n, int32_t* h_ids, float* h_t, std::string& err) {
+    RT_CUDA(cudaSetDevice(D.device));
+    if (n <= 0) return RT_OK;
+    if (n > RT_INTERSECT_STATIC_MAX) { err = "rt_intersect_static: n above RT_INTERSECT_STATIC_MAX"; return RT_E_INVALID; }
+    unsigned char* base = nullptr;
+    int rc = intersect_static_base(D.device, &base, err);
+    if (rc) return rc;
+    constexpr size_t M = (size_t)RT_INTERSECT_STATIC_MAX;
+    float* d_o = (float*)base; float* d_d = (float*)(base + 12 * M);
+    int32_t* d_ids = (int32_t*)(base + 24 * M); float* d_t = (float*)(base + 36 * M);
+    RT_CUDA(cudaMemcpyAsync(d_o, h_origins, (size_t)n * 12, cudaMemcpyHostToDevice, D.stream));
+    RT_CUDA(cudaMemcpyAsync(d_d, h_dirs, (size_t)n * 12, cudaMemcpyHostToDevice, D.stream));
+    int grid = (n + RT_BLOCK - 1) / RT_BLOCK;
+    if (grid > D.sm_count * 16) grid = D.sm_count * 16;
+    k_intersect_static<<<grid, RT_BLOCK, RT_STACK_SMEM, D.stream>>>(D.S, n, mk3(D.obox[0], D.obox[1], D.obox[2]), mk3(D.obox[3], D.obox[4], D.obox[5]),
+                                                                     d_o, d_d, d_ids, d_t);
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(h_ids, d_ids, (size_t)n * 12, cudaMemcpyDeviceToHost, D.stream));
+    RT_CUDA(cudaMemcpyAsync(h_t, d_t, (size_t)n * 4, cudaMemcpyDeviceToHost, D.stream));
+    RT_CUDA(cudaStreamSynchronize(D.stream));
+    return RT_OK;
+}

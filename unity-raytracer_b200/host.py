@@ -20,7 +20,7 @@ RT_OUT_ALL = 15
 ABI_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_begin", "rt_scene_spheres",
                "rt_scene_triangles", "rt_scene_mesh", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
                "rt_scene_update_triangles", "rt_scene_update_spheres", "rt_scene_update_lights", "rt_scene_recommit", "rt_scene_refit", "rt_render",
-               "rt_render_device", "rt_read_outputs", "rt_device_outputs", "rt_intersect", "rt_get_stats", "rt_set_stream",
+               "rt_render_device", "rt_read_outputs", "rt_device_outputs", "rt_intersect", "rt_intersect_static", "rt_get_stats", "rt_set_stream",
                "rt_set_partition", "rt_host_register", "rt_host_unregister", "rt_alloc_outputs", "rt_export_outputs", "rt_import_outputs", "rt_set_option"]
 
 
@@ -100,6 +100,7 @@ def load_library():
     L.rt_read_outputs.argtypes = [vp, vp, vp, vp, vp]
     L.rt_device_outputs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
     L.rt_intersect.argtypes = [vp, fp, fp, C.c_int, ip, fp]
+    L.rt_intersect_static.argtypes = [vp, fp, fp, C.c_int, ip, fp]
     L.rt_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.rt_set_stream.argtypes = [vp, vp]
     L.rt_set_partition.argtypes = [vp, C.c_int, C.c_int, C.c_int]
@@ -266,6 +267,18 @@ class RayTracer:
         n = o.shape[0]
         ids = np.zeros((n, 3), np.int32); t = np.zeros(n, np.float32)
         self._chk(self.L.rt_intersect(self.h, _fptr(o), _fptr(d), n, ids.ctypes.data_as(C.POINTER(C.c_int32)), _fptr(t)))
+        return ids, t
+
+    INTERSECT_STATIC_MAX = 65536          # RT_INTERSECT_STATIC_MAX
+
+    def intersect_static(self, origins, dirs):
+        """rt_intersect_static: the same query without any device allocation (staging in a static device array of the
+        library, at most INTERSECT_STATIC_MAX rays per call; no counterpart in the reference)."""
+        o = np.ascontiguousarray(np.atleast_2d(origins), dtype=np.float32)
+        d = np.ascontiguousarray(np.atleast_2d(dirs), dtype=np.float32)
+        n = o.shape[0]
+        ids = np.zeros((n, 3), np.int32); t = np.zeros(n, np.float32)
+        self._chk(self.L.rt_intersect_static(self.h, _fptr(o), _fptr(d), n, ids.ctypes.data_as(C.POINTER(C.c_int32)), _fptr(t)))
         return ids, t
 
     # ---- plumbing ----
