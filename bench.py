@@ -35,6 +35,8 @@ def workload(name, scenes):
         return scenes.cfg3_scene(), scenes.cfg3_params(), "1 003 520-triangle displaced geodesic sphere + ground quad, 3840x2160, 2 point lights, depth 0, 1 spp"
     if name == "cfg4":
         return scenes.cfg4_scene(), scenes.cfg4_params(), "125 baked instances x 81 920 = 10 240 000 triangles, 7680x4320, 2 point lights"
+    if name == "cfg4i":      # the same picture class as cfg4 from ONE base mesh + 125 instance matrices (rt_scene_mesh_instance)
+        return scenes.cfg4_instanced(), scenes.cfg4_params(), "ONE 81 920-triangle base mesh x 125 instances (rt_scene_mesh_instance; = 10 240 000 baked triangles), 7680x4320, 2 point lights"
     if name == "cfg5":
         return scenes.cfg5_scene(), scenes.cfg5_params(), "100 000 spheres (10% mirrors) + 5 000 000-triangle sphere + ground, 3840x2160 x 16 spp, depth 4, 2 lights"
     raise SystemExit(f"unknown workload {name}")

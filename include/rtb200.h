@@ -101,6 +101,27 @@ int rt_scene_triangles(rt_ctx* ctx, const float* v, const float* normals, const 
  * computed it (SceneMesh.cs:22-31) — it is a *semantic* cull in Scene.IntersectRay (Scene.cs:67) and is used verbatim. */
 int rt_scene_mesh(rt_ctx* ctx, const float* v, const float* normals, int n_tris, const rt_material* material,
                   const float aabb[6]);
+/* Instanced meshes: SceneMesh.Mesh (SceneComponents/SceneMesh.cs:11-53) WITHOUT the per-frame world bake.  The reference
+ * multiplies every vertex of every mesh by transform.localToWorldMatrix on every frame (SceneMesh.cs:21-31) and hands the scan
+ * baked triangles (Data/Objects/Mesh.cs:7-12).  Here the mesh stays in object space, is stored once however often it occurs, and
+ * each occurrence is a 3x4 matrix: the library bakes triangles on the fly with the bake's own arithmetic —
+ *   world = Matrix4x4.MultiplyPoint3x4(v): ((m00*x + m01*y) + m02*z) + m03 per row, binary32, left to right (SceneMesh.cs:28),
+ *   TriangleNormals[i] = -Triangle.Normal of the world triangle (SceneMesh.cs:45, Data/Objects/Triangle.cs:13-21)
+ * — so an instanced mesh renders bit-identically to the same mesh baked by the caller with that formula and sent through
+ * rt_scene_mesh (ids, distances, colours; no edge exemption), while re-posing it costs 48 bytes instead of 48 bytes per triangle.
+ * rt_scene_base_mesh: v = 9 floats per triangle in OBJECT space (MeshFilter.sharedMesh vertices gathered by its index buffer,
+ *   SceneMesh.cs:15-17,36-41; finite values only).  Returns the base-mesh index (>= 0, call order) or a negative rt_status.  A base
+ *   mesh is not part of the scan by itself.
+ * rt_scene_mesh_instance: one occurrence; takes the place of ONE rt_scene_mesh call — instances and baked meshes share the call-order
+ *   numbering that is ObjectId.MeshIndex, in any mix.  m3x4 = rows of localToWorldMatrix (m00 m01 m02 m03, m10 .., m20 ..); must be
+ *   finite and invertible (condition number below 1e5), else RT_E_UNSUPPORTED: bake such a mesh.  aabb = Mesh.AABB as the caller
+ *   computed it (the semantic cull of Scene.cs:67, used verbatim) or NULL -> computed as SceneMesh.cs:22-31 does (min / max of the
+ *   baked vertices; costs a pass over the base mesh on the host).
+ * rt_scene_update_instance: re-pose an instance of a committed scene (dirty-tracking update: follow with rt_scene_recommit or
+ *   rt_scene_refit; both rebuild the instance tree, which takes microseconds, and leave the base meshes alone). */
+int rt_scene_base_mesh(rt_ctx* ctx, const float* v, int n_tris);
+int rt_scene_mesh_instance(rt_ctx* ctx, int base_mesh, const float m3x4[12], const rt_material* material, const float aabb[6]);
+int rt_scene_update_instance(rt_ctx* ctx, int mesh_index, const float m3x4[12], const float aabb[6]);
 /* Scene.PointLights (6 floats each = PointLightData{Position,Intensity}, PointLightData.cs:9-10) + AmbientLight.Radiance;
  * ambient_radiance NULL = default(AmbientLightData) = 0 (RTS:132) */
 int rt_scene_lights(rt_ctx* ctx, const float* pos_intensity, int n, const float ambient_radiance[3]);

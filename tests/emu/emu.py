@@ -25,6 +25,10 @@ def lib():
         L.emu_scene_triangles.argtypes = [vp, fp, fp, vp, C.c_int]
         L.emu_scene_mesh.argtypes = [vp, fp, fp, C.c_int, vp, fp]
         L.emu_scene_lights.argtypes = [vp, fp, C.c_int, fp]
+        L.emu_scene_base_mesh.argtypes = [vp, fp, C.c_int]
+        L.emu_scene_mesh_instance.argtypes = [vp, C.c_int, fp, vp, fp]
+        L.emu_scene_update_instance.argtypes = [vp, C.c_int, fp, fp]
+        L.emu_scene_recommit.argtypes = [vp, fp]
         L.emu_scene_commit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double, C.c_int]
         L.emu_scene_clear.argtypes = [vp]
         L.emu_scene_refit.argtypes = [vp, fp, C.c_int, C.c_double, C.c_double]
@@ -69,7 +73,17 @@ class EmuTracer:
         if sa.tris.shape[0]:
             v, n, m = f32(sa.tris), f32(sa.tri_normals), np.ascontiguousarray(sa.tri_mats)
             L.emu_scene_triangles(h, _fp(v), _fp(n), m.ctypes.data, v.shape[0])
-        for (v, n, mat, aabb) in sa.meshes:
+        scenes = host.scenes
+        for bv in getattr(sa, "base_meshes", []):
+            bv = f32(bv)
+            assert L.emu_scene_base_mesh(h, _fp(bv), bv.shape[0]) >= 0
+        for m in sa.meshes:
+            if isinstance(m, scenes.MeshInstance):                  # (the emulation wants the AABB: compute it as the bake does)
+                mm, mat = f32(m.m3x4), np.ascontiguousarray(m.mat)
+                bb = f32(m.aabb if m.aabb is not None else scenes.bake_tris(sa.base_meshes[m.base], m.m3x4)[2])
+                assert L.emu_scene_mesh_instance(h, int(m.base), _fp(mm), mat.ctypes.data, _fp(bb)) == 0
+                continue
+            v, n, mat, aabb = m
             v, n, aabb, mat = f32(v), f32(n), f32(aabb), np.ascontiguousarray(mat)
             L.emu_scene_mesh(h, _fp(v), _fp(n), v.shape[0], mat.ctypes.data, _fp(aabb))
         li, amb = f32(sa.lights), f32(sa.ambient)
@@ -79,6 +93,14 @@ class EmuTracer:
             assert L.emu_scene_refit(h, bb, self.opts[0], self.opts[1], self.opts[2]) == 0
             return
         L.emu_scene_commit(h, bb, self.opts[0], self.opts[1], self.opts[2], self.opts[3])
+
+    def update_instance(self, mesh_index, m3x4, aabb):
+        mm, bb = np.ascontiguousarray(m3x4, dtype=np.float32), np.ascontiguousarray(aabb, dtype=np.float32)
+        assert self.L.emu_scene_update_instance(self.h, int(mesh_index), _fp(mm), _fp(bb)) == 0
+
+    def recommit(self, scene_aabb=None):
+        bb = None if scene_aabb is None else _fp(np.ascontiguousarray(scene_aabb, dtype=np.float32))
+        assert self.L.emu_scene_recommit(self.h, bb) == 0
 
     def scene_aabb(self):
         out = np.zeros(6, np.float32)

@@ -11,6 +11,7 @@
 #include "../../unity-raytracer_b200/csrc/rt_build_steps.h"
 #include "../../unity-raytracer_b200/csrc/rt_host_scene.h"
 #include "../../unity-raytracer_b200/csrc/rt_sah.h"
+#include "../../unity-raytracer_b200/csrc/rt_instances.h"
 
 namespace {
 
@@ -25,8 +26,9 @@ struct Emu {
     RtHostScene host;
     // "device" memory
     std::vector<float> raw_v, raw_n; std::vector<float4> raw_s;
-    std::vector<int32_t> mesh_base;
+    std::vector<int32_t> mesh_base, mesh_raw;
     std::vector<float4> nodes, prims, pinfo, mats, mesh_aabb, lights;
+    std::vector<float4> inodes, iprims, inst; std::vector<int32_t> inst_vbase;      // RtDevice::inodes / iprims / inst / inst_vbase
     std::vector<int32_t> order;               // slot -> scan key of the committed tree (the device keeps it in vals_alt)
     int32_t root = 0;
     double presplit = 0.0; int presplit_depth = 3;   // RtOptions::presplit / presplit_depth
@@ -45,7 +47,9 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
     E.raw_n = H.mesh_n; E.raw_n.insert(E.raw_n.end(), H.loose_n.begin(), H.loose_n.end());
     E.raw_s.resize(n_sp);
     for (int i = 0; i < n_sp; ++i) E.raw_s[i] = make_float4(H.spheres[4 * i], H.spheres[4 * i + 1], H.spheres[4 * i + 2], H.spheres[4 * i + 3]);
-    E.mesh_base = H.mesh_base; E.mesh_base.push_back(n_mt);
+    const int n_kt = H.n_keytris();
+    E.mesh_base = H.mesh_base; E.mesh_base.push_back(n_kt);
+    E.mesh_raw = H.mesh_raw; E.mesh_raw.push_back(n_mt);
     std::vector<float> m = H.pack_materials();
     E.has_mirror = H.has_mirror;
     E.mats.resize(m.size() / 4);
@@ -61,15 +65,16 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
         E.lights[2 * k + 1] = make_float4(H.lights[6 * k + 3], H.lights[6 * k + 4], H.lights[6 * k + 5], 0.f);
     }
     RtScene& S = E.S; S = RtScene{};
-    S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_mt; S.n_spheres = n_sp; S.n_lights = n_li;
+    S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_kt; S.n_spheres = n_sp; S.n_lights = n_li;
     S.aabb_min = mk3(H.aabb[0], H.aabb[1], H.aabb[2]); S.aabb_max = mk3(H.aabb[3], H.aabb[4], H.aabb[5]);
     S.ambient = mk3(H.ambient[0], H.ambient[1], H.ambient[2]);
     S.t_slack = (float)t_slack;
     S.backcull = H.backcull_ok() ? 1 : 0;
     S.mats = E.mats.data(); S.mesh_aabb = E.mesh_aabb.data(); S.mesh_base = E.mesh_base.data(); S.lights = E.lights.data();
     if (!refit) E.n_nodes = 0;
-    if (n == 0) return;
-    RtRaw R{E.raw_v.data(), E.raw_n.data(), E.raw_s.data(), E.mesh_base.data(), n_me, n_mt, n_sp, n_lo, mk3(0.f, 0.f, 0.f), mk3(0.f, 0.f, 0.f), 0.0f};
+    if (n == 0 && !H.inst.any()) return;
+    RtRaw R{E.raw_v.data(), E.raw_n.data(), E.raw_s.data(), E.mesh_raw.data(), n_me, n_mt, n_sp, n_lo, mk3(0.f, 0.f, 0.f), mk3(0.f, 0.f, 0.f), 0.0f,
+            E.mesh_base.data(), n_kt};
     leaf_max = leaf_max < 1 ? 1 : (leaf_max > 8 ? 8 : leaf_max);
     float b[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (int i = 0; i < n; ++i) {                                  // k_bounds: un-inflated sphere boxes (R.sphere_k = 0)
@@ -78,9 +83,22 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
         b[3] = fmaxf(b[3], hi.x); b[4] = fmaxf(b[4], hi.y); b[5] = fmaxf(b[5], hi.z);
     }
     float amax = 0.f; for (int k = 0; k < 6; ++k) if (std::isfinite(b[k])) amax = fmaxf(amax, fabsf(b[k]));
+    float bo[6]; for (int k = 0; k < 6; ++k) bo[k] = b[k];
+    H.inst.grow_bounds(bo, amax);                                  // origin box and padding: instances included (rt_device_commit)
     const float pad = (float)(amax * pad_scale) + 1e-30f;
     S.origin_reach = rt_origin_reach(pad);
-    H.origin_box(b, amax, E.obox);                                 // rt_device_commit's set_obox
+    H.origin_box(bo, amax, E.obox);                                // rt_device_commit's set_obox
+    if (H.inst.any()) {                                            // rt_device_commit's upload_instances
+        const char* why = nullptr;
+        if (!H.inst.pack(E.mesh_base, amax, pad, pad_scale, leaf_max, 2, 116, &why)) { fprintf(stderr, "emu: %s\n", why ? why : "pack failed"); abort(); }
+        auto as4 = [](const std::vector<float>& v, std::vector<float4>& o) { o.assign(v.size() / 4 + 1, float4{}); if (!v.empty()) memcpy(o.data(), v.data(), v.size() * 4); };
+        as4(H.inst.inodes, E.inodes); as4(H.inst.iprims, E.iprims); as4(H.inst.inst, E.inst);
+        E.inst_vbase = H.inst.vbase;
+        S.inodes = E.inodes.data(); S.iprims = E.iprims.data(); S.inst = E.inst.data(); S.inst_vbase = E.inst_vbase.data();
+        S.tlas_root = H.inst.tlas_root; S.n_inst = H.inst.n_packed;
+        S.origin_reach = fminf(S.origin_reach, 2.0f * amax);
+    }
+    if (n == 0) { S.n_slots = 0; return; }
     R.obox_lo = mk3(E.obox[0], E.obox[1], E.obox[2]); R.obox_hi = mk3(E.obox[3], E.obox[4], E.obox[5]); R.sphere_k = RT_SPHERE_K;
     S.n_slots = refit ? (int)E.order.size() : n;
     f3 bmin = mk3(b[0], b[1], b[2]);
@@ -184,6 +202,12 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
     S.root = 0; S.nodes = E.nodes.data(); E.root = 0;
 }
 
+// the product picks the INST instantiation of every kernel when the committed scene has instanced meshes (rt_render.cu)
+template <bool ANY, bool FAR>
+bool trav(const RtScene& S, f3 O, f3 D, f3 inv, float d2, VecStack& stk, float& bt, int& bs) {
+    return S.n_inst > 0 ? rt_traverse<ANY, FAR, true>(S, O, D, inv, d2, stk, bt, bs) : rt_traverse<ANY, FAR, false>(S, O, D, inv, d2, stk, bt, bs);
+}
+
 RtView make_view(const rt_render_params* p, int rank, int world, int band_rows) {
     RtView V{};
     V.pos = mk3(p->pos[0], p->pos[1], p->pos[2]); V.fwd = mk3(p->fwd[0], p->fwd[1], p->fwd[2]);
@@ -220,10 +244,44 @@ int emu_scene_triangles(void* e, const float* v, const float* nn, const rt_mater
 }
 int emu_scene_mesh(void* e, const float* v, const float* nn, int n, const rt_material* m, const float* aabb) {
     Emu* E = (Emu*)e;
-    E->host.mesh_base.push_back(E->host.n_meshtris());
+    E->host.push_mesh(-1, *m, aabb);
     E->host.mesh_v.insert(E->host.mesh_v.end(), v, v + 9 * (size_t)n); E->host.mesh_n.insert(E->host.mesh_n.end(), nn, nn + 3 * (size_t)n);
     E->host.mesh_tris += n;
-    E->host.mesh_mats.push_back(*m); E->host.mesh_aabb.insert(E->host.mesh_aabb.end(), aabb, aabb + 6); return 0;
+    return 0;
+}
+// rt_scene_base_mesh / rt_scene_mesh_instance / rt_scene_update_instance as rt_abi.cu implements them (aabb must be given here)
+int emu_scene_base_mesh(void* e, const float* v, int n) {
+    Emu* E = (Emu*)e;
+    RtBaseMesh B; B.v.assign(v, v + 9 * (size_t)n);
+    if (!RtInstanceSet::set_bounds(B)) return -5;
+    E->host.inst.bases.push_back(std::move(B)); E->host.inst.blas_changed = true;
+    return (int)E->host.inst.bases.size() - 1;
+}
+int emu_scene_mesh_instance(void* e, int base, const float* m12, const rt_material* m, const float* aabb) {
+    Emu* E = (Emu*)e; RtHostScene& H = E->host;
+    if (base < 0 || base >= (int)H.inst.bases.size()) return -1;
+    RtInstance I; I.base = base; I.mesh = H.n_meshes();
+    if (!RtInstanceSet::set_matrix(I, m12, H.inst.bases[(size_t)base])) return -5;
+    H.push_mesh((int32_t)H.inst.insts.size(), *m, aabb);
+    H.inst.insts.push_back(I);
+    H.inst_tris += H.inst.bases[(size_t)base].n_tris();
+    return 0;
+}
+int emu_scene_update_instance(void* e, int mesh_index, const float* m12, const float* aabb) {
+    Emu* E = (Emu*)e; RtHostScene& H = E->host;
+    if (mesh_index < 0 || mesh_index >= H.n_meshes() || H.mesh_inst[(size_t)mesh_index] < 0) return -1;
+    RtInstance I = H.inst.insts[(size_t)H.mesh_inst[(size_t)mesh_index]];
+    if (!RtInstanceSet::set_matrix(I, m12, H.inst.bases[(size_t)I.base])) return -5;
+    H.inst.insts[(size_t)H.mesh_inst[(size_t)mesh_index]] = I;
+    for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = aabb[k];
+    return 0;
+}
+// rt_scene_recommit after rt_scene_update_instance: same arrays, instance tree rebuilt
+int emu_scene_recommit(void* e, const float* aabb) {
+    Emu* E = (Emu*)e;
+    if (aabb) for (int k = 0; k < 6; ++k) E->host.aabb[k] = aabb[k]; else E->host.calc_aabb();
+    commit(*E, E->opt_leaf_max, E->opt_pad_scale, E->opt_t_slack, E->opt_builder);
+    return 0;
 }
 int emu_scene_lights(void* e, const float* pi, int n, const float* amb) {
     Emu* E = (Emu*)e; E->host.lights.assign(pi, pi + 6 * (size_t)n);
@@ -276,10 +334,10 @@ int emu_intersect(void* e, const float* o, const float* d, int n, int32_t* out_i
         { f3 inv = rt_rcp3(D);
           if (rt_scene_gate(S, O, inv)) {                              // k_intersect
               const float dd = um_dot(D, D);
-              if (S.n_spheres > 0 && !(fabsf(dd - 1.0f) <= 0x1p-20f)) rt_scan_all(S, O, D, inv, bt, bs);
-              else { stk.sp = 0; rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+              if (S.n_spheres > 0 && !(fabsf(dd - 1.0f) <= 0x1p-20f)) { if (S.n_inst > 0) rt_scan_all<true>(S, O, D, inv, bt, bs); else rt_scan_all<false>(S, O, D, inv, bt, bs); }
+              else { stk.sp = 0; trav<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
           } }
-        int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
+        int32_t ty, ix, me; if (S.n_inst > 0) rt_slot_to_id<true>(S, bs, ty, ix, me); else rt_slot_to_id<false>(S, bs, ty, ix, me);
         out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
     }
     if (stk.max_sp > E->max_stack) E->max_stack = stk.max_sp;
@@ -316,7 +374,7 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
                 int x, y; bool valid = rt_item_to_pixel(V, tb + t, lane, x, y);
                 float bt = FLT_MAX; int bs = -1;
                 if (valid) { f3 O, D; rt_primary_ray(V, x, y, si, sj, O, D); { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0;
-                    if (V.far_origin) rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); else rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } } }
+                    if (V.far_origin) trav<false, true>(S, O, D, inv, 0.f, stk, bt, bs); else trav<false, false>(S, O, D, inv, 0.f, stk, bt, bs); } } }
                 size_t q = (size_t)t * 32 + lane; hit0_t[q] = bt; hit0_slot[q] = valid ? bs : -2;
             }
             for (int d = 0; d <= maxd; ++d) {
@@ -326,7 +384,7 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
                 if (d > 0) for (unsigned q = 0; q < n; ++q) {                                  // k_trace_queue
                     f3 O = mk3(rin[2 * q].x, rin[2 * q].y, rin[2 * q].z), D = mk3(rin[2 * q + 1].x, rin[2 * q + 1].y, rin[2 * q + 1].z);
                     float bt = FLT_MAX; int bs = -1;
-                    { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0; rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs); } }
+                    { f3 inv = rt_rcp3(D); if (rt_scene_gate(S, O, inv)) { stk.sp = 0; trav<false, false>(S, O, D, inv, 0.f, stk, bt, bs); } }
                     ht[q] = bt; hs[q] = bs;
                 }
                 const int n_chunks = (S.n_lights + 31) / 32;
@@ -340,7 +398,8 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
                         if (hs[q] >= 0) {
                             f3 O, D; ray_of(q, O, D);
                             uint32_t ns = 0;
-                            mask = rt_shadow_mask(S, O, D, ht[q], hs[q], c * 32, std::min(32, S.n_lights - c * 32), stk, ns);
+                            mask = S.n_inst > 0 ? rt_shadow_mask<true>(S, O, D, ht[q], hs[q], c * 32, std::min(32, S.n_lights - c * 32), stk, ns)
+                                                : rt_shadow_mask<false>(S, O, D, ht[q], hs[q], c * 32, std::min(32, S.n_lights - c * 32), stk, ns);
                             n_shadow += ns;
                         }
                         occl[(size_t)c * W + q] = mask;
@@ -351,7 +410,8 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
                     if (slot == -1) local[d][q] = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);
                     else if (slot >= 0) {
                         f3 O, D; ray_of(q, O, D);
-                        f3 c = rt_shade_masked(S, O, D, ht[q], slot, d, V.max_bounces, occl.data(), W, q, mir);
+                        f3 c = S.n_inst > 0 ? rt_shade_masked<true>(S, O, D, ht[q], slot, d, V.max_bounces, occl.data(), W, q, mir)
+                                            : rt_shade_masked<false>(S, O, D, ht[q], slot, d, V.max_bounces, occl.data(), W, q, mir);
                         local[d][q] = make_float4(c.x, c.y, c.z, 0.f);
                     }
                     if (mir.emit) {
@@ -362,8 +422,10 @@ int emu_render(void* e, const rt_render_params* p, int rank, int world, int band
                 }
             }
             for (int d = maxd; d >= 1; --d) for (unsigned q = 0; q < count[d]; ++q) rt_fold_item(q, link[d].data(), local[d].data(), local[d - 1].data());
-            for (unsigned q = 0; q < (unsigned)nt * 32u; ++q)
-                rt_finalize_item(S, V, tb, q, pass, n_pass, local[0].data(), hit0_t.data(), hit0_slot.data(), accum.data(), out);
+            for (unsigned q = 0; q < (unsigned)nt * 32u; ++q) {
+                if (S.n_inst > 0) rt_finalize_item<true>(S, V, tb, q, pass, n_pass, local[0].data(), hit0_t.data(), hit0_slot.data(), accum.data(), out);
+                else rt_finalize_item<false>(S, V, tb, q, pass, n_pass, local[0].data(), hit0_t.data(), hit0_slot.data(), accum.data(), out);
+            }
         }
     if (stk.max_sp > E->max_stack) E->max_stack = stk.max_sp;
     if (stats3) { stats3[0] = (uint64_t)V.res_x * V.n_local_rows * n_pass; stats3[1] = n_shadow; stats3[2] = n_mirror; }

@@ -17,6 +17,8 @@ t0 = time.time()
 if cfg == "cfg2": s, p = sc.rt_unity(True), sc.rt_unity_params(3840, 2160, 4)
 elif cfg == "cfg3": s, p = sc.cfg3_scene(), sc.cfg3_params()
 elif cfg == "cfg4": s, p = sc.cfg4_scene(), sc.cfg4_params()
+elif cfg == "cfg4i": s, p = sc.cfg4_instanced(), sc.cfg4_params()            # one base mesh + 125 instances
+elif cfg == "cfg4ib": s, p = sc.cfg4_instanced().baked(), sc.cfg4_params()    # its baked twin (bit-identical frame)
 elif cfg == "cfg5": s, p = sc.cfg5_scene(), sc.cfg5_params()
 else: s, p = sc.cfg3_scene(n=int(cfg)), sc.cfg3_params()
 print(f"scene {cfg}: {s.n_prims} prims, generated in {time.time()-t0:.1f}s", flush=True)

@@ -35,6 +35,7 @@ void device_release(RtDevice& D) {
     if (D.device < 0) return;
     cudaSetDevice(D.device);
     for (DevBuf* b : {&D.raw_v, &D.raw_n, &D.raw_s, &D.nodes, &D.prims, &D.pinfo, &D.mats, &D.mesh_aabb, &D.mesh_base, &D.lights, &D.keys,
+                      &D.mesh_raw, &D.inodes, &D.iprims, &D.inst, &D.inst_vbase,
                       &D.keys_alt, &D.vals, &D.vals_alt, &D.cub_tmp, &D.bounds, &D.topo_i32, &D.leaf_lo, &D.leaf_hi, &D.int_lo, &D.int_hi,
                       &D.flags, &D.new_index, &D.accum, &D.stats, &D.own_rgba32f, &D.own_rgba8, &D.own_hit_id, &D.own_hit_t})
         b->release();
@@ -365,8 +366,8 @@ int rt_scene_mesh(rt_ctx* c, const float* v, const float* normals, int n_tris, c
     if (!c) return RT_E_INVALID;
     if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_mesh outside rt_scene_begin/commit");
     if (n_tris < 0 || !mat || !aabb || (n_tris > 0 && (!v || !normals))) return fail(c, RT_E_INVALID, "rt_scene_mesh: bad arguments");
-    if ((int64_t)c->host.mesh_tris + n_tris > (int64_t)(1 << 28)) return fail(c, RT_E_UNSUPPORTED, "too many primitives (limit 2^28)");
-    c->host.mesh_base.push_back(c->host.n_meshtris());
+    if ((int64_t)c->host.mesh_tris + c->host.inst_tris + n_tris > (int64_t)(1 << 28)) return fail(c, RT_E_UNSUPPORTED, "too many primitives (limit 2^28)");
+    c->host.push_mesh(-1, *mat, aabb);
     if (c->host.mesh_on_device) {
         auto t0 = std::chrono::steady_clock::now();
         int rc = rt_device_stage_mesh(c->devs[0], v, normals, c->host.mesh_tris, n_tris, c->opt.upload_threads, c->err);
@@ -378,8 +379,51 @@ int rt_scene_mesh(rt_ctx* c, const float* v, const float* normals, int n_tris, c
         c->host.mesh_n.insert(c->host.mesh_n.end(), normals, normals + 3 * (size_t)n_tris);
     }
     c->host.mesh_tris += n_tris;
-    c->host.mesh_mats.push_back(*mat);
-    c->host.mesh_aabb.insert(c->host.mesh_aabb.end(), aabb, aabb + 6);
+    return RT_OK;
+}
+
+// ---- instanced meshes: SceneMesh.cs:11-53 without the per-frame world bake (rt_instances.h) ----
+int rt_scene_base_mesh(rt_ctx* c, const float* v, int n_tris) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_base_mesh outside rt_scene_begin/commit");
+    if (n_tris < 0 || (n_tris > 0 && !v)) return fail(c, RT_E_INVALID, "rt_scene_base_mesh: bad arguments");
+    if (n_tris > (1 << 26)) return fail(c, RT_E_UNSUPPORTED, "rt_scene_base_mesh: more than 2^26 triangles");
+    RtBaseMesh B;
+    B.v.assign(v, v + 9 * (size_t)n_tris);
+    if (!RtInstanceSet::set_bounds(B)) return fail(c, RT_E_UNSUPPORTED, "rt_scene_base_mesh: vertices must be finite (bake such a mesh and use rt_scene_mesh)");
+    c->host.inst.bases.push_back(std::move(B));
+    c->host.inst.blas_changed = true;
+    return (int)c->host.inst.bases.size() - 1;
+}
+
+// world AABB of an instance exactly as SceneMesh.cs:22-31 computes it: min / max over the baked vertices (Encapsulate, AABB.cs:10-20)
+static void instance_aabb(const RtBaseMesh& B, const float m[12], float out[6]) {
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};       // float.MaxValue / float.MinValue
+    const float4 r0 = make_float4(m[0], m[1], m[2], m[3]), r1 = make_float4(m[4], m[5], m[6], m[7]), r2 = make_float4(m[8], m[9], m[10], m[11]);
+    for (size_t i = 0; i < B.v.size() / 3; ++i) {
+        const f3 w = rt_xform_point(r0, r1, r2, mk3(B.v[3 * i], B.v[3 * i + 1], B.v[3 * i + 2]));
+        mn[0] = um_min(mn[0], w.x); mn[1] = um_min(mn[1], w.y); mn[2] = um_min(mn[2], w.z);
+        mx[0] = um_max(mx[0], w.x); mx[1] = um_max(mx[1], w.y); mx[2] = um_max(mx[2], w.z);
+    }
+    for (int k = 0; k < 3; ++k) { out[k] = mn[k]; out[3 + k] = mx[k]; }
+}
+
+int rt_scene_mesh_instance(rt_ctx* c, int base_mesh, const float m3x4[12], const rt_material* mat, const float aabb[6]) {
+    if (!c) return RT_E_INVALID;
+    if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_mesh_instance outside rt_scene_begin/commit");
+    RtHostScene& H = c->host;
+    if (base_mesh < 0 || base_mesh >= (int)H.inst.bases.size() || !m3x4 || !mat) return fail(c, RT_E_INVALID, "rt_scene_mesh_instance: bad arguments");
+    const RtBaseMesh& B = H.inst.bases[(size_t)base_mesh];
+    if ((int64_t)H.mesh_tris + H.inst_tris + B.n_tris() > (int64_t)(1 << 28)) return fail(c, RT_E_UNSUPPORTED, "too many primitives (limit 2^28)");
+    RtInstance I;
+    I.base = base_mesh; I.mesh = H.n_meshes();
+    if (!RtInstanceSet::set_matrix(I, m3x4, B))
+        return fail(c, RT_E_UNSUPPORTED, "rt_scene_mesh_instance: matrix not finite, singular or too ill-conditioned for an instance (bake the mesh and use rt_scene_mesh)");
+    float box[6];
+    if (aabb) for (int k = 0; k < 6; ++k) box[k] = aabb[k]; else instance_aabb(B, m3x4, box);
+    H.push_mesh((int32_t)H.inst.insts.size(), *mat, box);
+    H.inst.insts.push_back(I);
+    H.inst_tris += B.n_tris();
     return RT_OK;
 }
 
@@ -415,7 +459,7 @@ static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, 
         up += u; bd += b; bytes += by;
     }
     c->stats.ms_commit_upload = up + c->stream_ms; c->stats.ms_commit_build = bd; c->stats.h2d_bytes = bytes + c->stream_bytes;
-    c->stats.n_prims = (uint32_t)c->host.n_prims(); c->stats.n_nodes = c->devs[0].n_nodes;
+    c->stats.n_prims = (uint32_t)(c->host.n_prims() + c->host.inst_tris); c->stats.n_nodes = c->devs[0].n_nodes;
     c->stream_ms = 0.f; c->stream_bytes = 0;
     c->in_scene = false; c->committed = true;
     return RT_OK;
@@ -453,8 +497,9 @@ int rt_scene_update_mesh(rt_ctx* c, int mesh_index, const float* v, const float*
     if (rc) return rc;
     RtHostScene& H = c->host;
     if (mesh_index < 0 || mesh_index >= H.n_meshes() || !aabb) return fail(c, RT_E_INVALID, "rt_scene_update_mesh: bad arguments");
-    const int64_t first = H.mesh_base[mesh_index];
-    const int64_t n = (mesh_index + 1 < H.n_meshes() ? (int64_t)H.mesh_base[mesh_index + 1] : H.mesh_tris) - first;
+    if (H.mesh_inst[(size_t)mesh_index] >= 0) return fail(c, RT_E_INVALID, "rt_scene_update_mesh: mesh is an instance (use rt_scene_update_instance)");
+    const int64_t first = H.mesh_raw[mesh_index];
+    const int64_t n = (mesh_index + 1 < H.n_meshes() ? (int64_t)H.mesh_raw[mesh_index + 1] : H.mesh_tris) - first;
     if (n > 0 && (!v || !normals)) return fail(c, RT_E_INVALID, "rt_scene_update_mesh: bad arguments");
     if ((rc = update_mark(c))) return rc;
     for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = aabb[k];
@@ -462,6 +507,24 @@ int rt_scene_update_mesh(rt_ctx* c, int mesh_index, const float* v, const float*
     // on every update (host memory bandwidth is what binds an update), so they are refreshed from the device when needed
     if (!H.mesh_on_device && n > 0) H.mesh_stale = true;
     return update_raw(c, 0, first, n, v, normals);
+}
+
+int rt_scene_update_instance(rt_ctx* c, int mesh_index, const float m3x4[12], const float aabb[6]) {
+    int rc = update_prolog(c, "rt_scene_update_instance");
+    if (rc) return rc;
+    RtHostScene& H = c->host;
+    if (mesh_index < 0 || mesh_index >= H.n_meshes() || !m3x4 || H.mesh_inst[(size_t)mesh_index] < 0)
+        return fail(c, RT_E_INVALID, "rt_scene_update_instance: bad arguments (not an instanced mesh?)");
+    RtInstance I = H.inst.insts[(size_t)H.mesh_inst[(size_t)mesh_index]];
+    const RtBaseMesh& B = H.inst.bases[(size_t)I.base];
+    if (!RtInstanceSet::set_matrix(I, m3x4, B))
+        return fail(c, RT_E_UNSUPPORTED, "rt_scene_update_instance: matrix not finite, singular or too ill-conditioned for an instance");
+    if ((rc = update_mark(c))) return rc;
+    H.inst.insts[(size_t)H.mesh_inst[(size_t)mesh_index]] = I;
+    float box[6];
+    if (aabb) for (int k = 0; k < 6; ++k) box[k] = aabb[k]; else instance_aabb(B, m3x4, box);
+    for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = box[k];
+    return RT_OK;
 }
 
 int rt_scene_update_triangles(rt_ctx* c, int first, int n, const float* v, const float* normals) {

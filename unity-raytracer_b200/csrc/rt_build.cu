@@ -259,14 +259,19 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     for (int m = 0; m < n_me; ++m) { for (int k = 0; k < 3; ++k) { maabb[8 * m + k] = H.mesh_aabb[6 * m + k]; maabb[8 * m + 4 + k] = H.mesh_aabb[6 * m + 3 + k]; } }
     RT_CUDA(D.mesh_aabb.ensure(maabb.size() * 4));
     if (n_me) RT_CUDA(cudaMemcpyAsync(D.mesh_aabb.p, maabb.data(), maabb.size() * 4, cudaMemcpyHostToDevice, st));
-    std::vector<int32_t> mbase(H.mesh_base); mbase.push_back(n_mt);
+    const int32_t n_kt = H.n_keytris();                        // scan keys of all mesh triangles, instanced ones included
+    if ((int64_t)n64 + H.inst_tris > (int64_t)(1 << 28) - 8) { err = "too many primitives (limit 2^28)"; return RT_E_UNSUPPORTED; }
+    std::vector<int32_t> mbase(H.mesh_base); mbase.push_back(n_kt);
     RT_CUDA(D.mesh_base.ensure(mbase.size() * 4));
     RT_CUDA(cudaMemcpyAsync(D.mesh_base.p, mbase.data(), mbase.size() * 4, cudaMemcpyHostToDevice, st));
+    std::vector<int32_t> mraw(H.mesh_raw); mraw.push_back(n_mt);
+    RT_CUDA(D.mesh_raw.ensure(mraw.size() * 4));
+    RT_CUDA(cudaMemcpyAsync(D.mesh_raw.p, mraw.data(), mraw.size() * 4, cudaMemcpyHostToDevice, st));
     std::vector<float> lights((size_t)n_li * 8, 0.f);
     for (int l = 0; l < n_li; ++l) { for (int k = 0; k < 3; ++k) { lights[8 * l + k] = H.lights[6 * l + k]; lights[8 * l + 4 + k] = H.lights[6 * l + 3 + k]; } }
     RT_CUDA(D.lights.ensure(lights.size() * 4));
     if (n_li) RT_CUDA(cudaMemcpyAsync(D.lights.p, lights.data(), lights.size() * 4, cudaMemcpyHostToDevice, st));
-    up += mats.size() * 4 + maabb.size() * 4 + mbase.size() * 4 + lights.size() * 4;
+    up += mats.size() * 4 + maabb.size() * 4 + mbase.size() * 8 + lights.size() * 4;
     RT_CUDA(cudaStreamSynchronize(st));        // staging vectors above go out of scope; also separates upload/build timing
     RT_CUDA(cudaEventRecord(D.ev1, st));
     RT_CUDA(cudaEventSynchronize(D.ev1));
@@ -278,10 +283,11 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     D.hint_ready = false;                      // tile-cost hints describe the previous scene's frames
     const int32_t old_prims = D.bvh_prims, old_root = D.bvh_root, old_slots = D.bvh_slots;
     const uint32_t old_nodes = D.n_nodes;
+    if (refit && n <= 0 && H.inst.any()) refit = false;       // nothing but instances: a refit is the TLAS rebuild every commit does
     if (refit && (old_prims != n || n <= 0 || old_slots < n || D.vals_alt.bytes < (size_t)old_slots * 4)) { err = "rt_scene_refit: no committed tree over this many primitives"; return RT_E_STATE; }
     D.bvh_prims = -1;
     S = RtScene{};
-    S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_mt; S.n_spheres = n_sp; S.n_lights = n_li;
+    S.n_prims = n; S.n_meshes = n_me; S.n_meshtris = n_kt; S.n_spheres = n_sp; S.n_lights = n_li;
     S.aabb_min = mk3(H.aabb[0], H.aabb[1], H.aabb[2]); S.aabb_max = mk3(H.aabb[3], H.aabb[4], H.aabb[5]);
     S.ambient = mk3(H.ambient[0], H.ambient[1], H.ambient[2]);
     S.t_slack = (float)opt.t_slack;
@@ -296,9 +302,53 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
     S.lights = D.lights.as<float4>();
     D.n_nodes = 0;
     RT_CUDA(cudaEventRecord(D.ev0, st));
+    // Instanced meshes: BLAS / TLAS / instance records (rt_instances.h), packed once per commit (device 0 of the ctx; bounds and
+    // builders are deterministic, so the other devices upload the same arrays) once the scene's extent — which sizes the
+    // padding — is known.  The BLAS part travels only when it changed; a re-pose sends the TLAS and 128 bytes per instance.
+    RtInstanceSet& IS = const_cast<RtHostScene&>(H).inst;
+    auto upload_instances = [&](float amax_w, float pad_w) -> int {
+        if (!IS.any()) return RT_OK;
+        if (D.rank == 0) {
+            const char* why = nullptr;
+            int threads = (int)std::thread::hardware_concurrency();
+            const int leaf_max_i = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 8 ? 8 : opt.leaf_max);
+            if (!IS.pack(mbase, amax_w, pad_w, opt.pad_scale, leaf_max_i, threads < 1 ? 1 : threads, RT_STACK_ENTRIES, &why)) { err = why ? why : "instance packing failed"; return RT_E_UNSUPPORTED; }
+        }
+        if ((int64_t)S.n_slots + IS.n_tris() > (int64_t)0x7fffff00) { err = "too many instanced triangles (virtual slots exceed 2^31)"; return RT_E_UNSUPPORTED; }
+        const size_t blas_floats = (size_t)IS.tlas_base * 16;
+        const bool grow = D.inodes.bytes < IS.inodes.size() * 4 + 64;
+        RT_CUDA(D.inodes.ensure(IS.inodes.size() * 4 + 64)); RT_CUDA(D.iprims.ensure(IS.iprims.size() * 4 + 48));
+        RT_CUDA(D.inst.ensure(IS.inst.size() * 4 + 16)); RT_CUDA(D.inst_vbase.ensure(IS.vbase.size() * 4));
+        if (grow || D.inst_blas_gen != IS.blas_generation) {
+            if (blas_floats) RT_CUDA(cudaMemcpyAsync(D.inodes.p, IS.inodes.data(), blas_floats * 4, cudaMemcpyHostToDevice, st));
+            if (!IS.iprims.empty()) RT_CUDA(cudaMemcpyAsync(D.iprims.p, IS.iprims.data(), IS.iprims.size() * 4, cudaMemcpyHostToDevice, st));
+            D.inst_blas_gen = IS.blas_generation;
+        }
+        if (IS.inodes.size() > blas_floats)
+            RT_CUDA(cudaMemcpyAsync((char*)D.inodes.p + blas_floats * 4, IS.inodes.data() + blas_floats, (IS.inodes.size() - blas_floats) * 4, cudaMemcpyHostToDevice, st));
+        if (!IS.inst.empty()) RT_CUDA(cudaMemcpyAsync(D.inst.p, IS.inst.data(), IS.inst.size() * 4, cudaMemcpyHostToDevice, st));
+        RT_CUDA(cudaMemcpyAsync(D.inst_vbase.p, IS.vbase.data(), IS.vbase.size() * 4, cudaMemcpyHostToDevice, st));
+        RT_CUDA(cudaStreamSynchronize(st));                      // the packed arrays may be re-packed by the next commit
+        S.inodes = D.inodes.as<float4>(); S.iprims = D.iprims.as<float4>(); S.inst = D.inst.as<float4>(); S.inst_vbase = D.inst_vbase.as<int32_t>();
+        S.tlas_root = IS.tlas_root; S.n_inst = IS.n_packed;
+        // cameras beyond 2 x the scene's extent take the FAR form (ray-dependent padding): the BLAS padding assumes it (need_pad)
+        S.origin_reach = fminf(S.origin_reach, 2.0f * amax_w);
+        return RT_OK;
+    };
+    if (n <= 0 && IS.any()) {                                   // nothing but instances: no world BVH
+        float b6[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}, amax = 0.f;
+        IS.grow_bounds(b6, amax);
+        const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
+        S.origin_reach = rt_origin_reach(pad);
+        H.origin_box(b6, amax, D.obox);
+        S.n_slots = 0;
+        int rc = upload_instances(amax, pad);
+        if (rc) return rc;
+        D.bvh_prims = 0; D.bvh_slots = 0; D.bvh_root = 0; D.bvh_parents = false;
+    }
     if (n > 0) {
-        RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_base.as<int32_t>(), n_me, n_mt, n_sp, n_lo,
-                mk3(0.f, 0.f, 0.f), mk3(0.f, 0.f, 0.f), 0.0f};   // sphere boxes un-inflated until the origin box is known (set_obox)
+        RtRaw R{D.raw_v.as<float>(), D.raw_n.as<float>(), D.raw_s.as<float4>(), D.mesh_raw.as<int32_t>(), n_me, n_mt, n_sp, n_lo,
+                mk3(0.f, 0.f, 0.f), mk3(0.f, 0.f, 0.f), 0.0f, D.mesh_base.as<int32_t>(), n_kt};   // sphere boxes un-inflated until the origin box is known (set_obox)
         auto set_obox = [&](const float b6[6], float amax_) {
             H.origin_box(b6, amax_, D.obox);
             R.obox_lo = mk3(D.obox[0], D.obox[1], D.obox[2]); R.obox_hi = mk3(D.obox[3], D.obox[4], D.obox[5]);
@@ -319,10 +369,12 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             RT_CUDA(cudaStreamSynchronize(st));
             float amax = 0.f, b6[6];
             for (int k = 0; k < 6; ++k) { b6[k] = f_unord(bord[k]); if (std::isfinite(b6[k])) amax = fmaxf(amax, fabsf(b6[k])); }
+            IS.grow_bounds(b6, amax);
             const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
             S.origin_reach = rt_origin_reach(pad);
             set_obox(b6, amax);
             S.n_slots = old_slots;
+            { int rci = upload_instances(amax, pad); if (rci) return rci; }
             k_emit_slots<<<grid_for(old_slots), BT, 0, st>>>(R, old_slots, D.vals_alt.as<int32_t>(), D.prims.as<float4>(), D.pinfo.as<float4>(), D.leaf_lo.as<float4>(), D.leaf_hi.as<float4>());
             D.n_nodes = old_nodes;
             if (old_nodes > 0) {
@@ -357,6 +409,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
                 for (size_t i = 0; i < (size_t)n_mt * 9; ++i) grow(H.mesh_v[i], (int)(i % 3));
                 for (size_t i = 0; i < (size_t)n_lo * 9; ++i) grow(H.loose_v[i], (int)(i % 3));
                 for (int32_t i = 0; i < n_sp; ++i) { const float* sp = H.spheres.data() + 4 * (size_t)i; const float r = sqrtf(sp[3]); for (int k = 0; k < 3; ++k) { grow(sp[k] - r, k); grow(sp[k] + r, k); } }
+                IS.grow_bounds(b6, am);
                 set_obox(b6, am);
             }
             for (int32_t key = 0; key < n; ++key) {
@@ -374,6 +427,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
                     if (std::isfinite(x.hi[k])) amax = fmaxf(amax, fabsf(x.hi[k]));
                 }
             }
+            { float bi[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX}; IS.grow_bounds(bi, amax); }
             const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
             S.origin_reach = rt_origin_reach(pad);
             RtSahBuilder B;
@@ -410,6 +464,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
             S.root = root;
             S.n_slots = ns;
+            { int rci = upload_instances(amax, pad); if (rci) return rci; }
             D.bvh_prims = n; D.bvh_slots = ns; D.bvh_root = root; D.bvh_parents = false;
             RT_CUDA(cudaEventRecord(D.ev1, st));
             RT_CUDA(cudaEventSynchronize(D.ev1));
@@ -427,9 +482,12 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
         RT_CUDA(cudaStreamSynchronize(st));
         float b[6]; for (int k = 0; k < 6; ++k) b[k] = f_unord(bord[k]);
         float amax = 0.f; for (int k = 0; k < 6; ++k) if (std::isfinite(b[k])) amax = fmaxf(amax, fabsf(b[k]));
+        { float bo[6]; for (int k = 0; k < 6; ++k) bo[k] = b[k];          // origin box and padding: instances included; Morton grid: world primitives only
+          IS.grow_bounds(bo, amax);
+          const float pad0 = (float)(amax * opt.pad_scale) + 1e-30f;
+          S.origin_reach = rt_origin_reach(pad0);
+          set_obox(bo, amax); }
         const float pad = (float)(amax * opt.pad_scale) + 1e-30f;
-        S.origin_reach = rt_origin_reach(pad);
-        set_obox(b, amax);
         f3 bmin = mk3(b[0], b[1], b[2]);
         f3 inv_ext = mk3(b[3] > b[0] ? 1.0f / (b[3] - b[0]) : 0.f, b[4] > b[1] ? 1.0f / (b[4] - b[1]) : 0.f, b[5] > b[2] ? 1.0f / (b[5] - b[2]) : 0.f);
         // morton + sort
@@ -480,6 +538,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             S.nodes = D.nodes.as<float4>();
         }
         RT_CUDA(cudaGetLastError());
+        { int rci = upload_instances(amax, pad); if (rci) return rci; }
         D.bvh_prims = n; D.bvh_slots = n; D.bvh_root = S.root; D.bvh_parents = false;
     }
     RT_CUDA(cudaEventRecord(D.ev1, st));

@@ -19,6 +19,13 @@ struct RtRaw {                    // raw uploaded arrays, in the reference's sca
     // sphere_k = 0 switches the inflation off (the pass that computes the primitive bounds themselves).
     f3 obox_lo, obox_hi;
     float sphere_k;
+    // Scenes with instanced meshes (rt_instances.h): the instanced triangles have scan keys (they are meshes of the reference's
+    // scan, Scene.cs:64-93) but no entry in the raw arrays, so for everything that IS in the raw arrays the enumeration index
+    // used by the builders ("build index": mesh triangles in tri_v, spheres, loose triangles) and the scan key differ:
+    //   mesh_base / n_meshtris above index the RAW arrays; mesh_key[m] = scan key of triangle 0 of mesh m; key_tris = scan keys
+    //   taken by all mesh triangles, instanced ones included.  Without instances mesh_key == mesh_base and key_tris == n_meshtris.
+    const int32_t* mesh_key;
+    int32_t key_tris;
 };
 
 // Box half-width of a sphere.  RMath.RaySphereIntersection (RMath.cs:81-108) evaluates
@@ -46,17 +53,23 @@ RT_HD float rt_sphere_box_radius(const RtRaw& R, float4 s) {
 
 RT_HD int32_t rt_raw_nprims(const RtRaw& R) { return R.n_meshtris + R.n_spheres + R.n_loose; }
 
-// scan key -> (kind, raw index, mesh index, material id)
-RT_HD void rt_key_decode(const RtRaw& R, int32_t key, int32_t& kind, int32_t& raw, int32_t& mesh, int32_t& mat) {
+// build index -> (kind, raw index, mesh index, material id, scan key)
+RT_HD void rt_key_decode(const RtRaw& R, int32_t key, int32_t& kind, int32_t& raw, int32_t& mesh, int32_t& mat, int32_t& scan_key) {
     if (key < R.n_meshtris) {
-        int32_t lo = 0, hi = R.n_meshes;                // largest m with mesh_base[m] <= key
+        int32_t lo = 0, hi = R.n_meshes;                // largest m with mesh_base[m] <= key (instanced meshes own no raw range)
         while (hi - lo > 1) { int32_t mid = (lo + hi) >> 1; if (R.mesh_base[mid] <= key) lo = mid; else hi = mid; }
         kind = 0; raw = key; mesh = lo; mat = lo;
+        scan_key = R.mesh_key[lo] + (key - R.mesh_base[lo]);
     } else if (key < R.n_meshtris + R.n_spheres) {
         kind = 1; raw = key - R.n_meshtris; mesh = -1; mat = R.n_meshes + raw;
+        scan_key = R.key_tris + raw;
     } else {
         kind = 0; raw = key - R.n_spheres; mesh = -1; mat = R.n_meshes + R.n_spheres + (key - R.n_meshtris - R.n_spheres);
+        scan_key = R.key_tris + (key - R.n_meshtris);
     }
+}
+RT_HD void rt_key_decode(const RtRaw& R, int32_t key, int32_t& kind, int32_t& raw, int32_t& mesh, int32_t& mat) {
+    int32_t sk; rt_key_decode(R, key, kind, raw, mesh, mat, sk);
 }
 
 RT_HD void rt_prim_box(const RtRaw& R, int32_t key, f3& lo, f3& hi) {
@@ -149,9 +162,9 @@ RT_HD void rt_karras_node(const uint64_t* keys, int32_t n, int32_t i, const RtTo
 }
 
 // per-slot primitive records (layout: RtScene in rt_core.h)
-RT_HD void rt_emit_slot(const RtRaw& R, int32_t slot, int32_t key, float4* prims, float4* pinfo, float4* leaf_lo, float4* leaf_hi) {
-    int32_t kind, raw, mesh, mat; rt_key_decode(R, key, kind, raw, mesh, mat);
-    f3 lo, hi; rt_prim_box(R, key, lo, hi);
+RT_HD void rt_emit_slot(const RtRaw& R, int32_t slot, int32_t bkey, float4* prims, float4* pinfo, float4* leaf_lo, float4* leaf_hi) {
+    int32_t kind, raw, mesh, mat, key; rt_key_decode(R, bkey, kind, raw, mesh, mat, key);
+    f3 lo, hi; rt_prim_box(R, bkey, lo, hi);
     leaf_lo[slot] = make_float4(lo.x, lo.y, lo.z, 0.f);
     leaf_hi[slot] = make_float4(hi.x, hi.y, hi.z, 0.f);
     float4* pp = prims + 3 * (size_t)slot;

@@ -49,7 +49,20 @@ struct RtScene {
     float coherent_spread2;   // packet mode needs the warp's ray origins within this squared distance of each other
     float origin_reach;       // ray origins within this distance of the world origin are covered by the node padding alone
                               // (= RT_FAR_ORIGIN_FACTOR * pad * 2^16, see rt_far_pad); set at commit
+    // ---- instanced meshes (rt_scene_mesh_instance; "Instancing" below).  n_inst = 0 / null pointers without them ----
+    const float4* inodes;     // TLAS nodes, then the BLAS nodes of every base mesh: same 64-byte node format; child refs are indices
+                              // into this array, BLAS leaf refs are slots of iprims
+    const float4* iprims;     // BLAS leaf slots, 3 x float4 per OBJECT-space triangle: (v0, triangle index in its mesh) (v1, 0) (v2, 0)
+    const float4* inst;       // RT_INST_F4 x float4 per instance, in TLAS leaf order:
+                              //   [0..2] rows of the object->world matrix M (m00 m01 m02 m03)      -> the exact world vertices
+                              //   [3..5] rows of the world->object matrix (box culling only)
+                              //   [6]    int bits: (BLAS root ref, first BLAS slot, MeshIndex, scan key of triangle 0 = mesh_base[MeshIndex])
+                              //   [7]    (virtual-slot base as int bits, material id as int bits, far-pad factor |Minv|, 0)
+    const int32_t* inst_vbase;// [n_inst + 1] prefix sums of the instances' triangle counts (TLAS order): a hit on slot s of instance j
+                              // is reported as virtual slot n_slots + inst_vbase[j] + (s - first BLAS slot of j)
+    int32_t tlas_root, n_inst;
 };
+enum { RT_INST_F4 = 8 };
 
 struct RtView {
     f3 pos, fwd, right, up;
@@ -146,6 +159,44 @@ RT_HD bool rt_ray_sphere(f3 O, f3 D, f3 c, float r2, float& t_out) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Instancing (rt_scene_mesh_instance).  The reference bakes transform.localToWorldMatrix into world-space vertices for every
+// mesh on every frame (SceneComponents/SceneMesh.cs:21-31) and Scene.IntersectRay sees only the baked triangles
+// (Data/Objects/Mesh.cs:7-12).  An instance keeps the base mesh in OBJECT space plus the 3x4 matrix and produces the same world
+// triangle on the fly, with the arithmetic of the bake —
+//     Matrix4x4.MultiplyPoint3x4:  w.x = ((m00*x + m01*y) + m02*z) + m03      (binary32, left to right; SceneMesh.cs:28)
+//     edge1 = w1 - w0, edge2 = w2 - w0                                         (RMath.cs:34-35)
+//     normal = -(cross(w2 - w0, w1 - w0) / length(...))                        (SceneMesh.cs:45, Triangle.cs:13-21)
+// — so the exact triangle test sees bit-identical operands: an instanced mesh gives the same hits, distances and colours as
+// the same mesh baked by the caller, bit for bit, at 48 bytes per re-posed mesh instead of 48 bytes per triangle.  Object space
+// is used for CULLING only: the ray is carried into it approximately and tested against BLAS boxes padded for that
+// approximation (rt_instances.h).  t is preserved by an affine map (the direction is not renormalised), so cull distances
+// carry over unchanged.
+// ---------------------------------------------------------------------------------------------------------------
+RT_HD f3 rt_xform_point(float4 r0, float4 r1, float4 r2, f3 p) {             // MultiplyPoint3x4, exact operation order
+    return mk3(((r0.x * p.x + r0.y * p.y) + r0.z * p.z) + r0.w,
+               ((r1.x * p.x + r1.y * p.y) + r1.z * p.z) + r1.w,
+               ((r2.x * p.x + r2.y * p.y) + r2.z * p.z) + r2.w);
+}
+// culling-side transforms (any rounding will do: the BLAS padding covers it)
+RT_HD f3 rt_xform_point_cull(float4 r0, float4 r1, float4 r2, f3 p) {
+    return mk3(rt_fma(r0.x, p.x, rt_fma(r0.y, p.y, rt_fma(r0.z, p.z, r0.w))), rt_fma(r1.x, p.x, rt_fma(r1.y, p.y, rt_fma(r1.z, p.z, r1.w))),
+               rt_fma(r2.x, p.x, rt_fma(r2.y, p.y, rt_fma(r2.z, p.z, r2.w))));
+}
+RT_HD f3 rt_xform_dir_cull(float4 r0, float4 r1, float4 r2, f3 d) {
+    return mk3(rt_fma(r0.x, d.x, rt_fma(r0.y, d.y, r0.z * d.z)), rt_fma(r1.x, d.x, rt_fma(r1.y, d.y, r1.z * d.z)),
+               rt_fma(r2.x, d.x, rt_fma(r2.y, d.y, r2.z * d.z)));
+}
+// -Triangle.Normal of a world triangle (Triangle.cs:13-21: v = cross(V2 - V0, V1 - V0); v / length(v); SceneMesh.cs:45 negates)
+RT_HD f3 rt_tri_normal_neg(f3 w0, f3 w1, f3 w2) {
+    f3 c = um_cross(w2 - w0, w1 - w0);
+    f3 n = c / um_length(c);
+    return mk3(-n.x, -n.y, -n.z);
+}
+// Stack sentinels of the two-level walk (real leaf refs lie above them: at most 2^28 - 8 slots; RT_PACKET_DONE = 0x80000000)
+#define RT_SENT_TLAS ((int32_t)0x80000001)    // the world BVH is done: continue at the TLAS root
+#define RT_SENT_EXIT ((int32_t)0x80000002)    // the BLAS of the current instance is done: back to the TLAS, world-space slabs again
+
+// ---------------------------------------------------------------------------------------------------------------
 // BVH traversal.  Result-equivalent to the reference's linear scan (Scene.cs:43-122):
 //   closest: argmin over all primitives that pass the exact test of (t, scan key)  == strict-'>' update in scan order
 //   any    : true iff some primitive passes with t*t < d2  == closest-hit-then-compare (RayTracingSetup.cs:333-345),
@@ -194,25 +245,31 @@ RT_HD float rt_far_pad(f3 O) {
     return d == d ? d : INFINITY;
 }
 
-template <bool ANY, bool FAR = false, class STK>
+// INST: the scene has instanced meshes (S.n_inst > 0 possible): after the world BVH the walk continues through the TLAS
+// (S.inodes / S.tlas_root) and, per instance, through the base mesh's BLAS with the ray carried into object space for the box
+// tests; every triangle test runs in world space on the on-the-fly baked vertices ("Instancing" above).
+template <bool ANY, bool FAR = false, bool INST = false, class STK>
 RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& stk, float& best_t, int32_t& best_slot) {
     best_t = FLT_MAX; best_slot = -1;
     stk.sp = 0;                       // an any-hit query returns early and leaves entries behind
-    if (S.n_prims <= 0) return false;
+    if (S.n_prims <= 0 && !(INST && S.n_inst > 0)) return false;
     float idx_ = rt_safe_inv(D.x, inv.x), idy_ = rt_safe_inv(D.y, inv.y), idz_ = rt_safe_inv(D.z, inv.z);
     float oodx = O.x * idx_, oody = O.y * idy_, oodz = O.z * idz_;
     // FAR: every slab plane moved outward by dl in space = by dl * |1/d| along the ray (inf * 0 cannot occur: |1/d| > 0)
     const float dl = FAR ? rt_far_pad(O) : 0.0f;
-    const float ex = dl * fabsf(idx_), ey = dl * fabsf(idy_), ez = dl * fabsf(idz_);
+    float ex = dl * fabsf(idx_), ey = dl * fabsf(idy_), ez = dl * fabsf(idz_);
     uint32_t best_key = 0xffffffffu;
     float tcull = ANY ? rt_sqrt(any_d2) * S.t_slack : INFINITY;
     int32_t gate_mesh = -1; bool gate_ok = true;
     int32_t node = S.root;
+    const float4* nodes = S.nodes;
+    int32_t level = 0, cur = -1;      // INST: 0 = world BVH, 1 = TLAS, 2 = BLAS of instance `cur`
+    if (INST && S.n_inst > 0) { if (S.n_prims > 0) stk.push(RT_SENT_TLAS); else node = RT_SENT_TLAS; }
     RT_COUNT((ANY ? 10 : 0) + 0, 1);
     for (;;) {
         while (node >= 0) {
             RT_COUNT((ANY ? 10 : 0) + 1, 1);
-            const float4* np = S.nodes + 4 * (size_t)node;
+            const float4* np = (INST ? nodes : S.nodes) + 4 * (size_t)node;
             float4 n0 = RT_LDG4(np), n1 = RT_LDG4(np + 1), n2 = RT_LDG4(np + 2), n3 = RT_LDG4(np + 3);
             float ax0 = rt_fma(n0.x, idx_, -oodx), ax1 = rt_fma(n0.y, idx_, -oodx);
             float ay0 = rt_fma(n0.z, idy_, -oody), ay1 = rt_fma(n0.w, idy_, -oody);
@@ -246,23 +303,58 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
                 node = stk.pop();
             }
         }
+        if (INST && node <= RT_SENT_EXIT) {                         // a sentinel, not a leaf
+            if (node == RT_SENT_TLAS) { nodes = S.inodes; level = 1; node = S.tlas_root; continue; }
+            idx_ = rt_safe_inv(D.x, inv.x); idy_ = rt_safe_inv(D.y, inv.y); idz_ = rt_safe_inv(D.z, inv.z);     // RT_SENT_EXIT
+            oodx = O.x * idx_; oody = O.y * idy_; oodz = O.z * idz_;
+            if (FAR) { ex = dl * fabsf(idx_); ey = dl * fabsf(idy_); ez = dl * fabsf(idz_); }
+            level = 1;
+            if (stk.empty()) return best_slot >= 0;
+            node = stk.pop();
+            continue;
+        }
+        if (INST && level == 1) {                                   // TLAS leaf: instances [first, first + cnt)
+            const int32_t ref = ~node, first = ref >> 3, cnt = (ref & 7) + 1;
+            if (cnt > 1) stk.push(~((first + 1) * 8 + (cnt - 2)));  // the rest of the leaf, after this instance
+            stk.push(RT_SENT_EXIT);
+            cur = first;
+            const float4* ip = S.inst + RT_INST_F4 * (size_t)cur;
+            const float4 a0 = RT_LDG4(ip + 3), a1 = RT_LDG4(ip + 4), a2 = RT_LDG4(ip + 5);
+            const f3 Oo = rt_xform_point_cull(a0, a1, a2, O), Do = rt_xform_dir_cull(a0, a1, a2, D);
+            idx_ = rt_safe_inv(Do.x, rt_div(1.0f, Do.x)); idy_ = rt_safe_inv(Do.y, rt_div(1.0f, Do.y)); idz_ = rt_safe_inv(Do.z, rt_div(1.0f, Do.z));
+            oodx = Oo.x * idx_; oody = Oo.y * idy_; oodz = Oo.z * idz_;
+            if (FAR) { const float dlo = dl * RT_LDG4(ip + 7).z; ex = dlo * fabsf(idx_); ey = dlo * fabsf(idy_); ez = dlo * fabsf(idz_); }
+            level = 2;
+            node = f2i(RT_LDG4(ip + 6).x);
+            continue;
+        }
         // leaf
         {
             int32_t ref = ~node;
             int32_t first = ref >> 3, cnt = (ref & 7) + 1;
             for (int32_t k = 0; k < cnt; ++k) {
                 int32_t slot = first + k;
-                const float4* pp = S.prims + 3 * (size_t)slot;
+                const float4* pp = ((INST && level == 2) ? S.iprims : S.prims) + 3 * (size_t)slot;
                 float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
                 RT_COUNT((ANY ? 10 : 0) + 2, 1);
                 float t; bool hit;
-                if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
-                else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);
+                uint32_t key; int32_t mesh;
+                if (INST && level == 2) {                           // object-space triangle of instance `cur`: bake it, test it in world space
+                    const float4* ip = S.inst + RT_INST_F4 * (size_t)cur;
+                    const float4 m0 = RT_LDG4(ip), m1 = RT_LDG4(ip + 1), m2 = RT_LDG4(ip + 2), ii = RT_LDG4(ip + 6);
+                    const f3 w0 = rt_xform_point(m0, m1, m2, mk3(p0.x, p0.y, p0.z)), w1 = rt_xform_point(m0, m1, m2, mk3(p1.x, p1.y, p1.z)),
+                             w2 = rt_xform_point(m0, m1, m2, mk3(p2.x, p2.y, p2.z));
+                    hit = rt_ray_tri(O, D, w0, w1 - w0, w2 - w0, tcull, t);
+                    key = (uint32_t)(f2i(ii.w) + f2i(p0.w)); mesh = f2i(ii.z);
+                    slot = S.n_slots + f2i(RT_LDG4(ip + 7).x) + (slot - f2i(ii.y));      // virtual slot (rt_inst_decode)
+                } else {
+                    if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
+                    else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);
+                    key = (uint32_t)f2i(p0.w); mesh = f2i(p2.w);
+                }
                 if (!hit) continue;
-                uint32_t key = (uint32_t)f2i(p0.w);
                 bool better = ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key));
                 if (!better) continue;
-                int32_t mesh = f2i(p2.w);
                 if (mesh >= 0) {                                    // Scene.cs:67
                     if (mesh != gate_mesh) {
                         gate_mesh = mesh;
@@ -284,9 +376,28 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
 // The same query without the tree: every slot tested, argmin over (t, scan key), per-mesh gate on acceptance.  For explicit
 // rays whose direction is not normalised (rt_intersect): the reference's sphere test then no longer describes the sphere the
 // boxes were built for, so nothing may be culled.
+template <bool INST = false>
 RT_HD bool rt_scan_all(const RtScene& S, f3 O, f3 D, f3 inv, float& best_t, int32_t& best_slot) {
     best_t = FLT_MAX; best_slot = -1;
     uint32_t best_key = 0xffffffffu;
+    if (INST) for (int32_t j = 0; j < S.n_inst; ++j) {              // instanced meshes: every triangle, baked on the fly
+        const float4* ip = S.inst + RT_INST_F4 * (size_t)j;
+        const float4 m0 = RT_LDG4(ip), m1 = RT_LDG4(ip + 1), m2 = RT_LDG4(ip + 2), ii = RT_LDG4(ip + 6);
+        const int32_t mesh = f2i(ii.z), cnt = S.inst_vbase[j + 1] - S.inst_vbase[j];
+        float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
+        if (!rt_ray_aabb_inv(O, inv, mk3(lo.x, lo.y, lo.z), mk3(hi.x, hi.y, hi.z))) continue;      // Scene.cs:67
+        for (int32_t k = 0; k < cnt; ++k) {
+            const float4* pp = S.iprims + 3 * (size_t)(f2i(ii.y) + k);
+            float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+            const f3 w0 = rt_xform_point(m0, m1, m2, mk3(p0.x, p0.y, p0.z)), w1 = rt_xform_point(m0, m1, m2, mk3(p1.x, p1.y, p1.z)),
+                     w2 = rt_xform_point(m0, m1, m2, mk3(p2.x, p2.y, p2.z));
+            float t;
+            if (!rt_ray_tri(O, D, w0, w1 - w0, w2 - w0, INFINITY, t)) continue;
+            const uint32_t key = (uint32_t)(f2i(ii.w) + f2i(p0.w));
+            if (!(t < best_t || (t == best_t && key < best_key))) continue;
+            best_t = t; best_key = key; best_slot = S.n_slots + S.inst_vbase[j] + k;
+        }
+    }
     for (int32_t slot = 0; slot < S.n_slots; ++slot) {
         const float4* pp = S.prims + 3 * (size_t)slot;
         float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
@@ -307,8 +418,32 @@ RT_HD bool rt_scan_all(const RtScene& S, f3 O, f3 D, f3 inv, float& best_t, int3
 }
 
 // slot -> ObjectId {Type, Index, MeshIndex} (ObjectId.cs:7-9)
+// virtual slot of an instanced hit -> (instance in TLAS order, BLAS slot)
+RT_HD void rt_inst_decode(const RtScene& S, int32_t slot, int32_t& j, int32_t& bslot) {
+    const int32_t v = slot - S.n_slots;
+    int32_t lo = 0, hi = S.n_inst;                                  // largest j with inst_vbase[j] <= v (skips empty instances)
+    while (hi - lo > 1) { const int32_t mid = (lo + hi) >> 1; if (S.inst_vbase[mid] <= v) lo = mid; else hi = mid; }
+    j = lo;
+    bslot = f2i(RT_LDG4(S.inst + RT_INST_F4 * (size_t)j + 6).y) + (v - S.inst_vbase[j]);
+}
+// world vertices of an instanced hit, as the reference's bake computes them (SceneMesh.cs:28)
+RT_HD void rt_inst_world_tri(const RtScene& S, int32_t j, int32_t bslot, f3& w0, f3& w1, f3& w2) {
+    const float4* ip = S.inst + RT_INST_F4 * (size_t)j;
+    const float4 m0 = RT_LDG4(ip), m1 = RT_LDG4(ip + 1), m2 = RT_LDG4(ip + 2);
+    const float4* pp = S.iprims + 3 * (size_t)bslot;
+    const float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+    w0 = rt_xform_point(m0, m1, m2, mk3(p0.x, p0.y, p0.z)); w1 = rt_xform_point(m0, m1, m2, mk3(p1.x, p1.y, p1.z));
+    w2 = rt_xform_point(m0, m1, m2, mk3(p2.x, p2.y, p2.z));
+}
+
+template <bool INST = false>
 RT_HD void rt_slot_to_id(const RtScene& S, int32_t slot, int32_t& type, int32_t& index, int32_t& mesh) {
     if (slot < 0) { type = 0; index = -1; mesh = -1; return; }
+    if (INST && slot >= S.n_slots) {                                // a triangle of an instanced mesh: MeshTriangle, Index within its mesh
+        int32_t j, bslot; rt_inst_decode(S, slot, j, bslot);
+        type = 3; index = f2i(RT_LDG4(S.iprims + 3 * (size_t)bslot).w); mesh = f2i(RT_LDG4(S.inst + RT_INST_F4 * (size_t)j + 6).z);
+        return;
+    }
     const float4* pp = S.prims + 3 * (size_t)slot;
     int32_t key = f2i(RT_LDG4(pp).w), kind = f2i(RT_LDG4(pp + 1).w), m = f2i(RT_LDG4(pp + 2).w);
     if (kind != 0) { type = 1; index = key - S.n_meshtris; mesh = -1; }
@@ -332,7 +467,16 @@ struct RtSurf {
 };
 
 // RTS:321-323: surface point and normal (stored normal for triangles, RTS:420-431; GetSphereNormal, RTS:402-407)
+template <bool INST = false>
 RT_HD void rt_surf_geom(const RtScene& S, f3 O, f3 D, float t, int32_t slot, f3& P, f3& N, int32_t& mat_id) {
+    if (INST && slot >= S.n_slots) {                                // instanced triangle: the normal the bake would have stored
+        int32_t j, bslot; rt_inst_decode(S, slot, j, bslot);
+        f3 w0, w1, w2; rt_inst_world_tri(S, j, bslot, w0, w1, w2);
+        P = O + D * t;
+        N = rt_tri_normal_neg(w0, w1, w2);
+        mat_id = f2i(RT_LDG4(S.inst + RT_INST_F4 * (size_t)j + 7).y);
+        return;
+    }
     const float4* pp = S.prims + 3 * (size_t)slot;
     float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1);
     float4 pi = RT_LDG4(S.pinfo + slot);
@@ -343,9 +487,10 @@ RT_HD void rt_surf_geom(const RtScene& S, f3 O, f3 D, float t, int32_t slot, f3&
 }
 
 // RTS:321-325: + material lookup (RTS:409-436), ambient term (RTS:438-441), view vector
+template <bool INST = false>
 RT_HD void rt_surf_begin(const RtScene& S, f3 O, f3 D, float t, int32_t slot, RtSurf& sf) {
     int32_t mat_id;
-    rt_surf_geom(S, O, D, t, slot, sf.P, sf.N, mat_id);
+    rt_surf_geom<INST>(S, O, D, t, slot, sf.P, sf.N, mat_id);
     const float4* mp = S.mats + 4 * (size_t)mat_id;
     float4 m0 = RT_LDG4(mp), m1 = RT_LDG4(mp + 1), m2 = RT_LDG4(mp + 2), m3 = RT_LDG4(mp + 3);
     sf.kd = mk3(m0.x, m0.y, m0.z); sf.km = mk3(m2.x, m2.y, m2.z); sf.ks = mk3(m3.x, m3.y, m3.z);
@@ -403,11 +548,11 @@ RT_HD bool rt_shadow_irrelevant(const RtScene& S, f3 Ldir, f3 N, float d2) {
 
 // Shadow queries of one hit for lights [light_begin, light_begin + n) (n <= 32), one lane: bit i set = light
 // light_begin+i is occluded (RTS:331-345).  The kernels run the same loop warp-uniformly with packet traversal.
-template <class STK>
+template <bool INST = false, class STK>
 RT_HD uint32_t rt_shadow_mask(const RtScene& S, f3 O, f3 D, float t, int32_t slot, int32_t light_begin, int32_t n, STK& stk,
                               uint32_t& n_shadow) {
     f3 P, N; int32_t mat_id;
-    rt_surf_geom(S, O, D, t, slot, P, N, mat_id);
+    rt_surf_geom<INST>(S, O, D, t, slot, P, N, mat_id);
     f3 sO = P + N * RT_SHADOW_EPS;                                           // RTS:331
     uint32_t mask = 0;
     for (int32_t i = 0; i < n; ++i) {
@@ -418,17 +563,18 @@ RT_HD uint32_t rt_shadow_mask(const RtScene& S, f3 O, f3 D, float t, int32_t slo
         f3 inv = rt_rcp3(Ldir);
         if (rt_scene_gate(S, sO, inv)) {                                     // Scene.cs:54 inside the shadow query
             float st; int32_t ss;
-            if (rt_traverse<true>(S, sO, Ldir, inv, d2, stk, st, ss)) mask |= 1u << i;
+            if (rt_traverse<true, false, INST>(S, sO, Ldir, inv, d2, stk, st, ss)) mask |= 1u << i;
         }
     }
     return mask;
 }
 
 // Shade (RTS:304-366 minus the recursion) with the shadow results already known: occl[(li >> 5) * stride + q] bit (li & 31).
+template <bool INST = false>
 RT_HD f3 rt_shade_masked(const RtScene& S, f3 O, f3 D, float t, int32_t slot, int32_t bounce, int32_t max_bounces,
                          const uint32_t* occl, size_t stride, size_t q, RtMirror& mir) {
     RtSurf sf;
-    rt_surf_begin(S, O, D, t, slot, sf);
+    rt_surf_begin<INST>(S, O, D, t, slot, sf);
     uint32_t mask = 0;
     for (int32_t li = 0; li < S.n_lights; ++li) {
         if ((li & 31) == 0) mask = occl[(size_t)(li >> 5) * stride + q];
@@ -526,6 +672,7 @@ struct RtOut { float4* rgba32f; uint32_t* rgba8; int32_t* hit_id; float* hit_t; 
 
 // One work item of a finished wave -> framebuffer(s).  pass/n_pass: sample index of the spp_grid^2 extension; colours are
 // summed in pass order and divided once, before Rgb.Color (Rgb.cs:13) and the u8 quantisation.
+template <bool INST = false>
 RT_HD void rt_finalize_value(const RtScene& S, const RtView& V, int32_t tile_begin, uint32_t q, int32_t pass, int32_t n_pass,
                              float4 c, float ht, int32_t hslot, float4* accum, const RtOut& out) {
     int32_t x, y;
@@ -533,7 +680,7 @@ RT_HD void rt_finalize_value(const RtScene& S, const RtView& V, int32_t tile_beg
     size_t pix = (size_t)x + (size_t)y * (size_t)V.res_x;                  // GetPixelIndex, RayTracingSetup.cs:243-246
     if (pass == 0) {
         if (out.hit_id) {
-            int32_t ty, ix, me; rt_slot_to_id(S, hslot, ty, ix, me);
+            int32_t ty, ix, me; rt_slot_to_id<INST>(S, hslot, ty, ix, me);
             out.hit_id[3 * pix] = ty; out.hit_id[3 * pix + 1] = ix; out.hit_id[3 * pix + 2] = me;
         }
         if (out.hit_t) RT_ST_STREAM(out.hit_t + pix, ht);
@@ -549,7 +696,8 @@ RT_HD void rt_finalize_value(const RtScene& S, const RtView& V, int32_t tile_beg
     if (out.rgba8) RT_ST_STREAM(out.rgba8 + pix, (uint32_t)rt_quant(c.x) | ((uint32_t)rt_quant(c.y) << 8) | ((uint32_t)rt_quant(c.z) << 16) | 0xff000000u);
 }
 
+template <bool INST = false>
 RT_HD void rt_finalize_item(const RtScene& S, const RtView& V, int32_t tile_begin, uint32_t q, int32_t pass, int32_t n_pass,
                             const float4* local0, const float* hit_t, const int32_t* hit_slot, float4* accum, const RtOut& out) {
-    rt_finalize_value(S, V, tile_begin, q, pass, n_pass, local0[q], hit_t[q], hit_slot[q], accum, out);
+    rt_finalize_value<INST>(S, V, tile_begin, q, pass, n_pass, local0[q], hit_t[q], hit_slot[q], accum, out);
 }

@@ -8,12 +8,19 @@
 #include <cmath>
 #include <cfloat>
 #include "rt_hd.h"
+#include "rt_instances.h"
 #include "../../include/rtb200.h"
 
 struct RtHostScene {
     // scan order: mesh triangles (mesh order, triangle order), spheres, loose triangles  (Scene.cs:64-115)
     std::vector<float> mesh_v, mesh_n;          // 9 / 3 floats per mesh triangle
     std::vector<int32_t> mesh_base;             // first scan key of each mesh (+ total at the end after finish())
+    // Instanced meshes (rt_scene_mesh_instance) are meshes of the scan like any other — MeshIndex, scan keys, material, AABB —
+    // but own no range of mesh_v / mesh_n: mesh_raw[m] = first triangle of mesh m in the RAW arrays (== mesh_base[m] as long as
+    // no instanced mesh precedes it), mesh_inst[m] = its index in inst.insts or -1, inst_tris = scan keys taken by instances.
+    std::vector<int32_t> mesh_raw, mesh_inst;
+    int64_t inst_tris = 0;
+    RtInstanceSet inst;
     std::vector<float> mesh_aabb;               // 6 floats per mesh, verbatim (Mesh.cs:12)
     std::vector<rt_material> mesh_mats;
     std::vector<float> spheres;                 // 4 floats each
@@ -68,6 +75,7 @@ struct RtHostScene {
     // keeps the capacity of the staging vectors: a scene that is re-committed every frame (RayTracingSetup.cs:120-128) must
     // not pay for fresh pages each time (48 MB of first-touch page faults cost more than the copy itself)
     void clear() {
+        mesh_raw.clear(); mesh_inst.clear(); inst_tris = 0; inst.clear();
         mesh_v.clear(); mesh_n.clear(); mesh_base.clear(); mesh_aabb.clear(); mesh_mats.clear(); spheres.clear(); sphere_mats.clear();
         loose_v.clear(); loose_n.clear(); loose_mats.clear(); lights.clear();
         for (int k = 0; k < 3; ++k) ambient[k] = 0.f;
@@ -75,7 +83,13 @@ struct RtHostScene {
         has_mirror = false; mesh_on_device = false; mesh_stale = false; mesh_tris = 0; builder = 0;
     }
     int32_t n_meshes() const { return (int32_t)mesh_mats.size(); }
-    int32_t n_meshtris() const { return (int32_t)mesh_tris; }
+    int32_t n_meshtris() const { return (int32_t)mesh_tris; }                  // triangles in the raw arrays (baked meshes)
+    int32_t n_keytris() const { return (int32_t)(mesh_tris + inst_tris); }      // scan keys taken by mesh triangles, instanced ones included
+    // one more mesh of the scan (rt_scene_mesh: inst_index -1; rt_scene_mesh_instance: its index in inst.insts)
+    void push_mesh(int32_t inst_index, const rt_material& mat, const float aabb6[6]) {
+        mesh_base.push_back(n_keytris()); mesh_raw.push_back(n_meshtris()); mesh_inst.push_back(inst_index);
+        mesh_mats.push_back(mat); mesh_aabb.insert(mesh_aabb.end(), aabb6, aabb6 + 6);
+    }
     int32_t n_spheres() const { return (int32_t)(spheres.size() / 4); }
     int32_t n_loose() const { return (int32_t)(loose_v.size() / 9); }
     int64_t n_prims() const { return (int64_t)n_meshtris() + n_spheres() + n_loose(); }

@@ -87,6 +87,9 @@ struct RtDevice {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // ---- scene ----
     DevBuf raw_v, raw_n, raw_s, nodes, prims, pinfo, mats, mesh_aabb, mesh_base, lights;
+    // instanced meshes (rt_instances.h): first raw triangle per mesh, BLAS + TLAS nodes, object-space triangles, instance records
+    DevBuf mesh_raw, inodes, iprims, inst, inst_vbase;
+    uint64_t inst_blas_gen = 0;         // RtInstanceSet::blas_generation this device holds in iprims / the BLAS part of inodes
     RtScene S{};
     uint32_t n_nodes = 0;
     bool has_mirror = false;

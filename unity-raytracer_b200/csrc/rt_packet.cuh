@@ -132,13 +132,27 @@ __device__ __forceinline__ int32_t rt_packet_descend(const float4* __restrict__ 
     return node;
 }
 
-template <bool ANY, class STK>
+// direction octant shared by every lane that has a ray (8 = mixed); lanes without a ray fail every box test anyway
+__device__ __forceinline__ int rt_packet_octant(float idx_, float idy_, float idz_, bool active) {
+    const unsigned full = 0xffffffffu;
+    int oct = (idx_ < 0.0f ? 1 : 0) | (idy_ < 0.0f ? 2 : 0) | (idz_ < 0.0f ? 4 : 0);
+    unsigned am = __ballot_sync(full, active);
+    int lead = __shfl_sync(full, oct, am ? __ffs(am) - 1 : 0);
+    bool sane = idx_ == idx_ && idy_ == idy_ && idz_ == idz_;
+    return __all_sync(full, !active || (oct == lead && sane)) ? lead : 8;
+}
+
+// INST: two-level walk for scenes with instanced meshes, as in rt_traverse<.., INST> (rt_core.h "Instancing"): the packet walks
+// the world BVH, then the TLAS, and inside an instance the base mesh's BLAS with every lane's ray carried into object space for
+// the box tests (an affine map keeps the rays of a packet coherent and their t unchanged); triangle tests stay in world space
+// on the vertices baked on the fly.  The level and the current instance are warp-uniform.
+template <bool ANY, bool INST = false, class STK>
 __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D, f3 inv, bool active, float any_d2, STK& stk,
                                                    float& best_t, int32_t& best_slot) {
     const unsigned full = 0xffffffffu;
     best_t = FLT_MAX; best_slot = -1;
     stk.sp = 0;
-    if (S.n_prims <= 0) return false;
+    if (S.n_prims <= 0 && !(INST && S.n_inst > 0)) return false;
     float idx_ = rt_safe_inv(D.x, inv.x), idy_ = rt_safe_inv(D.y, inv.y), idz_ = rt_safe_inv(D.z, inv.z);
     float oodx = O.x * idx_, oody = O.y * idy_, oodz = O.z * idz_;
     uint32_t best_key = 0xffffffffu;
@@ -146,21 +160,44 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
     if (!active) tcull = -1.0f;                       // every box test of this lane fails (tmin >= 0 > tcull)
     int32_t gate_mesh = -1; bool gate_ok = true;
     bool found = false;                               // ANY: this lane already has its occluder
-    // direction octant shared by every lane that has a ray (8 = mixed); lanes without a ray fail every test anyway
-    int oct = (idx_ < 0.0f ? 1 : 0) | (idy_ < 0.0f ? 2 : 0) | (idz_ < 0.0f ? 4 : 0);
-    {
-        unsigned am = __ballot_sync(full, active);
-        int lead = __shfl_sync(full, oct, am ? __ffs(am) - 1 : 0);
-        bool sane = idx_ == idx_ && idy_ == idy_ && idz_ == idz_;
-        oct = __all_sync(full, !active || (oct == lead && sane)) ? lead : 8;
-    }
+    int oct = rt_packet_octant(idx_, idy_, idz_, active);
     const float4* __restrict__ nodes = S.nodes;
     int32_t node = S.root;                            // warp-uniform from here on
+    int32_t level = 0, cur = -1;                      // INST: 0 = world BVH, 1 = TLAS, 2 = BLAS of instance `cur` (warp-uniform)
+    if (INST && S.n_inst > 0) { if (S.n_prims > 0) stk.push_packet(RT_SENT_TLAS, -INFINITY); else node = RT_SENT_TLAS; }
 #ifdef RT_COUNT_VISITS
     { unsigned am = __ballot_sync(full, active);
       if ((threadIdx.x & 31) == 0) { RT_COUNT((ANY ? 10 : 0) + 3, 1); RT_COUNT((ANY ? 10 : 0) + 4, __popc(am)); } }
 #endif
     for (;;) {
+        if (INST && node < 0 && node != RT_PACKET_DONE) {
+            if (node <= RT_SENT_EXIT) {                                 // a sentinel, not a leaf
+                if (node == RT_SENT_TLAS) { nodes = S.inodes; level = 1; node = S.tlas_root; continue; }
+                idx_ = rt_safe_inv(D.x, inv.x); idy_ = rt_safe_inv(D.y, inv.y); idz_ = rt_safe_inv(D.z, inv.z);     // RT_SENT_EXIT
+                oodx = O.x * idx_; oody = O.y * idy_; oodz = O.z * idz_;
+                oct = rt_packet_octant(idx_, idy_, idz_, active);
+                level = 1;
+                node = rt_packet_pop(stk, tcull RT_CNT_ARG(ANY));
+                if (node == RT_PACKET_DONE) return ANY ? found : best_slot >= 0;
+                continue;
+            }
+            if (level == 1) {                                           // TLAS leaf: instances [first, first + cnt)
+                const int32_t ref = ~node, first = ref >> 3, cnt = (ref & 7) + 1;
+                if (cnt > 1) stk.push_packet(~((first + 1) * 8 + (cnt - 2)), -INFINITY);     // the rest of the leaf (its box was passed already)
+                stk.push_packet(RT_SENT_EXIT, -INFINITY);
+                cur = first;
+                const float4* ip = S.inst + RT_INST_F4 * (size_t)cur;
+                const float4 a0 = RT_LDG4(ip + 3), a1 = RT_LDG4(ip + 4), a2 = RT_LDG4(ip + 5);
+                const f3 Oo = rt_xform_point_cull(a0, a1, a2, O), Do = rt_xform_dir_cull(a0, a1, a2, D);
+                idx_ = rt_safe_inv(Do.x, rt_div(1.0f, Do.x)); idy_ = rt_safe_inv(Do.y, rt_div(1.0f, Do.y)); idz_ = rt_safe_inv(Do.z, rt_div(1.0f, Do.z));
+                oodx = Oo.x * idx_; oody = Oo.y * idy_; oodz = Oo.z * idz_;
+                oct = rt_packet_octant(idx_, idy_, idz_, active);
+                level = 2;
+                node = f2i(RT_LDG4(ip + 6).x);
+                continue;
+            }
+        }
+        if (!INST || node >= 0)
         switch (oct) {
             case 0: node = rt_packet_descend<0, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
             case 1: node = rt_packet_descend<1, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
@@ -173,23 +210,37 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
             default: node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
         }
         if (node == RT_PACKET_DONE) return ANY ? found : best_slot >= 0;
+        if (INST && (node <= RT_SENT_EXIT || level == 1)) continue;     // sentinel or TLAS leaf: handled at the top of the loop
         {
             int32_t ref = ~node;
             int32_t first = ref >> 3, cnt = (ref & 7) + 1;
             for (int32_t k = 0; k < cnt; ++k) {
                 int32_t slot = first + k;
-                const float4* pp = S.prims + 3 * (size_t)slot;
+                const float4* pp = ((INST && level == 2) ? S.iprims : S.prims) + 3 * (size_t)slot;
                 float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
 #ifdef RT_COUNT_VISITS
                 { unsigned live = __ballot_sync(full, tcull >= 0.0f);
                   if ((threadIdx.x & 31) == 0) { RT_COUNT((ANY ? 10 : 0) + 7, 1); RT_COUNT((ANY ? 10 : 0) + 8, __popc(live)); } }
 #endif
                 float t = 0.0f; bool hit = false;
+                uint32_t key; int32_t mesh;
+                if (INST && level == 2) {                               // object-space triangle of instance `cur`: bake it, test it in world space
+                    const float4* ip = S.inst + RT_INST_F4 * (size_t)cur;
+                    const float4 m0 = RT_LDG4(ip), m1 = RT_LDG4(ip + 1), m2 = RT_LDG4(ip + 2), ii = RT_LDG4(ip + 6);
+                    if (tcull >= 0.0f) {
+                        const f3 w0 = rt_xform_point(m0, m1, m2, mk3(p0.x, p0.y, p0.z)), w1 = rt_xform_point(m0, m1, m2, mk3(p1.x, p1.y, p1.z)),
+                                 w2 = rt_xform_point(m0, m1, m2, mk3(p2.x, p2.y, p2.z));
+                        hit = rt_ray_tri(O, D, w0, w1 - w0, w2 - w0, tcull, t);
+                    }
+                    key = (uint32_t)(f2i(ii.w) + f2i(p0.w)); mesh = f2i(ii.z);
+                    slot = S.n_slots + f2i(RT_LDG4(ip + 7).x) + (slot - f2i(ii.y));          // virtual slot (rt_inst_decode)
+                } else {
                 if (tcull >= 0.0f) {                                    // else: lane has no ray / is already occluded
                     if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);
                     else hit = rt_ray_tri(O, D, mk3(p0.x, p0.y, p0.z), mk3(p1.x, p1.y, p1.z), mk3(p2.x, p2.y, p2.z), tcull, t);
                 }
-                const uint32_t key = (uint32_t)f2i(p0.w);
+                key = (uint32_t)f2i(p0.w); mesh = f2i(p2.w);
+                }
                 bool cand = hit && (ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key)));
                 if (!__any_sync(full, cand)) continue;                  // warp-uniform: nobody would accept this primitive
                 // Per-mesh AABB gate (Scene.cs:67) of a candidate.  The primitive, hence its mesh, is the same for all lanes, so
@@ -198,7 +249,6 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                 // each lane met its first candidate cost up to 32 divergent evaluations per query (ncu: ~5 % of the fused shadow
                 // kernel's instructions).  rcp(ray.Direction) is recomputed here — same bits as the caller's `inv` — which frees
                 // three registers across the loops.
-                const int32_t mesh = f2i(p2.w);
                 if (mesh >= 0) {
                     if (mesh != gate_mesh) {
                         gate_mesh = mesh;

@@ -27,6 +27,10 @@ namespace {
 #ifndef RT_MIN_CTAS_PRIMARY
 #define RT_MIN_CTAS_PRIMARY 12
 #endif
+// the instantiations for scenes with instanced meshes (INST) carry the two-level state and bake triangles on the fly
+#ifndef RT_MIN_CTAS_INST
+#define RT_MIN_CTAS_INST 8
+#endif
 #ifndef RT_STK_CAP
 #define RT_STK_CAP 12
 #endif
@@ -166,8 +170,8 @@ __device__ unsigned long long* g_rt_tile_dbg = nullptr;      // per tile: (start
 #endif
 // FAR (RtView::far_origin, a camera many scene extents away): per-lane loop with ray-dependent node padding (rt_far_pad) —
 // a kernel of its own so that its registers do not count against the packet loop's
-template <bool FAR>
-__global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
+template <bool FAR, bool INST>
+__global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS_PRIMARY) k_trace_primary(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                         float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work,
                                                         RtHintIn hin, RtHintOut hout) {
     RT_DECL_STACK(stk);
@@ -188,10 +192,10 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtSc
         if (valid) rt_primary_ray(V, x, y, si, sj, O, D);
         const f3 inv = rt_rcp3(D);
         if (valid) active = rt_scene_gate(S, O, inv);                                               // Scene.cs:54
-        if (FAR) { if (active) rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+        if (FAR) { if (active) rt_traverse<false, true, INST>(S, O, D, inv, 0.f, stk, bt, bs); }
         else if (S.packet) {              // rays of one 8x4 pixel tile share the origin and are almost parallel
-            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
-        } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false, INST>(S, O, D, inv, active, 0.f, stk, bt, bs);
+        } else if (active) rt_traverse<false, false, INST>(S, O, D, inv, 0.f, stk, bt, bs);
         size_t q = (size_t)t * 32 + lane;
         RT_ST_STREAM(hit_t + q, bt); RT_ST_STREAM(hit_slot + q, valid ? bs : -2);
         rt_hint_record(hout, t, (unsigned)clock() - c0, lane);
@@ -202,7 +206,8 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS_PRIMARY) k_trace_primary(RtSc
     }
 }
 
-__global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_queue(RtScene S, const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays,
+template <bool INST>
+__global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_trace_queue(RtScene S, const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays,
                                                       float* __restrict__ hit_t, int* __restrict__ hit_slot, unsigned* work) {
     RT_DECL_STACK(stk);
     const int lane = threadIdx.x & 31;
@@ -220,8 +225,8 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_queue(RtScene S, con
         if (q < n) active = rt_scene_gate(S, O, inv);
         float bt = FLT_MAX; int bs = -1;
         if (S.packet && rt_warp_coherent(O, D, active, S.coherent_spread2)) {
-            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false>(S, O, D, inv, active, 0.f, stk, bt, bs);
-        } else if (active) rt_traverse<false>(S, O, D, inv, 0.f, stk, bt, bs);
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false, INST>(S, O, D, inv, active, 0.f, stk, bt, bs);
+        } else if (active) rt_traverse<false, false, INST>(S, O, D, inv, 0.f, stk, bt, bs);
         if (q < n) { hit_t[q] = bt; hit_slot[q] = bs; }
     }
 }
@@ -252,8 +257,8 @@ struct RtFuse {
 
 // (A "mega" variant that also ran k_trace_primary's body here, camera ray to final colour in registers, was measured
 // SLOWER on cfg3 — 2.49 -> 3.06 ms, instruction-cache pressure of the two traversal instantiations in one loop — and removed.)
-template <bool DEPTH0, bool FUSE>
-__global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
+template <bool DEPTH0, bool FUSE, bool INST>
+__global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_trace_shadow(RtScene S, RtView V, int tile_begin, int n_tiles, int si, int sj,
                                                           const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
                                                           const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
                                                           int light_begin, int n_l, uint32_t* __restrict__ occl, unsigned* work,
@@ -284,7 +289,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
                 int mat_id;
                 item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
                 ht = RT_LD_STREAM(hit_t + q);
-                rt_surf_geom(S, O, D, ht, slot, P, N, mat_id);
+                rt_surf_geom<INST>(S, O, D, ht, slot, P, N, mat_id);
                 sO = P + N * RT_SHADOW_EPS;                                                        // RTS:331
             }
             const int i0 = one_light >= 0 ? one_light : 0, i1 = one_light >= 0 ? one_light + 1 : n_l;
@@ -301,8 +306,8 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
                 if (has && !occluded) act = rt_scene_gate(S, sO, inv);                                 // Scene.cs:54
                 float st; int ss;
                 if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
-                    if (__any_sync(full, act) && rt_traverse_packet<true>(S, sO, Ldir, inv, act, d2, stk, st, ss)) occluded = true;
-                } else if (act) occluded = rt_traverse<true>(S, sO, Ldir, inv, d2, stk, st, ss);
+                    if (__any_sync(full, act) && rt_traverse_packet<true, INST>(S, sO, Ldir, inv, act, d2, stk, st, ss)) occluded = true;
+                } else if (act) occluded = rt_traverse<true, false, INST>(S, sO, Ldir, inv, d2, stk, st, ss);
                 if (occluded) mask |= 1u << i;
             }
         }
@@ -324,7 +329,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
         RtMirror mir; mir.emit = false;
         float4 col = make_float4(V.bg255.x, V.bg255.y, V.bg255.z, 0.f);                            // RTS:310-311
         if (has) {
-            f3 c = rt_shade_masked(S, O, D, ht, slot, F.depth, V.max_bounces, &mask, 0, 0, mir);
+            f3 c = rt_shade_masked<INST>(S, O, D, ht, slot, F.depth, V.max_bounces, &mask, 0, 0, mir);
             col = make_float4(c.x, c.y, c.z, 0.f);
         }
         if (!(DEPTH0 && F.fin) && slot >= -1) RT_ST_STREAM(F.local_out + q, col);
@@ -340,7 +345,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
                 F.link_out[o] = make_float4(mir.km.x, mir.km.y, mir.km.z, __int_as_float((int)q));
             }
         }
-        if (DEPTH0 && F.fin && slot >= -1) rt_finalize_value(S, V, tile_begin, q, F.pass, F.n_pass, col, has ? ht : FLT_MAX, slot, F.accum, F.out);
+        if (DEPTH0 && F.fin && slot >= -1) rt_finalize_value<INST>(S, V, tile_begin, q, F.pass, F.n_pass, col, has ? ht : FLT_MAX, slot, F.accum, F.out);
         if (DEPTH0) rt_hint_record(hout, wt, (unsigned)clock() - c0, lane);
 #ifdef RT_TILE_TIMING
         // shadow-kernel tile costs (cycles; per-light items of a split tile add up) behind the primary kernel's records
@@ -356,7 +361,7 @@ __global__ void __launch_bounds__(128, RT_MIN_CTAS) k_trace_shadow(RtScene S, Rt
 
 // Shading + light loop with the shadow results known (rt_shade_masked); appends the reflection rays of mirror hits to
 // the next depth's queue with a warp-aggregated (ballot/popc) reservation.  Pure streaming kernel: no traversal.
-template <bool DEPTH0>
+template <bool DEPTH0, bool INST>
 __global__ void __launch_bounds__(256) k_shade(RtScene S, RtView V, int depth, int tile_begin, int n_tiles, int si, int sj,
                                                 const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in,
                                                 const float* __restrict__ hit_t, const int* __restrict__ hit_slot,
@@ -374,7 +379,7 @@ __global__ void __launch_bounds__(256) k_shade(RtScene S, RtView V, int depth, i
         else if (slot >= 0) {
             f3 O, D;
             item_ray<DEPTH0>(V, tile_begin, q, lane, si, sj, rays_in, O, D);
-            f3 c = rt_shade_masked(S, O, D, hit_t[q], slot, depth, V.max_bounces, occl, occl_stride, q, mir);
+            f3 c = rt_shade_masked<INST>(S, O, D, hit_t[q], slot, depth, V.max_bounces, occl, occl_stride, q, mir);
             local_out[q] = make_float4(c.x, c.y, c.z, 0.f);
         }
         unsigned m = __ballot_sync(full, mir.emit);
@@ -397,13 +402,15 @@ __global__ void k_fold(const unsigned* __restrict__ n_ptr, const float4* __restr
     for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) rt_fold_item(q, link, local_cur, local_prev);
 }
 
+template <bool INST>
 __global__ void k_finalize(RtScene S, RtView V, int tile_begin, int n_tiles, int pass, int n_pass, const float4* __restrict__ local0,
                            const float* __restrict__ hit_t, const int* __restrict__ hit_slot, float4* accum, RtOut out) {
     const unsigned n = (unsigned)n_tiles * 32u;
     for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x)
-        rt_finalize_item(S, V, tile_begin, q, pass, n_pass, local0, hit_t, hit_slot, accum, out);
+        rt_finalize_item<INST>(S, V, tile_begin, q, pass, n_pass, local0, hit_t, hit_slot, accum, out);
 }
 
+template <bool INST>
 __global__ void __launch_bounds__(128) k_intersect(RtScene S, int n, const float* __restrict__ o, const float* __restrict__ d,
                                                     int32_t* __restrict__ out_id, float* __restrict__ out_t) {
     RT_DECL_STACK(stk);
@@ -415,10 +422,10 @@ __global__ void __launch_bounds__(128) k_intersect(RtScene S, int n, const float
             // explicit rays come from anywhere: always the ray-padded walk.  A direction that is not normalised in binary32
             // breaks what the sphere boxes assume (rt_sphere_box_radius), so such a ray scans the primitives like the reference.
             const float dd = um_dot(D, D);
-            if (S.n_spheres > 0 && !(fabsf(dd - 1.0f) <= 0x1p-20f)) rt_scan_all(S, O, D, inv, bt, bs);
-            else { stk.sp = 0; rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+            if (S.n_spheres > 0 && !(fabsf(dd - 1.0f) <= 0x1p-20f)) rt_scan_all<INST>(S, O, D, inv, bt, bs);
+            else { stk.sp = 0; rt_traverse<false, true, INST>(S, O, D, inv, 0.f, stk, bt, bs); }
         }
-        int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
+        int32_t ty, ix, me; rt_slot_to_id<INST>(S, bs, ty, ix, me);
         out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
     }
 }
@@ -588,7 +595,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         long long plan_hash = 1469598103934665603ll;
         for (int tbk : wave_tb) plan_hash = (plan_hash ^ tbk) * 1099511628211ll;
         const long long sig[RtDevice::HINT_SIG] = {V.n_tiles, (long long)wave_tiles * 64 + waves_per_pass, V.res_x, V.res_y, V.rank, V.world, V.band_rows,
-                                                   (long long)D.S.n_prims, D.S.n_lights, fuse ? 1 : 0, plan_hash, n_pass};
+                                                   (long long)D.S.n_prims + ((long long)D.S.n_inst << 32), D.S.n_lights, fuse ? 1 : 0, plan_hash, n_pass};
         bool hint_in = opt.hints && D.hint_ready;
         for (int k = 0; k < RtDevice::HINT_SIG; ++k) hint_in = hint_in && D.hint_sig[k] == sig[k];
         const bool hint_in_shadow = hint_in && D.hint_shadow_ready;
@@ -618,13 +625,22 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
             if (hint_rec && on) h = RtHintOut{hh.lists[hb_out].as<int>() + tb, hh.counts[hb_out].as<unsigned>() + (size_t)wi * RT_NCLS, hstride};
             return h;
         };
-        const int g_trace = V.far_origin ? persistent_grid(k_trace_primary<true>, block, smem, D.sm_count, opt.ctas_per_sm)
-                                         : persistent_grid(k_trace_primary<false>, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_traceq = persistent_grid(k_trace_queue, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shadow0 = fuse ? persistent_grid(k_trace_shadow<true, true>, block, smem, D.sm_count, opt.ctas_per_sm)
-                                   : persistent_grid(k_trace_shadow<true, false>, block, smem, D.sm_count, opt.ctas_per_sm);
-        const int g_shadown = fuse ? persistent_grid(k_trace_shadow<false, true>, block, smem, D.sm_count, opt.ctas_per_sm)
-                                   : persistent_grid(k_trace_shadow<false, false>, block, smem, D.sm_count, opt.ctas_per_sm);
+        // the instantiations for this frame: INST when the scene has instanced meshes, FAR for a camera beyond the node padding's reach
+        const bool inst = D.S.n_inst > 0;
+        const auto kp_primary = inst ? (V.far_origin ? k_trace_primary<true, true> : k_trace_primary<false, true>)
+                                     : (V.far_origin ? k_trace_primary<true, false> : k_trace_primary<false, false>);
+        const auto kp_queue = inst ? k_trace_queue<true> : k_trace_queue<false>;
+        const auto kp_shadow0 = inst ? (fuse ? k_trace_shadow<true, true, true> : k_trace_shadow<true, false, true>)
+                                     : (fuse ? k_trace_shadow<true, true, false> : k_trace_shadow<true, false, false>);
+        const auto kp_shadown = inst ? (fuse ? k_trace_shadow<false, true, true> : k_trace_shadow<false, false, true>)
+                                     : (fuse ? k_trace_shadow<false, true, false> : k_trace_shadow<false, false, false>);
+        const auto kp_shade0 = inst ? k_shade<true, true> : k_shade<true, false>;
+        const auto kp_shaden = inst ? k_shade<false, true> : k_shade<false, false>;
+        const auto kp_finalize = inst ? k_finalize<true> : k_finalize<false>;
+        const int g_trace = persistent_grid(kp_primary, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_traceq = persistent_grid(kp_queue, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadow0 = persistent_grid(kp_shadow0, block, smem, D.sm_count, opt.ctas_per_sm);
+        const int g_shadown = persistent_grid(kp_shadown, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_flat = D.sm_count * 8;
         unsigned long long* ST = D.stats.as<unsigned long long>();
         RtOut out{(want & RT_OUT_RGBA32F) ? (float4*)D.o_rgba32f : nullptr, (want & RT_OUT_RGBA8) ? (uint32_t*)D.o_rgba8 : nullptr,
@@ -648,10 +664,8 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                     RT_CUDA(cudaMemsetAsync(C, 0, C_TOTAL * 4, st));
                     {
                     kbegin(RT_K_TRACE_PRIMARY);
-                    if (V.far_origin) k_trace_primary<true><<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
-                                                                                           hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
-                    else k_trace_primary<false><<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
-                                                                              hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
+                    kp_primary<<<g_trace, block, smem, st>>>(D.S, V, tb, nt, si, sj, L.hit0_t.as<float>(), L.hit0_slot.as<int>(), C + C_WORK,
+                                                              hin_of(D.hint_primary, tb, wi), hout_of(D.hint_primary, tb, wi, pass == 0));
                     kend(); ++launches;
                     }
                     for (int d = 0; d <= maxd; ++d) {
@@ -663,7 +677,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                         unsigned* wk = C + C_WORK + 8 * d;
                         if (d > 0) {
                             kbegin(RT_K_TRACE_QUEUE);
-                            k_trace_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, L.hitq_t.as<float>(), L.hitq_slot.as<int>(), wk);
+                            kp_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, L.hitq_t.as<float>(), L.hitq_slot.as<int>(), wk);
                             kend(); ++launches;
                         }
                         if (fuse) {
@@ -671,9 +685,9 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                                      n_pass > 1 ? D.accum.as<float4>() : nullptr, out, L.split_occl.as<uint32_t>(), L.split_acc.as<unsigned long long>()};
                             if (F.fin && n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
-                            if (d == 0) k_trace_shadow<true, true><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
-                                                                                                  hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0));
-                            else k_trace_shadow<false, true><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
+                            if (d == 0) kp_shadow0<<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
+                                                                                  hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0));
+                            else kp_shadown<<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                             continue;
                         }
@@ -682,14 +696,14 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                             if (c >= 7) RT_CUDA(cudaMemsetAsync(wc, 0, 4, st));
                             const int lb = c * 32, nl = (D.S.n_lights - lb) < 32 ? (D.S.n_lights - lb) : 32;
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
-                            if (d == 0) k_trace_shadow<true, false><<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
-                                                                                                   hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0 && c == 0));
-                            else k_trace_shadow<false, false><<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
+                            if (d == 0) kp_shadow0<<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{},
+                                                                                  hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0 && c == 0));
+                            else kp_shadown<<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, lb, nl, OC + (size_t)c * W, wc, ST, RtFuse{}, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                         }
                         kbegin(d ? RT_K_SHADE_QUEUE : RT_K_SHADE_PRIMARY);
-                        if (d == 0) k_shade<true><<<g_flat, 256, 0, st>>>(D.S, V, 0, tb, nt, si, sj, nullptr, nullptr, ht, hs, OC, W, L.local[0].as<float4>(), rout, lout, C + 1, ST);
-                        else k_shade<false><<<g_flat, 256, 0, st>>>(D.S, V, d, 0, 0, 0, 0, C + d, rin, ht, hs, OC, W, L.local[d].as<float4>(), rout, lout, C + d + 1, ST);
+                        if (d == 0) kp_shade0<<<g_flat, 256, 0, st>>>(D.S, V, 0, tb, nt, si, sj, nullptr, nullptr, ht, hs, OC, W, L.local[0].as<float4>(), rout, lout, C + 1, ST);
+                        else kp_shaden<<<g_flat, 256, 0, st>>>(D.S, V, d, 0, 0, 0, 0, C + d, rin, ht, hs, OC, W, L.local[d].as<float4>(), rout, lout, C + d + 1, ST);
                         kend(); ++launches;
                     }
                     for (int d = maxd; d >= 1; --d) {
@@ -702,7 +716,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                         // spp passes accumulate per pixel: pass p of these tiles must follow pass p-1 of the same tiles
                         if (n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
                         kbegin(RT_K_FINALIZE);
-                        k_finalize<<<g_flat, 256, 0, st>>>(D.S, V, tb, nt, pass, n_pass, L.local[0].as<float4>(), L.hit0_t.as<float>(), L.hit0_slot.as<int>(),
+                        kp_finalize<<<g_flat, 256, 0, st>>>(D.S, V, tb, nt, pass, n_pass, L.local[0].as<float4>(), L.hit0_t.as<float>(), L.hit0_slot.as<int>(),
                                                             n_pass > 1 ? D.accum.as<float4>() : nullptr, out);
                         kend();
                         ++launches;
@@ -781,7 +795,8 @@ int rt_device_intersect(RtDevice& D, const float* d_origins, const float* d_dirs
     const size_t smem = RT_STACK_SMEM;
     int grid = (n + block - 1) / block;
     if (grid > D.sm_count * 16) grid = D.sm_count * 16;
-    k_intersect<<<grid, block, smem, D.stream>>>(D.S, n, d_origins, d_dirs, d_ids, d_t);
+    if (D.S.n_inst > 0) k_intersect<true><<<grid, block, smem, D.stream>>>(D.S, n, d_origins, d_dirs, d_ids, d_t);
+    else k_intersect<false><<<grid, block, smem, D.stream>>>(D.S, n, d_origins, d_dirs, d_ids, d_t);
     RT_CUDA(cudaGetLastError());
     return RT_OK;
 }
@@ -804,6 +819,7 @@ namespace {
 // k_intersect with one difference: this entry point may not refit the sphere boxes for origins outside the origin box of the
 // last commit (rt_abi.cu cover_origin allocates), so such a ray — like one whose direction is not normalised — takes the
 // reference's own linear scan (Scene.cs:43-122), which needs no boxes at all.  Same primitive tests, same (t, key) argmin.
+template <bool INST>
 __global__ void __launch_bounds__(128) k_intersect_static(RtScene S, int n, f3 obox_lo, f3 obox_hi, const float* __restrict__ o,
                                                            const float* __restrict__ d, int32_t* __restrict__ out_id, float* __restrict__ out_t) {
     RT_DECL_STACK(stk);
@@ -814,10 +830,10 @@ __global__ void __launch_bounds__(128) k_intersect_static(RtScene S, int n, f3 o
         if (rt_scene_gate(S, O, inv)) {
             const float dd = um_dot(D, D);
             const bool covered = O.x >= obox_lo.x && O.x <= obox_hi.x && O.y >= obox_lo.y && O.y <= obox_hi.y && O.z >= obox_lo.z && O.z <= obox_hi.z;
-            if (S.n_spheres > 0 && (!covered || !(fabsf(dd - 1.0f) <= 0x1p-20f))) rt_scan_all(S, O, D, inv, bt, bs);
-            else { stk.sp = 0; rt_traverse<false, true>(S, O, D, inv, 0.f, stk, bt, bs); }
+            if (S.n_spheres > 0 && (!covered || !(fabsf(dd - 1.0f) <= 0x1p-20f))) rt_scan_all<INST>(S, O, D, inv, bt, bs);
+            else { stk.sp = 0; rt_traverse<false, true, INST>(S, O, D, inv, 0.f, stk, bt, bs); }
         }
-        int32_t ty, ix, me; rt_slot_to_id(S, bs, ty, ix, me);
+        int32_t ty, ix, me; rt_slot_to_id<INST>(S, bs, ty, ix, me);
         out_id[3 * i] = ty; out_id[3 * i + 1] = ix; out_id[3 * i + 2] = me; out_t[i] = bt;
     }
 }
@@ -856,8 +872,9 @@ int rt_device_intersect_static(RtDevice& D, const float* h_origins, const float*
     RT_CUDA(cudaMemcpyAsync(d_d, h_dirs, (size_t)n * 12, cudaMemcpyHostToDevice, D.stream));
     int grid = (n + RT_BLOCK - 1) / RT_BLOCK;
     if (grid > D.sm_count * 16) grid = D.sm_count * 16;
-    k_intersect_static<<<grid, RT_BLOCK, RT_STACK_SMEM, D.stream>>>(D.S, n, mk3(D.obox[0], D.obox[1], D.obox[2]), mk3(D.obox[3], D.obox[4], D.obox[5]),
-                                                                     d_o, d_d, d_ids, d_t);
+    const f3 olo = mk3(D.obox[0], D.obox[1], D.obox[2]), ohi = mk3(D.obox[3], D.obox[4], D.obox[5]);
+    if (D.S.n_inst > 0) k_intersect_static<true><<<grid, RT_BLOCK, RT_STACK_SMEM, D.stream>>>(D.S, n, olo, ohi, d_o, d_d, d_ids, d_t);
+    else k_intersect_static<false><<<grid, RT_BLOCK, RT_STACK_SMEM, D.stream>>>(D.S, n, olo, ohi, d_o, d_d, d_ids, d_t);
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaMemcpyAsync(h_ids, d_ids, (size_t)n * 12, cudaMemcpyDeviceToHost, D.stream));
     RT_CUDA(cudaMemcpyAsync(h_t, d_t, (size_t)n * 4, cudaMemcpyDeviceToHost, D.stream));

@@ -11,6 +11,8 @@ import ctypes as C
 import os
 import numpy as np
 
+from . import scenes
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librtb200.so")
 
@@ -18,7 +20,7 @@ RT_OUT_RGBA32F, RT_OUT_RGBA8, RT_OUT_HIT_ID, RT_OUT_HIT_T = 1, 2, 4, 8
 RT_OUT_ALL = 15
 
 ABI_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_begin", "rt_scene_spheres",
-               "rt_scene_triangles", "rt_scene_mesh", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
+               "rt_scene_triangles", "rt_scene_mesh", "rt_scene_base_mesh", "rt_scene_mesh_instance", "rt_scene_update_instance", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
                "rt_scene_update_triangles", "rt_scene_update_spheres", "rt_scene_update_lights", "rt_scene_recommit", "rt_scene_refit", "rt_render",
                "rt_render_device", "rt_read_outputs", "rt_device_outputs", "rt_intersect", "rt_intersect_static", "rt_get_stats", "rt_set_stream",
                "rt_set_partition", "rt_host_register", "rt_host_unregister", "rt_alloc_outputs", "rt_export_outputs", "rt_import_outputs", "rt_set_option"]
@@ -87,6 +89,9 @@ def load_library():
     L.rt_scene_triangles.argtypes = [vp, fp, fp, vp, C.c_int]
     L.rt_scene_mesh.argtypes = [vp, fp, fp, C.c_int, vp, fp]
     L.rt_scene_lights.argtypes = [vp, fp, C.c_int, fp]
+    L.rt_scene_base_mesh.argtypes = [vp, fp, C.c_int]
+    L.rt_scene_mesh_instance.argtypes = [vp, C.c_int, fp, vp, fp]
+    L.rt_scene_update_instance.argtypes = [vp, C.c_int, fp, fp]
     L.rt_scene_commit.argtypes = [vp, fp]
     L.rt_scene_get_aabb.argtypes = [vp, fp]
     L.rt_scene_update_mesh.argtypes = [vp, C.c_int, fp, fp, fp]
@@ -157,7 +162,18 @@ class RayTracer:
         if sa.tris.shape[0]:
             v, n, m = f32(sa.tris), f32(sa.tri_normals), np.ascontiguousarray(sa.tri_mats)
             self._chk(L.rt_scene_triangles(h, _fptr(v), _fptr(n), m.ctypes.data, v.shape[0]))
-        for (v, n, mat, aabb) in sa.meshes:
+        for bv in getattr(sa, "base_meshes", []):                  # object-space meshes the instances refer to
+            bv = f32(bv)
+            rc = L.rt_scene_base_mesh(h, _fptr(bv), bv.shape[0])
+            if rc < 0:
+                self._chk(rc)
+        for m in sa.meshes:                                         # call order == MeshIndex, baked meshes and instances alike
+            if isinstance(m, scenes.MeshInstance):
+                mm, mat = f32(m.m3x4), np.ascontiguousarray(m.mat)
+                bb = None if m.aabb is None else f32(m.aabb)
+                self._chk(L.rt_scene_mesh_instance(h, int(m.base), _fptr(mm), mat.ctypes.data, _fptr(bb) if bb is not None else None))
+                continue
+            v, n, mat, aabb = m
             v, n, aabb, mat = f32(v), f32(n), f32(aabb), np.ascontiguousarray(mat)
             self._chk(L.rt_scene_mesh(h, _fptr(v), _fptr(n), v.shape[0], mat.ctypes.data, _fptr(aabb)))
         li, amb = f32(sa.lights), f32(sa.ambient)
@@ -172,6 +188,12 @@ class RayTracer:
     def update_mesh(self, mesh_index, v, n, aabb):
         v, n, aabb = (np.ascontiguousarray(a, dtype=np.float32) for a in (v, n, aabb))
         self._chk(self.L.rt_scene_update_mesh(self.h, int(mesh_index), _fptr(v), _fptr(n), _fptr(aabb)))
+
+    def update_instance(self, mesh_index, m3x4, aabb=None):
+        """rt_scene_update_instance: new localToWorldMatrix (and Mesh.AABB, None = computed) of an instanced mesh."""
+        mm = np.ascontiguousarray(m3x4, dtype=np.float32)
+        bb = None if aabb is None else np.ascontiguousarray(aabb, dtype=np.float32)
+        self._chk(self.L.rt_scene_update_instance(self.h, int(mesh_index), _fptr(mm), _fptr(bb) if bb is not None else None))
 
     def update_triangles(self, first, v, n):
         v, n = np.ascontiguousarray(v, dtype=np.float32), np.ascontiguousarray(n, dtype=np.float32)

@@ -23,6 +23,13 @@ def material(diffuse=(0, 0, 0), ambient=(0, 0, 0), mirror=(0, 0, 0), specular=(0
     return m
 
 
+class MeshInstance:
+    """An instanced mesh of a SceneArrays: base-mesh index, 3x4 localToWorldMatrix, material, Mesh.AABB or None."""
+
+    def __init__(self, base, m3x4, mat, aabb):
+        self.base, self.m3x4, self.mat, self.aabb = base, m3x4, mat, aabb
+
+
 class SceneArrays:
     """The reference's `Scene` struct (Data/Objects/Scene.cs:8-15) as flat arrays.
 
@@ -61,13 +68,40 @@ class SceneArrays:
         self.meshes.append((np.ascontiguousarray(verts9, F), np.ascontiguousarray(normals, F), mat,
                             np.ascontiguousarray(aabb, F)))
 
+    # ---- instanced meshes (rt_scene_base_mesh / rt_scene_mesh_instance): SceneMesh.cs:11-53 without the per-frame bake ----
+    def add_base_mesh(self, verts9_object):
+        """Object-space triangles (n,9) of a mesh that instances refer to; returns its index."""
+        if not hasattr(self, "base_meshes"):
+            self.base_meshes = []
+        self.base_meshes.append(np.ascontiguousarray(verts9_object, F).reshape(-1, 9))
+        return len(self.base_meshes) - 1
+
+    def add_instance(self, base, m3x4, mat, aabb=None):
+        """One occurrence of base mesh `base` under the 3x4 localToWorldMatrix m3x4; takes one MeshIndex like add_mesh.
+        aabb None = let the library compute Mesh.AABB as SceneMesh.cs:22-31 does."""
+        self.meshes.append(MeshInstance(base, np.ascontiguousarray(m3x4, F).reshape(3, 4), mat,
+                                        None if aabb is None else np.ascontiguousarray(aabb, F)))
+
+    def baked(self):
+        """The same scene with every instance baked the way the reference does it (bake_tris): what the oracle consumes."""
+        out = SceneArrays()
+        out.spheres, out.sphere_mats, out.tris, out.tri_normals, out.tri_mats = self.spheres, self.sphere_mats, self.tris, self.tri_normals, self.tri_mats
+        out.lights, out.ambient, out.scene_aabb = self.lights, self.ambient, self.scene_aabb
+        for m in self.meshes:
+            if isinstance(m, MeshInstance):
+                tris, normals, aabb = bake_tris(self.base_meshes[m.base], m.m3x4)
+                out.add_mesh(tris, normals, m.mat, aabb if m.aabb is None else m.aabb)
+            else:
+                out.meshes.append(m)
+        return out
+
     def add_light(self, pos, intensity):
         inten = np.broadcast_to(np.asarray(intensity, F), (3,))        # ScenePointLight.cs:12 scalar -> float3
         self.lights = np.vstack([self.lights, np.array([[*pos, *inten]], F)])
 
     @property
     def n_mesh_tris(self):
-        return sum(m[0].shape[0] for m in self.meshes)
+        return sum((self.base_meshes[m.base].shape[0] if isinstance(m, MeshInstance) else m[0].shape[0]) for m in self.meshes)
 
     @property
     def n_prims(self):
@@ -131,6 +165,17 @@ def bake_mesh(local_verts, indices, M):
     return tris, normals, aabb
 
 
+def bake_tris(tris9_object, M):
+    """SceneMesh.cs:21-52 for an un-indexed triangle list: MultiplyPoint3x4 of every vertex, AABB of the baked vertices,
+    negated Triangle.Normal.  This is the arithmetic rt_scene_mesh_instance reproduces on the device."""
+    w = multiply_point_3x4(np.asarray(M, F), np.asarray(tris9_object, F).reshape(-1, 3)).astype(F)
+    if w.shape[0] == 0:                                             # aabb.Min = float.MaxValue, aabb.Max = float.MinValue (SceneMesh.cs:23-24)
+        return np.zeros((0, 9), F), np.zeros((0, 3), F), np.array([np.finfo(F).max] * 3 + [-np.finfo(F).max] * 3, F)
+    aabb = np.concatenate([w.min(axis=0), w.max(axis=0)]).astype(F)
+    tris = w.reshape(-1, 9)
+    return tris, (-triangle_normal(tris)).astype(F), aabb
+
+
 # Unity built-in Cube (default-resources fileID 10202): 24 verts, 12 tris. Not in the repo; restated (SURVEY §8(c)).
 _CUBE_V = np.array([(.5, -.5, .5), (-.5, -.5, .5), (.5, .5, .5), (-.5, .5, .5), (.5, .5, -.5), (-.5, .5, -.5),
                     (.5, -.5, -.5), (-.5, -.5, -.5), (.5, .5, .5), (-.5, .5, .5), (.5, .5, -.5), (-.5, .5, -.5),
@@ -151,11 +196,12 @@ def make_params(res_x, res_y, dist, half_h, half_v, background=(0, 0, 0), bounce
     return p
 
 
-def rt_unity(mirror_sphere=False):
+def rt_unity(mirror_sphere=False, instanced=False):
     """Demo-RayTracing/RayTracing.unity transcribed (RT.unity:244-684 + Prefabs/*.prefab).
 
     mirror_sphere=False: as shipped (the Sphere instance overrides IsMirror=0 and ks=0, RT.unity:445-458).
     mirror_sphere=True : Sphere prefab defaults restored (Prefabs/Sphere.prefab:99-117) = BASELINE config 2.
+    instanced=True     : the Cube goes in as an instance (object-space cube + localToWorldMatrix) instead of baked triangles.
     """
     s = SceneArrays()
     # SceneSphere.cs:13-21: radius = localScale.x * 0.5, stores r^2. Scale 20 -> r 10 -> r2 100.
@@ -173,7 +219,10 @@ def rt_unity(mirror_sphere=False):
     # Cube mesh: RT.unity:380-436, Prefabs/Cube.prefab (scale 28.664,10,10)
     M = trs_matrix((-24.7, 1.5497656e-6, 27.6), (-0.37513673, 0.13105033, 0.3026398, 0.8663183), (28.664, 10, 10))
     tris, normals, aabb = bake_mesh(_CUBE_V, _CUBE_I, M)
-    s.add_mesh(tris, normals, material((0, 1, 1)), aabb)
+    if instanced:
+        s.add_instance(s.add_base_mesh(_CUBE_V[np.asarray(_CUBE_I, np.int64).reshape(-1, 3)].reshape(-1, 9)), M, material((0, 1, 1)), aabb)
+    else:
+        s.add_mesh(tris, normals, material((0, 1, 1)), aabb)
     s.add_light((5.79, 0, 0), 100000.0)
     s.ambient = np.array((15, 15, 15), F)
     return s
@@ -322,6 +371,71 @@ def cfg4_scene(n=64, grid=5, radius=4.0):
     s.add_light((40, 40, 0), 2e5)
     s.add_light((-40, 40, 0), 2e5)
     s.ambient = np.array((15, 15, 15), F)
+    return s
+
+
+def cfg4_instanced(n=64, grid=5, radius=4.0):
+    """BASELINE config 4 as what its name says, an instanced-mesh scene: ONE displaced geodesic sphere in object space
+    (n=64: 81 920 triangles) and grid^3 instances of it, each with its own rotation, position and diffuse colour.  `.baked()`
+    gives the equivalent scene of grid^3 baked meshes (the reference's SceneMesh.cs:21-31 arithmetic), bit-comparable with it."""
+    s = SceneArrays()
+    base_tris, _ = displaced_icosphere(n, radius, (0.0, 0.0, 0.0), SEED)
+    b = s.add_base_mesh(base_tris)
+    spacing = 3.0 * radius
+    half = (grid - 1) / 2.0
+    k = 0
+    for ix in range(grid):
+        for iy in range(grid):
+            for iz in range(grid):
+                M = np.zeros((3, 4), F)
+                M[:, :3] = random_rotation(SEED + 1, k).astype(F)
+                M[:, 3] = ((ix - half) * spacing, (iy - half) * spacing, 70.0 + (iz - half) * spacing)
+                kd = tuple(0.2 + 0.8 * float(uniform01(SEED + 2, 3 * k + j)) for j in range(3))
+                s.add_instance(b, M, material(kd, (1, 1, 1), (0, 0, 0), (1, 1, 1), 20.0, 0))
+                k += 1
+    s.add_light((40, 40, 0), 2e5)
+    s.add_light((-40, 40, 0), 2e5)
+    s.ambient = np.array((15, 15, 15), F)
+    return s
+
+
+def instanced_soup(seed=21, n_bases=3, n_instances=9, n_baked=2, extent=30.0, mirror_frac=0.3):
+    """Parity fixture for instancing: a few small object-space meshes, instances of them under random rotations, non-uniform
+    scales and translations (some of them mirrors), interleaved in MeshIndex order with baked meshes, plus the spheres and
+    loose triangles of random_soup."""
+    rng = np.random.default_rng(seed)
+    s = random_soup(n_tris=300, n_spheres=60, n_meshes=0, seed=seed + 1, extent=extent, mirror_frac=mirror_frac)
+    bases = []
+    for b in range(n_bases):
+        k = int(rng.integers(20, 200))
+        c = rng.uniform(-3, 3, (k, 1, 3))
+        tr = (c + rng.normal(scale=1.2, size=(k, 3, 3))).reshape(k, 9).astype(F)
+        bases.append(s.add_base_mesh(tr))
+
+    def rand_matrix():
+        q = rng.normal(size=4); q /= np.linalg.norm(q)
+        x, y, z, w = q
+        R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                      [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                      [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+        M = np.zeros((3, 4), F)
+        M[:, :3] = (R * rng.uniform(0.4, 2.5, 3)[None, :]).astype(F)
+        M[:, 3] = rng.uniform(-extent * 0.7, extent * 0.7, 3) + np.array([0, 0, 2.5 * extent])
+        return M
+
+    order = ["i"] * n_instances + ["b"] * n_baked
+    rng.shuffle(order)
+    for kind in order:
+        mir = rng.uniform() < mirror_frac
+        mat = material(tuple(rng.uniform(0.1, 1.0, 3)), (1, 1, 1), (0.7, 0.7, 0.7) if mir else (0, 0, 0), (1, 1, 1), 20.0, 1 if mir else 0)
+        if kind == "i":
+            s.add_instance(bases[int(rng.integers(0, n_bases))], rand_matrix(), mat)
+        else:
+            k = int(rng.integers(10, 80))
+            c = rng.uniform(-extent * 0.7, extent * 0.7, (1, 1, 3)) + np.array([0, 0, 2.5 * extent])
+            tr = (c + rng.normal(scale=2.0, size=(k, 3, 3))).reshape(k, 9).astype(F)
+            normals, aabb = mesh_from_world_tris(tr)
+            s.add_mesh(tr, normals, mat, aabb)
     return s
 
 

@@ -49,6 +49,9 @@ namespace RayTracer
 		[DllImport(Lib)] static extern int rt_scene_spheres(IntPtr ctx, Sphere[] centerR2, NativeMaterial[] materials, int n);
 		[DllImport(Lib)] static extern int rt_scene_triangles(IntPtr ctx, Triangle[] v, float3[] normals, NativeMaterial[] materials, int n);
 		[DllImport(Lib)] static extern int rt_scene_mesh(IntPtr ctx, Triangle[] v, float3[] normals, int nTris, ref NativeMaterial material, ref AABB aabb);
+		[DllImport(Lib)] static extern int rt_scene_base_mesh(IntPtr ctx, Triangle[] objectSpaceTriangles, int nTris);
+		[DllImport(Lib)] static extern int rt_scene_mesh_instance(IntPtr ctx, int baseMesh, float[] m3x4, ref NativeMaterial material, IntPtr aabbOrNull);
+		[DllImport(Lib)] static extern int rt_scene_update_instance(IntPtr ctx, int meshIndex, float[] m3x4, IntPtr aabbOrNull);
 		[DllImport(Lib)] static extern int rt_scene_lights(IntPtr ctx, PointLightData[] posIntensity, int n, ref float3 ambientRadiance);
 		[DllImport(Lib)] static extern int rt_scene_commit(IntPtr ctx, ref AABB sceneAabb);
 		[DllImport(Lib)] static extern int rt_scene_update_mesh(IntPtr ctx, int meshIndex, Triangle[] v, float3[] normals, ref AABB aabb);
@@ -69,11 +72,33 @@ namespace RayTracer
 			if (rc != 0) throw new InvalidOperationException("librtb200: " + Marshal.PtrToStringAnsi(rt_last_error(ctx)));
 		}
 
-		static NativeMaterial[] Convert(List<MaterialData> mats)
+		// Scratch arrays that only ever grow: the reference refills its List<T>s every frame (RayTracingSetup.cs:159-169,258-268), and
+		// List<T>.ToArray() would allocate a fresh array per list per frame.  List<T>.CopyTo fills the scratch array in place; the
+		// native side reads only the first `n` entries, so the arrays may be longer than the lists.
+		static Sphere[] sphereBuf = new Sphere[0];
+		static Triangle[] triBuf = new Triangle[0];
+		static float3[] normalBuf = new float3[0];
+		static PointLightData[] lightBuf = new PointLightData[0];
+		static NativeMaterial[] sphereMatBuf = new NativeMaterial[0], triMatBuf = new NativeMaterial[0];
+
+		static T[] Fill<T>(List<T> src, ref T[] buf)
 		{
-			var r = new NativeMaterial[mats.Count];
-			for (int i = 0; i < r.Length; i++) r[i] = new NativeMaterial(mats[i]);
-			return r;
+			if (buf.Length < src.Count) buf = new T[Math.Max(src.Count, 2 * buf.Length)];
+			src.CopyTo(buf);
+			return buf;
+		}
+
+		static NativeMaterial[] Convert(List<MaterialData> mats, ref NativeMaterial[] buf)
+		{
+			if (buf.Length < mats.Count) buf = new NativeMaterial[Math.Max(mats.Count, 2 * buf.Length)];
+			for (int i = 0; i < mats.Count; i++) buf[i] = new NativeMaterial(mats[i]);
+			return buf;
+		}
+
+		// rows of the 3x4 part of a Matrix4x4 (UnityEngine stores it column-major: m00 m10 m20 m30 m01 ...)
+		static float[] Rows3x4(Matrix4x4 m)
+		{
+			return new[] { m.m00, m.m01, m.m02, m.m03, m.m10, m.m11, m.m12, m.m13, m.m20, m.m21, m.m22, m.m23 };
 		}
 
 		/// Replaces what UpdateScene() hands to the CPU path (RayTracingSetup.cs:120-128): call after Scene.CalculateAABB().
@@ -81,9 +106,9 @@ namespace RayTracer
 		{
 			if (ctx == IntPtr.Zero) Check(rt_create(out ctx, new[] { 0 }, 1));
 			Check(rt_scene_begin(ctx));
-			Check(rt_scene_spheres(ctx, scene.SphereData.Spheres.ToArray(), Convert(scene.SphereData.Materials), scene.SphereData.Spheres.Count));
-			Check(rt_scene_triangles(ctx, scene.TriangleData.Triangles.ToArray(), scene.TriangleData.Normals.ToArray(),
-			                         Convert(scene.TriangleData.Materials), scene.TriangleData.Triangles.Count));
+			Check(rt_scene_spheres(ctx, Fill(scene.SphereData.Spheres, ref sphereBuf), Convert(scene.SphereData.Materials, ref sphereMatBuf), scene.SphereData.Spheres.Count));
+			Check(rt_scene_triangles(ctx, Fill(scene.TriangleData.Triangles, ref triBuf), Fill(scene.TriangleData.Normals, ref normalBuf),
+			                         Convert(scene.TriangleData.Materials, ref triMatBuf), scene.TriangleData.Triangles.Count));
 			foreach (var mesh in scene.MeshData.Meshes)          // list order == ObjectId.MeshIndex (Scene.cs:64)
 			{
 				var mat = new NativeMaterial(mesh.MaterialData);
@@ -91,9 +116,39 @@ namespace RayTracer
 				Check(rt_scene_mesh(ctx, mesh.Triangles, mesh.TriangleNormals, mesh.Triangles.Length, ref mat, ref box));
 			}
 			var ambient = scene.AmbientLight.Radiance;
-			Check(rt_scene_lights(ctx, scene.PointLights.ToArray(), scene.PointLights.Count, ref ambient));
+			Check(rt_scene_lights(ctx, Fill(scene.PointLights, ref lightBuf), scene.PointLights.Count, ref ambient));
 			var aabb = scene.AABB;                               // Scene.cs:15, computed by Scene.CalculateAABB()
 			Check(rt_scene_commit(ctx, ref aabb));
+		}
+
+		// ---- instanced meshes: SceneMesh.Mesh (SceneMesh.cs:11-53) without the per-frame world bake (INTEGRATION.md section 6) ----
+		// Between rt_scene_begin and rt_scene_commit, in place of the rt_scene_mesh call of that SceneMesh:
+		//   int b = BaseMesh(objectSpaceTriangles)            once per distinct MeshFilter.sharedMesh (gathered through its index buffer, SceneMesh.cs:36-41)
+		//   MeshInstance(b, transform.localToWorldMatrix, material)      once per SceneMesh, in MeshIndex order (baked meshes and instances share it)
+		// Later frames: UpdateInstance(meshIndex, transform.localToWorldMatrix) for the ones that moved, then Recommit().
+		public static int BaseMesh(Triangle[] objectSpaceTriangles)
+		{
+			int rc = rt_scene_base_mesh(ctx, objectSpaceTriangles, objectSpaceTriangles.Length);
+			if (rc < 0) Check(rc);
+			return rc;
+		}
+
+		/// Mesh.AABB is computed by the library exactly as SceneMesh.cs:22-31 does (min / max of the baked vertices).
+		public static void MeshInstance(int baseMesh, Matrix4x4 localToWorld, MaterialData material)
+		{
+			var mat = new NativeMaterial(material);
+			Check(rt_scene_mesh_instance(ctx, baseMesh, Rows3x4(localToWorld), ref mat, IntPtr.Zero));
+		}
+
+		public static void UpdateInstance(int meshIndex, Matrix4x4 localToWorld)
+		{
+			Check(rt_scene_update_instance(ctx, meshIndex, Rows3x4(localToWorld), IntPtr.Zero));
+		}
+
+		/// After UpdateInstance calls: rebuilds the instance tree (microseconds) and whatever else was updated.  sceneAabb = Scene.AABB.
+		public static void Recommit(AABB sceneAabb)
+		{
+			Check(rt_scene_recommit(ctx, ref sceneAabb));
 		}
 
 		/// Dirty-tracking alternative to UploadScene for frames in which the object COUNTS did not change (the usual case: only
@@ -110,11 +165,11 @@ namespace RayTracer
 				var box = meshes[i].AABB;
 				Check(rt_scene_update_mesh(ctx, i, meshes[i].Triangles, meshes[i].TriangleNormals, ref box));
 			}
-			Check(rt_scene_update_spheres(ctx, 0, scene.SphereData.Spheres.Count, scene.SphereData.Spheres.ToArray()));
-			Check(rt_scene_update_triangles(ctx, 0, scene.TriangleData.Triangles.Count, scene.TriangleData.Triangles.ToArray(),
-			                                scene.TriangleData.Normals.ToArray()));
+			Check(rt_scene_update_spheres(ctx, 0, scene.SphereData.Spheres.Count, Fill(scene.SphereData.Spheres, ref sphereBuf)));
+			Check(rt_scene_update_triangles(ctx, 0, scene.TriangleData.Triangles.Count, Fill(scene.TriangleData.Triangles, ref triBuf),
+			                                Fill(scene.TriangleData.Normals, ref normalBuf)));
 			var ambient = scene.AmbientLight.Radiance;
-			Check(rt_scene_update_lights(ctx, scene.PointLights.ToArray(), scene.PointLights.Count, ref ambient));
+			Check(rt_scene_update_lights(ctx, Fill(scene.PointLights, ref lightBuf), scene.PointLights.Count, ref ambient));
 			var aabb = scene.AABB;
 			if (refitOnly) Check(rt_scene_refit(ctx, ref aabb));
 			else Check(rt_scene_recommit(ctx, ref aabb));
