@@ -518,7 +518,10 @@ def run_ours(args, rank, world, local_rank):
                                  "(per_ray), `frac_packet_lanes` counts every lane of every packet visit; the HBM figures are under `hbm`"})
         # ---- commit path as a stage of its own: the reference rebuilds its Scene every frame ----
         steady = None
-        if world == 1 and not args.no_commit:
+        inst_scene = any(isinstance(m, rtb.scenes.MeshInstance) for m in scene.meshes)
+        if world == 1 and not args.no_commit and inst_scene:
+            steady = instancing_leg(torch, rtb, rt, scene, params, want, local_rank, args)
+        elif world == 1 and not args.no_commit:
             rt2 = rtb.RayTracer((local_rank,))                     # device LBVH builder = the per-frame (dynamic scene) path
             rt2.set_scene(scene)                                   # first commit allocates
             full = []
@@ -544,7 +547,7 @@ def run_ours(args, rank, world, local_rank):
             steady["frame_loop"] = frame_loop(rtb, scene, params, local_rank)
         cb = None
         if world == 1 and not args.no_cpu:
-            cb, _ = cpu_baseline(scene, params, 12.0, os.cpu_count() or 1)
+            cb, _ = cpu_baseline(scene.baked() if inst_scene else scene, params, 12.0, os.cpu_count() or 1)
             cb.pop("seconds", None)
         skipped = st.get("rays_shadow_skipped", 0)
         frac_skipped = skipped / max(1, rays_rank)
@@ -604,6 +607,66 @@ def moving_camera_leg(torch, rt, stream, flush, scene, params, want, steps, rays
     v = rays / (sum(ms) * 1e-3) / 1e6
     return {"value": v, "unit": UNIT, "ms_per_step": sum(ms) / len(ms), "rays_per_step": rays // max(1, steps), "vs_static_camera": v / value_static,
             "what": "camera orbits the scene centre 2 degrees per frame: tile-order hints are one frame stale; L2 flushed between frames; device-resident like `value`"}
+
+
+def instancing_leg(torch, rtb, rt, scene, params, want, dev, args):
+    """Workloads made of instanced meshes (rt_scene_mesh_instance): what the instancing buys and costs against the baked twin —
+    the scene the reference would build by baking every instance every frame (SceneMesh.cs:21-31).  Device memory of the
+    scene, wall time to re-pose EVERY instance (rt_scene_update_instance x N + rt_scene_recommit) against re-sending the baked
+    meshes (rt_scene_update_mesh x N + rt_scene_recommit), frame time instanced vs baked, frames compared bit for bit."""
+    S = rtb.scenes
+    free0 = torch.cuda.mem_get_info()[0]
+    ri = rtb.RayTracer((dev,)); ri.set_option("builder", 1 if args.builder == "sah" else 0)
+    t0 = time.perf_counter(); ri.set_scene(scene); commit_i = time.perf_counter() - t0
+    mem_i = free0 - torch.cuda.mem_get_info()[0]
+    baked = scene.baked()
+    free1 = torch.cuda.mem_get_info()[0]
+    rb = rtb.RayTracer((dev,)); rb.set_option("builder", 1 if args.builder == "sah" else 0)
+    t0 = time.perf_counter(); rb.set_scene(baked); commit_b = time.perf_counter() - t0
+    mem_b = free1 - torch.cuda.mem_get_info()[0]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def frame_ms(r, n=5):
+        out = []
+        for _ in range(n + 2):
+            flush.zero_(); torch.cuda.synchronize()
+            out.append(r.render_device(params, want, sync_stats=True)["ms_render"])
+        return sorted(out[2:])[len(out[2:]) // 2]
+    ms_i, ms_b = frame_ms(ri), frame_ms(rb)
+    allw = rtb.host.RT_OUT_ALL
+    fi, fb = ri.render(params, allw), rb.render(params, allw)
+    same = all(bool(np.array_equal(fi[k], fb[k], equal_nan=True)) for k in ("rgba32f", "rgba8", "hit_id", "hit_t"))
+    del fi, fb
+    inst = [(i, m) for i, m in enumerate(scene.meshes) if isinstance(m, S.MeshInstance)]
+    boxes = [S.bake_tris(scene.base_meshes[m.base], m.m3x4)[2] for _, m in inst]
+    rep_i, rep_b = [], []
+    for _ in range(4):
+        t0 = time.perf_counter()
+        for (i, m), bb in zip(inst, boxes):
+            ri.update_instance(i, m.m3x4, bb)
+        ri.recommit(); rep_i.append(time.perf_counter() - t0)
+    st_i = ri.stats()
+    for _ in range(2):
+        t0 = time.perf_counter()
+        for i, m in enumerate(baked.meshes):
+            rb.update_mesh(i, m[0], m[1], m[3])
+        rb.recommit(); rep_b.append(time.perf_counter() - t0)
+    ri.close(); rb.close()
+    del flush
+    torch.cuda.empty_cache()
+    if not same:
+        raise SystemExit("bench.py: the instanced frame differs from the frame of its baked twin")
+    return {"kind": "instancing", "instances": len(inst), "base_meshes": len(scene.base_meshes), "triangles_if_baked": int(scene.n_mesh_tris),
+            "device_scene_bytes": {"instanced": int(mem_i), "baked": int(mem_b)},
+            "commit_wall_s": {"instanced": commit_i, "baked": commit_b},
+            "frame_ms_device": {"instanced": ms_i, "baked": ms_b, "ratio": ms_i / ms_b},
+            "repose_all_wall_ms": {"instanced": 1e3 * sorted(rep_i)[1], "baked": 1e3 * sorted(rep_b)[0],
+                                   "instanced_device_ms": st_i["ms_commit_upload"] + st_i["ms_commit_build"]},
+            "frames_bit_identical": same,
+            "what": "instanced = rt_scene_base_mesh + rt_scene_mesh_instance (object-space mesh stored once, triangles baked on the fly with the "
+                    "reference's MultiplyPoint3x4 arithmetic); baked = the same matrices applied on the host and sent through rt_scene_mesh. "
+                    "repose = new matrix for EVERY instance + rt_scene_recommit (instanced: TLAS rebuilt on the host, 128 B per instance uploaded; "
+                    "baked: every triangle re-sent and the BVH rebuilt); L2 flushed between the timed frames"}
 
 
 def extra_cfg4(torch, dist, rtb, rank, world, local_rank, args, steps=5):

@@ -222,6 +222,8 @@ int rt_host_unregister(rt_ctx* ctx, void* ptr);
  *   light_split    fused shadow kernel: tiles of cost class >= this are handed out as one work item per light (0 = off, -1 = auto,
  *                  the default: class 6 on partitions of a quarter frame or less); needs hints
  *   hints          1 = heavy-first tile order from the previous frame's measured tile costs (default)
+ *   sort_queue     mirror-ray queues are re-ordered by (direction bin, origin cell) before they are traced, so that the lanes of a warp
+ *                  walk similar paths: 1 = always, 0 = never, -1 = auto (default: scenes of >= 65 536 primitives)
  *   waves, lanes   minimum number of waves rt_render_device cuts a pass into (default 0 = auto: 2, or 1 on a quarter-frame partition or less) and the 1..8 streams they rotate over
  *                  (default 2: the drain of one wave overlaps the start of the next)
  *   deep_lanes     lanes of a frame with mirror depths and >= 4 waves (spp passes), whose many small queue kernels then run side by side (1..8, default 8)

@@ -7,7 +7,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "librt_emu.so")
+_LIB = os.environ.get("RT_EMU_LIB") or os.path.join(_HERE, "librt_emu.so")          # override: sanitizer builds (tools/sanitize_host.sh)
 host = importlib.import_module("unity-raytracer_b200.host")
 
 _lib = None
@@ -16,7 +16,8 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        subprocess.check_call(["make", "-s", "-C", _HERE])
+        if not os.environ.get("RT_EMU_LIB"):
+            subprocess.check_call(["make", "-s", "-C", _HERE])
         L = C.CDLL(_LIB)
         fp, ip, vp = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_void_p
         L.emu_new.restype = vp

@@ -53,7 +53,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
     std::vector<float> m = H.pack_materials();
     E.has_mirror = H.has_mirror;
     E.mats.resize(m.size() / 4);
-    memcpy(E.mats.data(), m.data(), m.size() * 4);
+    if (!m.empty()) memcpy(E.mats.data(), m.data(), m.size() * 4);            // (memcpy with a null source is undefined even for 0 bytes: UBSan)
     E.mesh_aabb.resize(2 * n_me);
     for (int k = 0; k < n_me; ++k) {
         E.mesh_aabb[2 * k] = make_float4(H.mesh_aabb[6 * k], H.mesh_aabb[6 * k + 1], H.mesh_aabb[6 * k + 2], 0.f);
@@ -90,7 +90,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
     H.origin_box(bo, amax, E.obox);                                // rt_device_commit's set_obox
     if (H.inst.any()) {                                            // rt_device_commit's upload_instances
         const char* why = nullptr;
-        if (!H.inst.pack(E.mesh_base, amax, pad, pad_scale, leaf_max, 2, 116, &why)) { fprintf(stderr, "emu: %s\n", why ? why : "pack failed"); abort(); }
+        if (!H.inst.pack(E.mesh_base, amax, pad, pad_scale, leaf_max > 3 ? 3 : leaf_max, 2, 116, &why)) { fprintf(stderr, "emu: %s\n", why ? why : "pack failed"); abort(); }
         auto as4 = [](const std::vector<float>& v, std::vector<float4>& o) { o.assign(v.size() / 4 + 1, float4{}); if (!v.empty()) memcpy(o.data(), v.data(), v.size() * 4); };
         as4(H.inst.inodes, E.inodes); as4(H.inst.iprims, E.iprims); as4(H.inst.inst, E.inst);
         E.inst_vbase = H.inst.vbase;
@@ -159,7 +159,7 @@ void commit(Emu& E, int leaf_max, double pad_scale, double t_slack, int builder,
         for (int s = 0; s < ns; ++s) rt_emit_slot(R, s, B.order[s], E.prims.data(), E.pinfo.data(), leaf_lo.data(), leaf_hi.data());
         E.n_nodes = (int)(B.nodes.size() / 16);
         E.nodes.assign(std::max<size_t>(4, B.nodes.size() / 4), float4{});
-        memcpy(E.nodes.data(), B.nodes.data(), B.nodes.size() * 4);
+        if (!B.nodes.empty()) memcpy(E.nodes.data(), B.nodes.data(), B.nodes.size() * 4);
         S.prims = E.prims.data(); S.pinfo = E.pinfo.data(); S.nodes = E.nodes.data(); S.root = root;
         S.n_slots = ns;
         E.order = B.order; E.root = root;
@@ -254,6 +254,7 @@ int emu_scene_base_mesh(void* e, const float* v, int n) {
     Emu* E = (Emu*)e;
     RtBaseMesh B; B.v.assign(v, v + 9 * (size_t)n);
     if (!RtInstanceSet::set_bounds(B)) return -5;
+    E->host.inst.build_blas(B, E->opt_leaf_max > 3 ? 3 : (E->opt_leaf_max < 1 ? 1 : E->opt_leaf_max), 2);      // as rt_scene_base_mesh does
     E->host.inst.bases.push_back(std::move(B)); E->host.inst.blas_changed = true;
     return (int)E->host.inst.bases.size() - 1;
 }

@@ -13,13 +13,16 @@ sc = rtb.scenes
 if wl == "cfg2": s, p = sc.rt_unity(True), sc.rt_unity_params(3840, 2160, 4)
 elif wl == "cfg3": s, p = sc.cfg3_scene(), sc.cfg3_params()
 elif wl == "cfg4": s, p = sc.cfg4_scene(), sc.cfg4_params()
+elif wl == "cfg4i": s, p = sc.cfg4_instanced(), sc.cfg4_params()
+elif wl == "cfg4ib": s, p = sc.cfg4_instanced().baked(), sc.cfg4_params()
 else: s, p = sc.cfg5_scene(), sc.cfg5_params()
 L = H.load_library()
 L.rt_debug_visit_counts.argtypes = [C.c_void_p, C.c_int]
 names = ["lane_rays", "lane_node_visits", "lane_prim_tests", "packet_warps", "packet_rays", "packet_node_fetches", "packet_lane_node_visits",
          "packet_prim_fetches", "packet_lane_prim_tests", "packet_pops_culled"]
 out = {"workload": wl}
-for builder in (1, 0):
+builders = [int(b) for b in os.environ.get("VC_BUILDERS", "1,0").split(",")]
+for builder in builders:
     for packet in (1, 0):
         rt = rtb.RayTracer((0,)); rt.set_option("builder", builder); rt.set_option("packet", packet); rt.set_option("hints", 0)
         rt.set_scene(s)

@@ -41,7 +41,7 @@ void device_release(RtDevice& D) {
         b->release();
     rt_upload_release(D);
     for (auto& L : D.lanes) {
-        for (DevBuf* b : {&L.hit0_t, &L.hit0_slot, &L.hitq_t, &L.hitq_slot, &L.rays[0], &L.rays[1], &L.counters, &L.occl, &L.split_occl, &L.split_acc}) b->release();
+        for (DevBuf* b : {&L.hit0_t, &L.hit0_slot, &L.hitq_t, &L.hitq_slot, &L.rays[0], &L.rays[1], &L.counters, &L.occl, &L.split_occl, &L.split_acc, &L.link_tmp, &L.qs_hist}) b->release();
         for (auto& b : L.local) b.release();
         for (auto& b : L.link) b.release();
         if (L.done) cudaEventDestroy(L.done);
@@ -391,6 +391,10 @@ int rt_scene_base_mesh(rt_ctx* c, const float* v, int n_tris) {
     RtBaseMesh B;
     B.v.assign(v, v + 9 * (size_t)n_tris);
     if (!RtInstanceSet::set_bounds(B)) return fail(c, RT_E_UNSUPPORTED, "rt_scene_base_mesh: vertices must be finite (bake such a mesh and use rt_scene_mesh)");
+    {   // the BLAS is built here rather than at commit: the instances declared next take their world bounds from its top levels
+        int threads = (int)std::thread::hardware_concurrency();
+        c->host.inst.build_blas(B, c->opt.leaf_max < 1 ? 1 : (c->opt.leaf_max > 3 ? 3 : c->opt.leaf_max), threads < 1 ? 1 : threads);
+    }
     c->host.inst.bases.push_back(std::move(B));
     c->host.inst.blas_changed = true;
     return (int)c->host.inst.bases.size() - 1;
@@ -813,6 +817,7 @@ int rt_set_option(rt_ctx* c, const char* key, double value) {
     else if (k == "backcull") { c->opt.backcull = value != 0; }
     else if (k == "light_split") { c->opt.light_split = (int)value; }
     else if (k == "hints") { c->opt.hints = value != 0; }
+    else if (k == "sort_queue") { c->opt.sort_queue = value < 0 ? -1 : (int)value; }
     else if (k == "copy_plan") { if (value < 0) return fail(c, RT_E_INVALID, "copy_plan < 0"); c->opt.copy_plan = (long long)value; }
     else if (k == "copy_waves_part") { if (value < 0 || value > 64) return fail(c, RT_E_INVALID, "copy_waves_part must be 0 (auto) or 1..64"); c->opt.copy_waves_part = (int)value; }
     else if (k == "copy_waves") { if (value < 1 || value > 64) return fail(c, RT_E_INVALID, "copy_waves must be 1..64"); c->opt.copy_waves = (int)value; }

@@ -311,7 +311,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
         if (D.rank == 0) {
             const char* why = nullptr;
             int threads = (int)std::thread::hardware_concurrency();
-            const int leaf_max_i = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 8 ? 8 : opt.leaf_max);
+            const int leaf_max_i = opt.leaf_max < 1 ? 1 : (opt.leaf_max > 3 ? 3 : opt.leaf_max);     // <= 3 triangles per BLAS leaf: one cooperative bake (rt_packet.cuh)
             if (!IS.pack(mbase, amax_w, pad_w, opt.pad_scale, leaf_max_i, threads < 1 ? 1 : threads, RT_STACK_ENTRIES, &why)) { err = why ? why : "instance packing failed"; return RT_E_UNSUPPORTED; }
         }
         if ((int64_t)S.n_slots + IS.n_tris() > (int64_t)0x7fffff00) { err = "too many instanced triangles (virtual slots exceed 2^31)"; return RT_E_UNSUPPORTED; }

@@ -186,6 +186,14 @@ RT_HD f3 rt_xform_dir_cull(float4 r0, float4 r1, float4 r2, f3 d) {
     return mk3(rt_fma(r0.x, d.x, rt_fma(r0.y, d.y, r0.z * d.z)), rt_fma(r1.x, d.x, rt_fma(r1.y, d.y, r1.z * d.z)),
                rt_fma(r2.x, d.x, rt_fma(r2.y, d.y, r2.z * d.z)));
 }
+// 1 / x for the object-space slab constants: any value within a few ulps will do (one MUFU.RCP instead of an IEEE division)
+RT_HD float rt_rcp_cull(float x) {
+#if defined(__CUDA_ARCH__)
+    float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+#else
+    return 1.0f / x;
+#endif
+}
 // -Triangle.Normal of a world triangle (Triangle.cs:13-21: v = cross(V2 - V0, V1 - V0); v / length(v); SceneMesh.cs:45 negates)
 RT_HD f3 rt_tri_normal_neg(f3 w0, f3 w1, f3 w2) {
     f3 c = um_cross(w2 - w0, w1 - w0);
@@ -321,7 +329,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
             const float4* ip = S.inst + RT_INST_F4 * (size_t)cur;
             const float4 a0 = RT_LDG4(ip + 3), a1 = RT_LDG4(ip + 4), a2 = RT_LDG4(ip + 5);
             const f3 Oo = rt_xform_point_cull(a0, a1, a2, O), Do = rt_xform_dir_cull(a0, a1, a2, D);
-            idx_ = rt_safe_inv(Do.x, rt_div(1.0f, Do.x)); idy_ = rt_safe_inv(Do.y, rt_div(1.0f, Do.y)); idz_ = rt_safe_inv(Do.z, rt_div(1.0f, Do.z));
+            idx_ = rt_safe_inv(Do.x, rt_rcp_cull(Do.x)); idy_ = rt_safe_inv(Do.y, rt_rcp_cull(Do.y)); idz_ = rt_safe_inv(Do.z, rt_rcp_cull(Do.z));
             oodx = Oo.x * idx_; oody = Oo.y * idy_; oodz = Oo.z * idz_;
             if (FAR) { const float dlo = dl * RT_LDG4(ip + 7).z; ex = dlo * fabsf(idx_); ey = dlo * fabsf(idy_); ez = dlo * fabsf(idz_); }
             level = 2;

@@ -25,6 +25,11 @@ struct RtBaseMesh {
     int32_t root = -1;
     int depth = 0;
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0}, amax = 0.f;     // object-space bounds, max |coordinate|
+    // Object-space boxes that together cover the mesh: the BLAS cut off after ~RT_HULL_BOXES nodes.  An instance's world bounds
+    // are the union of the TRANSFORMED boxes: for a rotated instance the transformed corners of the one object box reach up to
+    // sqrt(3) times too far per axis (cfg4: boxes of neighbouring instances overlapped and every ray entered 3 - 5 instances it
+    // could not hit); the pieces of a cut are small, so their rotated boxes hug the surface.
+    std::vector<float> hull;              // 6 floats per box (lo, hi)
     int32_t n_tris() const { return (int32_t)(v.size() / 9); }
 };
 
@@ -76,14 +81,22 @@ struct RtInstanceSet {
             I.inv[4 * r + 3] = (float)-(A[3 * r] * m[3] + A[3 * r + 1] * m[7] + A[3 * r + 2] * m[11]);
         }
         I.inv_norm = (float)(ninv * 1.0001);
-        // world bounds: the 8 corners of the object bounds, in double, rounded outward (padding is added by the callers)
+        // world bounds: the 8 corners of every box of the mesh's cover (RtBaseMesh::hull; the one object box when there is none),
+        // in double, rounded outward (padding is added by the callers)
         double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
         if (B.n_tris() == 0) { for (int k = 0; k < 3; ++k) { lo[k] = hi[k] = m[4 * k + 3]; } }
-        else for (int cx = 0; cx < 8; ++cx) {
-            const double x = (cx & 1) ? B.hi[0] : B.lo[0], y = (cx & 2) ? B.hi[1] : B.lo[1], z = (cx & 4) ? B.hi[2] : B.lo[2];
-            for (int r = 0; r < 3; ++r) {
-                const double w = (double)m[4 * r] * x + (double)m[4 * r + 1] * y + (double)m[4 * r + 2] * z + (double)m[4 * r + 3];
-                lo[r] = std::fmin(lo[r], w); hi[r] = std::fmax(hi[r], w);
+        else {
+            const size_t nb = B.hull.empty() ? 1 : B.hull.size() / 6;
+            for (size_t bx = 0; bx < nb; ++bx) {
+                const float* blo = B.hull.empty() ? B.lo : B.hull.data() + 6 * bx;
+                const float* bhi = B.hull.empty() ? B.hi : B.hull.data() + 6 * bx + 3;
+                for (int cx = 0; cx < 8; ++cx) {
+                    const double x = (cx & 1) ? bhi[0] : blo[0], y = (cx & 2) ? bhi[1] : blo[1], z = (cx & 4) ? bhi[2] : blo[2];
+                    for (int r = 0; r < 3; ++r) {
+                        const double w = (double)m[4 * r] * x + (double)m[4 * r + 1] * y + (double)m[4 * r + 2] * z + (double)m[4 * r + 3];
+                        lo[r] = std::fmin(lo[r], w); hi[r] = std::fmax(hi[r], w);
+                    }
+                }
             }
         }
         for (int k = 0; k < 3; ++k) {
@@ -129,7 +142,32 @@ struct RtInstanceSet {
         B.root = S.run(pb.data(), n, leaf_max, 0.0f, threads);
         B.nodes = S.nodes; B.order = S.order; B.depth = S.max_depth.load();
         B.built = true;
+        // cover of the mesh: cut the tree breadth-first after RT_HULL_BOXES pieces (child boxes are stored in the parent node)
+        B.hull.clear();
+        if (B.root >= 0) {
+            struct Piece { int32_t ref; float b[6]; };
+            std::vector<Piece> cur, next;
+            Piece r0; r0.ref = B.root; for (int k = 0; k < 3; ++k) { r0.b[k] = B.lo[k]; r0.b[3 + k] = B.hi[k]; }
+            cur.push_back(r0);
+            for (int round = 0; round < 16; ++round) {
+                size_t inner = 0; for (auto& p : cur) inner += p.ref >= 0 ? 1 : 0;
+                if (inner == 0 || cur.size() + inner > RT_HULL_BOXES) break;
+                next.clear();
+                for (auto& p : cur) {
+                    if (p.ref < 0) { next.push_back(p); continue; }
+                    const float* np = B.nodes.data() + 16 * (size_t)p.ref;
+                    Piece a, c;
+                    std::memcpy(&a.ref, np + 12, 4); std::memcpy(&c.ref, np + 13, 4);
+                    a.b[0] = np[0]; a.b[3] = np[1]; a.b[1] = np[2]; a.b[4] = np[3]; a.b[2] = np[8]; a.b[5] = np[9];
+                    c.b[0] = np[4]; c.b[3] = np[5]; c.b[1] = np[6]; c.b[4] = np[7]; c.b[2] = np[10]; c.b[5] = np[11];
+                    next.push_back(a); next.push_back(c);
+                }
+                cur.swap(next);
+            }
+            if (cur.size() > 1) for (auto& p : cur) B.hull.insert(B.hull.end(), p.b, p.b + 6);
+        }
     }
+    static constexpr size_t RT_HULL_BOXES = 128;
 
     // Padding of a BLAS, in object units.  A box test inside an instance sees (1) the ray carried into object space in binary32
     // (origin ~4u (|A||O| + |a|), direction ~4u relative, i.e. ~4u |A| x path length), (2) the slab arithmetic itself (~4u (|O'| +

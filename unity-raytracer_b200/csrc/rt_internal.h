@@ -72,6 +72,8 @@ struct RtOptions {
                                        // 1/4 frame or less, off otherwise — it shortens the heaviest tiles (1/8 partition: shadow
                                        // kernel -5..11 %) but costs 4 % on a full frame (duplicated set-up, lost cache sharing)
     int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs
+    int sort_queue = -1;               // mirror-ray queues are re-ordered by (direction bin, origin cell) before they are traced (rt_render.cu
+                                       // k_qs_*): 1 = always, 0 = never, -1 = auto (scenes of >= 65 536 primitives, where incoherent lanes cost)
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };
 
@@ -108,6 +110,7 @@ struct RtDevice {
         cudaStream_t own_stream = nullptr;   // lane 0 runs on D.stream, the others on their own stream
         cudaEvent_t done = nullptr;
         DevBuf hit0_t, hit0_slot, hitq_t, hitq_slot, rays[2], counters, occl, split_occl, split_acc;
+        DevBuf link_tmp, qs_hist;           // option sort_queue: emission target of the links, bin counters of the queue sort
         std::vector<DevBuf> local;          // [depth] float4 per entry
         std::vector<DevBuf> link;           // [depth>=1] float4 (km.xyz, parent index bits)
     };

@@ -146,9 +146,15 @@ __device__ __forceinline__ int rt_packet_octant(float idx_, float idy_, float id
 // the world BVH, then the TLAS, and inside an instance the base mesh's BLAS with every lane's ray carried into object space for
 // the box tests (an affine map keeps the rays of a packet coherent and their t unchanged); triangle tests stay in world space
 // on the vertices baked on the fly.  The level and the current instance are warp-uniform.
+// bake: INST only — 9 float4 of shared memory owned by this warp (RT_BAKE_F4): the world-space vertices of the current BLAS leaf.
+// A triangle of an instance is the same for all 32 lanes, so its bake (27 multiplications + 27 additions, SceneMesh.cs:28) is done
+// ONCE per leaf by the warp — lane i computes coordinate i % 3 of vertex i / 3 with the reference's operation order — instead of
+// by every lane for itself: the instanced triangle test then costs what the baked one costs (ncu, cfg4 as instances: the
+// per-lane bake was 20 % of the fused shadow kernel's instructions, its triangle tests twice the baked scene's).
+#define RT_BAKE_F4 9
 template <bool ANY, bool INST = false, class STK>
 __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D, f3 inv, bool active, float any_d2, STK& stk,
-                                                   float& best_t, int32_t& best_slot) {
+                                                   float& best_t, int32_t& best_slot, float4* bake = nullptr) {
     const unsigned full = 0xffffffffu;
     best_t = FLT_MAX; best_slot = -1;
     stk.sp = 0;
@@ -164,6 +170,7 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
     const float4* __restrict__ nodes = S.nodes;
     int32_t node = S.root;                            // warp-uniform from here on
     int32_t level = 0, cur = -1;                      // INST: 0 = world BVH, 1 = TLAS, 2 = BLAS of instance `cur` (warp-uniform)
+    int32_t cur_mesh = -1, cur_key0 = 0, cur_vslot0 = 0;   // of instance `cur`: MeshIndex, scan key of its triangle 0, virtual slot of BLAS slot 0
     if (INST && S.n_inst > 0) { if (S.n_prims > 0) stk.push_packet(RT_SENT_TLAS, -INFINITY); else node = RT_SENT_TLAS; }
 #ifdef RT_COUNT_VISITS
     { unsigned am = __ballot_sync(full, active);
@@ -189,11 +196,13 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                 const float4* ip = S.inst + RT_INST_F4 * (size_t)cur;
                 const float4 a0 = RT_LDG4(ip + 3), a1 = RT_LDG4(ip + 4), a2 = RT_LDG4(ip + 5);
                 const f3 Oo = rt_xform_point_cull(a0, a1, a2, O), Do = rt_xform_dir_cull(a0, a1, a2, D);
-                idx_ = rt_safe_inv(Do.x, rt_div(1.0f, Do.x)); idy_ = rt_safe_inv(Do.y, rt_div(1.0f, Do.y)); idz_ = rt_safe_inv(Do.z, rt_div(1.0f, Do.z));
+                idx_ = rt_safe_inv(Do.x, rt_rcp_cull(Do.x)); idy_ = rt_safe_inv(Do.y, rt_rcp_cull(Do.y)); idz_ = rt_safe_inv(Do.z, rt_rcp_cull(Do.z));
                 oodx = Oo.x * idx_; oody = Oo.y * idy_; oodz = Oo.z * idz_;
                 oct = rt_packet_octant(idx_, idy_, idz_, active);
                 level = 2;
-                node = f2i(RT_LDG4(ip + 6).x);
+                const float4 ii = RT_LDG4(ip + 6);
+                cur_mesh = f2i(ii.z); cur_key0 = f2i(ii.w); cur_vslot0 = S.n_slots + f2i(RT_LDG4(ip + 7).x) - f2i(ii.y);
+                node = f2i(ii.x);
                 continue;
             }
         }
@@ -214,26 +223,37 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
         {
             int32_t ref = ~node;
             int32_t first = ref >> 3, cnt = (ref & 7) + 1;
+            if (INST && level == 2) {                                   // bake the leaf's (<= 3) triangles once for the whole warp
+                const int lane = threadIdx.x & 31;
+                __syncwarp(full);                                       // every lane is done with the previous leaf's vertices
+                if (lane < 9 * cnt) {
+                    const int vtx = lane / 3, comp = lane - 3 * vtx;
+                    const float4 pv = RT_LDG4(S.iprims + 3 * (size_t)first + vtx);
+                    const float4 mr = RT_LDG4(S.inst + RT_INST_F4 * (size_t)cur + comp);
+                    float* wb = (float*)bake;
+                    wb[4 * vtx + comp] = ((mr.x * pv.x + mr.y * pv.y) + mr.z * pv.z) + mr.w;      // MultiplyPoint3x4, exact operation order
+                    if (comp == 0) wb[4 * vtx + 3] = pv.w;              // (vertex 0 of a triangle carries its index in the mesh)
+                }
+                __syncwarp(full);
+            }
             for (int32_t k = 0; k < cnt; ++k) {
                 int32_t slot = first + k;
-                const float4* pp = ((INST && level == 2) ? S.iprims : S.prims) + 3 * (size_t)slot;
-                float4 p0 = RT_LDG4(pp), p1 = RT_LDG4(pp + 1), p2 = RT_LDG4(pp + 2);
+                float4 p0, p1, p2;
+                if (INST && level == 2) { p0 = bake[3 * k]; p1 = bake[3 * k + 1]; p2 = bake[3 * k + 2]; }
+                else { const float4* pp = S.prims + 3 * (size_t)slot; p0 = RT_LDG4(pp); p1 = RT_LDG4(pp + 1); p2 = RT_LDG4(pp + 2); }
 #ifdef RT_COUNT_VISITS
                 { unsigned live = __ballot_sync(full, tcull >= 0.0f);
                   if ((threadIdx.x & 31) == 0) { RT_COUNT((ANY ? 10 : 0) + 7, 1); RT_COUNT((ANY ? 10 : 0) + 8, __popc(live)); } }
 #endif
                 float t = 0.0f; bool hit = false;
                 uint32_t key; int32_t mesh;
-                if (INST && level == 2) {                               // object-space triangle of instance `cur`: bake it, test it in world space
-                    const float4* ip = S.inst + RT_INST_F4 * (size_t)cur;
-                    const float4 m0 = RT_LDG4(ip), m1 = RT_LDG4(ip + 1), m2 = RT_LDG4(ip + 2), ii = RT_LDG4(ip + 6);
+                if (INST && level == 2) {                               // triangle of instance `cur`, baked above: tested in world space
                     if (tcull >= 0.0f) {
-                        const f3 w0 = rt_xform_point(m0, m1, m2, mk3(p0.x, p0.y, p0.z)), w1 = rt_xform_point(m0, m1, m2, mk3(p1.x, p1.y, p1.z)),
-                                 w2 = rt_xform_point(m0, m1, m2, mk3(p2.x, p2.y, p2.z));
-                        hit = rt_ray_tri(O, D, w0, w1 - w0, w2 - w0, tcull, t);
+                        const f3 w0 = mk3(p0.x, p0.y, p0.z);
+                        hit = rt_ray_tri(O, D, w0, mk3(p1.x, p1.y, p1.z) - w0, mk3(p2.x, p2.y, p2.z) - w0, tcull, t);      // edge1, edge2: RMath.cs:34-35
                     }
-                    key = (uint32_t)(f2i(ii.w) + f2i(p0.w)); mesh = f2i(ii.z);
-                    slot = S.n_slots + f2i(RT_LDG4(ip + 7).x) + (slot - f2i(ii.y));          // virtual slot (rt_inst_decode)
+                    key = (uint32_t)(cur_key0 + f2i(p0.w)); mesh = cur_mesh;
+                    slot = cur_vslot0 + slot;                           // virtual slot (rt_inst_decode)
                 } else {
                 if (tcull >= 0.0f) {                                    // else: lane has no ray / is already occluded
                     if (f2i(p1.w) != 0) hit = rt_ray_sphere(O, D, mk3(p0.x, p0.y, p0.z), p1.x, t);

@@ -85,6 +85,9 @@ struct SmemStack {
     }
 };
 constexpr size_t RT_STACK_SMEM = (size_t)STK_CAP * RT_BLOCK * 8;
+// INST instantiations: behind the stacks, RT_BAKE_F4 float4 per warp for the vertices of the BLAS leaf the warp bakes (rt_packet.cuh)
+constexpr size_t RT_BAKE_SMEM = (size_t)(RT_BLOCK / 32) * RT_BAKE_F4 * 16;
+#define RT_WARP_BAKE() (reinterpret_cast<float4*>(g_smem_stack + RT_STACK_SMEM / 4) + (threadIdx.x >> 5) * RT_BAKE_F4)
 #define RT_DECL_STACK(name) int name##_ovf[STK_OVF]; float name##_ovfd[STK_OVF]; \
     SmemStack name(g_smem_stack + 2 * threadIdx.x, name##_ovf, name##_ovfd)
 
@@ -194,7 +197,7 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS_PRI
         if (valid) active = rt_scene_gate(S, O, inv);                                               // Scene.cs:54
         if (FAR) { if (active) rt_traverse<false, true, INST>(S, O, D, inv, 0.f, stk, bt, bs); }
         else if (S.packet) {              // rays of one 8x4 pixel tile share the origin and are almost parallel
-            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false, INST>(S, O, D, inv, active, 0.f, stk, bt, bs);
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false, INST>(S, O, D, inv, active, 0.f, stk, bt, bs, INST ? RT_WARP_BAKE() : nullptr);
         } else if (active) rt_traverse<false, false, INST>(S, O, D, inv, 0.f, stk, bt, bs);
         size_t q = (size_t)t * 32 + lane;
         RT_ST_STREAM(hit_t + q, bt); RT_ST_STREAM(hit_slot + q, valid ? bs : -2);
@@ -225,7 +228,7 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_
         if (q < n) active = rt_scene_gate(S, O, inv);
         float bt = FLT_MAX; int bs = -1;
         if (S.packet && rt_warp_coherent(O, D, active, S.coherent_spread2)) {
-            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false, INST>(S, O, D, inv, active, 0.f, stk, bt, bs);
+            if (__any_sync(0xffffffffu, active)) rt_traverse_packet<false, INST>(S, O, D, inv, active, 0.f, stk, bt, bs, INST ? RT_WARP_BAKE() : nullptr);
         } else if (active) rt_traverse<false, false, INST>(S, O, D, inv, 0.f, stk, bt, bs);
         if (q < n) { hit_t[q] = bt; hit_slot[q] = bs; }
     }
@@ -306,7 +309,7 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_
                 if (has && !occluded) act = rt_scene_gate(S, sO, inv);                                 // Scene.cs:54
                 float st; int ss;
                 if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
-                    if (__any_sync(full, act) && rt_traverse_packet<true, INST>(S, sO, Ldir, inv, act, d2, stk, st, ss)) occluded = true;
+                    if (__any_sync(full, act) && rt_traverse_packet<true, INST>(S, sO, Ldir, inv, act, d2, stk, st, ss, INST ? RT_WARP_BAKE() : nullptr)) occluded = true;
                 } else if (act) occluded = rt_traverse<true, false, INST>(S, sO, Ldir, inv, d2, stk, st, ss);
                 if (occluded) mask |= 1u << i;
             }
@@ -430,6 +433,83 @@ __global__ void __launch_bounds__(128) k_intersect(RtScene S, int n, const float
     }
 }
 
+// ---- re-ordering of a mirror-ray queue (option "sort_queue") -------------------------------------------------------------------
+// Mirror rays leave the shading kernel in the order their warps happened to reserve queue space: neighbours in the queue start
+// anywhere in the scene and point anywhere (cfg5: reflections off 10 000 small mirror spheres), so the 32 lanes of a queue warp
+// walk 32 unrelated paths — the per-lane loop at a third of its lanes, every node fetch its own L1 wavefront (17 M mirror rays
+// took 80 ms, 0.2 Grays/s, against 7 Grays/s for primary rays).  Before a depth is traced its queue is therefore counting-sorted
+// by (direction bin, origin cell): 6 cube-map faces x 4 x 4 direction bins (major key: the lanes of a warp then share their
+// octant and mostly their path) and an 8^3 grid over Scene.AABB in Morton order (minor key).  A queue entry is (ray, link) and
+// the link carries the parent index (rt_fold_item), each parent has at most one reflection ray, and entries are independent:
+// their order can change nothing but the time.  Three small kernels per depth and wave; the sorted copy lives in the queue
+// buffer the previous depth no longer needs.
+constexpr int RT_QS_CELLS = 8, RT_QS_DIRS = 96;
+constexpr int RT_QS_BINS = RT_QS_DIRS * RT_QS_CELLS * RT_QS_CELLS * RT_QS_CELLS;       // 49 152
+struct RtQsGrid { f3 lo, scale; };
+__device__ __forceinline__ unsigned rt_qs_bin(const RtQsGrid& G, float4 ro, float4 rd) {
+    const float ax = fabsf(rd.x), ay = fabsf(rd.y), az = fabsf(rd.z);
+    int face; float m, u, v;
+    if (ax >= ay && ax >= az) { face = rd.x < 0.f ? 1 : 0; m = ax; u = rd.y; v = rd.z; }
+    else if (ay >= az) { face = rd.y < 0.f ? 3 : 2; m = ay; u = rd.x; v = rd.z; }
+    else { face = rd.z < 0.f ? 5 : 4; m = az; u = rd.x; v = rd.y; }
+    const float im = m > 0.f ? __frcp_rn(m) : 0.f;
+    int iu = (int)fminf(fmaxf((u * im + 1.0f) * 2.0f, 0.0f), 3.0f), iv = (int)fminf(fmaxf((v * im + 1.0f) * 2.0f, 0.0f), 3.0f);   // NaN -> 0
+    const unsigned cx = (unsigned)fminf(fmaxf((ro.x - G.lo.x) * G.scale.x, 0.0f), (float)(RT_QS_CELLS - 1));
+    const unsigned cy = (unsigned)fminf(fmaxf((ro.y - G.lo.y) * G.scale.y, 0.0f), (float)(RT_QS_CELLS - 1));
+    const unsigned cz = (unsigned)fminf(fmaxf((ro.z - G.lo.z) * G.scale.z, 0.0f), (float)(RT_QS_CELLS - 1));
+    unsigned mo = 0;
+#pragma unroll
+    for (int b = 0; b < 3; ++b) mo |= (((cx >> b) & 1u) << (3 * b)) | (((cy >> b) & 1u) << (3 * b + 1)) | (((cz >> b) & 1u) << (3 * b + 2));
+    return (unsigned)(face * 16 + iu * 4 + iv) * (unsigned)(RT_QS_CELLS * RT_QS_CELLS * RT_QS_CELLS) + mo;
+}
+__global__ void k_qs_hist(const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays, RtQsGrid G, unsigned* hist) {
+    const unsigned n = *n_ptr;
+    for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x)
+        atomicAdd(hist + rt_qs_bin(G, rays[2 * (size_t)q], rays[2 * (size_t)q + 1]), 1u);
+}
+// exclusive scan of the RT_QS_BINS counters in place: one CTA of 1024 threads walks the array in coalesced tiles of 1024
+// (warp-shuffle scan inside a warp, 32 warp totals through shared memory, running carry between tiles)
+__global__ void __launch_bounds__(1024) k_qs_scan(unsigned* hist) {
+    __shared__ unsigned wsum[32];
+    __shared__ unsigned carry;
+    static_assert(RT_QS_BINS % 1024 == 0, "whole tiles");
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0u;
+    __syncthreads();
+    for (int tile = 0; tile < RT_QS_BINS / 1024; ++tile) {
+        const unsigned v = hist[tile * 1024 + tid];
+        unsigned incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned n = __shfl_up_sync(full, incl, o); if (lane >= o) incl += n; }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const unsigned w = wsum[lane];
+            unsigned wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const unsigned n = __shfl_up_sync(full, wi, o); if (lane >= o) wi += n; }
+            wsum[lane] = wi - w;                                // exclusive prefix of the warp totals
+        }
+        __syncthreads();
+        const unsigned base = carry + wsum[warp];
+        hist[tile * 1024 + tid] = base + incl - v;
+        __syncthreads();
+        if (tid == 1023) carry = base + incl;
+        __syncthreads();
+    }
+}
+__global__ void k_qs_scatter(const unsigned* __restrict__ n_ptr, const float4* __restrict__ rays_in, const float4* __restrict__ link_in, RtQsGrid G,
+                             unsigned* offsets, float4* __restrict__ rays_out, float4* __restrict__ link_out) {
+    const unsigned n = *n_ptr;
+    for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) {
+        const float4 ro = rays_in[2 * (size_t)q], rd = rays_in[2 * (size_t)q + 1];
+        const unsigned pos = atomicAdd(offsets + rt_qs_bin(G, ro, rd), 1u);
+        rays_out[2 * (size_t)pos] = ro; rays_out[2 * (size_t)pos + 1] = rd;
+        link_out[pos] = link_in[q];
+    }
+}
+
 // Frame prologue (option "prefetch"): pull the BVH (nodes + primitive records) into L2 at HBM streaming speed.  Traversal
 // is a dependent pointer chase, so on a cold L2 every first touch of a node costs a DRAM round trip on the critical path
 // of some warp; one bulk pass over the ~70 MB of a 1M-triangle scene takes ~15 us.
@@ -496,7 +576,6 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
     D.wave_marks.clear();
     if (V.n_tiles > 0 && V.res_x > 0) {
         const int block = RT_BLOCK;
-        const size_t smem = RT_STACK_SMEM;
         int wave_tiles = (opt.chunk_pixels / 32) < 1 ? 1 : (opt.chunk_pixels / 32);
         if (wave_tiles > V.n_tiles) wave_tiles = V.n_tiles;
         const int chunk_tiles = wave_tiles;                                 // capacity limit set by chunk_pixels
@@ -552,6 +631,21 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         }
         const size_t W = (size_t)wave_tiles * 32;
         const int maxd = V.max_bounces;
+        // mirror queues are re-ordered before they are traced (k_qs_*) when the scene is big enough for ray incoherence to cost something
+        const bool sort_queue = maxd > 0 && (opt.sort_queue > 0 || (opt.sort_queue < 0 && (int64_t)D.S.n_prims + (D.S.n_inst > 0 ? 65536 : 0) >= 65536));
+        // Sorted neighbours are similar, not parallel: they pass the packet's coherence test (rt_warp_coherent: within ~18 degrees) and
+        // would then walk the UNION of 32 paths that really differ — measured 3x slower than unsorted.  Sorted queues are therefore
+        // traced by the per-lane loop, which profits from the order through convergent lanes and shared cache lines (sort_queue = 2
+        // keeps the packet test: development).
+        RtScene Sq = D.S;
+        if (sort_queue && opt.sort_queue != 2) Sq.packet = 0;
+        RtQsGrid qsg;
+        {
+            const f3 lo = D.S.aabb_min, hi = D.S.aabb_max;
+            auto sc = [](float a, float b) { const float e = b - a; return (e > 0.f && std::isfinite(e)) ? (float)RT_QS_CELLS / e : 0.f; };
+            qsg.lo = mk3(std::isfinite(lo.x) ? lo.x : 0.f, std::isfinite(lo.y) ? lo.y : 0.f, std::isfinite(lo.z) ? lo.z : 0.f);
+            qsg.scale = mk3(sc(lo.x, hi.x), sc(lo.y, hi.y), sc(lo.z, hi.z));
+        }
         const int n_chunks = (D.S.n_lights + 31) / 32;                      // shadow launches per depth
         for (int li = 0; li < n_lanes; ++li) {                              // work buffers of each lane
             RtDevice::Lane& L = D.lanes[li];
@@ -564,6 +658,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                 RT_CUDA(L.hitq_t.ensure(W * 4)); RT_CUDA(L.hitq_slot.ensure(W * 4));
                 RT_CUDA(L.rays[0].ensure(W * 32)); RT_CUDA(L.rays[1].ensure(W * 32));
                 for (int d = 1; d <= maxd; ++d) RT_CUDA(L.link[d].ensure(W * 16));
+                if (sort_queue) { RT_CUDA(L.link_tmp.ensure(W * 16)); RT_CUDA(L.qs_hist.ensure((size_t)RT_QS_BINS * 4)); }
             }
             RT_CUDA(L.occl.ensure(W * 4 * (size_t)(n_chunks < 1 ? 1 : n_chunks)));
             if (li > 0) {
@@ -637,6 +732,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
         const auto kp_shade0 = inst ? k_shade<true, true> : k_shade<true, false>;
         const auto kp_shaden = inst ? k_shade<false, true> : k_shade<false, false>;
         const auto kp_finalize = inst ? k_finalize<true> : k_finalize<false>;
+        const size_t smem = RT_STACK_SMEM + (inst ? RT_BAKE_SMEM : 0);
         const int g_trace = persistent_grid(kp_primary, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_traceq = persistent_grid(kp_queue, block, smem, D.sm_count, opt.ctas_per_sm);
         const int g_shadow0 = persistent_grid(kp_shadow0, block, smem, D.sm_count, opt.ctas_per_sm);
@@ -669,15 +765,25 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                     kend(); ++launches;
                     }
                     for (int d = 0; d <= maxd; ++d) {
-                        const float4* rin = d ? L.rays[(d - 1) & 1].as<float4>() : nullptr;
-                        float4* rout = d < maxd ? L.rays[d & 1].as<float4>() : nullptr;
-                        float4* lout = d < maxd ? L.link[d + 1].as<float4>() : nullptr;
+                        // queue buffers.  Unsorted: depth d reads rays[(d-1)&1] and emits into rays[d&1] / link[d+1].  Sorted: every depth
+                        // emits into rays[0] / link_tmp, the next depth sorts that into rays[1] / link[d] and reads it from there.
+                        const float4* rin = d ? L.rays[sort_queue ? 1 : ((d - 1) & 1)].as<float4>() : nullptr;
+                        float4* rout = d < maxd ? L.rays[sort_queue ? 0 : (d & 1)].as<float4>() : nullptr;
+                        float4* lout = d < maxd ? (sort_queue ? L.link_tmp.as<float4>() : L.link[d + 1].as<float4>()) : nullptr;
                         const float* ht = d ? L.hitq_t.as<float>() : L.hit0_t.as<float>();
                         const int* hs = d ? L.hitq_slot.as<int>() : L.hit0_slot.as<int>();
                         unsigned* wk = C + C_WORK + 8 * d;
                         if (d > 0) {
                             kbegin(RT_K_TRACE_QUEUE);
-                            kp_queue<<<g_traceq, block, smem, st>>>(D.S, C + d, rin, L.hitq_t.as<float>(), L.hitq_slot.as<int>(), wk);
+                            if (sort_queue) {
+                                unsigned* hist = L.qs_hist.as<unsigned>();
+                                RT_CUDA(cudaMemsetAsync(hist, 0, (size_t)RT_QS_BINS * 4, st));
+                                k_qs_hist<<<g_flat, 256, 0, st>>>(C + d, L.rays[0].as<float4>(), qsg, hist);
+                                k_qs_scan<<<1, 1024, 0, st>>>(hist);
+                                k_qs_scatter<<<g_flat, 256, 0, st>>>(C + d, L.rays[0].as<float4>(), L.link_tmp.as<float4>(), qsg, hist, L.rays[1].as<float4>(), L.link[d].as<float4>());
+                                launches += 3;
+                            }
+                            kp_queue<<<g_traceq, block, smem, st>>>(Sq, C + d, rin, L.hitq_t.as<float>(), L.hitq_slot.as<int>(), wk);
                             kend(); ++launches;
                         }
                         if (fuse) {
@@ -687,7 +793,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
                             if (d == 0) kp_shadow0<<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
                                                                                   hin_of(D.hint_shadow, tb, wi), hout_of(D.hint_shadow, tb, wi, pass == 0));
-                            else kp_shadown<<<g_shadown, block, smem, st>>>(D.S, V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
+                            else kp_shadown<<<g_shadown, block, smem, st>>>((opt.sort_queue == 3 ? Sq : D.S), V, 0, 0, 0, 0, C + d, rin, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F, RtHintIn{nullptr, nullptr, 0, RT_NCLS}, RtHintOut{nullptr, nullptr, 0});
                             kend(); ++launches;
                             continue;
                         }
