@@ -72,7 +72,7 @@ struct RtOptions {
                                        // 1/4 frame or less, off otherwise — it shortens the heaviest tiles (1/8 partition: shadow
                                        // kernel -5..11 %) but costs 4 % on a full frame (duplicated set-up, lost cache sharing)
     int hints = 1;                     // heavy-first tile order from the previous frame's measured tile costs
-    int sort_queue = -1;               // mirror-ray queues are re-ordered by (direction bin, origin cell) before they are traced (rt_render.cu
+    int sort_queue = 0;                // mirror-ray queues are re-ordered by (direction bin, origin cell) before they are traced (rt_render.cu
                                        // k_qs_*): 1 = always, 0 = never, -1 = auto (scenes of >= 65 536 primitives, where incoherent lanes cost)
     int kernel_timing = 0;             // 1 = CUDA events around every kernel launch (rt_stats.ms_kernel)
 };

@@ -152,6 +152,9 @@ __device__ __forceinline__ int rt_packet_octant(float idx_, float idy_, float id
 // by every lane for itself: the instanced triangle test then costs what the baked one costs (ncu, cfg4 as instances: the
 // per-lane bake was 20 % of the fused shadow kernel's instructions, its triangle tests twice the baked scene's).
 #define RT_BAKE_F4 9
+#ifndef RT_INST_OCT
+#define RT_INST_OCT 0
+#endif
 template <bool ANY, bool INST = false, class STK>
 __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D, f3 inv, bool active, float any_d2, STK& stk,
                                                    float& best_t, int32_t& best_slot, float4* bake = nullptr) {
@@ -206,8 +209,12 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                 continue;
             }
         }
-        if (!INST || node >= 0)
-        switch (oct) {
+        // RT_INST_OCT (INST instantiations): 2 = octant-specialised node loops everywhere, 1 = in the world BVH / TLAS only (inside an
+        // instance the octant is the OBJECT-space one, which differs from instance to instance: all eight copies of the loop are then
+        // hot at once and compete for the 32 KB instruction cache), 0 = generic loop only
+        if (INST && RT_INST_OCT == 0) { if (node >= 0) node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); }
+        else if (!INST || node >= 0)
+        switch ((INST && RT_INST_OCT == 1 && level == 2) ? 8 : oct) {
             case 0: node = rt_packet_descend<0, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
             case 1: node = rt_packet_descend<1, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
             case 2: node = rt_packet_descend<2, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;

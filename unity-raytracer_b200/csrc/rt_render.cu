@@ -308,7 +308,11 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_
                 const f3 inv = rt_rcp3(Ldir);
                 if (has && !occluded) act = rt_scene_gate(S, sO, inv);                                 // Scene.cs:54
                 float st; int ss;
+#ifdef RT_INST_ALWAYS_PACKET
+                if (S.packet && (INST || rt_warp_coherent(sO, Ldir, act, S.coherent_spread2))) {
+#else
                 if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
+#endif
                     if (__any_sync(full, act) && rt_traverse_packet<true, INST>(S, sO, Ldir, inv, act, d2, stk, st, ss, INST ? RT_WARP_BAKE() : nullptr)) occluded = true;
                 } else if (act) occluded = rt_traverse<true, false, INST>(S, sO, Ldir, inv, d2, stk, st, ss);
                 if (occluded) mask |= 1u << i;
