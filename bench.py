@@ -100,11 +100,39 @@ def csrc_hash():
     return h.hexdigest()[:12]
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """N > 1: run this rank's host threads on the CPUs of the NUMA node its GPU hangs off, so that the pages of the shared host
+    frame it touches first (its own bands, SharedFrame) are allocated there and its GPU's copy-out does not cross the socket
+    interconnect.  Best effort: returns the node or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]                                         # 00000000:1b:00.0 -> 0000:1b:00.0
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 class SharedFrame:
     """One host frame for all ranks of the node: a POSIX shared-memory file that every rank maps and page-locks
     (rt_host_register).  Each rank's rt_render copies its own bands into it over its own GPU's PCIe link."""
 
-    def __init__(self, rt, tag, spec, rank, world, dist):
+    def __init__(self, rt, tag, spec, rank, world, dist, res=None, band_rows=32):
         self.rt, self.arrays, self.paths, self.rank = rt, {}, [], rank
         names = [None]
         if rank == 0:
@@ -122,7 +150,14 @@ class SharedFrame:
             dist.barrier()
         for (k, (shape, dt)), path in zip(spec.items(), self.paths):
             a = np.memmap(path, dtype=dt, mode="r+", shape=shape)
-            if rank == 0:
+            if res is not None and world > 1:
+                # first touch by the rank that will fill them: the pages of a band land on the NUMA node of the GPU that copies
+                # into it (bind_to_gpu_numa_node), not all on rank 0's
+                X, Y = res
+                rows = a.reshape((Y, X) + tuple(shape[1:]))
+                for y0 in range(rank * band_rows, Y, world * band_rows):
+                    rows[y0:y0 + band_rows] = 0
+            elif rank == 0:
                 a[...] = 0                                   # touch the pages once
             self.arrays[k] = a
         if world > 1:
@@ -311,7 +346,9 @@ def run_ours(args, rank, world, local_rank):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback)")
     torch.cuda.set_device(local_rank)
+    run_ours.numa_node = None
     if world > 1:
+        run_ours.numa_node = bind_to_gpu_numa_node(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         # waits that must not occupy a GPU (an NCCL barrier is a spinning kernel): host-side group
         run_ours.host_group = dist.new_group(backend="gloo")
@@ -385,7 +422,7 @@ def run_ours(args, rank, world, local_rank):
     if world == 1:
         host_out = rt.alloc_host_outputs(params, want, pinned=True)
     else:
-        shared = SharedFrame(rt, "e2e", {"rgba32f": ((X * Y, 4), np.float32)}, rank, world, dist)
+        shared = SharedFrame(rt, "e2e", {"rgba32f": ((X * Y, 4), np.float32)}, rank, world, dist, res=(X, Y), band_rows=args.band_rows)
         host_out = dict(shared.arrays)
     walls = []
     for i in range(args.steps + 2):
@@ -401,7 +438,7 @@ def run_ours(args, rank, world, local_rank):
            "d2h_bytes_per_step": X * Y * 16, "ms_per_step": 1e3 * e2e_s / args.steps,
            "what": ("rt_render() into a pinned host Color[] (RGBA32F, the reference's PixelColors format); scene committed once" if world == 1 else
                     f"{world} ranks, each rt_render() into ONE shared host Color[] (POSIX shared memory, page-locked by every rank): a rank renders its "
-                    "bands into its own framebuffer and copies them out over its own GPU's PCIe link while it renders; per-step wall = max over ranks; "
+                    "bands into its own framebuffer and copies them out over its own GPU's PCIe link while it renders; per-step wall = max over ranks; every rank runs on the CPUs of its GPU's NUMA node and first-touches its own bands of the frame; "
                     "scene committed once")}
 
     # ---- N > 1: both assembled frames must be the 1-GPU frame, bit for bit, in all four outputs ----
@@ -711,7 +748,7 @@ def extra_cfg4(torch, dist, rtb, rank, world, local_rank, args, steps=5):
     dist.all_gather(allm, mine)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_step = float(ms.mean().item())
-    shared = SharedFrame(rt, "cfg4", {"rgba32f": ((X * Y, 4), np.float32)}, rank, world, dist)
+    shared = SharedFrame(rt, "cfg4", {"rgba32f": ((X * Y, 4), np.float32)}, rank, world, dist, res=(X, Y), band_rows=args.band_rows)
     walls = []
     for i in range(steps + 2):
         barrier()

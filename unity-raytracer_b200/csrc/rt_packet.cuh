@@ -152,6 +152,9 @@ __device__ __forceinline__ int rt_packet_octant(float idx_, float idy_, float id
 // by every lane for itself: the instanced triangle test then costs what the baked one costs (ncu, cfg4 as instances: the
 // per-lane bake was 20 % of the fused shadow kernel's instructions, its triangle tests twice the baked scene's).
 #define RT_BAKE_F4 9
+#ifndef RT_OCT_GENERIC
+#define RT_OCT_GENERIC 0            /* development: 1 = generic node loop in every instantiation */
+#endif
 #ifndef RT_INST_OCT
 #define RT_INST_OCT 0
 #endif
@@ -212,7 +215,7 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
         // RT_INST_OCT (INST instantiations): 2 = octant-specialised node loops everywhere, 1 = in the world BVH / TLAS only (inside an
         // instance the octant is the OBJECT-space one, which differs from instance to instance: all eight copies of the loop are then
         // hot at once and compete for the 32 KB instruction cache), 0 = generic loop only
-        if (INST && RT_INST_OCT == 0) { if (node >= 0) node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); }
+        if ((INST && RT_INST_OCT == 0) || RT_OCT_GENERIC) { if (node >= 0) node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); }
         else if (!INST || node >= 0)
         switch ((INST && RT_INST_OCT == 1 && level == 2) ? 8 : oct) {
             case 0: node = rt_packet_descend<0, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
