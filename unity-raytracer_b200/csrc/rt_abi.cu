@@ -4,6 +4,7 @@
 #include <new>
 #include <chrono>
 #include <thread>
+#include <atomic>
 
 struct rt_ctx {
     std::vector<RtDevice> devs;
@@ -18,6 +19,7 @@ struct rt_ctx {
     bool stats_pending = false;
     bool last_local = false;                                // the last render wrote per-device framebuffers (rt_render), not the gather target
     float stream_ms = 0.f; uint64_t stream_bytes = 0;      // streaming commit: time / bytes spent inside rt_scene_mesh
+    std::vector<int32_t> aabb_pending;                      // instanced meshes whose Mesh.AABB the library still has to compute (resolve_pending_aabbs)
     std::vector<RtFrameStats> fstats;
 };
 
@@ -336,7 +338,7 @@ int rt_scene_begin(rt_ctx* c) {
     if (!c) return RT_E_INVALID;
     int rc = sync_all(c);                       // frames still in flight read the buffers the new scene overwrites
     if (rc) return rc;
-    c->host.clear(); c->in_scene = true; c->committed = false; c->dirty = false;
+    c->host.clear(); c->aabb_pending.clear(); c->in_scene = true; c->committed = false; c->dirty = false;
     c->host.builder = c->opt.builder;           // latched: the builder decides where the mesh arrays are staged
     c->host.mesh_on_device = c->opt.stream_upload && c->opt.builder == 0 && c->devs.size() == 1;
     c->stream_ms = 0.f; c->stream_bytes = 0;
@@ -423,12 +425,38 @@ int rt_scene_mesh_instance(rt_ctx* c, int base_mesh, const float m3x4[12], const
     I.base = base_mesh; I.mesh = H.n_meshes();
     if (!RtInstanceSet::set_matrix(I, m3x4, B))
         return fail(c, RT_E_UNSUPPORTED, "rt_scene_mesh_instance: matrix not finite, singular or too ill-conditioned for an instance (bake the mesh and use rt_scene_mesh)");
-    float box[6];
-    if (aabb) for (int k = 0; k < 6; ++k) box[k] = aabb[k]; else instance_aabb(B, m3x4, box);
+    float box[6] = {0, 0, 0, 0, 0, 0};
+    if (aabb) for (int k = 0; k < 6; ++k) box[k] = aabb[k];
+    else c->aabb_pending.push_back(I.mesh);                      // computed at commit, all pending ones in parallel (a pass over the base mesh each)
     H.push_mesh((int32_t)H.inst.insts.size(), *mat, box);
     H.inst.insts.push_back(I);
     H.inst_tris += B.n_tris();
     return RT_OK;
+}
+
+// Mesh.AABB of the instances declared / re-posed with aabb == NULL: SceneMesh.cs:22-31 over the baked vertices, one host thread per
+// instance up to the core count (cfg4: 125 instances x 245 760 vertices = 95 ms on one thread)
+static void resolve_pending_aabbs(rt_ctx* c) {
+    RtHostScene& H = c->host;
+    std::vector<int32_t> todo;
+    todo.swap(c->aabb_pending);
+    if (todo.empty()) return;
+    std::atomic<size_t> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const size_t k = next.fetch_add(1);
+            if (k >= todo.size()) return;
+            const int32_t mesh = todo[k];
+            const RtInstance& I = H.inst.insts[(size_t)H.mesh_inst[(size_t)mesh]];
+            instance_aabb(H.inst.bases[(size_t)I.base], I.m, H.mesh_aabb.data() + 6 * (size_t)mesh);
+        }
+    };
+    size_t nt = std::thread::hardware_concurrency();
+    nt = nt < 1 ? 1 : (nt > todo.size() ? todo.size() : nt);
+    std::vector<std::thread> pool;
+    for (size_t t = 1; t < nt; ++t) pool.emplace_back(work);
+    work();
+    for (auto& t : pool) t.join();
 }
 
 int rt_scene_lights(rt_ctx* c, const float* pos_intensity, int n, const float ambient[3]) {
@@ -441,6 +469,7 @@ int rt_scene_lights(rt_ctx* c, const float* pos_intensity, int n, const float am
 }
 
 static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, bool refit) {
+    resolve_pending_aabbs(c);
     if (c->host.mesh_stale && !refit && c->host.builder == 1 && !c->host.mesh_on_device) {   // (the builder latched at rt_scene_begin, as rt_device_commit uses)   // host rebuild after device-only mesh updates
         RtDevice& D = c->devs[0];
         std::string& err = c->err;
@@ -525,9 +554,9 @@ int rt_scene_update_instance(rt_ctx* c, int mesh_index, const float m3x4[12], co
         return fail(c, RT_E_UNSUPPORTED, "rt_scene_update_instance: matrix not finite, singular or too ill-conditioned for an instance");
     if ((rc = update_mark(c))) return rc;
     H.inst.insts[(size_t)H.mesh_inst[(size_t)mesh_index]] = I;
-    float box[6];
-    if (aabb) for (int k = 0; k < 6; ++k) box[k] = aabb[k]; else instance_aabb(B, m3x4, box);
-    for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = box[k];
+    if (aabb) for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)mesh_index + k] = aabb[k];
+    else c->aabb_pending.push_back(mesh_index);
+    (void)B;
     return RT_OK;
 }
 

@@ -29,7 +29,7 @@ namespace {
 #endif
 // the instantiations for scenes with instanced meshes (INST) carry the two-level state and bake triangles on the fly
 #ifndef RT_MIN_CTAS_INST
-#define RT_MIN_CTAS_INST 8
+#define RT_MIN_CTAS_INST 10
 #endif
 #ifndef RT_STK_CAP
 #define RT_STK_CAP 12
@@ -234,17 +234,6 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_
     }
 }
 
-#ifdef RT_LANE_NOINLINE
-// development: the per-lane any-hit fallback of the shadow kernels as a call, so that its ~1000 instructions sit outside the packet loop's layout
-template <bool INST>
-__device__ __noinline__ bool shadow_lane_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float d2, int* smem_col) {
-    int ovf[STK_OVF]; float ovfd[STK_OVF];
-    SmemStack stk(smem_col, ovf, ovfd);
-    float st; int ss;
-    return rt_traverse<true, false, INST>(S, O, D, inv, d2, stk, st, ss);
-}
-#endif
-
 // item -> the ray that produced its hit. DEPTH0: regenerated from the pixel (never stored); else read from the queue.
 template <bool DEPTH0>
 __device__ __forceinline__ void item_ray(const RtView& V, int tile_begin, unsigned q, int lane, int si, int sj,
@@ -319,18 +308,9 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_
                 const f3 inv = rt_rcp3(Ldir);
                 if (has && !occluded) act = rt_scene_gate(S, sO, inv);                                 // Scene.cs:54
                 float st; int ss;
-#ifdef RT_INST_ALWAYS_PACKET
-                if (S.packet && (INST || rt_warp_coherent(sO, Ldir, act, S.coherent_spread2))) {
-#else
                 if (S.packet && rt_warp_coherent(sO, Ldir, act, S.coherent_spread2)) {
-#endif
                     if (__any_sync(full, act) && rt_traverse_packet<true, INST>(S, sO, Ldir, inv, act, d2, stk, st, ss, INST ? RT_WARP_BAKE() : nullptr)) occluded = true;
-                }
-#ifdef RT_LANE_NOINLINE
-                else if (act) occluded = shadow_lane_traverse<INST>(S, sO, Ldir, inv, d2, g_smem_stack + 2 * threadIdx.x);
-#else
-                else if (act) occluded = rt_traverse<true, false, INST>(S, sO, Ldir, inv, d2, stk, st, ss);
-#endif
+                } else if (act) occluded = rt_traverse<true, false, INST>(S, sO, Ldir, inv, d2, stk, st, ss);
                 if (occluded) mask |= 1u << i;
             }
         }
