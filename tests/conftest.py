@@ -20,6 +20,36 @@ def rtb():
     return importlib.import_module("unity-raytracer_b200")
 
 
+CHECK_KINDS = ["stack overflow", "node index", "leaf slot range", "TLAS leaf range", "tile index", "queue capacity", "virtual slot decode",
+               "pixel index", "hit slot", "mesh index", "light index", "bake leaf size"]
+_check_totals = {"tests": 0, "violations": 0}
+
+
+@pytest.fixture(autouse=True)
+def _self_checking_build(request, rtb):
+    """With RTB200_LIB pointing at a -DRT_CHECKED build (tools/checked_run.sh; compute-sanitizer is closed on this GPU pool) every
+    GPU test also asserts that none of the library's index checks fired while it ran."""
+    yield
+    if not os.environ.get("RTB200_LIB") or "gpu" not in request.keywords:
+        return
+    import ctypes as C
+    L = rtb.load_library()
+    if not hasattr(L, "rt_debug_checks"):
+        return
+    out = (C.c_uint * 16)()
+    assert L.rt_debug_checks(out, 1) == 0
+    bad = {CHECK_KINDS[i] if i < len(CHECK_KINDS) else str(i): int(v) for i, v in enumerate(out) if v}
+    _check_totals["tests"] += 1
+    _check_totals["violations"] += sum(bad.values())
+    assert not bad, f"RT_CHECKED build: index checks fired: {bad}"
+
+
+def pytest_terminal_summary(terminalreporter):
+    if os.environ.get("RTB200_LIB") and _check_totals["tests"]:
+        terminalreporter.write_line(f"RT_CHECKED build: {_check_totals['tests']} GPU tests ran with {len(CHECK_KINDS)} kinds of index checks compiled in; "
+                                    f"violations counted: {_check_totals['violations']}")
+
+
 @pytest.fixture(scope="session")
 def scenes(rtb):
     return rtb.scenes

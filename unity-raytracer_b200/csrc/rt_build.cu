@@ -331,6 +331,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
         RT_CUDA(cudaStreamSynchronize(st));                      // the packed arrays may be re-packed by the next commit
         S.inodes = D.inodes.as<float4>(); S.iprims = D.iprims.as<float4>(); S.inst = D.inst.as<float4>(); S.inst_vbase = D.inst_vbase.as<int32_t>();
         S.tlas_root = IS.tlas_root; S.n_inst = IS.n_packed;
+        S.n_inodes = (int32_t)(IS.inodes.size() / 16); S.n_islots = (int32_t)(IS.iprims.size() / 12);
         // cameras beyond 2 x the scene's extent take the FAR form (ray-dependent padding): the BLAS padding assumes it (need_pad)
         S.origin_reach = fminf(S.origin_reach, 2.0f * amax_w);
         return RT_OK;
@@ -394,6 +395,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             S.prims = D.prims.as<float4>(); S.pinfo = D.pinfo.as<float4>(); S.nodes = D.nodes.as<float4>();
             S.root = old_root;
             D.bvh_prims = n; D.bvh_slots = old_slots; D.bvh_root = old_root;
+            S.n_nodes = (int32_t)D.n_nodes;
             RT_CUDA(cudaEventRecord(D.ev1, st));
             RT_CUDA(cudaEventSynchronize(D.ev1));
             if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
@@ -466,6 +468,7 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
             S.n_slots = ns;
             { int rci = upload_instances(amax, pad); if (rci) return rci; }
             D.bvh_prims = n; D.bvh_slots = ns; D.bvh_root = root; D.bvh_parents = false;
+            S.n_nodes = (int32_t)D.n_nodes;
             RT_CUDA(cudaEventRecord(D.ev1, st));
             RT_CUDA(cudaEventSynchronize(D.ev1));
             if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
@@ -541,7 +544,8 @@ int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, st
         { int rci = upload_instances(amax, pad); if (rci) return rci; }
         D.bvh_prims = n; D.bvh_slots = n; D.bvh_root = S.root; D.bvh_parents = false;
     }
-    RT_CUDA(cudaEventRecord(D.ev1, st));
+    S.n_nodes = (int32_t)D.n_nodes;
+            RT_CUDA(cudaEventRecord(D.ev1, st));
     RT_CUDA(cudaEventSynchronize(D.ev1));
     if (ms_build) RT_CUDA(cudaEventElapsedTime(ms_build, D.ev0, D.ev1));
     return RT_OK;

@@ -61,8 +61,23 @@ struct RtScene {
     const int32_t* inst_vbase;// [n_inst + 1] prefix sums of the instances' triangle counts (TLAS order): a hit on slot s of instance j
                               // is reported as virtual slot n_slots + inst_vbase[j] + (s - first BLAS slot of j)
     int32_t tlas_root, n_inst;
+    int32_t n_nodes, n_inodes, n_islots;   // array sizes (nodes, inodes, BLAS slots in iprims): read only by the RT_CHECKED build
 };
 enum { RT_INST_F4 = 8 };
+
+// Self-checking development build (-DRT_CHECKED; tools/checked_run.sh).  compute-sanitizer is closed on this GPU pool, so every
+// index the render kernels form is tested against its bound right where it is used; violations are counted per kind in
+// g_rt_check[] (rt_debug_checks reads them) — the product build compiles all of it out.
+enum { RT_CHK_STACK = 0, RT_CHK_NODE = 1, RT_CHK_LEAF = 2, RT_CHK_TLAS_LEAF = 3, RT_CHK_TILE = 4, RT_CHK_QUEUE = 5, RT_CHK_VSLOT = 6,
+       RT_CHK_PIXEL = 7, RT_CHK_HIT_SLOT = 8, RT_CHK_MESH = 9, RT_CHK_LIGHT = 10, RT_CHK_BAKE = 11, RT_CHK_KINDS = 16 };
+#if defined(RT_CHECKED) && defined(__CUDACC__)
+static __device__ unsigned g_rt_check[RT_CHK_KINDS];
+#endif
+#if defined(RT_CHECKED) && defined(__CUDA_ARCH__)
+#define RT_CHECK(kind, cond) do { if (!(cond)) atomicAdd(&g_rt_check[kind], 1u); } while (0)
+#else
+#define RT_CHECK(kind, cond) ((void)0)
+#endif
 
 struct RtView {
     f3 pos, fwd, right, up;
@@ -277,6 +292,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
     for (;;) {
         while (node >= 0) {
             RT_COUNT((ANY ? 10 : 0) + 1, 1);
+            RT_CHECK(RT_CHK_NODE, node < ((INST && level > 0) ? S.n_inodes : S.n_nodes));
             const float4* np = (INST ? nodes : S.nodes) + 4 * (size_t)node;
             float4 n0 = RT_LDG4(np), n1 = RT_LDG4(np + 1), n2 = RT_LDG4(np + 2), n3 = RT_LDG4(np + 3);
             float ax0 = rt_fma(n0.x, idx_, -oodx), ax1 = rt_fma(n0.y, idx_, -oodx);
@@ -323,6 +339,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
         }
         if (INST && level == 1) {                                   // TLAS leaf: instances [first, first + cnt)
             const int32_t ref = ~node, first = ref >> 3, cnt = (ref & 7) + 1;
+            RT_CHECK(RT_CHK_TLAS_LEAF, first >= 0 && first + cnt <= S.n_inst);
             if (cnt > 1) stk.push(~((first + 1) * 8 + (cnt - 2)));  // the rest of the leaf, after this instance
             stk.push(RT_SENT_EXIT);
             cur = first;
@@ -340,6 +357,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
         {
             int32_t ref = ~node;
             int32_t first = ref >> 3, cnt = (ref & 7) + 1;
+            RT_CHECK(RT_CHK_LEAF, first >= 0 && first + cnt <= ((INST && level == 2) ? S.n_islots : S.n_slots));
             for (int32_t k = 0; k < cnt; ++k) {
                 int32_t slot = first + k;
                 const float4* pp = ((INST && level == 2) ? S.iprims : S.prims) + 3 * (size_t)slot;
@@ -364,6 +382,7 @@ RT_HD bool rt_traverse(const RtScene& S, f3 O, f3 D, f3 inv, float any_d2, STK& 
                 bool better = ANY ? (t * t < any_d2) : (t < best_t || (t == best_t && key < best_key));
                 if (!better) continue;
                 if (mesh >= 0) {                                    // Scene.cs:67
+                    RT_CHECK(RT_CHK_MESH, mesh < S.n_meshes);
                     if (mesh != gate_mesh) {
                         gate_mesh = mesh;
                         float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);
@@ -433,6 +452,7 @@ RT_HD void rt_inst_decode(const RtScene& S, int32_t slot, int32_t& j, int32_t& b
     while (hi - lo > 1) { const int32_t mid = (lo + hi) >> 1; if (S.inst_vbase[mid] <= v) lo = mid; else hi = mid; }
     j = lo;
     bslot = f2i(RT_LDG4(S.inst + RT_INST_F4 * (size_t)j + 6).y) + (v - S.inst_vbase[j]);
+    RT_CHECK(RT_CHK_VSLOT, v >= 0 && j >= 0 && j < S.n_inst && v < S.inst_vbase[S.n_inst] && v < S.inst_vbase[j + 1] && bslot >= 0 && bslot < S.n_islots);
 }
 // world vertices of an instanced hit, as the reference's bake computes them (SceneMesh.cs:28)
 RT_HD void rt_inst_world_tri(const RtScene& S, int32_t j, int32_t bslot, f3& w0, f3& w1, f3& w2) {
@@ -510,6 +530,7 @@ RT_HD void rt_surf_begin(const RtScene& S, f3 O, f3 D, float t, int32_t slot, Rt
 
 // RTS:329-334: shadow ray direction and lightDistanceSq for light li, from surface point P
 RT_HD void rt_light_ray(const RtScene& S, f3 P, int32_t li, f3& Ldir, float& d2) {
+    RT_CHECK(RT_CHK_LIGHT, li >= 0 && li < S.n_lights);
     float4 lp = RT_LDG4(S.lights + 2 * li);
     f3 Lpos = mk3(lp.x, lp.y, lp.z);
     Ldir = um_normalize(Lpos - P);                                           // RTS:330
@@ -686,6 +707,7 @@ RT_HD void rt_finalize_value(const RtScene& S, const RtView& V, int32_t tile_beg
     int32_t x, y;
     if (!rt_item_to_pixel(V, tile_begin + (int32_t)(q >> 5), (int32_t)(q & 31), x, y)) return;
     size_t pix = (size_t)x + (size_t)y * (size_t)V.res_x;                  // GetPixelIndex, RayTracingSetup.cs:243-246
+    RT_CHECK(RT_CHK_PIXEL, x >= 0 && y >= 0 && x < V.res_x && y < V.res_y);
     if (pass == 0) {
         if (out.hit_id) {
             int32_t ty, ix, me; rt_slot_to_id<INST>(S, hslot, ty, ix, me);

@@ -38,6 +38,13 @@ __device__ __forceinline__ bool rt_warp_coherent(f3 O, f3 D, bool active, float 
 // (the slab planes are monotone under the FMA, so near <= far always holds and the result is the same interval).
 // Returns the next leaf reference (< 0), or RT_PACKET_DONE when the stack ran empty.
 #define RT_PACKET_DONE ((int32_t)0x80000000)
+#ifdef RT_CHECKED
+#define RT_CHK_PARAM , int32_t n_bound
+#define RT_CHK_ARG , ((INST && level > 0) ? S.n_inodes : S.n_nodes)
+#else
+#define RT_CHK_PARAM
+#define RT_CHK_ARG
+#endif
 // Distance-culled pops (RT_POP_CULL, default on).  Every pushed reference carries, per lane, the lane's entry distance into
 // that box (+inf when the lane missed it).  Cull distances only shrink (closest hit found; any-hit lanes that have their
 // occluder drop to -1), so  entry > cull  now implies the lane's own box test would fail now: an entry no lane can reach is
@@ -73,9 +80,10 @@ __device__ __forceinline__ int32_t rt_packet_pop(STK& stk, float tcull RT_CNT_PA
 #endif
 template <int OCT, int ORD, class STK>
 __device__ __forceinline__ int32_t rt_packet_descend(const float4* __restrict__ nodes, float idx_, float idy_, float idz_,
-                                                     float oodx, float oody, float oodz, float tcull, STK& stk, int32_t node RT_CNT_PARAM) {
+                                                     float oodx, float oody, float oodz, float tcull, STK& stk, int32_t node RT_CNT_PARAM RT_CHK_PARAM) {
     const unsigned full = 0xffffffffu;
     while (node >= 0) {
+        RT_CHECK(RT_CHK_NODE, node < n_bound);
         const float4* np = nodes + 4 * (size_t)node;
         float4 n0 = RT_LDG4(np), n1 = RT_LDG4(np + 1), n2 = RT_LDG4(np + 2), n3 = RT_LDG4(np + 3);
 #ifdef RT_COUNT_VISITS
@@ -196,6 +204,7 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
             }
             if (level == 1) {                                           // TLAS leaf: instances [first, first + cnt)
                 const int32_t ref = ~node, first = ref >> 3, cnt = (ref & 7) + 1;
+                RT_CHECK(RT_CHK_TLAS_LEAF, first >= 0 && first + cnt <= S.n_inst);
                 if (cnt > 1) stk.push_packet(~((first + 1) * 8 + (cnt - 2)), -INFINITY);     // the rest of the leaf (its box was passed already)
                 stk.push_packet(RT_SENT_EXIT, -INFINITY);
                 cur = first;
@@ -215,24 +224,26 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
         // RT_INST_OCT (INST instantiations): 2 = octant-specialised node loops everywhere, 1 = in the world BVH / TLAS only (inside an
         // instance the octant is the OBJECT-space one, which differs from instance to instance: all eight copies of the loop are then
         // hot at once and compete for the 32 KB instruction cache), 0 = generic loop only
-        if ((INST && RT_INST_OCT == 0) || RT_OCT_GENERIC) { if (node >= 0) node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); }
+        if ((INST && RT_INST_OCT == 0) || RT_OCT_GENERIC) { if (node >= 0) node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); }
         else if (!INST || node >= 0)
         switch ((INST && RT_INST_OCT == 1 && level == 2) ? 8 : oct) {
-            case 0: node = rt_packet_descend<0, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            case 1: node = rt_packet_descend<1, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            case 2: node = rt_packet_descend<2, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            case 3: node = rt_packet_descend<3, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            case 4: node = rt_packet_descend<4, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            case 5: node = rt_packet_descend<5, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            case 6: node = rt_packet_descend<6, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            case 7: node = rt_packet_descend<7, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
-            default: node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY)); break;
+            case 0: node = rt_packet_descend<0, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            case 1: node = rt_packet_descend<1, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            case 2: node = rt_packet_descend<2, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            case 3: node = rt_packet_descend<3, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            case 4: node = rt_packet_descend<4, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            case 5: node = rt_packet_descend<5, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            case 6: node = rt_packet_descend<6, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            case 7: node = rt_packet_descend<7, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
+            default: node = rt_packet_descend<8, (ANY ? RT_ANY_ORDER : 0)>(nodes, idx_, idy_, idz_, oodx, oody, oodz, tcull, stk, node RT_CNT_ARG(ANY) RT_CHK_ARG); break;
         }
         if (node == RT_PACKET_DONE) return ANY ? found : best_slot >= 0;
         if (INST && (node <= RT_SENT_EXIT || level == 1)) continue;     // sentinel or TLAS leaf: handled at the top of the loop
         {
             int32_t ref = ~node;
             int32_t first = ref >> 3, cnt = (ref & 7) + 1;
+            RT_CHECK(RT_CHK_LEAF, first >= 0 && first + cnt <= ((INST && level == 2) ? S.n_islots : S.n_slots));
+            RT_CHECK(RT_CHK_BAKE, !(INST && level == 2) || cnt <= 3);
             if (INST && level == 2) {                                   // bake the leaf's (<= 3) triangles once for the whole warp
                 const int lane = threadIdx.x & 31;
                 __syncwarp(full);                                       // every lane is done with the previous leaf's vertices
@@ -280,6 +291,7 @@ __device__ __forceinline__ bool rt_traverse_packet(const RtScene& S, f3 O, f3 D,
                 // kernel's instructions).  rcp(ray.Direction) is recomputed here — same bits as the caller's `inv` — which frees
                 // three registers across the loops.
                 if (mesh >= 0) {
+                    RT_CHECK(RT_CHK_MESH, mesh < S.n_meshes);
                     if (mesh != gate_mesh) {
                         gate_mesh = mesh;
                         float4 lo = RT_LDG4(S.mesh_aabb + 2 * mesh), hi = RT_LDG4(S.mesh_aabb + 2 * mesh + 1);

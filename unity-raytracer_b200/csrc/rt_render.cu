@@ -58,6 +58,7 @@ struct SmemStack {
         asm volatile("" : "+r"(base));
     }
     __device__ __forceinline__ void push(int v) {
+        RT_CHECK(RT_CHK_STACK, sp >= 0 && sp < STK_CAP + STK_OVF);
         if (sp < STK_CAP) asm volatile("st.shared.b32 [%0], %1;" ::"r"(base + (unsigned)sp * stride), "r"(v) : "memory");
         else if (sp - STK_CAP < STK_OVF) ovf[sp - STK_CAP] = v;
         ++sp;
@@ -71,6 +72,7 @@ struct SmemStack {
     }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
     __device__ __forceinline__ void push_packet(int v, float dist) {
+        RT_CHECK(RT_CHK_STACK, sp >= 0 && sp < STK_CAP + STK_OVF);
         if (sp < STK_CAP) asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(base + (unsigned)sp * stride), "r"(v), "r"(__float_as_int(dist)) : "memory");
         else if (sp - STK_CAP < STK_OVF) { ovf[sp - STK_CAP] = v; ovfd[sp - STK_CAP] = dist; }
         ++sp;
@@ -183,6 +185,7 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS_PRI
         int t = warp_fetch(work, lane);
         if (t >= n_tiles) break;
         t = rt_hint_tile(hin, t, lane);
+        RT_CHECK(RT_CHK_TILE, t >= 0 && t < n_tiles);
         const unsigned c0 = (unsigned)clock();
 #ifdef RT_TILE_TIMING
         unsigned long long dbg_t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
@@ -256,6 +259,7 @@ struct RtFuse {
     int pass, n_pass; float4* accum; RtOut out;
     uint32_t* split_occl;              // per item: occlusion bits of a tile split by light (zero between uses)
     unsigned long long* split_acc;     // per tile: (cycles << 6 | arrivals) of its per-light items (zero between uses)
+    unsigned cap;                      // capacity of the queue buffers in entries (read only by the RT_CHECKED build)
 };
 
 // (A "mega" variant that also ran k_trace_primary's body here, camera ray to final colour in registers, was measured
@@ -278,12 +282,14 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_
             if ((unsigned)wt * 32u >= n) break;
             if (DEPTH0) wt = rt_hint_tile(hin, wt, lane);
         }
+        RT_CHECK(RT_CHK_TILE, wt >= 0 && (unsigned)wt * 32u < n + 32u);
         unsigned c0 = (unsigned)clock();
         const unsigned q = (unsigned)wt * 32u + lane;
         f3 O = mk3(0.f, 0.f, 0.f), D = mk3(0.f, 0.f, 1.f);
         float ht = 0.f;
         int slot;
         slot = q < n ? RT_LD_STREAM(hit_slot + q) : -2;
+        RT_CHECK(RT_CHK_HIT_SLOT, slot >= -2 && slot < S.n_slots + (INST && S.n_inst > 0 ? S.inst_vbase[S.n_inst] : 0));
         const bool has = slot >= 0;
         uint32_t mask = 0;
         if (__any_sync(full, has)) {
@@ -343,6 +349,7 @@ __global__ void __launch_bounds__(128, INST ? RT_MIN_CTAS_INST : RT_MIN_CTAS) k_
             base = __shfl_sync(full, base, 0);
             if (mir.emit) {
                 size_t o = base + __popc(m & ((1u << lane) - 1u));
+                RT_CHECK(RT_CHK_QUEUE, o < (size_t)F.cap);
                 F.rays_out[2 * o] = make_float4(mir.O.x, mir.O.y, mir.O.z, 0.f);
                 F.rays_out[2 * o + 1] = make_float4(mir.D.x, mir.D.y, mir.D.z, 0.f);
                 F.link_out[o] = make_float4(mir.km.x, mir.km.y, mir.km.z, __int_as_float((int)q));
@@ -788,7 +795,7 @@ int rt_device_render(RtDevice& D, const RtView& V_in, int want, const RtOptions&
                         }
                         if (fuse) {
                             RtFuse F{d, L.local[d].as<float4>(), rout, lout, C + d + 1, (d == 0 && maxd == 0) ? 1 : 0, pass, n_pass,
-                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out, L.split_occl.as<uint32_t>(), L.split_acc.as<unsigned long long>()};
+                                     n_pass > 1 ? D.accum.as<float4>() : nullptr, out, L.split_occl.as<uint32_t>(), L.split_acc.as<unsigned long long>(), (unsigned)W};
                             if (F.fin && n_pass > 1 && n_lanes > 1 && pass > 0) RT_CUDA(cudaStreamWaitEvent(st, D.fin_ev[wi], 0));
                             kbegin(d ? RT_K_SHADOW_QUEUE : RT_K_SHADOW_PRIMARY);
                             if (d == 0) kp_shadow0<<<g_shadow0, block, smem, st>>>(D.S, V, tb, nt, si, sj, nullptr, nullptr, ht, hs, 0, D.S.n_lights, OC, wk + 1, ST, F,
@@ -863,6 +870,15 @@ extern "C" int rt_debug_tile_times(int n_tiles, unsigned long long* host_out) { 
     if (n_tiles > cap) { if (buf) cudaFree(buf); cudaMalloc(&buf, (size_t)n_tiles * 24); cap = n_tiles; }
     cudaMemset(buf, 0, (size_t)cap * 24);
     return (int)cudaMemcpyToSymbol(g_rt_tile_dbg, &buf, sizeof(buf));
+}
+#endif
+
+#ifdef RT_CHECKED
+extern "C" int rt_debug_checks(unsigned* host_out16, int reset) {                       // violation counters of the RT_CHECKED build (rt_core.h)
+    int rc = 0;
+    if (host_out16) rc = (int)cudaMemcpyFromSymbol(host_out16, g_rt_check, RT_CHK_KINDS * sizeof(unsigned));
+    if (reset) { unsigned z[RT_CHK_KINDS] = {0}; rc |= (int)cudaMemcpyToSymbol(g_rt_check, z, sizeof(z)); }
+    return rc;
 }
 #endif
 

@@ -14,7 +14,7 @@ import numpy as np
 from . import scenes
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtb200.so")
+LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(_HERE, "librtb200.so")      # RTB200_LIB: an instrumented development build (tools/checked_run.sh)
 
 RT_OUT_RGBA32F, RT_OUT_RGBA8, RT_OUT_HIT_ID, RT_OUT_HIT_T = 1, 2, 4, 8
 RT_OUT_ALL = 15
