@@ -333,7 +333,7 @@ def run_reference(args, rank, world):
             "ms_per_step": 1e3 * secs / max(1, args.steps), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": {"workload": f"{args.workload}: {desc}", "rays_per_step": rays // max(1, args.steps), "sample": sample},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample + "; oracle/ C++ restatement of the reference's C# "
-                             "hot path with a midpoint-split CPU BVH, scalar code (the reference itself: single-threaded Mono linear scan, cannot run here)"},
+                             "hot path with a binned-SAH CPU BVH (leaves of <= 4), scalar code (the reference itself: single-threaded Mono linear scan, cannot run here)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), file=_OUT, flush=True)
 

@@ -335,6 +335,42 @@ struct Scene {
             f3 ext = cb.mx - cb.mn;
             int ax = 0; if (ext.y > ext.x) ax = 1; if (ext.z > idx(ext, ax)) ax = 2;
             float split = idx(cb.mn, ax) + idx(ext, ax) * 0.5f;
+            {   // binned surface-area heuristic over the three axes (16 bins); the midpoint of the longest axis is the fallback.
+                // Only the tree changes, never a result (same primitive tests, same (t, key) argmin): a fairer CPU baseline than
+                // the midpoint tree of round 1 ("reference-arm bias").
+                const int NB = 16;
+                float best_cost = FLT_MAX;
+                for (int a = 0; a < 3; ++a) {
+                    const float e = idx(ext, a);
+                    if (!(e > 0.f) || !std::isfinite(e)) continue;
+                    int bc_[NB] = {0}; AABB bb[NB];
+                    for (int k = 0; k < NB; ++k) bb[k] = AABB{bc(FLT_MAX), bc(-FLT_MAX)};
+                    const float sc = (float)NB / e, c0 = idx(cb.mn, a);
+                    for (uint32_t i = j.lo; i < j.hi; ++i) {
+                        int k = (int)((idx(cent[order[i]], a) - c0) * sc); k = k < 0 ? 0 : (k >= NB ? NB - 1 : k);
+                        const AABB& pb = boxes[order[i]];
+                        ++bc_[k];
+                        bb[k].mn = mk(std::fmin(bb[k].mn.x, pb.mn.x), std::fmin(bb[k].mn.y, pb.mn.y), std::fmin(bb[k].mn.z, pb.mn.z));
+                        bb[k].mx = mk(std::fmax(bb[k].mx.x, pb.mx.x), std::fmax(bb[k].mx.y, pb.mx.y), std::fmax(bb[k].mx.z, pb.mx.z));
+                    }
+                    auto area = [](const AABB& q) { f3 d = q.mx - q.mn; return (d.x < 0 || d.y < 0 || d.z < 0) ? 0.f : d.x * d.y + d.y * d.z + d.z * d.x; };
+                    float ra[NB]; int rc[NB]; AABB acc{bc(FLT_MAX), bc(-FLT_MAX)}; int c = 0;
+                    for (int k = NB - 1; k >= 1; --k) {
+                        if (bc_[k]) { acc.mn = mk(std::fmin(acc.mn.x, bb[k].mn.x), std::fmin(acc.mn.y, bb[k].mn.y), std::fmin(acc.mn.z, bb[k].mn.z));
+                                      acc.mx = mk(std::fmax(acc.mx.x, bb[k].mx.x), std::fmax(acc.mx.y, bb[k].mx.y), std::fmax(acc.mx.z, bb[k].mx.z)); }
+                        c += bc_[k]; ra[k] = area(acc); rc[k] = c;
+                    }
+                    acc = AABB{bc(FLT_MAX), bc(-FLT_MAX)}; c = 0;
+                    for (int k = 0; k < NB - 1; ++k) {
+                        if (bc_[k]) { acc.mn = mk(std::fmin(acc.mn.x, bb[k].mn.x), std::fmin(acc.mn.y, bb[k].mn.y), std::fmin(acc.mn.z, bb[k].mn.z));
+                                      acc.mx = mk(std::fmax(acc.mx.x, bb[k].mx.x), std::fmax(acc.mx.y, bb[k].mx.y), std::fmax(acc.mx.z, bb[k].mx.z)); }
+                        c += bc_[k];
+                        if (c == 0 || rc[k + 1] == 0) continue;
+                        const float cost = area(acc) * (float)c + ra[k + 1] * (float)rc[k + 1];
+                        if (cost < best_cost) { best_cost = cost; ax = a; split = c0 + (float)(k + 1) / sc; }
+                    }
+                }
+            }
             uint32_t mid = uint32_t(std::partition(order.begin() + j.lo, order.begin() + j.hi,
                                [&](uint32_t k) { return idx(cent[k], ax) < split; }) - order.begin());
             if (mid == j.lo || mid == j.hi) {
@@ -348,8 +384,12 @@ struct Scene {
             stack.push_back({nd.left, j.lo, mid});
             stack.push_back({nd.right, mid, j.hi});
         }
+        pref.resize(n);                                          // leaf order -> {type, index, mesh}: no per-test key decode
+        for (uint32_t i = 0; i < n; ++i) key_decode(order[i], pref[i].type, pref[i].index, pref[i].mesh);
         bvh_built = true;
     }
+    struct PRef { int type, index, mesh; };
+    std::vector<PRef> pref;
 
     // conservative slab test for BVH nodes: returns entry distance, or +inf when missed.
     // dl: every plane moved outward by this much for this ray — the rounding of (plane - o) and of the reference's own
@@ -395,8 +435,9 @@ struct Scene {
             }
             if (node_entry(ray.o, inv, nd.box, lim, dl) == INFINITY) continue;     // best may have shrunk since the push
             for (int i = 0; i < nd.count; ++i) {
-                uint32_t key = order[nd.first + i];
-                int type, index, mesh; key_decode(key, type, index, mesh);
+                const uint32_t key = order[nd.first + i];
+                const PRef& pr = pref[nd.first + i];
+                const int type = pr.type, index = pr.index, mesh = pr.mesh;
                 float d; bool hit;
                 if (type == T_SPHERE) hit = ray_sphere(ray, spheres[index], d);
                 else if (type == T_TRI) hit = ray_tri(ray, tris[index], d);
