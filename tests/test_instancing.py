@@ -236,6 +236,15 @@ def test_gpu_instance_updates_errors_and_explicit_rays(rtb, scenes, oracle):
         r.update_mesh(inst[0], m0[0], m0[1], m0[3])                         # an instance is not re-sent as triangles
     again = r.render(p)
     assert np.array_equal(again["rgba32f"], got["rgba32f"], equal_nan=True)
+    # the whole scene declared again (what a shim that re-sends everything per frame does): the unchanged base meshes get their BLAS
+    # back from the previous scene, a changed one is rebuilt; frames as from a fresh context
+    r.set_scene(s)
+    assert np.array_equal(r.render(p)["rgba32f"], got["rgba32f"], equal_nan=True)
+    s.base_meshes[0] = (s.base_meshes[0] * np.float32(1.25)).astype(np.float32)
+    r.set_scene(s)
+    fresh = rtb.RayTracer((0,)); fresh.set_scene(s)
+    assert np.array_equal(r.render(p)["rgba32f"], fresh.render(p)["rgba32f"], equal_nan=True)
+    fresh.close()
     r.close()
 
 

@@ -393,7 +393,9 @@ int rt_scene_base_mesh(rt_ctx* c, const float* v, int n_tris) {
     RtBaseMesh B;
     B.v.assign(v, v + 9 * (size_t)n_tris);
     if (!RtInstanceSet::set_bounds(B)) return fail(c, RT_E_UNSUPPORTED, "rt_scene_base_mesh: vertices must be finite (bake such a mesh and use rt_scene_mesh)");
-    {   // the BLAS is built here rather than at commit: the instances declared next take their world bounds from its top levels
+    B.hash = RtBaseMesh::hash_bytes(B.v.data(), B.v.size() * 4);
+    if (!c->host.inst.take_cached(B)) {
+        // the BLAS is built here rather than at commit: the instances declared next take their world bounds from its top levels
         int threads = (int)std::thread::hardware_concurrency();
         c->host.inst.build_blas(B, c->opt.leaf_max < 1 ? 1 : (c->opt.leaf_max > 3 ? 3 : c->opt.leaf_max), threads < 1 ? 1 : threads);
     }

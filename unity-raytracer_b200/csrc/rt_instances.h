@@ -30,7 +30,16 @@ struct RtBaseMesh {
     // sqrt(3) times too far per axis (cfg4: boxes of neighbouring instances overlapped and every ray entered 3 - 5 instances it
     // could not hit); the pieces of a cut are small, so their rotated boxes hug the surface.
     std::vector<float> hull;              // 6 floats per box (lo, hi)
+    uint64_t hash = 0;                    // of the vertex bytes: a base mesh re-declared unchanged after rt_scene_begin keeps its BLAS
     int32_t n_tris() const { return (int32_t)(v.size() / 9); }
+    static uint64_t hash_bytes(const void* p, size_t n) {
+        const unsigned char* b = (const unsigned char*)p;
+        uint64_t h = 0x9E3779B97F4A7C15ull ^ (uint64_t)n;
+        size_t i = 0;
+        for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, b + i, 8); h = (h ^ w) * 0xff51afd7ed558ccdull; h ^= h >> 32; }
+        for (; i < n; ++i) { h = (h ^ b[i]) * 0x100000001b3ull; }
+        return h;
+    }
 };
 
 struct RtInstance {
@@ -43,6 +52,8 @@ struct RtInstance {
 
 struct RtInstanceSet {
     std::vector<RtBaseMesh> bases;
+    std::vector<RtBaseMesh> prev_bases;   // the base meshes of the scene before the last clear(): a shim that re-sends its whole scene every
+                                          // frame (RayTracingSetup.cs:120-128) re-declares the same meshes and gets their BLAS back (take_cached)
     std::vector<RtInstance> insts;        // call order
     // ---- packed for the device ----
     std::vector<float> inodes;            // [BLAS nodes of base 0 .. B-1][TLAS nodes]
@@ -57,7 +68,16 @@ struct RtInstanceSet {
     uint64_t generation = 0;              // bumped by every pack()
     uint64_t blas_generation = 0;         // bumped whenever iprims / the BLAS sections were re-emitted: devices compare it with what they hold
 
-    void clear() { bases.clear(); insts.clear(); inodes.clear(); iprims.clear(); inst.clear(); vbase.clear(); node_base.clear(); slot_base.clear();
+    // the built BLAS of an identical base mesh declared in the previous scene, if any (moved out of the cache)
+    bool take_cached(RtBaseMesh& B) {
+        for (auto& P : prev_bases)
+            if (P.built && P.hash == B.hash && P.v.size() == B.v.size() && std::memcmp(P.v.data(), B.v.data(), B.v.size() * 4) == 0) {
+                B = std::move(P); P.built = false; P.v.clear();
+                return true;
+            }
+        return false;
+    }
+    void clear() { prev_bases.clear(); prev_bases.swap(bases); insts.clear(); inodes.clear(); iprims.clear(); inst.clear(); vbase.clear(); node_base.clear(); slot_base.clear();
                    blas_pad.clear(); tlas_base = 0; tlas_root = -1; n_packed = 0; depth = 0; blas_changed = true; }
     bool any() const { return !insts.empty(); }
     int64_t n_tris() const { int64_t n = 0; for (auto& i : insts) n += bases[(size_t)i.base].n_tris(); return n; }
