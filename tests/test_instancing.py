@@ -100,9 +100,8 @@ def test_emulated_repose_and_explicit_rays(emu, scenes, oracle):
     assert mesh.sum() > 30 and np.array_equal(rid[mesh, 2], gid[mesh, 2])
 
 
-def test_emulated_far_camera_and_extreme_instances(emu, scenes, oracle):
-    """(a) a camera hundreds of scene extents away (the FAR form pads the object-space slabs per ray), (b) instances scaled by
-    1e-3 and 1e3, sheared, mirrored (negative determinant) and an empty base mesh: culling stays conservative, results exact."""
+def _extreme_scene(scenes):
+    """instances scaled so that object coordinates are ~1e3 / ~1e-3, sheared, mirrored (negative determinant), and an empty base mesh"""
     s = scenes.SceneArrays()
     rng = np.random.default_rng(17)
     k = 120
@@ -123,14 +122,27 @@ def test_emulated_far_camera_and_extreme_instances(emu, scenes, oracle):
     s.add_instance(small, M(_rot((0, 1, 1), 70) * 4e3, (2, -8, 44)), mats[0])                       # object coordinates ~1e-3, scale 4e3
     s.add_light((30, 40, 0), 2e5); s.add_light((-30, 10, 20), 1e5)
     s.ambient = np.array((15, 15, 15), np.float32)
-    ora = oracle.OracleScene(s.baked())
+    return s
+
+
+def _cameras_near_and_far(scenes):
+    """the scene seen from inside, from 30 000 and from 60 000 units away (hundreds of scene extents: the FAR form of the walk)"""
+    out = []
     for pos in ((0.0, 0.0, 0.0), (0.0, 0.0, -30000.0), (52000.0, 31000.0, 44.0)):
         fwd = np.array((0, 0, 46.0)) - np.array(pos); dist = np.linalg.norm(fwd); fwd /= dist
         right = np.cross((0, 1, 0), fwd); right /= np.linalg.norm(right)
         up = np.cross(fwd, right)
         cam = dict(pos=tuple(np.float32(x) for x in pos), fwd=tuple(fwd.astype(np.float32)), right=tuple(right.astype(np.float32)), up=tuple(up.astype(np.float32)))
-        # the image plane at a distance that keeps the scene in view
-        p = scenes.make_params(64, 48, float(max(10.0, dist - 30.0)), 16.0, 12.0, (0.1, 0.1, 0.2), 2, 1, cam=cam)
+        out.append((pos, scenes.make_params(64, 48, float(max(10.0, dist - 30.0)), 16.0, 12.0, (0.1, 0.1, 0.2), 2, 1, cam=cam)))
+    return out
+
+
+def test_emulated_far_camera_and_extreme_instances(emu, scenes, oracle):
+    """(a) a camera hundreds of scene extents away (the FAR form pads the object-space slabs per ray), (b) instances whose object
+    coordinates are ~1e3 and ~1e-3, sheared, mirrored, and an empty base mesh: culling stays conservative, results exact."""
+    s = _extreme_scene(scenes)
+    ora = oracle.OracleScene(s.baked())
+    for pos, p in _cameras_near_and_far(scenes):
         for builder in (0, 1):
             e = emu.EmuTracer(builder=builder)
             e.set_scene(s)
@@ -246,6 +258,21 @@ def test_gpu_instance_updates_errors_and_explicit_rays(rtb, scenes, oracle):
     assert np.array_equal(r.render(p)["rgba32f"], fresh.render(p)["rgba32f"], equal_nan=True)
     fresh.close()
     r.close()
+
+
+@pytest.mark.gpu
+def test_gpu_far_camera_and_extreme_instances(rtb, scenes, oracle):
+    """the FAR instantiation of the instanced primary kernel and the padding of strongly scaled instances, on the GPU"""
+    s = _extreme_scene(scenes)
+    ora = oracle.OracleScene(s.baked())
+    for pos, p in _cameras_near_and_far(scenes):
+        ref = ora.render(p, oracle.FAITHFUL)
+        for packet in (1, 0):
+            r = rtb.RayTracer((0,)); r.set_option("packet", packet); r.set_scene(s)
+            got = r.render(p)
+            c = compare_renders(ref, got)
+            assert c["id"] == 0 and c["t"] == 0 and c["u8_gt1"] == 0 and c["f32_far"] == 0 and c["f32"] <= 2, (pos, packet, c)
+            r.close()
 
 
 @pytest.mark.gpu

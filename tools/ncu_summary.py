@@ -34,15 +34,21 @@ for key, label in M:
 if len(sys.argv) > 3 and sys.argv[2] == "--json":
     # python tools/ncu_summary.py X.ncu-rep --json <workload> : merge per-kernel facts into profiles/r1_ncu_kernels.json
     import json, os, re
-    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "r1_ncu_kernels.json")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = os.path.join(root, "profiles", sys.argv[4] if len(sys.argv) > 4 else "r2_ncu_kernels.json")
     db = json.load(open(out)) if os.path.exists(out) else {}
+    sys.path.insert(0, root)
+    import bench                                             # the content hash of csrc/ the capture ran on (bench.py drops stale captures)
+    db["csrc_hash"] = bench.csrc_hash()
     wl = db.setdefault(sys.argv[3], {})
     def val(r, key, scale=1.0):
         i = H.index(key); u = U[i]
         v = float(r[i].replace(",", ""))
         mult = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0, "ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(u, 1.0)
         return v * mult * scale
-    alias = {"k_trace_shadow<1, 1>": "k_shadow_primary", "k_trace_shadow<1, 0>": "k_shadow_primary", "k_trace_shadow<0, 1>": "k_shadow_queue",
+    alias = {"k_trace_shadow<1, 1, 0>": "k_shadow_primary", "k_trace_shadow<1, 0, 0>": "k_shadow_primary", "k_trace_shadow<0, 1, 0>": "k_shadow_queue",
+             "k_trace_shadow<0, 0, 0>": "k_shadow_queue", "k_trace_primary<0, 0>": "k_trace_primary", "k_trace_queue<0>": "k_trace_queue",
+             "k_trace_shadow<1, 1>": "k_shadow_primary", "k_trace_shadow<1, 0>": "k_shadow_primary", "k_trace_shadow<0, 1>": "k_shadow_queue",
              "k_trace_shadow<0, 0>": "k_shadow_queue", "k_trace_shadow<1>": "k_shadow_primary", "k_trace_shadow<0>": "k_shadow_queue"}
     # per kernel: the mean over its launches in the report (the two waves of a frame differ a lot); utilisation and lanes
     # weighted by duration / instructions
