@@ -110,12 +110,13 @@ struct RtInstanceSet {
             for (size_t bx = 0; bx < nb; ++bx) {
                 const float* blo = B.hull.empty() ? B.lo : B.hull.data() + 6 * bx;
                 const float* bhi = B.hull.empty() ? B.hi : B.hull.data() + 6 * bx + 3;
-                for (int cx = 0; cx < 8; ++cx) {
-                    const double x = (cx & 1) ? bhi[0] : blo[0], y = (cx & 2) ? bhi[1] : blo[1], z = (cx & 4) ? bhi[2] : blo[2];
-                    for (int r = 0; r < 3; ++r) {
-                        const double w = (double)m[4 * r] * x + (double)m[4 * r + 1] * y + (double)m[4 * r + 2] * z + (double)m[4 * r + 3];
-                        lo[r] = std::fmin(lo[r], w); hi[r] = std::fmax(hi[r], w);
-                    }
+                // box of a transformed box: centre through the map, half extents through |M| (the same as the min / max over its 8 corners)
+                const double cx = 0.5 * ((double)blo[0] + bhi[0]), cy = 0.5 * ((double)blo[1] + bhi[1]), cz = 0.5 * ((double)blo[2] + bhi[2]);
+                const double hx = 0.5 * ((double)bhi[0] - blo[0]), hy = 0.5 * ((double)bhi[1] - blo[1]), hz = 0.5 * ((double)bhi[2] - blo[2]);
+                for (int r = 0; r < 3; ++r) {
+                    const double wc = (double)m[4 * r] * cx + (double)m[4 * r + 1] * cy + (double)m[4 * r + 2] * cz + (double)m[4 * r + 3];
+                    const double wh = (std::fabs((double)m[4 * r]) * hx + std::fabs((double)m[4 * r + 1]) * hy + std::fabs((double)m[4 * r + 2]) * hz) * (1.0 + 1e-12);
+                    lo[r] = std::fmin(lo[r], wc - wh); hi[r] = std::fmax(hi[r], wc + wh);
                 }
             }
         }
