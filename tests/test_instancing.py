@@ -343,3 +343,29 @@ def test_gpu_cfg4_instanced_full_size(rtb, scenes, oracle):
     assert not np.array_equal(f2["hit_t"], fi["hit_t"])
     assert ms < 5.0, ms                                                     # 125 ctypes calls + TLAS rebuild + 16 KB upload (the baked twin: ~1 s)
     r.close(); rb.close()
+
+
+@pytest.mark.gpu
+def test_gpu_instances_on_an_in_process_two_device_context(rtb, scenes):
+    """rt_create with 2 devices and an instanced scene: both output modes (rt_render: per-device copy-out; rt_render_device: peer-store
+    gather) equal the 1-device frame; re-posing reaches every device."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    s, p = scenes.instanced_soup(seed=2, n_instances=12), scenes.soup_params(320, 256, 2)
+    one = rtb.RayTracer((0,)); one.set_scene(s); a = one.render(p)
+    two = rtb.RayTracer((0, 1)); two.set_partition(0, 1, 8); two.set_scene(s)
+    b = two.render(p)
+    two.render_device(p, 15); c = two.read_outputs(p, 15)
+    for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(a[k], b[k], equal_nan=True) and np.array_equal(a[k], c[k], equal_nan=True), k
+    inst = [i for i, m in enumerate(s.meshes) if isinstance(m, scenes.MeshInstance)]
+    for i in inst[::3]:
+        M = s.meshes[i].m3x4.copy(); M[:, 3] += np.float32(2.5); s.meshes[i].m3x4 = M
+        one.update_instance(i, M); two.update_instance(i, M)
+    one.recommit(); two.recommit()
+    a2, b2 = one.render(p), two.render(p)
+    for k in ("rgba32f", "rgba8", "hit_id", "hit_t"):
+        assert np.array_equal(a2[k], b2[k], equal_nan=True), k
+    assert not np.array_equal(a2["hit_t"], a["hit_t"])
+    one.close(); two.close()
