@@ -29,6 +29,8 @@ UNIT = "Mrays/s"
 
 def workload(name, scenes):
     """BASELINE.json configs[1..4]; returns (scene arrays, render params, description)."""
+    if name == "cfg1":       # the reference's own scene at its own resolution: launch-bound on a GPU, kept for the per-config CPU baselines
+        return scenes.rt_unity(), scenes.rt_unity_params(), "RayTracing.unity as shipped, 50x50, 1 light, bounces 5 (no mirror material)"
     if name == "cfg2":
         return scenes.rt_unity(True), scenes.rt_unity_params(3840, 2160, 4), "RayTracing.unity, sphere mirror restored, 3840x2160, depth 4, 1 light"
     if name == "cfg3":
