@@ -651,7 +651,7 @@ def moving_camera_leg(torch, rt, stream, flush, scene, params, want, steps, rays
 def instancing_leg(torch, rtb, rt, scene, params, want, dev, args):
     """Workloads made of instanced meshes (rt_scene_mesh_instance): what the instancing buys and costs against the baked twin —
     the scene the reference would build by baking every instance every frame (SceneMesh.cs:21-31).  Device memory of the
-    scene, wall time to re-pose EVERY instance (rt_scene_update_instance x N + rt_scene_recommit) against re-sending the baked
+    scene, wall time to re-pose EVERY instance (one rt_scene_update_instances call + rt_scene_recommit) against re-sending the baked
     meshes (rt_scene_update_mesh x N + rt_scene_recommit), frame time instanced vs baked, frames compared bit for bit."""
     S = rtb.scenes
     free0 = torch.cuda.mem_get_info()[0]
@@ -679,10 +679,10 @@ def instancing_leg(torch, rtb, rt, scene, params, want, dev, args):
     inst = [(i, m) for i, m in enumerate(scene.meshes) if isinstance(m, S.MeshInstance)]
     boxes = [S.bake_tris(scene.base_meshes[m.base], m.m3x4)[2] for _, m in inst]
     rep_i, rep_b = [], []
+    idx_all, m_all, b_all = np.array([i for i, _ in inst], np.int32), np.stack([m.m3x4 for _, m in inst]), np.stack(boxes)
     for _ in range(4):
         t0 = time.perf_counter()
-        for (i, m), bb in zip(inst, boxes):
-            ri.update_instance(i, m.m3x4, bb)
+        ri.update_instances(idx_all, m_all, b_all)                              # one rt_scene_update_instances call for all of them
         ri.recommit(); rep_i.append(time.perf_counter() - t0)
     st_i = ri.stats()
     for _ in range(2):

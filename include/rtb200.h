@@ -118,10 +118,15 @@ int rt_scene_mesh(rt_ctx* ctx, const float* v, const float* normals, int n_tris,
  *   computed it (the semantic cull of Scene.cs:67, used verbatim) or NULL -> computed as SceneMesh.cs:22-31 does (min / max of the
  *   baked vertices; costs a pass over the base mesh on the host).
  * rt_scene_update_instance: re-pose an instance of a committed scene (dirty-tracking update: follow with rt_scene_recommit or
- *   rt_scene_refit; both rebuild the instance tree, which takes microseconds, and leave the base meshes alone). */
+ *   rt_scene_refit; both rebuild the instance tree, which takes microseconds, and leave the base meshes alone).
+ * rt_scene_update_instances: the same for n instances in one call — what a frame of the reference does, which re-reads every
+ *   SceneMesh's localToWorldMatrix (RTS:120-128, SceneMesh.cs:21): mesh_indices[n], m3x4 = 12 floats per entry, aabbs = 6 floats per
+ *   entry or NULL (all computed).  All or nothing: when an entry is rejected (RT_E_INVALID: not an instanced mesh; RT_E_UNSUPPORTED:
+ *   its matrix) no pose has changed; rt_last_error names the entry.  A mesh index that appears twice ends with its later pose. */
 int rt_scene_base_mesh(rt_ctx* ctx, const float* v, int n_tris);
 int rt_scene_mesh_instance(rt_ctx* ctx, int base_mesh, const float m3x4[12], const rt_material* material, const float aabb[6]);
 int rt_scene_update_instance(rt_ctx* ctx, int mesh_index, const float m3x4[12], const float aabb[6]);
+int rt_scene_update_instances(rt_ctx* ctx, const int32_t* mesh_indices, const float* m3x4, const float* aabbs, int n);
 /* Scene.PointLights (6 floats each = PointLightData{Position,Intensity}, PointLightData.cs:9-10) + AmbientLight.Radiance;
  * ambient_radiance NULL = default(AmbientLightData) = 0 (RTS:132) */
 int rt_scene_lights(rt_ctx* ctx, const float* pos_intensity, int n, const float ambient_radiance[3]);

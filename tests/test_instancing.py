@@ -206,13 +206,17 @@ def test_gpu_instance_updates_errors_and_explicit_rays(rtb, scenes, oracle):
     inst = [i for i, m in enumerate(s.meshes) if isinstance(m, scenes.MeshInstance)]
     baked_mesh = [i for i, m in enumerate(s.meshes) if not isinstance(m, scenes.MeshInstance)]
     for rep in range(2):
+        batch = []
         for i in inst[rep::2]:
             m = s.meshes[i]
             M = m.m3x4.copy()
             M[:, :3] = (_rot(rng.normal(size=3), rng.uniform(0, 360)) @ M[:, :3].astype(np.float64) * rng.uniform(0.7, 1.4)).astype(np.float32)
             M[:, 3] += rng.uniform(-6, 6, 3).astype(np.float32)
             m.m3x4 = M
-            r.update_instance(i, M, None if rep else scenes.bake_tris(s.base_meshes[m.base], M)[2])    # AABB given / computed by the library
+            if rep == 0: r.update_instance(i, M, scenes.bake_tris(s.base_meshes[m.base], M)[2])          # one by one, Mesh.AABB given
+            else: batch.append((i, M))
+        if batch:                                                           # rt_scene_update_instances: one call, AABBs computed by the library
+            r.update_instances([i for i, _ in batch], np.stack([M for _, M in batch]), None)
         with pytest.raises(rtb.host.RtError) as ei:                         # dirty scene: rendering needs the recommit
             r.render(p)
         assert ei.value.code == -4
@@ -243,6 +247,13 @@ def test_gpu_instance_updates_errors_and_explicit_rays(rtb, scenes, oracle):
         with pytest.raises(rtb.host.RtError) as ei:
             r.update_instance(*bad)
         assert ei.value.code == code, bad
+    # the batched call is all or nothing: a bad LAST entry leaves the poses of the good ones before it untouched (scene not even dirty)
+    moved = ident.copy(); moved[:, 3] = 50.0
+    for bad_idx, bad_m, code in ((baked_mesh[0], ident, -1), (inst[1], np.zeros((3, 4), np.float32), -5), (-1, ident, -1)):
+        with pytest.raises(rtb.host.RtError) as ei:
+            r.update_instances([inst[0], bad_idx], np.stack([moved, bad_m]), None)
+        assert ei.value.code == code and "entry 1" in str(ei.value), (bad_idx, str(ei.value))
+    r.update_instances([], np.zeros((0, 12), np.float32), None)             # n = 0: a no-op, not an error, nothing dirty
     m0 = s.meshes[baked_mesh[0]]
     with pytest.raises(rtb.host.RtError):
         r.update_mesh(inst[0], m0[0], m0[1], m0[3])                         # an instance is not re-sent as triangles

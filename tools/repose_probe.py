@@ -1,6 +1,7 @@
 """Development aid: wall time of re-posing every instance of cfg4-as-instances (rt_scene_update_instance x 125 + rt_scene_recommit)."""
 import importlib, os, sys, time
 import numpy as np
+import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 rtb = importlib.import_module("unity-raytracer_b200")
 S = rtb.scenes
@@ -10,6 +11,7 @@ t0 = time.perf_counter(); r.set_scene(s); print(f"commit {1e3*(time.perf_counter
 r.render_device(p, 2)
 boxes = [S.bake_tris(s.base_meshes[m.base], m.m3x4)[2] for m in s.meshes]
 for rep in range(6):
+    torch.cuda.synchronize()                              # (the frame rendered at the end of the previous round is asynchronous)
     t0 = time.perf_counter()
     for i, m in enumerate(s.meshes):
         r.update_instance(i, m.m3x4, boxes[i])
@@ -18,5 +20,15 @@ for rep in range(6):
     t2 = time.perf_counter()
     st = r.stats()
     print(f"rep {rep}: 125 updates {1e3*(t1-t0):.3f} ms, recommit {1e3*(t2-t1):.3f} ms (device: upload {st['ms_commit_upload']:.3f} + build {st['ms_commit_build']:.3f})", flush=True)
+    r.render_device(p, 2)
+idx, mm, bb = np.arange(len(s.meshes), dtype=np.int32), np.stack([m.m3x4 for m in s.meshes]), np.stack(boxes)
+for rep in range(6):                                     # the same through ONE rt_scene_update_instances call
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    r.update_instances(idx, mm, bb)
+    t1 = time.perf_counter()
+    r.recommit()
+    t2 = time.perf_counter()
+    print(f"batched rep {rep}: 1 call {1e3*(t1-t0):.3f} ms, recommit {1e3*(t2-t1):.3f} ms", flush=True)
     r.render_device(p, 2)
 t0 = time.perf_counter(); r.set_scene(s); print(f"full re-declaration (BLAS cached) {1e3*(time.perf_counter()-t0):.2f} ms")

@@ -562,6 +562,36 @@ int rt_scene_update_instance(rt_ctx* c, int mesh_index, const float m3x4[12], co
     return RT_OK;
 }
 
+int rt_scene_update_instances(rt_ctx* c, const int32_t* mesh_indices, const float* m3x4, const float* aabbs, int n) {
+    int rc = update_prolog(c, "rt_scene_update_instances");
+    if (rc) return rc;
+    RtHostScene& H = c->host;
+    if (n < 0 || (n > 0 && (!mesh_indices || !m3x4))) return fail(c, RT_E_INVALID, "rt_scene_update_instances: bad arguments");
+    if (n == 0) return RT_OK;
+    // all or nothing: every pose is validated (and its inverse / bounds computed) before the first one is stored
+    std::vector<RtInstance> posed((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        const int m = mesh_indices[i];
+        if (m < 0 || m >= H.n_meshes() || H.mesh_inst[(size_t)m] < 0) {
+            char b[128]; snprintf(b, sizeof(b), "rt_scene_update_instances: entry %d: mesh %d is not an instanced mesh", i, m);
+            return fail(c, RT_E_INVALID, b);
+        }
+        posed[(size_t)i] = H.inst.insts[(size_t)H.mesh_inst[(size_t)m]];
+        if (!RtInstanceSet::set_matrix(posed[(size_t)i], m3x4 + 12 * (size_t)i, H.inst.bases[(size_t)posed[(size_t)i].base])) {
+            char b[160]; snprintf(b, sizeof(b), "rt_scene_update_instances: entry %d (mesh %d): matrix not finite, singular or too ill-conditioned for an instance", i, m);
+            return fail(c, RT_E_UNSUPPORTED, b);
+        }
+    }
+    if ((rc = update_mark(c))) return rc;
+    for (int i = 0; i < n; ++i) {
+        const int m = mesh_indices[i];
+        H.inst.insts[(size_t)H.mesh_inst[(size_t)m]] = posed[(size_t)i];
+        if (aabbs) for (int k = 0; k < 6; ++k) H.mesh_aabb[6 * (size_t)m + k] = aabbs[6 * (size_t)i + k];
+        else c->aabb_pending.push_back(m);
+    }
+    return RT_OK;
+}
+
 int rt_scene_update_triangles(rt_ctx* c, int first, int n, const float* v, const float* normals) {
     int rc = update_prolog(c, "rt_scene_update_triangles");
     if (rc) return rc;

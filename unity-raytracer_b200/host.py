@@ -20,7 +20,7 @@ RT_OUT_RGBA32F, RT_OUT_RGBA8, RT_OUT_HIT_ID, RT_OUT_HIT_T = 1, 2, 4, 8
 RT_OUT_ALL = 15
 
 ABI_SYMBOLS = ["rt_create", "rt_destroy", "rt_last_error", "rt_abi_version", "rt_scene_begin", "rt_scene_spheres",
-               "rt_scene_triangles", "rt_scene_mesh", "rt_scene_base_mesh", "rt_scene_mesh_instance", "rt_scene_update_instance", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
+               "rt_scene_triangles", "rt_scene_mesh", "rt_scene_base_mesh", "rt_scene_mesh_instance", "rt_scene_update_instance", "rt_scene_update_instances", "rt_scene_lights", "rt_scene_commit", "rt_scene_get_aabb", "rt_scene_update_mesh",
                "rt_scene_update_triangles", "rt_scene_update_spheres", "rt_scene_update_lights", "rt_scene_recommit", "rt_scene_refit", "rt_render",
                "rt_render_device", "rt_read_outputs", "rt_device_outputs", "rt_intersect", "rt_intersect_static", "rt_get_stats", "rt_set_stream",
                "rt_set_partition", "rt_host_register", "rt_host_unregister", "rt_alloc_outputs", "rt_export_outputs", "rt_import_outputs", "rt_set_option"]
@@ -92,6 +92,7 @@ def load_library():
     L.rt_scene_base_mesh.argtypes = [vp, fp, C.c_int]
     L.rt_scene_mesh_instance.argtypes = [vp, C.c_int, fp, vp, fp]
     L.rt_scene_update_instance.argtypes = [vp, C.c_int, fp, fp]
+    L.rt_scene_update_instances.argtypes = [vp, C.POINTER(C.c_int32), fp, fp, C.c_int]
     L.rt_scene_commit.argtypes = [vp, fp]
     L.rt_scene_get_aabb.argtypes = [vp, fp]
     L.rt_scene_update_mesh.argtypes = [vp, C.c_int, fp, fp, fp]
@@ -194,6 +195,14 @@ class RayTracer:
         mm = np.ascontiguousarray(m3x4, dtype=np.float32)
         bb = None if aabb is None else np.ascontiguousarray(aabb, dtype=np.float32)
         self._chk(self.L.rt_scene_update_instance(self.h, int(mesh_index), _fptr(mm), _fptr(bb) if bb is not None else None))
+
+    def update_instances(self, mesh_indices, m3x4s, aabbs=None):
+        """rt_scene_update_instances: many instances re-posed in one call (all or nothing); m3x4s [n, 12], aabbs [n, 6] or None."""
+        idx = np.ascontiguousarray(mesh_indices, dtype=np.int32).reshape(-1)
+        mm = np.ascontiguousarray(m3x4s, dtype=np.float32).reshape(-1)
+        bb = None if aabbs is None else np.ascontiguousarray(aabbs, dtype=np.float32).reshape(-1)
+        if mm.size != 12 * idx.size or (bb is not None and bb.size != 6 * idx.size): raise ValueError("update_instances: need 12 (and 6) floats per index")
+        self._chk(self.L.rt_scene_update_instances(self.h, idx.ctypes.data_as(C.POINTER(C.c_int32)), _fptr(mm), _fptr(bb) if bb is not None else None, int(idx.size)))
 
     def update_triangles(self, first, v, n):
         v, n = np.ascontiguousarray(v, dtype=np.float32), np.ascontiguousarray(n, dtype=np.float32)

@@ -52,6 +52,7 @@ namespace RayTracer
 		[DllImport(Lib)] static extern int rt_scene_base_mesh(IntPtr ctx, Triangle[] objectSpaceTriangles, int nTris);
 		[DllImport(Lib)] static extern int rt_scene_mesh_instance(IntPtr ctx, int baseMesh, float[] m3x4, ref NativeMaterial material, IntPtr aabbOrNull);
 		[DllImport(Lib)] static extern int rt_scene_update_instance(IntPtr ctx, int meshIndex, float[] m3x4, IntPtr aabbOrNull);
+		[DllImport(Lib)] static extern int rt_scene_update_instances(IntPtr ctx, int[] meshIndices, float[] m3x4, IntPtr aabbsOrNull, int n);
 		[DllImport(Lib)] static extern int rt_scene_lights(IntPtr ctx, PointLightData[] posIntensity, int n, ref float3 ambientRadiance);
 		[DllImport(Lib)] static extern int rt_scene_commit(IntPtr ctx, ref AABB sceneAabb);
 		[DllImport(Lib)] static extern int rt_scene_update_mesh(IntPtr ctx, int meshIndex, Triangle[] v, float3[] normals, ref AABB aabb);
@@ -143,6 +144,25 @@ namespace RayTracer
 		public static void UpdateInstance(int meshIndex, Matrix4x4 localToWorld)
 		{
 			Check(rt_scene_update_instance(ctx, meshIndex, Rows3x4(localToWorld), IntPtr.Zero));
+		}
+
+		/// Every moved instance in ONE native call (rt_scene_update_instances; all or nothing).  The arrays are grow-only scratch: no
+		/// allocation per frame once they have reached the scene's instance count.
+		static int[] instIdx = new int[0];
+		static float[] instRows = new float[0];
+		public static void UpdateInstances(IList<int> meshIndices, IList<Matrix4x4> localToWorld)
+		{
+			int n = meshIndices.Count;
+			if (instIdx.Length < n) { instIdx = new int[n]; instRows = new float[12 * n]; }
+			for (int i = 0; i < n; i++)
+			{
+				instIdx[i] = meshIndices[i];
+				Matrix4x4 m = localToWorld[i];
+				for (int r = 0; r < 3; r++)
+					for (int c = 0; c < 4; c++)
+						instRows[12 * i + 4 * r + c] = m[r, c];
+			}
+			Check(rt_scene_update_instances(ctx, instIdx, instRows, IntPtr.Zero, n));
 		}
 
 		/// After UpdateInstance calls: rebuilds the instance tree (microseconds) and whatever else was updated.  sceneAabb = Scene.AABB.
