@@ -272,6 +272,52 @@ def test_gpu_instance_updates_errors_and_explicit_rays(rtb, scenes, oracle):
 
 
 @pytest.mark.gpu
+def test_gpu_mesh_aabb_of_reposed_instances_computed_on_the_device(rtb, scenes):
+    """rt_scene_update_instance(s) with aabb = NULL on a committed scene: Mesh.AABB (SceneMesh.cs:22-31) comes from a reduction over the
+    base mesh resident on the device.  A scene of ONE instance has Scene.AABB == that Mesh.AABB (Scene.cs:17-41), which must equal the
+    min / max of the baked vertices bit for bit — for rotated, scaled and sheared poses, and for poses that put an extremum at exactly
+    0 (the sign of a zero depends on the vertex order: the library re-derives those on the host)."""
+    base, _ = scenes.displaced_icosphere(40, 3.0, (0.0, 0.0, 0.0), 77)              # 32 000 triangles, 96 000 vertices ...
+    base = np.concatenate([base, base[:2000] * np.float32(1.01)]).astype(np.float32)   # ... + 6 000: above the device path's threshold
+    assert 3 * len(base) >= 100000
+    s = scenes.SceneArrays()
+    b = s.add_base_mesh(base)
+    M0 = np.eye(3, 4, dtype=np.float32); M0[:, 3] = (0, 0, 30)
+    s.add_instance(b, M0, scenes.material((0.5, 0.5, 0.5), (1, 1, 1)))
+    s.add_light((10, 20, 0), 1e4)
+    p = scenes.make_params(64, 48, 10.0, 4.0, 3.0)
+    r = rtb.RayTracer((0,))
+    r.set_scene(s)
+    rng = np.random.default_rng(5)
+    vmin = base.reshape(-1, 3).min(axis=0)
+    poses = []
+    for k in range(6):
+        M = np.zeros((3, 4), np.float32)
+        M[:, :3] = (_rot(rng.normal(size=3), rng.uniform(0, 360)) * rng.uniform(0.5, 2.0)).astype(np.float32)
+        if k == 4: M[0, 1] += np.float32(0.3)                                           # shear
+        M[:, 3] = rng.uniform(-5, 5, 3).astype(np.float32) + np.float32((0, 0, 30))
+        poses.append(M)
+    Z = np.eye(3, 4, dtype=np.float32); Z[:, 3] = -vmin                                 # x + (-xmin) == 0 exactly: zero extrema on all three axes
+    poses.append(Z)
+    for k, M in enumerate(poses):
+        if k % 2: r.update_instance(0, M, None)
+        else: r.update_instances([0], M[None], None)
+        r.recommit()
+        want = scenes.bake_tris(base, M)[2]
+        got = r.scene_aabb()
+        assert np.array_equal(got.view(np.uint32), np.asarray(want, np.float32).view(np.uint32)), (k, got, want)
+    # and the frame is the one of a context that was GIVEN the box
+    s.meshes[0].m3x4 = poses[2]; s.meshes[0].aabb = scenes.bake_tris(base, poses[2])[2]
+    r.update_instance(0, poses[2], None); r.recommit()
+    fresh = rtb.RayTracer((0,)); fresh.set_scene(s)
+    a, f = r.render(p), fresh.render(p)
+    for k in ("hit_id", "hit_t", "rgba32f", "rgba8"):
+        assert np.array_equal(a[k], f[k], equal_nan=True), k
+    assert (a["hit_id"][:, 0] == 3).sum() > 100
+    fresh.close(); r.close()
+
+
+@pytest.mark.gpu
 def test_gpu_far_camera_and_extreme_instances(rtb, scenes, oracle):
     """the FAR instantiation of the instanced primary kernel and the padding of strongly scaled instances, on the GPU"""
     s = _extreme_scene(scenes)

@@ -31,4 +31,13 @@ for rep in range(6):                                     # the same through ONE 
     t2 = time.perf_counter()
     print(f"batched rep {rep}: 1 call {1e3*(t1-t0):.3f} ms, recommit {1e3*(t2-t1):.3f} ms", flush=True)
     r.render_device(p, 2)
+for rep in range(4):                                     # ... and with Mesh.AABB left to the library (device reduction over the resident base mesh)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    r.update_instances(idx, mm, None)
+    t1 = time.perf_counter()
+    r.recommit()
+    t2 = time.perf_counter()
+    print(f"batched, AABBs computed, rep {rep}: 1 call {1e3*(t1-t0):.3f} ms, recommit {1e3*(t2-t1):.3f} ms", flush=True)
+    r.render_device(p, 2)
 t0 = time.perf_counter(); r.set_scene(s); print(f"full re-declaration (BLAS cached) {1e3*(time.perf_counter()-t0):.2f} ms")

@@ -217,6 +217,61 @@ int rt_device_update_raw(RtDevice& D, int what, int64_t first, int64_t n, const 
 
 // raw_resident: the triangle / sphere arrays of this scene are already on the device (rt_scene_recommit after
 // rt_scene_update_*): only the small tables are uploaded before the BVH is rebuilt.
+// ---- Mesh.AABB of instances on the device (rt_scene_mesh_instance / rt_scene_update_instance(s) with aabb = NULL) -------------
+// SceneMesh.cs:22-31: min / max over the baked vertices.  The object-space vertices are resident (iprims, the BLAS leaf slots),
+// so a re-posed instance costs one pass over them at L2 bandwidth instead of one host thread's pass (cfg4: 125 instances of
+// 81 920 triangles, 8 ms on 16 host threads).  Min / max of finite values do not depend on the order, so the parallel reduction
+// gives the bits of the reference's sequential loop — except the sign of a zero extremum (math.min/max keep the LATER of +0 / -0),
+// which the caller re-derives on the host (rt_abi.cu resolve_pending_aabbs).
+struct RtAabbReq { int32_t first_slot, n_tris; float m[12]; };
+__global__ void k_instance_aabbs(const float4* __restrict__ iprims, const RtAabbReq* __restrict__ req, uint32_t* __restrict__ out) {
+    const RtAabbReq R = req[blockIdx.x];
+    const float4 r0 = make_float4(R.m[0], R.m[1], R.m[2], R.m[3]), r1 = make_float4(R.m[4], R.m[5], R.m[6], R.m[7]), r2 = make_float4(R.m[8], R.m[9], R.m[10], R.m[11]);
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};     // float.MaxValue / float.MinValue
+    const int64_t n_vert = 3 * (int64_t)R.n_tris;
+    for (int64_t i = (int64_t)blockIdx.y * blockDim.x + threadIdx.x; i < n_vert; i += (int64_t)gridDim.y * blockDim.x) {
+        const float4 p = iprims[3 * (size_t)R.first_slot + (size_t)i];
+        const f3 w = rt_xform_point(r0, r1, r2, mk3(p.x, p.y, p.z));                         // MultiplyPoint3x4, exact operation order
+        lo[0] = fminf(lo[0], w.x); lo[1] = fminf(lo[1], w.y); lo[2] = fminf(lo[2], w.z);     // (a NaN is skipped, as um_min / um_max skip it)
+        hi[0] = fmaxf(hi[0], w.x); hi[1] = fmaxf(hi[1], w.y); hi[2] = fmaxf(hi[2], w.z);
+    }
+    for (int k = 0; k < 3; ++k)
+        for (int o = 16; o > 0; o >>= 1) { lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o)); hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o)); }
+    if ((threadIdx.x & 31) == 0)
+        for (int k = 0; k < 3; ++k) { atomicMin(out + 6 * (size_t)blockIdx.x + k, f_ord(lo[k])); atomicMax(out + 6 * (size_t)blockIdx.x + 3 + k, f_ord(hi[k])); }
+}
+
+int rt_device_instance_aabbs(RtDevice& D, const RtInstanceSet& IS, const int32_t* inst_idx, int n, float* out6, std::string& err) {
+    if (n <= 0) return RT_OK;
+    if (D.inst_blas_gen != IS.blas_generation || IS.blas_changed || !D.iprims.p || IS.slot_base.size() != IS.bases.size() + 1) return RT_E_STATE;   // the device does not hold these base meshes
+    RT_CUDA(cudaSetDevice(D.device));
+    cudaStream_t st = D.stream;
+    std::vector<RtAabbReq> req((size_t)n);
+    std::vector<uint32_t> box((size_t)n * 6);
+    int32_t max_tris = 1;
+    for (int i = 0; i < n; ++i) {
+        const RtInstance& I = IS.insts[(size_t)inst_idx[i]];
+        req[(size_t)i].first_slot = IS.slot_base[(size_t)I.base]; req[(size_t)i].n_tris = IS.bases[(size_t)I.base].n_tris();
+        memcpy(req[(size_t)i].m, I.m, sizeof(I.m));
+        if (req[(size_t)i].n_tris > max_tris) max_tris = req[(size_t)i].n_tris;
+        for (int k = 0; k < 3; ++k) { box[6 * (size_t)i + k] = 0xffffffffu; box[6 * (size_t)i + 3 + k] = 0u; }
+    }
+    const size_t req_bytes = (size_t)n * sizeof(RtAabbReq), box_off = (req_bytes + 255) & ~(size_t)255, box_bytes = (size_t)n * 24;
+    RT_CUDA(D.cub_tmp.ensure(box_off + box_bytes));                     // (build scratch: free between commits)
+    RT_CUDA(cudaMemcpyAsync(D.cub_tmp.p, req.data(), req_bytes, cudaMemcpyHostToDevice, st));
+    RT_CUDA(cudaMemcpyAsync((char*)D.cub_tmp.p + box_off, box.data(), box_bytes, cudaMemcpyHostToDevice, st));
+    int parts = (D.sm_count * 8 + n - 1) / n;
+    const int max_parts = (3 * max_tris + 255) / 256;
+    parts = parts < 1 ? 1 : (parts > max_parts ? max_parts : parts);
+    if (parts > 65535) parts = 65535;
+    k_instance_aabbs<<<dim3((unsigned)n, (unsigned)parts), 256, 0, st>>>(D.iprims.as<float4>(), (const RtAabbReq*)D.cub_tmp.p, (uint32_t*)((char*)D.cub_tmp.p + box_off));
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaMemcpyAsync(box.data(), (char*)D.cub_tmp.p + box_off, box_bytes, cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    for (size_t k = 0; k < box.size(); ++k) out6[k] = f_unord(box[k]);
+    return RT_OK;
+}
+
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
                      float* ms_build, uint64_t* h2d_bytes, bool raw_resident, bool refit) {
     RT_CUDA(cudaSetDevice(D.device));

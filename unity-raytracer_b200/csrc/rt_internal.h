@@ -166,6 +166,9 @@ int rt_device_stage_mesh(RtDevice& D, const float* v, const float* normals, int6
 int rt_device_update_raw(RtDevice& D, int what, int64_t first, int64_t n, const float* a, const float* b, int threads, std::string& err);
 int rt_device_commit(RtDevice& D, const RtHostScene& H, const RtOptions& opt, std::string& err, float* ms_upload,
                      float* ms_build, uint64_t* h2d_bytes, bool raw_resident = false, bool refit = false);
+// Mesh.AABB (SceneMesh.cs:22-31) of n instances (indices into IS.insts) from the object-space vertices resident on D: out6 = 6 floats
+// each.  RT_E_STATE: D does not hold the current base meshes (the caller computes on the host).
+int rt_device_instance_aabbs(RtDevice& D, const RtInstanceSet& IS, const int32_t* inst_idx, int n, float* out6, std::string& err);
 // rt_render.cu
 struct RtFrameStats { uint64_t primary, shadow, mirror, shadow_skipped; uint32_t launches; float ms_kernel[RT_K_COUNT]; uint32_t launches_kernel[RT_K_COUNT]; };
 int rt_device_render(RtDevice& D, const RtView& V, int want, const RtOptions& opt, std::string& err, RtFrameStats* fs, int split = 0);
