@@ -268,6 +268,19 @@ def test_gpu_instance_updates_errors_and_explicit_rays(rtb, scenes, oracle):
     fresh = rtb.RayTracer((0,)); fresh.set_scene(s)
     assert np.array_equal(r.render(p)["rgba32f"], fresh.render(p)["rgba32f"], equal_nan=True)
     fresh.close()
+    # the packed BLAS sections are kept across a re-declaration only while they were emitted from exactly these base meshes: other base
+    # meshes declared in a scene WITHOUT instances (nothing is packed for it) and then again in a scene with instances must be emitted
+    sa, sa_plain = scenes.instanced_soup(seed=11, n_instances=7), scenes.instanced_soup(seed=11, n_instances=7)
+    sa_plain.meshes = [m for m in sa_plain.meshes if not isinstance(m, scenes.MeshInstance)]
+    r.set_scene(sa_plain); r.render(p)
+    r.set_scene(sa)
+    fresh = rtb.RayTracer((0,)); fresh.set_scene(sa)
+    a, f = r.render(p), fresh.render(p)
+    for k in ("hit_id", "hit_t", "rgba32f", "rgba8"):
+        assert np.array_equal(a[k], f[k], equal_nan=True), k
+    r.set_scene(sa)                                                         # and unchanged once more: nothing of the base meshes is re-sent
+    assert np.array_equal(r.render(p)["rgba32f"], f["rgba32f"], equal_nan=True)
+    fresh.close()
     r.close()
 
 

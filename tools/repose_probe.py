@@ -41,3 +41,25 @@ for rep in range(4):                                     # ... and with Mesh.AAB
     print(f"batched, AABBs computed, rep {rep}: 1 call {1e3*(t1-t0):.3f} ms, recommit {1e3*(t2-t1):.3f} ms", flush=True)
     r.render_device(p, 2)
 t0 = time.perf_counter(); r.set_scene(s); print(f"full re-declaration (BLAS cached) {1e3*(time.perf_counter()-t0):.2f} ms")
+# phases of the re-declaration (what host.set_scene does, call by call)
+from ctypes import byref
+L, h = r.L, r.h
+f32 = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+fp = rtb.host._fptr
+for rep in range(3):
+    torch.cuda.synchronize()
+    t = [time.perf_counter()]
+    L.rt_scene_begin(h); t.append(time.perf_counter())
+    for bv in s.base_meshes:
+        bv = f32(bv); L.rt_scene_base_mesh(h, fp(bv), bv.shape[0])
+    t.append(time.perf_counter())
+    for m in s.meshes:
+        mm, mat = f32(m.m3x4), np.ascontiguousarray(m.mat)
+        L.rt_scene_mesh_instance(h, int(m.base), fp(mm), mat.ctypes.data, None)
+    t.append(time.perf_counter())
+    li, amb = f32(s.lights), f32(s.ambient)
+    L.rt_scene_lights(h, fp(li), li.shape[0], fp(amb)); t.append(time.perf_counter())
+    L.rt_scene_commit(h, None); t.append(time.perf_counter())
+    d = [1e3 * (b - a) for a, b in zip(t, t[1:])]
+    print(f"re-declaration phases: begin {d[0]:.3f}, base mesh {d[1]:.3f}, 125 instances {d[2]:.3f}, lights {d[3]:.3f}, commit {d[4]:.3f} ms", flush=True)
+    r.render_device(p, 2)

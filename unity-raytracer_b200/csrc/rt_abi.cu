@@ -391,10 +391,11 @@ int rt_scene_base_mesh(rt_ctx* c, const float* v, int n_tris) {
     if (n_tris < 0 || (n_tris > 0 && !v)) return fail(c, RT_E_INVALID, "rt_scene_base_mesh: bad arguments");
     if (n_tris > (1 << 26)) return fail(c, RT_E_UNSUPPORTED, "rt_scene_base_mesh: more than 2^26 triangles");
     RtBaseMesh B;
-    B.v.assign(v, v + 9 * (size_t)n_tris);
-    if (!RtInstanceSet::set_bounds(B)) return fail(c, RT_E_UNSUPPORTED, "rt_scene_base_mesh: vertices must be finite (bake such a mesh and use rt_scene_mesh)");
-    B.hash = RtBaseMesh::hash_bytes(B.v.data(), B.v.size() * 4);
-    if (!c->host.inst.take_cached(B)) {
+    const uint64_t hash = RtBaseMesh::hash_bytes(v, 36 * (size_t)n_tris);
+    if (!c->host.inst.take_cached(v, 9 * (size_t)n_tris, hash, B)) {
+        B.v.assign(v, v + 9 * (size_t)n_tris);
+        if (!RtInstanceSet::set_bounds(B)) return fail(c, RT_E_UNSUPPORTED, "rt_scene_base_mesh: vertices must be finite (bake such a mesh and use rt_scene_mesh)");
+        B.hash = hash;
         // the BLAS is built here rather than at commit: the instances declared next take their world bounds from its top levels
         int threads = (int)std::thread::hardware_concurrency();
         c->host.inst.build_blas(B, c->opt.leaf_max < 1 ? 1 : (c->opt.leaf_max > 3 ? 3 : c->opt.leaf_max), threads < 1 ? 1 : threads);
@@ -447,7 +448,7 @@ static void resolve_pending_aabbs(rt_ctx* c) {
     // thread's pass per instance (worth the round trip from about 10^5 vertices on)
     int64_t verts = 0;
     for (int32_t mesh : todo) verts += 3 * (int64_t)H.inst.bases[(size_t)H.inst.insts[(size_t)H.mesh_inst[(size_t)mesh]].base].n_tris();
-    if (verts >= 100000 && (c->committed || c->dirty) && !c->devs.empty()) {
+    if (verts >= 100000 && !c->devs.empty()) {          // (rt_device_instance_aabbs refuses when the device does not hold these base meshes)
         std::vector<int32_t> idx(todo.size());
         for (size_t k = 0; k < todo.size(); ++k) idx[k] = H.mesh_inst[(size_t)todo[k]];
         std::vector<float> box(6 * todo.size());
@@ -524,6 +525,7 @@ static int commit_impl(rt_ctx* c, const float scene_aabb[6], bool raw_resident, 
 int rt_scene_commit(rt_ctx* c, const float scene_aabb[6]) {
     if (!c) return RT_E_INVALID;
     if (!c->in_scene) return fail(c, RT_E_STATE, "rt_scene_commit without rt_scene_begin");
+    c->host.inst.keep_blas_if_same();        // the same base meshes as the previous scene, in the same order: nothing of them is re-sent
     return commit_impl(c, scene_aabb, false, false);
 }
 

@@ -11,6 +11,7 @@
 //
 // Host only; shared by rt_build.cu and the CPU emulation of the device headers (tests/emu).
 #pragma once
+#include <atomic>
 #include <vector>
 #include <cmath>
 #include <cstring>
@@ -31,14 +32,20 @@ struct RtBaseMesh {
     // could not hit); the pieces of a cut are small, so their rotated boxes hug the surface.
     std::vector<float> hull;              // 6 floats per box (lo, hi)
     uint64_t hash = 0;                    // of the vertex bytes: a base mesh re-declared unchanged after rt_scene_begin keeps its BLAS
+    uint64_t uid = 0;                     // identity of the built BLAS (set by build_blas, travels with the cache): what the packed sections were emitted from
     int32_t n_tris() const { return (int32_t)(v.size() / 9); }
-    static uint64_t hash_bytes(const void* p, size_t n) {
+    static uint64_t hash_bytes(const void* p, size_t n) {             // four independent lanes: the multiplies of one lane are a dependent chain
         const unsigned char* b = (const unsigned char*)p;
-        uint64_t h = 0x9E3779B97F4A7C15ull ^ (uint64_t)n;
+        uint64_t h[4] = {0x9E3779B97F4A7C15ull ^ (uint64_t)n, 0xC2B2AE3D27D4EB4Full, 0x165667B19E3779F9ull, 0x27D4EB2F165667C5ull};
         size_t i = 0;
-        for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, b + i, 8); h = (h ^ w) * 0xff51afd7ed558ccdull; h ^= h >> 32; }
-        for (; i < n; ++i) { h = (h ^ b[i]) * 0x100000001b3ull; }
-        return h;
+        for (; i + 32 <= n; i += 32) {
+            uint64_t w[4]; std::memcpy(w, b + i, 32);
+            for (int k = 0; k < 4; ++k) { h[k] = (h[k] ^ w[k]) * 0xff51afd7ed558ccdull; h[k] ^= h[k] >> 32; }
+        }
+        uint64_t r = h[0];
+        for (int k = 1; k < 4; ++k) { r = (r ^ h[k]) * 0xc4ceb9fe1a85ec53ull; r ^= r >> 29; }
+        for (; i < n; ++i) { r = (r ^ b[i]) * 0x100000001b3ull; }
+        return r;
     }
 };
 
@@ -62,6 +69,7 @@ struct RtInstanceSet {
     std::vector<int32_t> vbase;           // [n_packed + 1]
     std::vector<int32_t> node_base, slot_base;                  // per base mesh
     std::vector<float> blas_pad;          // padding baked into each BLAS section of inodes
+    std::vector<uint64_t> packed_uid;     // RtBaseMesh::uid of the BLAS each section was emitted from
     int32_t tlas_base = 0, tlas_root = -1, n_packed = 0;
     int depth = 0;                        // stack entries the two-level walk may need below the world BVH
     bool blas_changed = true;             // iprims / the BLAS part of inodes must be (re)uploaded
@@ -69,16 +77,27 @@ struct RtInstanceSet {
     uint64_t blas_generation = 0;         // bumped whenever iprims / the BLAS sections were re-emitted: devices compare it with what they hold
 
     // the built BLAS of an identical base mesh declared in the previous scene, if any (moved out of the cache)
-    bool take_cached(RtBaseMesh& B) {
-        for (auto& P : prev_bases)
-            if (P.built && P.hash == B.hash && P.v.size() == B.v.size() && std::memcmp(P.v.data(), B.v.data(), B.v.size() * 4) == 0) {
+    // (compares the CALLER's array with the cached copies: a mesh re-declared unchanged is neither copied nor scanned again)
+    bool take_cached(const float* v, size_t n_floats, uint64_t hash, RtBaseMesh& B) {
+        for (size_t i = 0; i < prev_bases.size(); ++i) {
+            RtBaseMesh& P = prev_bases[i];
+            if (P.built && P.hash == hash && P.v.size() == n_floats && (n_floats == 0 || std::memcmp(P.v.data(), v, n_floats * 4) == 0)) {
                 B = std::move(P); P.built = false; P.v.clear();
                 return true;
             }
+        }
         return false;
     }
-    void clear() { prev_bases.clear(); prev_bases.swap(bases); insts.clear(); inodes.clear(); iprims.clear(); inst.clear(); vbase.clear(); node_base.clear(); slot_base.clear();
-                   blas_pad.clear(); tlas_base = 0; tlas_root = -1; n_packed = 0; depth = 0; blas_changed = true; }
+    // The packed BLAS sections (iprims, the head of inodes, node_base / slot_base / blas_pad) survive clear(): when the next scene
+    // declares the SAME base meshes in the same order (keep_blas_if_same) they are neither emitted nor uploaded again.
+    void clear() { prev_bases.clear(); prev_bases.swap(bases); insts.clear(); inst.clear(); vbase.clear();
+                   tlas_base = 0; tlas_root = -1; n_packed = 0; depth = 0; blas_changed = true; }
+    // at rt_scene_commit, once every base mesh is declared: the packed BLAS sections are still those of exactly this list of BLASes
+    void keep_blas_if_same() {
+        if (bases.empty() || packed_uid.size() != bases.size() || slot_base.size() != bases.size() + 1 || blas_pad.size() != bases.size()) return;
+        for (size_t i = 0; i < bases.size(); ++i) if (!bases[i].built || bases[i].uid == 0 || bases[i].uid != packed_uid[i]) return;
+        blas_changed = false;
+    }
     bool any() const { return !insts.empty(); }
     int64_t n_tris() const { int64_t n = 0; for (auto& i : insts) n += bases[(size_t)i.base].n_tris(); return n; }
 
@@ -130,11 +149,13 @@ struct RtInstanceSet {
     // object-space bounds of a base mesh; false when a vertex is not finite (object-space culling needs finite boxes)
     static bool set_bounds(RtBaseMesh& B) {
         float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX}, am = 0.f;
-        for (size_t i = 0; i < B.v.size(); ++i) {
-            const float x = B.v[i];
-            if (!std::isfinite(x) || std::fabs(x) > 1e30f) return false;
-            lo[i % 3] = std::fmin(lo[i % 3], x); hi[i % 3] = std::fmax(hi[i % 3], x); am = std::fmax(am, std::fabs(x));
-        }
+        const size_t nv = B.v.size() / 3;
+        for (size_t i = 0; i < nv; ++i)
+            for (int k = 0; k < 3; ++k) {
+                const float x = B.v[3 * i + k], ax = std::fabs(x);
+                if (!(ax <= 1e30f)) return false;                     // NaN, infinite or huge
+                lo[k] = x < lo[k] ? x : lo[k]; hi[k] = x > hi[k] ? x : hi[k]; am = ax > am ? ax : am;
+            }
         if (B.v.empty()) for (int k = 0; k < 3; ++k) lo[k] = hi[k] = 0.f;
         for (int k = 0; k < 3; ++k) { B.lo[k] = lo[k]; B.hi[k] = hi[k]; }
         B.amax = am;
@@ -163,6 +184,8 @@ struct RtInstanceSet {
         B.root = S.run(pb.data(), n, leaf_max, 0.0f, threads);
         B.nodes = S.nodes; B.order = S.order; B.depth = S.max_depth.load();
         B.built = true;
+        static std::atomic<uint64_t> next_uid{1};
+        B.uid = next_uid.fetch_add(1);
         // cover of the mesh: cut the tree breadth-first after RT_HULL_BOXES pieces (child boxes are stored in the parent node)
         B.hull.clear();
         if (B.root >= 0) {
@@ -215,6 +238,7 @@ struct RtInstanceSet {
         if (!blas_changed) for (size_t b = 0; b < nb; ++b) if (need[b] > blas_pad[b] || need[b] < 0.25f * blas_pad[b]) blas_changed = true;
         if (blas_changed) {
             node_base.assign(nb + 1, 0); slot_base.assign(nb + 1, 0); blas_pad.assign(nb, 0.f);
+            packed_uid.assign(nb, 0); for (size_t b = 0; b < nb; ++b) packed_uid[b] = bases[b].uid;
             for (size_t b = 0; b < nb; ++b) { node_base[b + 1] = node_base[b] + (int32_t)(bases[b].nodes.size() / 16); slot_base[b + 1] = slot_base[b] + bases[b].n_tris(); }
             iprims.assign((size_t)slot_base[nb] * 12, 0.f);
             inodes.assign((size_t)node_base[nb] * 16, 0.f);
