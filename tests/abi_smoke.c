@@ -118,6 +118,38 @@ static int with_gpu(void) {
             free(rgba); free(ht); free(hid);
         }
     }
+    /* ---- an instanced mesh (SceneMesh.cs:11-53 without the per-frame bake): KAT-4's triangle stored in OBJECT space around the
+     * origin and placed by its localToWorldMatrix; re-posed through rt_scene_update_instances; the batch is all or nothing ---- */
+    {
+        const float obj[9] = {0.f, 10.f, 0.f, -10.f, -10.f, 0.f, 10.f, -10.f, 0.f};        /* KAT-4's triangle minus (17.1, 0, 15) */
+        const float place[12] = {1.f, 0.f, 0.f, 17.f, 0.f, 1.f, 0.f, 0.f, 0.f, 0.f, 1.f, 15.f};
+        float moved[24];
+        const int32_t which[2] = {0, 0}, bad[2] = {0, 7};
+        const float o[3] = {17.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f};
+        rt_material m = material(0.f, 1.f, 0.f, 1.f);
+        int32_t id[3]; float t = 0.f, aabb[6];
+        int base;
+        CALL(ctx, rt_scene_begin(ctx));
+        base = rt_scene_base_mesh(ctx, obj, 1);
+        CHECK(base == 0, "rt_scene_base_mesh: %d (%s)", base, rt_last_error(ctx));
+        CALL(ctx, rt_scene_mesh_instance(ctx, base, place, &m, NULL));                         /* Mesh.AABB computed as SceneMesh.cs:22-31 */
+        CALL(ctx, rt_scene_lights(ctx, NULL, 0, NULL));
+        CALL(ctx, rt_scene_commit(ctx, NULL));
+        CALL(ctx, rt_scene_get_aabb(ctx, aabb));
+        CHECK(aabb[0] == 7.f && aabb[3] == 27.f && aabb[2] == 15.f && aabb[5] == 15.f, "instance AABB: x [%.9g, %.9g] z [%.9g, %.9g]", (double)aabb[0], (double)aabb[3], (double)aabb[2], (double)aabb[5]);
+        CALL(ctx, rt_intersect(ctx, o, d, 1, id, &t));
+        CHECK(id[0] == RT_TYPE_MESH_TRIANGLE && id[1] == 0 && id[2] == 0 && t == 15.0f, "instanced triangle: id {%d,%d,%d} t %.9g", id[0], id[1], id[2], (double)t);
+        memcpy(moved, place, sizeof(place)); memcpy(moved + 12, place, sizeof(place));
+        moved[11] = 99.f; moved[12 + 11] = 20.f;                                                /* the same mesh twice: its later pose stands */
+        CHECK(rt_scene_update_instances(ctx, bad, moved, NULL, 2) == RT_E_INVALID && strstr(rt_last_error(ctx), "entry 1") != NULL, "bad batch: %s", rt_last_error(ctx));
+        CALL(ctx, rt_intersect(ctx, o, d, 1, id, &t));                                           /* nothing moved, the scene is not even dirty */
+        CHECK(t == 15.0f, "after the rejected batch: t %.9g", (double)t);
+        CALL(ctx, rt_scene_update_instances(ctx, which, moved, NULL, 2));
+        CHECK(rt_intersect(ctx, o, d, 1, id, &t) == RT_E_STATE, "a dirty scene must be recommitted first");
+        CALL(ctx, rt_scene_recommit(ctx, NULL));
+        CALL(ctx, rt_intersect(ctx, o, d, 1, id, &t));
+        CHECK(id[0] == RT_TYPE_MESH_TRIANGLE && t == 20.0f, "re-posed instance: id {%d,%d,%d} t %.9g", id[0], id[1], id[2], (double)t);
+    }
     /* ---- error behaviour: NULL arguments and call order never crash, 0x0 is a no-op (SampleScene.unity) ---- */
     {
         rt_render_params p = plane(0, 0);
