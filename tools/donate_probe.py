@@ -1,5 +1,6 @@
-"""Work donation in the primary kernel (option `donate`, rt_render.cu "Work donation"): frames with and without it must be
-bit-identical; prints the kernel times of both on the full frame and on band partitions.  Development aid.
+"""Work donation in the primary kernel — an experiment that is NOT in the tree: apply profiles/r2_donate_experiment.patch first (it adds the
+option `donate`; write-up in profiles/r2_experiments.md).  Frames with and without it must be bit-identical; prints the kernel times of
+both on the full frame and on band partitions.  Development aid.
     python tools/donate_probe.py [cfg3|cfg2|cfg5] [lib=path] [worlds=1,8] [reps=4]"""
 import importlib, sys, os, json
 import numpy as np
